@@ -1,0 +1,234 @@
+/*
+ * dash_b200.h -- C ABI of the B200-native evaluator for Dash's online
+ * garbled-inference path.
+ *
+ * Everything here is `extern "C"`, plain pointers and sizes.  The library
+ * owns all device memory; the caller owns every host buffer it passes in.
+ * Every function returns DASHB_OK (0) or a negative DASHB_E* code and never
+ * throws; dashb_last_error() returns a thread-local description of the last
+ * failure.  There is no CPU fallback: without a CUDA device dashb_init()
+ * fails with DASHB_ENODEV and every later call fails too.
+ *
+ * Citations are file:line in UzL-ITS/dash (dash/include/... unless stated).
+ * The reference's own out-of-class operator boundary is the SGX ocall set
+ * (sgx/Enclave/Enclave.edl:52-134); the entry points below are that set
+ * generalised with a batch dimension and completed with the operators the
+ * reference never moved to the GPU (general rescale, base extension).
+ *
+ * Label layout at this boundary (identical to LabelTensor::get_components(),
+ * garbling/label_tensor.h:238-246): for CRT modulus j a host buffer of
+ * int16 `[batch][label][nc(p_j)]`, digit 0 = colour, digits in [0, p_j).
+ * nc(q) = floor(128 / log2 q) (label_tensor.h:1353-1357).
+ * Ciphertext tables are arrays of 16-byte little-endian unsigned integers
+ * (`__uint128_t` in the reference) in exactly the order the reference's
+ * garbler fills them; the per-operator comments give that order.
+ */
+#ifndef DASH_B200_H
+#define DASH_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DASHB_OK 0
+#define DASHB_EINVAL (-1)   /* bad argument / unsupported configuration      */
+#define DASHB_ENODEV (-2)   /* no CUDA device / library used before init     */
+#define DASHB_ECUDA (-3)    /* a CUDA runtime call or kernel failed          */
+#define DASHB_ESTATE (-4)   /* call order violated (e.g. add after finalize) */
+#define DASHB_EIO (-5)      /* material file could not be read / written     */
+#define DASHB_ENOMEM (-6)   /* device or host allocation failed              */
+
+/* One ciphertext row: the reference's __uint128_t, little endian. */
+typedef struct dashb_u128 {
+    uint64_t lo, hi;
+} dashb_u128;
+
+typedef struct dashb_circuit dashb_circuit; /* opaque */
+
+/* ---- process / device ------------------------------------------------- */
+
+/* Selects `device`, uploads the AES tables and the round keys of the fixed
+ * key 00..0f.  Replaces init_cuda() (misc/cuda_util.h:19-23) and the
+ * CUDAAESEngine constructor (crypto/cuda_aes_engine.h:533-545).  One process
+ * drives one GPU; call once per process before anything else. */
+int dashb_init(int device);
+const char* dashb_last_error(void);
+/* nc(q) exactly as LabelTensor::get_nr_comps (label_tensor.h:1353-1357). */
+int dashb_nr_comps(int modulus);
+/* The CUDA stream all work of this library is enqueued on (a cudaStream_t
+ * cast to void*), so a caller can bracket calls with its own events. */
+void* dashb_stream(void);
+
+/* ---- circuit construction (replaces GarbledCircuitInterface::cuda_move,
+ *      garbled_circuit_interface.h:477-549, and each layer's cuda_move) --- */
+
+/* crt_base[k], mrs_base[n_mrs] (n_mrs may be 0 for circuits without
+ * sign/ReLU/legacy-rescale layers); zero_labels[q-2] = int16[nc(q)] for
+ * q = 2..max_modulus (get_zero_labels(), garbled_circuit_interface.h:768);
+ * upshift_labels[j] = int16[nc(p_j)] (get_upshift_label, :786) or NULL when
+ * the circuit has no rescale layer; input_size = number of circuit inputs. */
+int dashb_circuit_create(dashb_circuit** out, const int32_t* crt_base, int k,
+                         const int32_t* mrs_base, int n_mrs, int max_modulus,
+                         const int16_t* const* zero_labels,
+                         const int16_t* const* upshift_labels,
+                         uint64_t input_size);
+
+/* GarbledDense (layer/garbled_dense.h:120-144,189-223; kernel
+ * MatMulModAddZero[TF], misc/cuda_util.h:95-138; ocall_cuda_eval_dense,
+ * Enclave.edl).  weights = get_qe_weights(): int64 [M][K] reduced to [0,P);
+ * bias_labels[j] = int16 [M][nc(p_j)]; channel_tf as Dense::get_channel_tf
+ * (0 = plain, >0 = TF channel-last input permutation). */
+int dashb_add_dense(dashb_circuit* c, uint64_t M, uint64_t K, int channel_tf,
+                    const int64_t* weights,
+                    const int16_t* const* bias_labels);
+
+/* GarbledConv2d (layer/garbled_conv2d.h:113-143; CPU semantics of
+ * LabelTensor::conv2d, label_tensor.h:920-1002, including its weight index
+ * v*fs*C + w*fs + i*filter_height + j).  weights int64
+ * [filters*channels*f_w*f_h] reduced to [0,P); bias_labels[j] = int16
+ * [filters][nc(p_j)]. */
+int dashb_add_conv2d(dashb_circuit* c, uint64_t in_w, uint64_t in_h,
+                     uint64_t channels, uint64_t filters, uint64_t f_w,
+                     uint64_t f_h, uint64_t s_w, uint64_t s_h,
+                     const int64_t* weights,
+                     const int16_t* const* bias_labels);
+
+/* GarbledRelu (layer/garbled_relu.h:181-223,258-294) = SignGadget with out
+ * modulus {2} and bounds (0,1) + one MixedModHalfGate per CRT modulus.
+ * With S = sum(crt_base), M' = sum(mrs_base[1:]):
+ *   approx    [n][n_mrs*S]     (sign_gadget.h:295-317; per element, CRT
+ *                               modulus j at n_mrs*prefix_j, MRS digit i at
+ *                               + i*p_j, row = colour)
+ *   cast1     [n][(k+1)*M']    (sign_gadget.h:489-529; per element, digits
+ *                               n_mrs-1..1, per digit k+1 tables of m_i rows)
+ *   cast2     [n][(k+1)*M']    (sign_gadget.h:443-445,534-552; per element,
+ *                               digits n_mrs-1..1, one table of (k+1)*m_i)
+ *   sign      [n][1][m_0]      (sign_gadget.h:557-576)
+ *   garbler   [n][S]           (garbled_relu.h:158)
+ *   evaluator [n][k][3]        (garbled_relu.h:160; rows 0,1 = projection
+ *                               2->p_j, row 2 = packed int16 mini gate,
+ *                               gates/projection_gate_mini.h:40-41) */
+int dashb_add_relu(dashb_circuit* c, uint64_t n, const dashb_u128* approx,
+                   const dashb_u128* cast1, const dashb_u128* cast2,
+                   const dashb_u128* sign, const dashb_u128* garbler,
+                   const dashb_u128* evaluator);
+
+/* GarbledSign (layer/garbled_sign.h:16-81): SignGadget, bounds (-1,1), out
+ * moduli = crt_base; sign table is [n][k][m_0]. */
+int dashb_add_sign(dashb_circuit* c, uint64_t n, const dashb_u128* approx,
+                   const dashb_u128* cast1, const dashb_u128* cast2,
+                   const dashb_u128* sign);
+
+/* GarbledRescale with general factors + BaseExtensionGadget
+ * (layer/garbled_rescale.h:75-103, gadgets/rescale_gadget.h:244-362,
+ * gadgets/base_extension_gadget.h:197-295; CPU-only in the reference).
+ * factors[nf] are CRT moduli; downshift_labels[j] = int16[nc(p_j)]
+ * (get_downshift_label, garbled_circuit_interface.h:803-815);
+ *   trans_mod  sequential [factor i][modulus j not yet ignored][element]
+ *              [s_i rows]                      (rescale_gadget.h:173-175)
+ *   be_ciphers sequential [i][j][element][m_i rows] over the swapped base
+ *              (base_extension_gadget.h:120-152). */
+int dashb_add_rescale(dashb_circuit* c, uint64_t n, const int32_t* factors,
+                      int nf, const int16_t* const* downshift_labels,
+                      const dashb_u128* trans_mod,
+                      const dashb_u128* be_ciphers);
+
+/* Legacy GarbledRescale{l}: l iterations of factor 2, each followed by a
+ * SignGadget with bounds (1,0), out modulus {2} that regenerates residue 0
+ * (layer/garbled_rescale.h:27-35,93-100; rescale_gadget.h:208-224,328-342).
+ * Requires crt_base[0] == 2.  Arrays are per iteration it < l:
+ * trans_mod[it] [(k-1)][n][2], then the four SignGadget tables as in
+ * dashb_add_relu (sign [n][1][m_0]). */
+int dashb_add_rescale_legacy(dashb_circuit* c, uint64_t n, int l,
+                             const int16_t* const* downshift_labels,
+                             const dashb_u128* const* trans_mod,
+                             const dashb_u128* const* approx,
+                             const dashb_u128* const* cast1,
+                             const dashb_u128* const* cast2,
+                             const dashb_u128* const* sign);
+
+/* GarbledProjection (layer/garbled_projection.h:118-134,168-194; kernel
+ * eval_proj, misc/cuda_util.h:297-317): ciphers[j] = [n][in_moduli[j]].
+ * The output labels live in out_moduli[j], which become the moduli of the
+ * following layer's input. */
+int dashb_add_projection(dashb_circuit* c, uint64_t n,
+                         const int32_t* in_moduli, const int32_t* out_moduli,
+                         const dashb_u128* const* ciphers);
+
+/* Decoding information (gen_decoding_information,
+ * garbled_circuit_interface.h:386-415): dec[j] = [p_j][output_size] hashes.
+ * Optional; needed only for dashb_decode_outputs. */
+int dashb_set_decoding_info(dashb_circuit* c, const dashb_u128* const* dec);
+
+/* Uploads weights and tables, re-lays them for the kernels and sizes the
+ * activation buffers for up to max_batch concurrent inferences. */
+int dashb_finalize(dashb_circuit* c, uint64_t max_batch);
+
+/* ---- online evaluation ------------------------------------------------ */
+
+/* cuda_move_inputs (garbled_circuit_interface.h:551-565), batched:
+ * in[j] = int16 [batch][input_size][nc(p_j)]. */
+int dashb_move_inputs(dashb_circuit* c, const int16_t* const* in,
+                      uint64_t batch);
+/* cuda_evaluate (garbled_circuit_interface.h:603-612): runs every layer on
+ * the labels left by dashb_move_inputs; asynchronous on dashb_stream(). */
+int dashb_evaluate_device(dashb_circuit* c);
+/* cuda_move_outputs (garbled_circuit_interface.h:733-736), batched:
+ * out[j] = int16 [batch][output_size][nc(q_j)], q_j = modulus j of the last
+ * layer's output.  Synchronises. */
+int dashb_move_outputs(dashb_circuit* c, int16_t* const* out);
+/* The three calls above in sequence. */
+int dashb_evaluate(dashb_circuit* c, const int16_t* const* in, uint64_t batch,
+                   int16_t* const* out);
+/* Debug/parity hook: copies the output labels of layer `layer` (index into
+ * the layers added, flatten not counted) of the last evaluation. */
+int dashb_layer_outputs(dashb_circuit* c, int layer, int16_t* const* out);
+/* decode_outputs (garbled_circuit_interface.h:422-467) on the device for
+ * the last evaluation: values[batch][output_size], CRT-recombined and
+ * mapped to the signed range; ok[batch] (optional) = 1 when every residue
+ * matched its decoding information. */
+int dashb_decode_outputs(dashb_circuit* c, int64_t* values, uint8_t* ok);
+
+/* ---- introspection ---------------------------------------------------- */
+uint64_t dashb_input_size(const dashb_circuit* c);
+uint64_t dashb_output_size(const dashb_circuit* c);
+int dashb_num_layers(const dashb_circuit* c);
+int dashb_crt_base_size(const dashb_circuit* c);
+/* Modulus j of the circuit's output labels. */
+int dashb_output_modulus(const dashb_circuit* c, int j);
+/* Kernel launches issued by the last dashb_evaluate_device. */
+uint64_t dashb_last_launch_count(const dashb_circuit* c);
+/* Algorithmic bytes / AES blocks of one inference through layer `layer`
+ * as defined in DESIGN.md (-1 = whole circuit). */
+double dashb_algorithmic_bytes(const dashb_circuit* c, int layer);
+double dashb_aes_blocks(const dashb_circuit* c, int layer);
+double dashb_reference_aes_blocks(const dashb_circuit* c, int layer);
+/* Device time (ms, CUDA events on dashb_stream()) each layer took in the
+ * last evaluation run with profiling enabled; keys are layer indices. */
+int dashb_set_layer_timing(dashb_circuit* c, int enabled);
+int dashb_layer_time_ms(dashb_circuit* c, int layer, float* ms);
+/* Layer type of layer `layer` (DASHB_LAYER_*). */
+int dashb_layer_type(const dashb_circuit* c, int layer);
+
+#define DASHB_LAYER_DENSE 1
+#define DASHB_LAYER_CONV2D 2
+#define DASHB_LAYER_RELU 3
+#define DASHB_LAYER_SIGN 4
+#define DASHB_LAYER_RESCALE 5
+#define DASHB_LAYER_RESCALE_LEGACY 6
+#define DASHB_LAYER_PROJECTION 7
+
+/* ---- garbled-material files (no counterpart in the reference, which keeps
+ *      a garbled circuit only in process memory; format in
+ *      include/dash_gcm_format.h) ---------------------------------------- */
+int dashb_circuit_load(dashb_circuit** out, const char* path);
+
+void dashb_circuit_destroy(dashb_circuit* c);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DASH_B200_H */
