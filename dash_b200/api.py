@@ -1,0 +1,231 @@
+"""ctypes front end of libdash_b200.so -- host-side mirror of the reference's
+GarbledCircuitInterface GPU calls (garbling/garbled_circuit_interface.h:
+477-612,733-736):
+
+    reference                      here
+    ---------                      ----
+    init_cuda() + cuda_move()      init(device); Circuit.load(path, max_batch)
+    cuda_move_inputs(g_inputs)     Circuit.move_inputs(labels)
+    cuda_evaluate(dev_in)          Circuit.evaluate_device()
+    cuda_move_outputs()            Circuit.move_outputs()
+    decode_outputs(g_out)          Circuit.decode_outputs()
+
+Labels cross this boundary exactly as LabelTensor::get_components() lays
+them out: per CRT modulus an int16 array [batch][labels][nc].  All compute
+is in the CUDA library; this module only marshals pointers and raises
+DashB200Error when the library reports a failure (including "no CUDA
+device": there is no CPU path).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+_lib = None
+
+
+class DashB200Error(RuntimeError):
+    pass
+
+
+def lib():
+    """Loads (building if necessary) the shared library."""
+    global _lib
+    if _lib is None:
+        path = _build.LIB
+        if not os.path.exists(path):
+            _build.build()
+        L = C.CDLL(path)
+        L.dashb_last_error.restype = C.c_char_p
+        L.dashb_stream.restype = C.c_void_p
+        L.dashb_circuit_load.argtypes = [C.POINTER(C.c_void_p), C.c_char_p]
+        L.dashb_finalize.argtypes = [C.c_void_p, C.c_uint64]
+        L.dashb_move_inputs.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+        L.dashb_evaluate_device.argtypes = [C.c_void_p]
+        L.dashb_move_outputs.argtypes = [C.c_void_p, C.c_void_p]
+        L.dashb_evaluate.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+        L.dashb_layer_outputs.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.dashb_decode_outputs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        for f in (L.dashb_input_size, L.dashb_output_size, L.dashb_last_launch_count):
+            f.restype = C.c_uint64
+            f.argtypes = [C.c_void_p]
+        for f in (L.dashb_num_layers, L.dashb_crt_base_size):
+            f.argtypes = [C.c_void_p]
+        L.dashb_output_modulus.argtypes = [C.c_void_p, C.c_int]
+        L.dashb_layer_type.argtypes = [C.c_void_p, C.c_int]
+        for f in (L.dashb_algorithmic_bytes, L.dashb_aes_blocks, L.dashb_reference_aes_blocks):
+            f.restype = C.c_double
+            f.argtypes = [C.c_void_p, C.c_int]
+        L.dashb_set_layer_timing.argtypes = [C.c_void_p, C.c_int]
+        L.dashb_layer_time_ms.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float)]
+        L.dashb_circuit_destroy.argtypes = [C.c_void_p]
+        L.dashb_hostcheck_compress.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+        L.dashb_hostcheck_digits.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+        L.dashb_hostcheck_colour.argtypes = [C.c_int, C.c_void_p]
+        L.dashb_hostcheck_hash.argtypes = [C.c_void_p, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise DashB200Error("dash_b200 error %d: %s" % (rc, lib().dashb_last_error().decode()))
+
+
+def init(device=0):
+    """init_cuda() + CUDAAESEngine setup of the reference, for one device."""
+    _check(lib().dashb_init(int(device)))
+
+
+def nr_comps(q):
+    return lib().dashb_nr_comps(int(q))
+
+
+def stream_handle():
+    return lib().dashb_stream()
+
+
+LAYER_NAMES = {1: "dense", 2: "conv2d", 3: "approx_relu", 4: "sign", 5: "rescale", 6: "rescale", 7: "projection"}
+
+
+def _ptr_array(arrs):
+    return (C.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
+
+
+class Circuit:
+    """A garbled circuit resident on the GPU (the result of cuda_move())."""
+
+    def __init__(self, handle, max_batch):
+        self.L = lib()
+        self.h = handle
+        self.max_batch = max_batch
+        self.k = self.L.dashb_crt_base_size(self.h)
+        self.input_size = self.L.dashb_input_size(self.h)
+        self.output_size = self.L.dashb_output_size(self.h)
+        self.n_layers = self.L.dashb_num_layers(self.h)
+        self.out_moduli = [self.L.dashb_output_modulus(self.h, j) for j in range(self.k)]
+        self.batch = 0
+        self.in_moduli = None
+
+    @classmethod
+    def load(cls, path, max_batch=1):
+        """Reads a DGCM material file and moves the circuit to the device."""
+        L = lib()
+        h = C.c_void_p()
+        _check(L.dashb_circuit_load(C.byref(h), os.fsencode(path)))
+        _check(L.dashb_finalize(h, int(max_batch)))
+        return cls(h, max_batch)
+
+    def close(self):
+        if self.h:
+            self.L.dashb_circuit_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _in_arrays(self, labels):
+        labels = [np.ascontiguousarray(l, dtype=np.int16) for l in labels]
+        if len(labels) != self.k:
+            raise ValueError("expected %d label tensors" % self.k)
+        batch = labels[0].shape[0]
+        for l in labels:
+            if l.ndim != 3 or l.shape[0] != batch or l.shape[1] != self.input_size:
+                raise ValueError("labels must be [batch][input_size][nc]")
+        return labels, batch
+
+    def move_inputs(self, labels):
+        labels, batch = self._in_arrays(labels)
+        _check(self.L.dashb_move_inputs(self.h, _ptr_array(labels), batch))
+        self.batch = batch
+        self._keep = labels
+
+    def evaluate_device(self):
+        _check(self.L.dashb_evaluate_device(self.h))
+
+    def _out_arrays(self, n, moduli):
+        return [np.zeros((self.batch, n, nr_comps(q)), dtype=np.int16) for q in moduli]
+
+    def move_outputs(self):
+        out = self._out_arrays(self.output_size, self.out_moduli)
+        _check(self.L.dashb_move_outputs(self.h, _ptr_array(out)))
+        return out
+
+    def evaluate(self, labels):
+        """cuda_move_inputs + cuda_evaluate + cuda_move_outputs."""
+        labels, batch = self._in_arrays(labels)
+        self.batch = batch
+        out = self._out_arrays(self.output_size, self.out_moduli)
+        _check(self.L.dashb_evaluate(self.h, _ptr_array(labels), batch, _ptr_array(out)))
+        return out
+
+    def layer_outputs(self, layer, n, moduli):
+        out = self._out_arrays(n, moduli)
+        _check(self.L.dashb_layer_outputs(self.h, layer, _ptr_array(out)))
+        return out
+
+    def decode_outputs(self):
+        vals = np.zeros((self.batch, self.output_size), dtype=np.int64)
+        ok = np.zeros(self.batch, dtype=np.uint8)
+        _check(self.L.dashb_decode_outputs(self.h, vals.ctypes.data, ok.ctypes.data))
+        return vals, ok.astype(bool)
+
+    def launch_count(self):
+        return self.L.dashb_last_launch_count(self.h)
+
+    def algorithmic_bytes(self, layer=-1):
+        return self.L.dashb_algorithmic_bytes(self.h, layer)
+
+    def aes_blocks(self, layer=-1):
+        return self.L.dashb_aes_blocks(self.h, layer)
+
+    def reference_aes_blocks(self, layer=-1):
+        return self.L.dashb_reference_aes_blocks(self.h, layer)
+
+    def layer_type(self, layer):
+        return self.L.dashb_layer_type(self.h, layer)
+
+    def set_layer_timing(self, enabled):
+        _check(self.L.dashb_set_layer_timing(self.h, int(bool(enabled))))
+
+    def layer_times_ms(self):
+        """Per layer-type device time of the last timed evaluation, keyed like
+        the reference's BENCHMARK map (garbled_circuit_interface.h:40-57)."""
+        per_layer = []
+        for i in range(self.n_layers):
+            ms = C.c_float(0)
+            _check(self.L.dashb_layer_time_ms(self.h, i, C.byref(ms)))
+            per_layer.append((LAYER_NAMES.get(self.layer_type(i), "?"), ms.value))
+        return per_layer
+
+
+# ---- host self-checks of the device primitives (CPU-only test tier) ----
+def hostcheck_compress(q, digits):
+    d = np.ascontiguousarray(digits, dtype=np.int16)
+    o = np.zeros(2, dtype=np.uint64)
+    lib().dashb_hostcheck_compress(int(q), d.ctypes.data, o.ctypes.data)
+    return int(o[0]) | (int(o[1]) << 64)
+
+
+def hostcheck_digits(q, x):
+    c = np.array([x & (2**64 - 1), x >> 64], dtype=np.uint64)
+    d = np.zeros(nr_comps(q), dtype=np.int16)
+    lib().dashb_hostcheck_digits(int(q), c.ctypes.data, d.ctypes.data)
+    return d
+
+
+def hostcheck_colour(q, x):
+    c = np.array([x & (2**64 - 1), x >> 64], dtype=np.uint64)
+    return lib().dashb_hostcheck_colour(int(q), c.ctypes.data)
+
+
+def hostcheck_hash(x):
+    c = np.array([x & (2**64 - 1), x >> 64], dtype=np.uint64)
+    o = np.zeros(2, dtype=np.uint64)
+    lib().dashb_hostcheck_hash(c.ctypes.data, o.ctypes.data)
+    return int(o[0]) | (int(o[1]) << 64)

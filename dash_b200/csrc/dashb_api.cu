@@ -1,0 +1,1071 @@
+/*
+ * dashb_api.cu -- host side of the B200 evaluator: the C ABI declared in
+ * include/dash_b200.h, the circuit object (device-resident weights,
+ * ciphertext tables, activation planes) and the per-layer launch plan.
+ * No label arithmetic happens on the host except the one-off preparation of
+ * constants at circuit-build time (weights mod q, constant labels, modular
+ * inverses) and the dashb_hostcheck_* self-test hooks.
+ */
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/dash_b200.h"
+#include "../../include/dash_b200_gcm.h"
+#include "kernels.h"
+
+using gc::ModInfo;
+using gc::u128;
+using namespace dashb;
+
+namespace {
+
+thread_local std::string g_err;
+int g_device = -1;
+cudaStream_t g_stream = nullptr;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(expr)                                                                              \
+    do {                                                                                      \
+        cudaError_t _e = (expr);                                                              \
+        if (_e != cudaSuccess)                                                                \
+            return fail(_e == cudaErrorMemoryAllocation ? DASHB_ENOMEM : DASHB_ECUDA, "%s: %s", #expr, \
+                        cudaGetErrorString(_e));                                              \
+    } while (0)
+
+int nr_comps(int q) { return (int)floor(128 / log2((double)q)); }
+
+ModInfo make_modinfo(uint32_t q) {
+    ModInfo m;
+    memset(&m, 0, sizeof(m));
+    m.q = q;
+    m.nc = (uint32_t)nr_comps((int)q);
+    /* t = max digits per chunk with q^(t+1) <= 2^32 */
+    uint64_t pw = q;
+    uint32_t t = 0;
+    while (pw * q <= (1ull << 32) && t < m.nc) {
+        pw *= q;
+        ++t;
+    }
+    if (t == 0) t = 1;
+    if (t > m.nc) t = m.nc;
+    m.t = t;
+    uint64_t Q = 1;
+    for (uint32_t i = 0; i < t; ++i) Q *= q;
+    m.Q = (uint32_t)Q;
+    m.nchunks = (m.nc + t - 1) / t;
+    m.top_len = m.nc - (m.nchunks - 1) * t;
+    m.MQ = ~0ull / Q;
+    if ((q & (q - 1)) == 0) {
+        m.shift = 0;
+        while ((1u << m.shift) < q) ++m.shift;
+        m.mq = 0;
+    } else {
+        m.shift = 0;
+        m.mq = (uint32_t)((1ull << 32) / q) + 1;
+    }
+    return m;
+}
+
+/* util::mul_inv (misc/util.h:92-103) */
+uint64_t mul_inv(unsigned __int128 a, uint16_t b) {
+    long long b0 = b, t, q;
+    long long x0 = 0, x1 = 1;
+    if (b == 1) return 1;
+    while (a > 1) {
+        if (b == 0) return 0; /* not invertible: rejected by the callers */
+        q = (long long)(a / b);
+        t = b, b = (uint16_t)(a % b), a = (unsigned __int128)(__int128)t;
+        t = x0, x0 = x1 - q * x0, x1 = t;
+    }
+    if (x1 < 0) x1 += b0;
+    return (uint64_t)x1;
+}
+
+struct DevMem {
+    void* p{nullptr};
+    size_t bytes{0};
+    DevMem() = default;
+    DevMem(const DevMem&) = delete;
+    DevMem& operator=(const DevMem&) = delete;
+    ~DevMem() {
+        if (p) cudaFree(p);
+    }
+    cudaError_t alloc(size_t n) {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = n;
+        return cudaMalloc(&p, n ? n : 16);
+    }
+    cudaError_t upload(const void* src, size_t n) {
+        cudaError_t e = alloc(n);
+        if (e != cudaSuccess) return e;
+        if (n) e = cudaMemcpy(p, src, n, cudaMemcpyHostToDevice);
+        return e;
+    }
+};
+
+/* int16 label digits -> u8 */
+std::vector<uint8_t> to_u8(const int16_t* d, size_t n) {
+    std::vector<uint8_t> v(n);
+    for (size_t i = 0; i < n; ++i) v[i] = (uint8_t)d[i];
+    return v;
+}
+
+u128 compress_host(const int16_t* d, const ModInfo& m) {
+    gc::Compressor c(m);
+    for (int i = (int)m.nc - 1; i >= 0; --i) c.push((uint32_t)d[i]);
+    return c.value();
+}
+
+struct Tensor {
+    uint64_t n{0};
+    int k{0};
+    int q[MAXK];
+    uint8_t* plane[MAXK];
+};
+
+size_t tensor_bytes(uint64_t n, int k, const int* q, uint32_t Bp) {
+    size_t total = 0;
+    for (int j = 0; j < k; ++j) total += ((size_t)n * nr_comps(q[j]) * Bp + 255) & ~(size_t)255;
+    return total;
+}
+
+void carve(Tensor& t, uint8_t* base, uint64_t n, int k, const int* q, uint32_t Bp) {
+    t.n = n;
+    t.k = k;
+    size_t off = 0;
+    for (int j = 0; j < k; ++j) {
+        t.q[j] = q[j];
+        t.plane[j] = base + off;
+        off += ((size_t)n * nr_comps(q[j]) * Bp + 255) & ~(size_t)255;
+    }
+}
+
+struct Layer {
+    int type{0};
+    uint64_t in_size{0}, out_size{0};
+    int out_q[MAXK];
+    /* linear */
+    uint64_t M{0}, K{0};
+    uint32_t Kp{0}, npix{1}, ow{1}, step_x{0}, step_y{0};
+    DevMem w4[MAXK], cst[MAXK], koff;
+    /* gadget tables */
+    DevMem approx, cast1, cast2, sign, garbler, evaluator;
+    /* rescale */
+    int nf{0}, l_iter{0};
+    DevMem down[MAXK], tm, be;
+    std::vector<std::unique_ptr<DevMem>> it_tables; /* legacy: 5 per iteration */
+    RescaleParams rp;
+    /* projection */
+    int in_q[MAXK];
+    DevMem proj[MAXK];
+    /* accounting */
+    double label_bytes{0}, weight_bytes{0}, aes{0}, ref_aes{0};
+    float ms{0};
+};
+
+}  // namespace
+
+struct dashb_circuit {
+    int k{0}, n_mrs{0}, max_modulus{0};
+    int crt[MAXK];
+    int mrs[MAXM];
+    ModInfo crt_mi[MAXK], mrs_mi[MAXM], cast_mi[MAXM];
+    uint64_t input_size{0};
+    std::vector<std::vector<int16_t>> zero; /* by modulus-2 */
+    DevMem d_zero[MAXK], d_up[MAXK];
+    bool has_up{false};
+    u128 carry0;
+    std::vector<std::unique_ptr<Layer>> layers;
+    int cur_q[MAXK];      /* moduli of the labels leaving the last added layer */
+    uint64_t cur_size{0}; /* their count */
+    bool finalized{false};
+    uint64_t max_batch{0};
+    uint32_t Bp{0}, batch{0};
+    DevMem buf_in, buf_a, buf_b, stage_in, stage_out;
+    DevMem dec[MAXK];
+    bool has_dec{false};
+    DevMem d_values, d_ok;
+    Tensor t_in, t_last;
+    uint64_t launches{0};
+    bool timing{false};
+    std::vector<cudaEvent_t> ev;
+    ~dashb_circuit() {
+        for (auto e : ev) cudaEventDestroy(e);
+    }
+};
+
+namespace {
+
+int check_building(dashb_circuit* c) {
+    if (!c) return fail(DASHB_EINVAL, "null circuit");
+    if (c->finalized) return fail(DASHB_ESTATE, "circuit already finalized");
+    return DASHB_OK;
+}
+
+int check_all_crt(dashb_circuit* c, const char* what) {
+    for (int j = 0; j < c->k; ++j)
+        if (c->cur_q[j] != c->crt[j]) return fail(DASHB_EINVAL, "%s needs its input labels in the CRT base", what);
+    return DASHB_OK;
+}
+
+/* Shared preparation of dense / conv2d: packs W mod q_j into the dp4a
+ * layout, builds the constant label (bias + zero-weight rule) per row. */
+int prep_linear(dashb_circuit* c, Layer& L, const std::vector<int64_t>& wrow /* [M][K] */, uint64_t M, uint64_t K,
+                const int16_t* const* bias_labels) {
+    if (K > 60000) return fail(DASHB_EINVAL, "linear layer with K=%llu taps exceeds the exact u32 range", (unsigned long long)K);
+    L.M = M;
+    L.K = K;
+    L.Kp = (uint32_t)((K + 3) & ~3ull);
+    const uint32_t k4 = L.Kp / 4, nvg = (uint32_t)((M + 7) / 8);
+    for (int j = 0; j < c->k; ++j) {
+        const uint32_t q = (uint32_t)c->crt[j], nc = c->crt_mi[j].nc;
+        std::vector<uint32_t> w4((size_t)nvg * k4 * 8, 0);
+        std::vector<uint8_t> cst((size_t)M * nc);
+        const int16_t* z = c->zero[q - 2].data();
+        for (uint64_t r = 0; r < M; ++r) {
+            uint64_t nz = 0;
+            for (uint64_t kk = 0; kk < K; ++kk) {
+                int64_t w = wrow[r * K + kk] % (int64_t)q;
+                if (w < 0) w += q;
+                if (w == 0) ++nz;
+                w4[((size_t)(r / 8) * k4 + kk / 4) * 8 + (r % 8)] |= (uint32_t)w << (8 * (kk % 4));
+            }
+            for (uint32_t d = 0; d < nc; ++d)
+                cst[r * nc + d] = (uint8_t)(((uint64_t)bias_labels[j][r * nc + d] + (nz % q) * (uint64_t)z[d]) % q);
+        }
+        CU(L.w4[j].upload(w4.data(), w4.size() * 4));
+        CU(L.cst[j].upload(cst.data(), cst.size()));
+    }
+    L.label_bytes = 16.0 * c->k * (double)(L.in_size + L.out_size);
+    L.weight_bytes = (double)c->k * (double)M * (double)K;
+    return DASHB_OK;
+}
+
+int upload_tables(DevMem& dst, const dashb_u128* src, size_t rows) {
+    if (!src && rows) return fail(DASHB_EINVAL, "null ciphertext table");
+    CU(dst.upload(src, rows * 16));
+    return DASHB_OK;
+}
+
+int sign_table_rows(dashb_circuit* c, uint64_t n, int n_out, size_t rows[4]) {
+    if (c->n_mrs < 1) return fail(DASHB_EINVAL, "sign gadget needs an MRS base");
+    size_t S = 0, Mp = 0;
+    for (int j = 0; j < c->k; ++j) S += (size_t)c->crt[j];
+    for (int i = 1; i < c->n_mrs; ++i) Mp += (size_t)c->mrs[i];
+    rows[0] = n * c->n_mrs * S;
+    rows[1] = n * (c->k + 1) * Mp;
+    rows[2] = rows[1];
+    rows[3] = n * (size_t)n_out * c->mrs[0];
+    return DASHB_OK;
+}
+
+void fill_sign_params(dashb_circuit* c, SignParams& p, uint64_t n, int n_out) {
+    memset(&p, 0, sizeof(p));
+    p.k = c->k;
+    p.n_mrs = c->n_mrs;
+    p.n_out = n_out;
+    p.n = n;
+    uint32_t S = 0, Mp = 0;
+    for (int j = 0; j < c->k; ++j) {
+        p.crt[j] = c->crt_mi[j];
+        p.prefix[j] = S;
+        S += (uint32_t)c->crt[j];
+    }
+    for (int i = 0; i < c->n_mrs; ++i) {
+        p.mrs[i] = c->mrs_mi[i];
+        p.cast[i] = c->cast_mi[i];
+        if (i) Mp += (uint32_t)c->mrs[i];
+    }
+    p.S = S;
+    p.Mp = Mp;
+    p.carry0 = c->carry0;
+}
+
+double sign_inner_aes_ref(const dashb_circuit* c) {
+    const int k = c->k, n = c->n_mrs;
+    return (double)k * n + (double)(k + 1) * (n - 1) + (n - 1);
+}
+double sign_inner_aes(const dashb_circuit* c) {
+    const int k = c->k, n = c->n_mrs;
+    return (double)k + (double)(k + 1) * (n - 1) + (n - 1) + 1;
+}
+
+void push_layer(dashb_circuit* c, std::unique_ptr<Layer> L) {
+    for (int j = 0; j < c->k; ++j) c->cur_q[j] = L->out_q[j];
+    c->cur_size = L->out_size;
+    c->layers.push_back(std::move(L));
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* dashb_last_error(void) { return g_err.c_str(); }
+int dashb_nr_comps(int modulus) { return modulus >= 2 ? nr_comps(modulus) : 0; }
+void* dashb_stream(void) { return (void*)g_stream; }
+
+int dashb_init(int device) {
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(DASHB_ENODEV, "no CUDA device (%s); this library has no CPU path",
+                    e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= count) return fail(DASHB_EINVAL, "device %d out of range (%d devices)", device, count);
+    CU(cudaSetDevice(device));
+    if (g_device != device) {
+        if (g_stream) cudaStreamDestroy(g_stream);
+        g_stream = nullptr;
+        CU(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking));
+    }
+    CU(upload_aes_tables());
+    g_device = device;
+    return DASHB_OK;
+}
+
+int dashb_circuit_create(dashb_circuit** out, const int32_t* crt_base, int k, const int32_t* mrs_base, int n_mrs,
+                         int max_modulus, const int16_t* const* zero_labels, const int16_t* const* upshift_labels,
+                         uint64_t input_size) {
+    if (!out) return fail(DASHB_EINVAL, "null out pointer");
+    *out = nullptr;
+    if (g_device < 0) return fail(DASHB_ENODEV, "dashb_init() has not succeeded; no device, no evaluation");
+    if (!crt_base || k < 1 || k > MAXK) return fail(DASHB_EINVAL, "crt base size %d unsupported (1..%d)", k, MAXK);
+    if (n_mrs < 0 || n_mrs > MAXM || (n_mrs && !mrs_base)) return fail(DASHB_EINVAL, "mrs base size %d unsupported", n_mrs);
+    if (!zero_labels || max_modulus < 2) return fail(DASHB_EINVAL, "zero labels missing");
+    if (input_size == 0) return fail(DASHB_EINVAL, "empty circuit input");
+    auto c = std::make_unique<dashb_circuit>();
+    c->k = k;
+    c->n_mrs = n_mrs;
+    c->max_modulus = max_modulus;
+    c->input_size = input_size;
+    for (int j = 0; j < k; ++j) {
+        if (crt_base[j] < 2 || crt_base[j] > 256)
+            return fail(DASHB_EINVAL, "CRT modulus %d outside the u8 digit range [2,256]", crt_base[j]);
+        if (crt_base[j] > max_modulus) return fail(DASHB_EINVAL, "no zero label for CRT modulus %d", crt_base[j]);
+        c->crt[j] = crt_base[j];
+        c->crt_mi[j] = make_modinfo((uint32_t)crt_base[j]);
+        c->cur_q[j] = crt_base[j];
+    }
+    c->cur_size = input_size;
+    c->zero.resize((size_t)max_modulus - 1);
+    for (int q = 2; q <= max_modulus; ++q) {
+        if (!zero_labels[q - 2]) return fail(DASHB_EINVAL, "zero label of modulus %d missing", q);
+        c->zero[q - 2].assign(zero_labels[q - 2], zero_labels[q - 2] + nr_comps(q));
+    }
+    for (int i = 0; i < n_mrs; ++i) {
+        if (mrs_base[i] < 2 || mrs_base[i] > 32767) return fail(DASHB_EINVAL, "bad MRS modulus %d", mrs_base[i]);
+        c->mrs[i] = mrs_base[i];
+        c->mrs_mi[i] = make_modinfo((uint32_t)mrs_base[i]);
+        const int64_t cm = (int64_t)(k + 1) * mrs_base[i];
+        if (i > 0 && cm > 32767) return fail(DASHB_EINVAL, "cast modulus %lld too large", (long long)cm);
+        c->cast_mi[i] = make_modinfo((uint32_t)(i > 0 ? cm : mrs_base[i]));
+    }
+    if (n_mrs) {
+        const int ql = mrs_base[n_mrs - 1];
+        if (ql > max_modulus) return fail(DASHB_EINVAL, "no zero label for MRS modulus %d", ql);
+        c->carry0 = compress_host(c->zero[ql - 2].data(), c->mrs_mi[n_mrs - 1]);
+    }
+    for (int j = 0; j < k; ++j) {
+        auto z = to_u8(c->zero[c->crt[j] - 2].data(), c->crt_mi[j].nc);
+        CU(c->d_zero[j].upload(z.data(), z.size()));
+        if (upshift_labels) {
+            if (!upshift_labels[j]) return fail(DASHB_EINVAL, "upshift label %d missing", j);
+            auto u = to_u8(upshift_labels[j], c->crt_mi[j].nc);
+            CU(c->d_up[j].upload(u.data(), u.size()));
+        }
+    }
+    c->has_up = upshift_labels != nullptr;
+    *out = c.release();
+    return DASHB_OK;
+}
+
+int dashb_add_dense(dashb_circuit* c, uint64_t M, uint64_t K, int channel_tf, const int64_t* weights,
+                    const int16_t* const* bias_labels) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if ((rc = check_all_crt(c, "dense"))) return rc;
+    if (!weights || !bias_labels || M == 0 || K == 0) return fail(DASHB_EINVAL, "dense: bad arguments");
+    if (K != c->cur_size) return fail(DASHB_EINVAL, "dense: K=%llu but previous layer has %llu labels", (unsigned long long)K, (unsigned long long)c->cur_size);
+    if (channel_tf < 0 || (channel_tf > 0 && K % (uint64_t)channel_tf != 0)) return fail(DASHB_EINVAL, "dense: bad channel_tf");
+    auto L = std::make_unique<Layer>();
+    L->type = DASHB_LAYER_DENSE;
+    L->in_size = K;
+    L->out_size = M;
+    for (int j = 0; j < c->k; ++j) L->out_q[j] = c->crt[j];
+    std::vector<int64_t> w(weights, weights + M * K);
+    if ((rc = prep_linear(c, *L, w, M, K, bias_labels))) return rc;
+    std::vector<int32_t> koff(L->Kp, 0);
+    for (uint64_t kk = 0; kk < K; ++kk) {
+        /* matvecmul_tf input permutation (label_tensor.h:848) */
+        koff[kk] = channel_tf ? (int32_t)(kk / channel_tf + (kk % channel_tf) * (K / channel_tf)) : (int32_t)kk;
+    }
+    CU(L->koff.upload(koff.data(), koff.size() * 4));
+    push_layer(c, std::move(L));
+    return DASHB_OK;
+}
+
+int dashb_add_conv2d(dashb_circuit* c, uint64_t in_w, uint64_t in_h, uint64_t channels, uint64_t filters,
+                     uint64_t f_w, uint64_t f_h, uint64_t s_w, uint64_t s_h, const int64_t* weights,
+                     const int16_t* const* bias_labels) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if ((rc = check_all_crt(c, "conv2d"))) return rc;
+    if (!weights || !bias_labels || !in_w || !in_h || !channels || !filters || !f_w || !f_h || !s_w || !s_h ||
+        f_w > in_w || f_h > in_h)
+        return fail(DASHB_EINVAL, "conv2d: bad geometry");
+    if (in_w * in_h * channels != c->cur_size) return fail(DASHB_EINVAL, "conv2d: input size mismatch");
+    const uint64_t ow = (in_w - f_w) / s_w + 1, oh = (in_h - f_h) / s_h + 1;
+    const uint64_t fs = f_w * f_h, K = channels * fs, nw = filters * channels * fs;
+    auto L = std::make_unique<Layer>();
+    L->type = DASHB_LAYER_CONV2D;
+    L->in_size = c->cur_size;
+    L->out_size = ow * oh * filters;
+    for (int j = 0; j < c->k; ++j) L->out_q[j] = c->crt[j];
+    /* taps ordered (channel w, filter row i, filter column j); the weight of
+     * a tap is read at the reference's index v*fs*C + w*fs + i*f_h + j
+     * (label_tensor.h:967-969) */
+    std::vector<int64_t> wrow(filters * K);
+    std::vector<int32_t> koff((K + 3) & ~3ull, 0);
+    for (uint64_t v = 0; v < filters; ++v)
+        for (uint64_t w = 0; w < channels; ++w)
+            for (uint64_t i = 0; i < f_h; ++i)
+                for (uint64_t jx = 0; jx < f_w; ++jx) {
+                    const uint64_t widx = v * fs * channels + w * fs + i * f_h + jx;
+                    if (widx >= nw) return fail(DASHB_EINVAL, "conv2d: the reference's weight index leaves the array for this filter shape");
+                    const uint64_t kk = (w * f_h + i) * f_w + jx;
+                    wrow[v * K + kk] = weights[widx];
+                    koff[kk] = (int32_t)(w * in_w * in_h + i * in_w + jx);
+                }
+    if ((rc = prep_linear(c, *L, wrow, filters, K, bias_labels))) return rc;
+    L->npix = (uint32_t)(ow * oh);
+    L->ow = (uint32_t)ow;
+    L->step_x = (uint32_t)s_w;
+    L->step_y = (uint32_t)(s_h * in_w);
+    if ((uint64_t)L->npix * ((filters + 7) / 8) > 65535) return fail(DASHB_EINVAL, "conv2d: output grid too large");
+    CU(L->koff.upload(koff.data(), koff.size() * 4));
+    push_layer(c, std::move(L));
+    return DASHB_OK;
+}
+
+static int add_sign_common(dashb_circuit* c, Layer& L, uint64_t n, int n_out, const dashb_u128* approx,
+                           const dashb_u128* cast1, const dashb_u128* cast2, const dashb_u128* sign) {
+    size_t rows[4];
+    int rc = sign_table_rows(c, n, n_out, rows);
+    if (rc) return rc;
+    if ((rc = upload_tables(L.approx, approx, rows[0]))) return rc;
+    if ((rc = upload_tables(L.cast1, cast1, rows[1]))) return rc;
+    if ((rc = upload_tables(L.cast2, cast2, rows[2]))) return rc;
+    return upload_tables(L.sign, sign, rows[3]);
+}
+
+int dashb_add_relu(dashb_circuit* c, uint64_t n, const dashb_u128* approx, const dashb_u128* cast1,
+                   const dashb_u128* cast2, const dashb_u128* sign, const dashb_u128* garbler,
+                   const dashb_u128* evaluator) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if ((rc = check_all_crt(c, "relu"))) return rc;
+    if (n != c->cur_size) return fail(DASHB_EINVAL, "relu: size mismatch");
+    if (2 > c->max_modulus) return fail(DASHB_EINVAL, "relu: modulus 2 unavailable");
+    auto L = std::make_unique<Layer>();
+    L->type = DASHB_LAYER_RELU;
+    L->in_size = L->out_size = n;
+    for (int j = 0; j < c->k; ++j) L->out_q[j] = c->crt[j];
+    if ((rc = add_sign_common(c, *L, n, 1, approx, cast1, cast2, sign))) return rc;
+    size_t S = 0;
+    for (int j = 0; j < c->k; ++j) S += (size_t)c->crt[j];
+    if ((rc = upload_tables(L->garbler, garbler, n * S))) return rc;
+    if ((rc = upload_tables(L->evaluator, evaluator, n * (size_t)c->k * 3))) return rc;
+    L->ref_aes = (double)n * (sign_inner_aes_ref(c) + 1 + 3.0 * c->k);
+    L->aes = (double)n * (sign_inner_aes(c) + 1);
+    L->label_bytes = (double)n * (32.0 * c->k + 16.0 * (sign_inner_aes_ref(c) + 1 + 3.0 * c->k));
+    push_layer(c, std::move(L));
+    return DASHB_OK;
+}
+
+int dashb_add_sign(dashb_circuit* c, uint64_t n, const dashb_u128* approx, const dashb_u128* cast1,
+                   const dashb_u128* cast2, const dashb_u128* sign) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if ((rc = check_all_crt(c, "sign"))) return rc;
+    if (n != c->cur_size) return fail(DASHB_EINVAL, "sign: size mismatch");
+    auto L = std::make_unique<Layer>();
+    L->type = DASHB_LAYER_SIGN;
+    L->in_size = L->out_size = n;
+    for (int j = 0; j < c->k; ++j) L->out_q[j] = c->crt[j];
+    if ((rc = add_sign_common(c, *L, n, c->k, approx, cast1, cast2, sign))) return rc;
+    L->ref_aes = (double)n * (sign_inner_aes_ref(c) + c->k);
+    L->aes = (double)n * sign_inner_aes(c);
+    L->label_bytes = (double)n * (32.0 * c->k + 16.0 * (sign_inner_aes_ref(c) + c->k));
+    push_layer(c, std::move(L));
+    return DASHB_OK;
+}
+
+static int upload_downshift(dashb_circuit* c, Layer& L, const int16_t* const* downshift_labels) {
+    if (!downshift_labels) return fail(DASHB_EINVAL, "rescale: downshift labels missing");
+    if (!c->has_up) return fail(DASHB_EINVAL, "rescale: circuit was created without upshift labels");
+    for (int j = 0; j < c->k; ++j) {
+        if (!downshift_labels[j]) return fail(DASHB_EINVAL, "rescale: downshift label %d missing", j);
+        auto d = to_u8(downshift_labels[j], c->crt_mi[j].nc);
+        CU(L.down[j].upload(d.data(), d.size()));
+    }
+    return DASHB_OK;
+}
+
+/* fills the parts of RescaleParams that do not depend on the batch */
+static int fill_rescale_static(dashb_circuit* c, Layer& L, uint64_t n, const int32_t* factors, int nf, int legacy) {
+    RescaleParams& p = L.rp;
+    memset(&p, 0, sizeof(p));
+    const int k = c->k;
+    p.k = k;
+    p.nf = nf;
+    p.n = n;
+    p.legacy = legacy;
+    uint32_t off = 0;
+    for (int j = 0; j < k; ++j) {
+        p.crt[j] = c->crt_mi[j];
+        p.loff[j] = off;
+        off += c->crt_mi[j].nc;
+    }
+    if (off > LW_MAX) return fail(DASHB_EINVAL, "rescale: CRT base too wide for the per-thread workspace");
+    /* Step 2 bookkeeping: sequential cipher counter over (factor, modulus) */
+    bool ignored[MAXK] = {false};
+    uint64_t cnt = 0;
+    for (int i = 0; i < nf; ++i) {
+        int f = -1;
+        for (int j = 0; j < k; ++j)
+            if (c->crt[j] == factors[i] && f < 0) f = j;
+        if (f < 0) return fail(DASHB_EINVAL, "rescale: factor %d is not a CRT modulus", factors[i]);
+        if (ignored[f]) return fail(DASHB_EINVAL, "rescale: duplicate factor %d", factors[i]);
+        ignored[f] = true;
+        p.fidx[i] = f;
+        p.factor[i] = (uint32_t)factors[i];
+        for (int j = 0; j < k; ++j) {
+            if (ignored[j]) {
+                p.tm_off[i][j] = ~0ull;
+                continue;
+            }
+            p.tm_off[i][j] = cnt;
+            cnt += n * (uint64_t)factors[i];
+            const uint64_t inv = mul_inv((unsigned __int128)factors[i], (uint16_t)c->crt[j]);
+            if ((inv * (uint64_t)factors[i]) % (uint64_t)c->crt[j] != 1)
+                return fail(DASHB_EINVAL, "rescale: factor %d not invertible mod %d", factors[i], c->crt[j]);
+            p.inv_f[i][j] = (uint16_t)inv;
+        }
+    }
+    if (legacy) return DASHB_OK;
+    /* base extension constants (base_extension_gadget.h:334-377) */
+    int perm[MAXK], swapped[MAXK];
+    for (int j = 0; j < k; ++j) perm[j] = j;
+    for (int i = 1; i <= nf; ++i) {
+        const int a = p.fidx[nf - i], b = k - i;
+        std::swap(perm[a], perm[b]);
+    }
+    for (int j = 0; j < k; ++j) {
+        swapped[j] = c->crt[perm[j]];
+        p.perm[j] = perm[j];
+    }
+    p.non_ext = k - nf;
+    uint64_t bcnt = 0;
+    for (int i = 0; i < p.non_ext; ++i)
+        for (int t = i + 1; t < k; ++t) {
+            p.be_off[i][t] = bcnt;
+            bcnt += n * (uint64_t)swapped[i];
+            p.inv_partial[i][t] = (uint16_t)(int16_t)mul_inv((unsigned __int128)swapped[i], (uint16_t)swapped[t]);
+        }
+    for (int x = 0; x < nf; ++x) {
+        int acc_i = 1; /* std::accumulate with an int accumulator (:351) */
+        for (int j = 0; j < p.non_ext; ++j) acc_i = (int)((unsigned long)(long)acc_i * (unsigned long)swapped[j]);
+        const unsigned long acc = (unsigned long)(long)acc_i;
+        const int16_t inv_total = (int16_t)mul_inv((unsigned __int128)acc, (uint16_t)factors[x]);
+        const int16_t invv = (int16_t)mul_inv((unsigned __int128)(__int128)inv_total, (uint16_t)factors[x]);
+        int64_t neg = (-(int64_t)invv) % (int64_t)factors[x];
+        if (neg < 0) neg += factors[x];
+        p.neg_invv[x] = (uint16_t)neg;
+        p.extra_idx[x] = p.fidx[x];
+        for (int j = 0; j < k; ++j)
+            if (swapped[j] == factors[x]) {
+                p.extra_pos[x] = j;
+                break;
+            }
+    }
+    return DASHB_OK;
+}
+
+int dashb_add_rescale(dashb_circuit* c, uint64_t n, const int32_t* factors, int nf,
+                      const int16_t* const* downshift_labels, const dashb_u128* trans_mod,
+                      const dashb_u128* be_ciphers) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if ((rc = check_all_crt(c, "rescale"))) return rc;
+    if (n != c->cur_size) return fail(DASHB_EINVAL, "rescale: size mismatch");
+    if (!factors || nf < 1 || nf > MAXF || nf >= c->k) return fail(DASHB_EINVAL, "rescale: bad factor list");
+    auto L = std::make_unique<Layer>();
+    L->type = DASHB_LAYER_RESCALE;
+    L->in_size = L->out_size = n;
+    L->nf = nf;
+    for (int j = 0; j < c->k; ++j) L->out_q[j] = c->crt[j];
+    if ((rc = upload_downshift(c, *L, downshift_labels))) return rc;
+    if ((rc = fill_rescale_static(c, *L, n, factors, nf, 0))) return rc;
+    const int k = c->k;
+    size_t tm_rows = 0, be_rows = 0;
+    for (int i = 0; i < nf; ++i) tm_rows += (size_t)(k - 1 - i) * n * (size_t)factors[i];
+    for (int i = 0; i < L->rp.non_ext; ++i) be_rows += (size_t)(k - i - 1) * n * (size_t)c->crt[L->rp.perm[i]];
+    if ((rc = upload_tables(L->tm, trans_mod, tm_rows))) return rc;
+    if ((rc = upload_tables(L->be, be_ciphers, be_rows))) return rc;
+    double gates = 0, hashes = nf + L->rp.non_ext;
+    for (int i = 0; i < nf; ++i) gates += k - 1 - i;
+    for (int i = 0; i < L->rp.non_ext; ++i) gates += k - i - 1;
+    L->ref_aes = (double)n * gates;
+    L->aes = (double)n * hashes;
+    L->label_bytes = (double)n * (32.0 * k + 16.0 * gates);
+    push_layer(c, std::move(L));
+    return DASHB_OK;
+}
+
+int dashb_add_rescale_legacy(dashb_circuit* c, uint64_t n, int l, const int16_t* const* downshift_labels,
+                             const dashb_u128* const* trans_mod, const dashb_u128* const* approx,
+                             const dashb_u128* const* cast1, const dashb_u128* const* cast2,
+                             const dashb_u128* const* sign) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if ((rc = check_all_crt(c, "rescale"))) return rc;
+    if (n != c->cur_size) return fail(DASHB_EINVAL, "rescale: size mismatch");
+    if (l < 1 || l > 16 || !trans_mod || !approx || !cast1 || !cast2 || !sign) return fail(DASHB_EINVAL, "rescale: bad arguments");
+    if (c->crt[0] != 2 || c->k < 2) return fail(DASHB_EINVAL, "legacy rescale needs crt_base[0] == 2");
+    auto L = std::make_unique<Layer>();
+    L->type = DASHB_LAYER_RESCALE_LEGACY;
+    L->in_size = L->out_size = n;
+    L->l_iter = l;
+    for (int j = 0; j < c->k; ++j) L->out_q[j] = c->crt[j];
+    if ((rc = upload_downshift(c, *L, downshift_labels))) return rc;
+    const int32_t two = 2;
+    if ((rc = fill_rescale_static(c, *L, n, &two, 1, 1))) return rc;
+    size_t rows[4];
+    if ((rc = sign_table_rows(c, n, 1, rows))) return rc;
+    for (int it = 0; it < l; ++it) {
+        const dashb_u128* src[5] = {trans_mod[it], approx[it], cast1[it], cast2[it], sign[it]};
+        const size_t nrows[5] = {n * (size_t)(c->k - 1) * 2, rows[0], rows[1], rows[2], rows[3]};
+        for (int a = 0; a < 5; ++a) {
+            auto m = std::make_unique<DevMem>();
+            if ((rc = upload_tables(*m, src[a], nrows[a]))) return rc;
+            L->it_tables.push_back(std::move(m));
+        }
+    }
+    const double gates = (c->k - 1) + sign_inner_aes_ref(c) + 1;
+    L->ref_aes = (double)n * l * gates;
+    L->aes = (double)n * l * (1 + sign_inner_aes(c));
+    L->label_bytes = (double)n * l * (32.0 * c->k + 16.0 * gates);
+    push_layer(c, std::move(L));
+    return DASHB_OK;
+}
+
+int dashb_add_projection(dashb_circuit* c, uint64_t n, const int32_t* in_moduli, const int32_t* out_moduli,
+                         const dashb_u128* const* ciphers) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if (!in_moduli || !out_moduli || !ciphers) return fail(DASHB_EINVAL, "projection: bad arguments");
+    if (n != c->cur_size) return fail(DASHB_EINVAL, "projection: size mismatch");
+    auto L = std::make_unique<Layer>();
+    L->type = DASHB_LAYER_PROJECTION;
+    L->in_size = L->out_size = n;
+    for (int j = 0; j < c->k; ++j) {
+        if (in_moduli[j] != c->cur_q[j]) return fail(DASHB_EINVAL, "projection: input modulus %d does not match the incoming labels (%d)", in_moduli[j], c->cur_q[j]);
+        if (out_moduli[j] < 2 || out_moduli[j] > 256) return fail(DASHB_EINVAL, "projection: output modulus %d outside the u8 digit range", out_moduli[j]);
+        L->in_q[j] = in_moduli[j];
+        L->out_q[j] = out_moduli[j];
+        if ((rc = upload_tables(L->proj[j], ciphers[j], n * (size_t)in_moduli[j]))) return rc;
+    }
+    L->ref_aes = L->aes = (double)n * c->k;
+    L->label_bytes = 48.0 * n * c->k;
+    push_layer(c, std::move(L));
+    return DASHB_OK;
+}
+
+int dashb_set_decoding_info(dashb_circuit* c, const dashb_u128* const* dec) {
+    if (!c || !dec) return fail(DASHB_EINVAL, "null argument");
+    if (c->finalized && c->has_dec) return fail(DASHB_ESTATE, "decoding information already set");
+    for (int j = 0; j < c->k; ++j) {
+        if (!dec[j]) return fail(DASHB_EINVAL, "decoding information %d missing", j);
+        CU(c->dec[j].upload(dec[j], (size_t)c->crt[j] * c->cur_size * 16));
+    }
+    c->has_dec = true;
+    return DASHB_OK;
+}
+
+int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if (max_batch == 0 || max_batch > (1u << 24)) return fail(DASHB_EINVAL, "bad max_batch");
+    c->max_batch = max_batch;
+    const uint32_t Bp = (uint32_t)((max_batch + 15) & ~15ull);
+    size_t in_bytes = tensor_bytes(c->input_size, c->k, c->crt, Bp);
+    size_t act_bytes = 256;
+    size_t stage_in = 0, stage_out = 0;
+    for (int j = 0; j < c->k; ++j) stage_in += (size_t)max_batch * c->input_size * c->crt_mi[j].nc * 2;
+    for (auto& L : c->layers) {
+        size_t b = tensor_bytes(L->out_size, c->k, L->out_q, Bp);
+        if (b > act_bytes) act_bytes = b;
+        size_t so = 0;
+        for (int j = 0; j < c->k; ++j) so += (size_t)max_batch * L->out_size * nr_comps(L->out_q[j]) * 2;
+        if (so > stage_out) stage_out = so;
+    }
+    if (stage_in > stage_out) stage_out = stage_in; /* zero-layer circuits echo the input */
+    CU(c->buf_in.alloc(in_bytes));
+    CU(c->buf_a.alloc(act_bytes));
+    CU(c->buf_b.alloc(act_bytes));
+    CU(c->stage_in.alloc(stage_in));
+    CU(c->stage_out.alloc(stage_out));
+    CU(cudaMemset(c->buf_in.p, 0, in_bytes));
+    CU(cudaMemset(c->buf_a.p, 0, act_bytes));
+    CU(cudaMemset(c->buf_b.p, 0, act_bytes));
+    CU(c->d_values.alloc((size_t)max_batch * c->cur_size * 8));
+    CU(c->d_ok.alloc(max_batch));
+    c->ev.resize(c->layers.size() + 1);
+    for (auto& e : c->ev) CU(cudaEventCreate(&e));
+    c->finalized = true;
+    return DASHB_OK;
+}
+
+int dashb_move_inputs(dashb_circuit* c, const int16_t* const* in, uint64_t batch) {
+    if (!c || !in) return fail(DASHB_EINVAL, "null argument");
+    if (!c->finalized) return fail(DASHB_ESTATE, "circuit not finalized");
+    if (batch == 0 || batch > c->max_batch) return fail(DASHB_EINVAL, "batch %llu outside 1..%llu", (unsigned long long)batch, (unsigned long long)c->max_batch);
+    c->batch = (uint32_t)batch;
+    c->Bp = (uint32_t)((batch + 15) & ~15ull);
+    carve(c->t_in, (uint8_t*)c->buf_in.p, c->input_size, c->k, c->crt, c->Bp);
+    size_t off = 0;
+    for (int j = 0; j < c->k; ++j) {
+        if (!in[j]) return fail(DASHB_EINVAL, "input labels %d missing", j);
+        const uint64_t rows = c->input_size * c->crt_mi[j].nc;
+        const size_t bytes = (size_t)batch * rows * 2;
+        int16_t* st = (int16_t*)((char*)c->stage_in.p + off);
+        CU(cudaMemcpyAsync(st, in[j], bytes, cudaMemcpyHostToDevice, g_stream));
+        CU(launch_ingest(st, c->t_in.plane[j], rows, c->batch, c->Bp, g_stream));
+        off += bytes;
+    }
+    c->t_last = c->t_in;
+    return DASHB_OK;
+}
+
+static int run_layers(dashb_circuit* c, int upto) {
+    Tensor cur = c->t_in;
+    uint8_t* bufs[2] = {(uint8_t*)c->buf_a.p, (uint8_t*)c->buf_b.p};
+    int which = 0;
+    c->launches = 0;
+    const uint32_t B = c->batch, Bp = c->Bp;
+    if (c->timing) CU(cudaEventRecord(c->ev[0], g_stream));
+    for (int li = 0; li <= upto; ++li) {
+        Layer& L = *c->layers[li];
+        Tensor out;
+        carve(out, bufs[which], L.out_size, c->k, L.out_q, Bp);
+        which ^= 1;
+        switch (L.type) {
+            case DASHB_LAYER_DENSE:
+            case DASHB_LAYER_CONV2D: {
+                LinearParams p;
+                memset(&p, 0, sizeof(p));
+                p.k = c->k;
+                for (int j = 0; j < c->k; ++j) {
+                    p.in[j] = cur.plane[j];
+                    p.out[j] = out.plane[j];
+                    p.w4[j] = (const uint32_t*)L.w4[j].p;
+                    p.cst[j] = (const uint8_t*)L.cst[j].p;
+                    p.mod[j] = c->crt_mi[j];
+                }
+                p.koff = (const int32_t*)L.koff.p;
+                p.M = (uint32_t)L.M;
+                p.K = (uint32_t)L.K;
+                p.Kp = L.Kp;
+                p.npix = L.npix;
+                p.ow = L.ow;
+                p.step_x = L.step_x;
+                p.step_y = L.step_y;
+                p.Bp = Bp;
+                CU(launch_linear(p, g_stream));
+                c->launches += 1;
+                break;
+            }
+            case DASHB_LAYER_RELU:
+            case DASHB_LAYER_SIGN: {
+                const bool relu = L.type == DASHB_LAYER_RELU;
+                SignParams p;
+                fill_sign_params(c, p, L.in_size, relu ? 1 : c->k);
+                for (int j = 0; j < c->k; ++j) {
+                    p.in[j] = cur.plane[j];
+                    p.out[j] = out.plane[j];
+                    p.outm[j] = c->crt_mi[j];
+                }
+                p.approx = (const u128*)L.approx.p;
+                p.cast1 = (const u128*)L.cast1.p;
+                p.cast2 = (const u128*)L.cast2.p;
+                p.sign = (const u128*)L.sign.p;
+                p.garbler = (const u128*)L.garbler.p;
+                p.evaluator = (const u128*)L.evaluator.p;
+                p.batch = B;
+                p.Bp = Bp;
+                CU(launch_sign(p, relu, g_stream));
+                c->launches += 1;
+                break;
+            }
+            case DASHB_LAYER_RESCALE:
+            case DASHB_LAYER_RESCALE_LEGACY: {
+                const bool legacy = L.type == DASHB_LAYER_RESCALE_LEGACY;
+                const int iters = legacy ? L.l_iter : 1;
+                for (int it = 0; it < iters; ++it) {
+                    RescaleParams p = L.rp;
+                    for (int j = 0; j < c->k; ++j) {
+                        p.in[j] = it == 0 ? cur.plane[j] : out.plane[j];
+                        p.out[j] = out.plane[j];
+                        p.up[j] = (const uint8_t*)c->d_up[j].p;
+                        p.down[j] = (const uint8_t*)L.down[j].p;
+                        p.zero[j] = (const uint8_t*)c->d_zero[j].p;
+                    }
+                    p.tm = (const u128*)(legacy ? L.it_tables[5 * it]->p : L.tm.p);
+                    p.be = (const u128*)L.be.p;
+                    p.batch = B;
+                    p.Bp = Bp;
+                    CU(launch_rescale(p, g_stream));
+                    c->launches += 1;
+                    if (legacy) {
+                        /* base extension by sign gadget: regenerates residue 0 in place */
+                        SignParams sp;
+                        fill_sign_params(c, sp, L.in_size, 1);
+                        for (int j = 0; j < c->k; ++j) sp.in[j] = out.plane[j];
+                        sp.out[0] = out.plane[0];
+                        sp.outm[0] = c->crt_mi[0];
+                        sp.approx = (const u128*)L.it_tables[5 * it + 1]->p;
+                        sp.cast1 = (const u128*)L.it_tables[5 * it + 2]->p;
+                        sp.cast2 = (const u128*)L.it_tables[5 * it + 3]->p;
+                        sp.sign = (const u128*)L.it_tables[5 * it + 4]->p;
+                        sp.batch = B;
+                        sp.Bp = Bp;
+                        CU(launch_sign(sp, false, g_stream));
+                        AddLabelParams ap;
+                        memset(&ap, 0, sizeof(ap));
+                        ap.k = c->k;
+                        ap.n = L.in_size;
+                        ap.Bp = Bp;
+                        ap.subtract = 1;
+                        for (int j = 0; j < c->k; ++j) {
+                            ap.plane[j] = out.plane[j];
+                            ap.label[j] = (const uint8_t*)L.down[j].p;
+                            ap.crt[j] = c->crt_mi[j];
+                        }
+                        CU(launch_add_label(ap, g_stream));
+                        c->launches += 2;
+                    }
+                }
+                break;
+            }
+            case DASHB_LAYER_PROJECTION: {
+                ProjParams p;
+                memset(&p, 0, sizeof(p));
+                p.k = c->k;
+                p.n = L.in_size;
+                p.batch = B;
+                p.Bp = Bp;
+                for (int j = 0; j < c->k; ++j) {
+                    p.in[j] = cur.plane[j];
+                    p.out[j] = out.plane[j];
+                    p.min[j] = make_modinfo((uint32_t)L.in_q[j]);
+                    p.mout[j] = make_modinfo((uint32_t)L.out_q[j]);
+                    p.ciphers[j] = (const u128*)L.proj[j].p;
+                }
+                CU(launch_projection(p, g_stream));
+                c->launches += 1;
+                break;
+            }
+            default: return fail(DASHB_EINVAL, "unknown layer type");
+        }
+        if (c->timing) CU(cudaEventRecord(c->ev[li + 1], g_stream));
+        cur = out;
+    }
+    c->t_last = cur;
+    return DASHB_OK;
+}
+
+int dashb_evaluate_device(dashb_circuit* c) {
+    if (!c) return fail(DASHB_EINVAL, "null circuit");
+    if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "no inputs moved");
+    int rc = run_layers(c, (int)c->layers.size() - 1);
+    if (rc) return rc;
+    if (c->timing) {
+        CU(cudaStreamSynchronize(g_stream));
+        for (size_t i = 0; i < c->layers.size(); ++i) CU(cudaEventElapsedTime(&c->layers[i]->ms, c->ev[i], c->ev[i + 1]));
+    }
+    return DASHB_OK;
+}
+
+static int copy_out(dashb_circuit* c, const Tensor& t, int16_t* const* out) {
+    size_t off = 0;
+    for (int j = 0; j < c->k; ++j) {
+        if (!out[j]) return fail(DASHB_EINVAL, "output buffer %d missing", j);
+        const uint64_t rows = t.n * (uint64_t)nr_comps(t.q[j]);
+        const size_t bytes = (size_t)c->batch * rows * 2;
+        int16_t* st = (int16_t*)((char*)c->stage_out.p + off);
+        CU(launch_egress(t.plane[j], st, rows, c->batch, c->Bp, g_stream));
+        CU(cudaMemcpyAsync(out[j], st, bytes, cudaMemcpyDeviceToHost, g_stream));
+        off += bytes;
+    }
+    CU(cudaStreamSynchronize(g_stream));
+    return DASHB_OK;
+}
+
+int dashb_move_outputs(dashb_circuit* c, int16_t* const* out) {
+    if (!c || !out) return fail(DASHB_EINVAL, "null argument");
+    if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "nothing evaluated");
+    return copy_out(c, c->t_last, out);
+}
+
+int dashb_evaluate(dashb_circuit* c, const int16_t* const* in, uint64_t batch, int16_t* const* out) {
+    int rc = dashb_move_inputs(c, in, batch);
+    if (rc) return rc;
+    if ((rc = dashb_evaluate_device(c))) return rc;
+    return dashb_move_outputs(c, out);
+}
+
+int dashb_layer_outputs(dashb_circuit* c, int layer, int16_t* const* out) {
+    if (!c || !out) return fail(DASHB_EINVAL, "null argument");
+    if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "no inputs moved");
+    if (layer < 0 || layer >= (int)c->layers.size()) return fail(DASHB_EINVAL, "layer index out of range");
+    const bool t = c->timing;
+    c->timing = false;
+    int rc = run_layers(c, layer);
+    c->timing = t;
+    if (rc) return rc;
+    return copy_out(c, c->t_last, out);
+}
+
+int dashb_decode_outputs(dashb_circuit* c, int64_t* values, uint8_t* ok) {
+    if (!c || !values) return fail(DASHB_EINVAL, "null argument");
+    if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "nothing evaluated");
+    if (!c->has_dec) return fail(DASHB_ESTATE, "no decoding information");
+    for (int j = 0; j < c->k; ++j)
+        if (c->t_last.q[j] != c->crt[j]) return fail(DASHB_EINVAL, "outputs are not in the CRT base");
+    DecodeParams p;
+    memset(&p, 0, sizeof(p));
+    p.k = c->k;
+    p.n = c->t_last.n;
+    p.batch = c->batch;
+    p.Bp = c->Bp;
+    /* util::chinese_remainder accumulates `prod` in an int (misc/util.h:123) */
+    int prod_i = 1;
+    long long crt_modulus = 1;
+    for (int j = 0; j < c->k; ++j) {
+        prod_i = (int)((unsigned __int128)(__int128)prod_i * (unsigned __int128)c->crt[j]);
+        crt_modulus *= c->crt[j];
+    }
+    if (prod_i <= 0) return fail(DASHB_EINVAL, "CRT modulus overflows the reference's int accumulator");
+    p.prod = prod_i;
+    p.crt_modulus = crt_modulus;
+    for (int j = 0; j < c->k; ++j) {
+        p.in[j] = c->t_last.plane[j];
+        p.crt[j] = c->crt_mi[j];
+        p.dec[j] = (const u128*)c->dec[j].p;
+        p.pdiv[j] = prod_i / c->crt[j];
+        p.inv[j] = (int64_t)(mul_inv((unsigned __int128)p.pdiv[j], (uint16_t)c->crt[j]) % (uint64_t)prod_i);
+    }
+    p.values = (int64_t*)c->d_values.p;
+    p.ok = (uint8_t*)c->d_ok.p;
+    CU(cudaMemsetAsync(p.ok, 1, c->batch, g_stream));
+    CU(launch_decode(p, g_stream));
+    CU(cudaMemcpyAsync(values, p.values, (size_t)c->batch * p.n * 8, cudaMemcpyDeviceToHost, g_stream));
+    if (ok) CU(cudaMemcpyAsync(ok, p.ok, c->batch, cudaMemcpyDeviceToHost, g_stream));
+    CU(cudaStreamSynchronize(g_stream));
+    return DASHB_OK;
+}
+
+uint64_t dashb_input_size(const dashb_circuit* c) { return c ? c->input_size : 0; }
+uint64_t dashb_output_size(const dashb_circuit* c) { return c ? c->cur_size : 0; }
+int dashb_num_layers(const dashb_circuit* c) { return c ? (int)c->layers.size() : 0; }
+int dashb_crt_base_size(const dashb_circuit* c) { return c ? c->k : 0; }
+int dashb_output_modulus(const dashb_circuit* c, int j) { return (c && j >= 0 && j < c->k) ? c->cur_q[j] : 0; }
+uint64_t dashb_last_launch_count(const dashb_circuit* c) { return c ? c->launches : 0; }
+int dashb_layer_type(const dashb_circuit* c, int layer) {
+    return (c && layer >= 0 && layer < (int)c->layers.size()) ? c->layers[layer]->type : 0;
+}
+
+static double layer_sum(const dashb_circuit* c, int layer, int what) {
+    if (!c) return 0;
+    double s = 0;
+    for (int i = 0; i < (int)c->layers.size(); ++i) {
+        if (layer >= 0 && i != layer) continue;
+        const Layer& L = *c->layers[i];
+        if (what == 0) s += L.label_bytes + L.weight_bytes / (c->batch ? c->batch : 1);
+        if (what == 1) s += L.aes;
+        if (what == 2) s += L.ref_aes;
+    }
+    return s;
+}
+double dashb_algorithmic_bytes(const dashb_circuit* c, int layer) { return layer_sum(c, layer, 0); }
+double dashb_aes_blocks(const dashb_circuit* c, int layer) { return layer_sum(c, layer, 1); }
+double dashb_reference_aes_blocks(const dashb_circuit* c, int layer) { return layer_sum(c, layer, 2); }
+
+int dashb_set_layer_timing(dashb_circuit* c, int enabled) {
+    if (!c) return fail(DASHB_EINVAL, "null circuit");
+    c->timing = enabled != 0;
+    return DASHB_OK;
+}
+int dashb_layer_time_ms(dashb_circuit* c, int layer, float* ms) {
+    if (!c || !ms || layer < 0 || layer >= (int)c->layers.size()) return fail(DASHB_EINVAL, "bad argument");
+    *ms = c->layers[layer]->ms;
+    return DASHB_OK;
+}
+
+int dashb_circuit_load(dashb_circuit** out, const char* path) {
+    if (!out || !path) return fail(DASHB_EINVAL, "null argument");
+    *out = nullptr;
+    if (g_device < 0) return fail(DASHB_ENODEV, "dashb_init() has not succeeded; no device, no evaluation");
+    gcm_circuit g;
+    if (gcm_load(&g, path) != 0) return fail(DASHB_EIO, "cannot read DGCM file %s", path);
+    int rc = dashb_circuit_from_gcm(&g, out);
+    gcm_free(&g);
+    return rc;
+}
+
+void dashb_circuit_destroy(dashb_circuit* c) { delete c; }
+
+/* ---- host self-checks of the device primitives (CPU-only test tier) ----
+ * These run the __host__ __device__ label primitives of gc_common.cuh on the
+ * host so that `pytest -m "not gpu"` can pin them against the oracle without
+ * a GPU.  They are not an evaluation path: no circuit can be run with them. */
+void dashb_hostcheck_compress(int q, const int16_t* digits, uint64_t out2[2]) {
+    ModInfo m = make_modinfo((uint32_t)q);
+    u128 x = compress_host(digits, m);
+    out2[0] = x.lo;
+    out2[1] = x.hi;
+}
+void dashb_hostcheck_digits(int q, const uint64_t in2[2], int16_t* digits) {
+    ModInfo m = make_modinfo((uint32_t)q);
+    gc::for_each_digit(gc::make_u128(in2[0], in2[1]), m, [&](uint32_t d, uint32_t v) { digits[d] = (int16_t)v; });
+}
+int dashb_hostcheck_colour(int q, const uint64_t in2[2]) {
+    ModInfo m = make_modinfo((uint32_t)q);
+    return (int)gc::colour_of(gc::make_u128(in2[0], in2[1]), m);
+}
+void dashb_hostcheck_hash(const uint64_t in2[2], uint64_t out2[2]) {
+    const uint32_t *t0, *t1, *t2, *t3, *rk;
+    const uint8_t* sb;
+    host_aes_tables(&t0, &t1, &t2, &t3, &sb, &rk);
+    u128 y = gc::aes128_encrypt(gc::make_u128(in2[0], in2[1]), t0, t1, t2, t3, sb, rk);
+    out2[0] = y.lo;
+    out2[1] = y.hi;
+}
+
+}  // extern "C"

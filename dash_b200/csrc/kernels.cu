@@ -1,0 +1,645 @@
+/*
+ * kernels.cu -- hand-written sm_100a kernels of the B200 evaluator for
+ * Dash's online garbled inference.  One thread evaluates one (element,
+ * inference) pair of a gadget; the batch is the fastest-varying thread index
+ * so that the 32 lanes of a warp share one element's ciphertext tables
+ * (L1/L2-resident) and read/write 32 consecutive bytes of every digit row.
+ *
+ * Reference kernels / CPU routines each kernel replaces are cited at the
+ * kernel (paths relative to dash/include/ of UzL-ITS/dash).
+ */
+#include <cuda_runtime.h>
+
+#include "kernels.h"
+
+namespace dashb {
+
+using gc::ModInfo;
+using gc::u128;
+
+/* ------------------------------------------------------------ AES tables */
+/* Round keys of the fixed key 00..0f (crypto/cpu_aes_engine.h:23-25) as
+ * big-endian words; uniform across a warp -> constant cache. */
+__constant__ uint32_t c_rk[44];
+/* T-table Te0 and the S-box; copied into shared memory by every CTA that
+ * hashes (cuda_aes_engine.h:27-32 keeps four tables in __constant__, which
+ * serialises divergent lookups). */
+__device__ uint32_t g_te0[256];
+__device__ uint8_t g_sbox[256];
+
+static uint32_t h_te[4][256];
+static uint8_t h_sbox[256];
+static uint32_t h_rk[44];
+static bool h_tables_ready = false;
+
+static void build_host_tables() {
+    if (h_tables_ready) return;
+    /* S-box from the multiplicative inverse in GF(2^8) + affine map (FIPS-197 5.1.1) */
+    uint8_t p = 1, q = 1;
+    do {
+        p = (uint8_t)(p ^ (p << 1) ^ ((p & 0x80) ? 0x1b : 0));
+        q ^= (uint8_t)(q << 1);
+        q ^= (uint8_t)(q << 2);
+        q ^= (uint8_t)(q << 4);
+        if (q & 0x80) q ^= 0x09;
+        uint8_t x = (uint8_t)(q ^ ((q << 1) | (q >> 7)) ^ ((q << 2) | (q >> 6)) ^ ((q << 3) | (q >> 5)) ^
+                              ((q << 4) | (q >> 4)));
+        h_sbox[p] = (uint8_t)(x ^ 0x63);
+    } while (p != 1);
+    h_sbox[0] = 0x63;
+    for (int i = 0; i < 256; ++i) {
+        uint32_t s = h_sbox[i];
+        uint32_t s2 = ((s << 1) ^ ((s >> 7) * 0x1b)) & 0xff;
+        uint32_t s3 = s2 ^ s;
+        uint32_t t = (s2 << 24) | (s << 16) | (s << 8) | s3;
+        h_te[0][i] = t;
+        h_te[1][i] = (t >> 8) | (t << 24);
+        h_te[2][i] = (t >> 16) | (t << 16);
+        h_te[3][i] = (t >> 24) | (t << 8);
+    }
+    static const uint8_t rcon[10] = {0x01, 0x02, 0x04, 0x08, 0x10, 0x20, 0x40, 0x80, 0x1b, 0x36};
+    for (int i = 0; i < 4; ++i)
+        h_rk[i] = ((uint32_t)(4 * i) << 24) | ((uint32_t)(4 * i + 1) << 16) | ((uint32_t)(4 * i + 2) << 8) |
+                  (uint32_t)(4 * i + 3);
+    for (int i = 4; i < 44; ++i) {
+        uint32_t t = h_rk[i - 1];
+        if (i % 4 == 0) {
+            t = (t << 8) | (t >> 24);
+            t = ((uint32_t)h_sbox[t >> 24] << 24) | ((uint32_t)h_sbox[(t >> 16) & 0xff] << 16) |
+                ((uint32_t)h_sbox[(t >> 8) & 0xff] << 8) | (uint32_t)h_sbox[t & 0xff];
+            t ^= (uint32_t)rcon[i / 4 - 1] << 24;
+        }
+        h_rk[i] = h_rk[i - 4] ^ t;
+    }
+    h_tables_ready = true;
+}
+
+void host_aes_tables(const uint32_t** te0, const uint32_t** te1, const uint32_t** te2, const uint32_t** te3,
+                     const uint8_t** sbox, const uint32_t** rk) {
+    build_host_tables();
+    *te0 = h_te[0];
+    *te1 = h_te[1];
+    *te2 = h_te[2];
+    *te3 = h_te[3];
+    *sbox = h_sbox;
+    *rk = h_rk;
+}
+
+cudaError_t upload_aes_tables() {
+    build_host_tables();
+    cudaError_t e = cudaMemcpyToSymbol(c_rk, h_rk, sizeof(h_rk));
+    if (e != cudaSuccess) return e;
+    e = cudaMemcpyToSymbol(g_te0, h_te[0], sizeof(h_te[0]));
+    if (e != cudaSuccess) return e;
+    return cudaMemcpyToSymbol(g_sbox, h_sbox, sizeof(h_sbox));
+}
+
+/* Shared-memory copy of the hash tables of one CTA. */
+struct AesSmem {
+    uint32_t te0[256], te1[256], te2[256], te3[256];
+    uint8_t sbox[256];
+};
+
+__device__ __forceinline__ void aes_smem_load(AesSmem& a) {
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        uint32_t t = g_te0[i];
+        a.te0[i] = t;
+        a.te1[i] = (t >> 8) | (t << 24);
+        a.te2[i] = (t >> 16) | (t << 16);
+        a.te3[i] = (t >> 24) | (t << 8);
+        a.sbox[i] = g_sbox[i];
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ u128 hash(const AesSmem& a, u128 x) {
+    return gc::aes128_encrypt(x, a.te0, a.te1, a.te2, a.te3, a.sbox, c_rk);
+}
+
+__device__ __forceinline__ u128 ldg128(const u128* p) {
+    uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+    u128 r;
+    r.lo = (uint64_t)v.x | ((uint64_t)v.y << 32);
+    r.hi = (uint64_t)v.z | ((uint64_t)v.w << 32);
+    return r;
+}
+
+/* compress the label (element e, inference b) of a digit plane */
+__device__ __forceinline__ u128 load_compress(const uint8_t* plane, const ModInfo& m, uint64_t e, uint32_t b,
+                                               uint32_t Bp, uint32_t& colour) {
+    const uint8_t* p = plane + e * (uint64_t)m.nc * Bp + b;
+    gc::Compressor c(m);
+    uint32_t dg = 0;
+    for (int d = (int)m.nc - 1; d >= 0; --d) {
+        dg = p[(uint32_t)d * Bp];
+        c.push(dg);
+    }
+    colour = dg;
+    return c.value();
+}
+
+/* write the digits of compressed label x into a plane */
+__device__ __forceinline__ void store_digits(uint8_t* plane, const ModInfo& m, uint64_t e, uint32_t b, uint32_t Bp,
+                                             u128 x) {
+    uint8_t* p = plane + e * (uint64_t)m.nc * Bp + b;
+    gc::for_each_digit(x, m, [&](uint32_t d, uint32_t v) { p[d * Bp] = (uint8_t)v; });
+}
+
+/* --------------------------------------------------- ingest / egress */
+/* Host layout int16 [batch][rows] (rows = labels*nc, LabelTensor order,
+ * garbling/label_tensor.h:238-246) <-> device plane u8 [rows][Bp].
+ * Replaces the per-modulus cudaMemcpy of cuda_move_inputs /
+ * cuda_move_outputs (garbled_circuit_interface.h:551-565,733-736). */
+__global__ void k_ingest(const int16_t* __restrict__ src, uint8_t* __restrict__ plane, uint64_t rows, uint32_t batch,
+                         uint32_t Bp) {
+    __shared__ uint8_t tile[32][33];
+    const uint64_t r0 = (uint64_t)blockIdx.x * 32;
+    const uint32_t b0 = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        uint32_t b = b0 + i;
+        uint64_t r = r0 + threadIdx.x;
+        tile[i][threadIdx.x] = (b < batch && r < rows) ? (uint8_t)src[(uint64_t)b * rows + r] : 0;
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        uint64_t r = r0 + i;
+        uint32_t b = b0 + threadIdx.x;
+        if (r < rows && b < Bp) plane[r * Bp + b] = tile[threadIdx.x][i];
+    }
+}
+
+__global__ void k_egress(const uint8_t* __restrict__ plane, int16_t* __restrict__ dst, uint64_t rows, uint32_t batch,
+                         uint32_t Bp) {
+    __shared__ uint8_t tile[32][33];
+    const uint64_t r0 = (uint64_t)blockIdx.x * 32;
+    const uint32_t b0 = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        uint64_t r = r0 + i;
+        uint32_t b = b0 + threadIdx.x;
+        tile[i][threadIdx.x] = (r < rows && b < Bp) ? plane[r * Bp + b] : 0;
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        uint32_t b = b0 + i;
+        uint64_t r = r0 + threadIdx.x;
+        if (b < batch && r < rows) dst[(uint64_t)b * rows + r] = (int16_t)tile[threadIdx.x][i];
+    }
+}
+
+cudaError_t launch_ingest(const int16_t* src, uint8_t* plane, uint64_t rows, uint32_t batch, uint32_t Bp,
+                          cudaStream_t s) {
+    dim3 grid((unsigned)((rows + 31) / 32), (Bp + 31) / 32), block(32, 8);
+    k_ingest<<<grid, block, 0, s>>>(src, plane, rows, batch, Bp);
+    return cudaGetLastError();
+}
+cudaError_t launch_egress(const uint8_t* plane, int16_t* dst, uint64_t rows, uint32_t batch, uint32_t Bp,
+                          cudaStream_t s) {
+    dim3 grid((unsigned)((rows + 31) / 32), (Bp + 31) / 32), block(32, 8);
+    k_egress<<<grid, block, 0, s>>>(plane, dst, rows, batch, Bp);
+    return cudaGetLastError();
+}
+
+/* ------------------------------------------------------------- linear */
+/*
+ * Garbled dense / conv2d for all CRT moduli in one launch:
+ *   out[v*npix+pix][d][b] = ( sum_k Wq[v][k] * in[base(pix)+koff[k]][d][b]
+ *                             + cst[v][d] ) mod q
+ * with Wq = W mod q and cst = bias label + (#zero residues in row v) * zero
+ * label -- the exact reformulation of LabelTensor::matvecmul[_tf] /
+ * conv2d with their zero-weight rule (garbling/label_tensor.h:783-858,
+ * 920-1002) and of MatMulModAddZero[TF] / Conv2dModZero
+ * (misc/cuda_util.h:95-138,209-268).  u8 x u8 -> u32 dot products with
+ * dp4a: a thread owns 4 adjacent columns (one 32-bit word of a digit row)
+ * and 8 output rows; four input rows are byte-transposed in registers into
+ * K-packed words.  K <= 65536 keeps the u32 accumulators exact.
+ */
+constexpr int LIN_THREADS = 128;
+constexpr int LIN_ROWS = 8;
+constexpr int LIN_KC = 1024; /* taps staged in shared memory per chunk */
+
+__global__ void __launch_bounds__(LIN_THREADS) k_linear(const __grid_constant__ LinearParams P) {
+    __shared__ uint4 s_w[LIN_KC / 4][2];  /* [k/4][8 rows] packed weights */
+    __shared__ int32_t s_koff[LIN_KC];
+    const int j = blockIdx.z;
+    const ModInfo m = P.mod[j];
+    const uint32_t ncols = m.nc * P.Bp;
+    const uint32_t col = (blockIdx.x * LIN_THREADS + threadIdx.x) * 4;
+    const uint32_t nvg = (P.M + LIN_ROWS - 1) / LIN_ROWS;
+    const uint32_t vg = blockIdx.y % nvg;
+    const uint32_t pix = blockIdx.y / nvg;
+    const uint64_t base = (uint64_t)(pix / P.ow) * P.step_y + (uint64_t)(pix % P.ow) * P.step_x;
+    const uint64_t rowlen = ncols;
+    const bool active = col < ncols;
+    const uint8_t* in = P.in[j] + base * rowlen + col;
+
+    uint32_t acc[LIN_ROWS][4];
+#pragma unroll
+    for (int r = 0; r < LIN_ROWS; ++r)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[r][c] = 0;
+
+    const uint32_t k4_total = P.Kp / 4;
+    for (uint32_t k4_0 = 0; k4_0 < k4_total; k4_0 += LIN_KC / 4) {
+        const uint32_t k4_n = min((uint32_t)(LIN_KC / 4), k4_total - k4_0);
+        __syncthreads();
+        const uint4* wsrc = reinterpret_cast<const uint4*>(P.w4[j]) + ((uint64_t)vg * k4_total + k4_0) * 2;
+        for (uint32_t i = threadIdx.x; i < k4_n * 2; i += LIN_THREADS) (&s_w[0][0])[i] = __ldg(wsrc + i);
+        for (uint32_t i = threadIdx.x; i < k4_n * 4; i += LIN_THREADS) s_koff[i] = __ldg(P.koff + k4_0 * 4 + i);
+        __syncthreads();
+        if (!active) continue;
+        for (uint32_t kk = 0; kk < k4_n; ++kk) {
+            const uint32_t x0 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 0] * rowlen));
+            const uint32_t x1 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 1] * rowlen));
+            const uint32_t x2 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 2] * rowlen));
+            const uint32_t x3 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 3] * rowlen));
+            /* 4x4 byte transpose: y_c = (x0.c, x1.c, x2.c, x3.c) */
+            const uint32_t t0 = __byte_perm(x0, x1, 0x5140), t1 = __byte_perm(x0, x1, 0x7362);
+            const uint32_t u0 = __byte_perm(x2, x3, 0x5140), u1 = __byte_perm(x2, x3, 0x7362);
+            const uint32_t y0 = __byte_perm(t0, u0, 0x5410), y1 = __byte_perm(t0, u0, 0x7632);
+            const uint32_t y2 = __byte_perm(t1, u1, 0x5410), y3 = __byte_perm(t1, u1, 0x7632);
+            const uint4 wa = s_w[kk][0], wb = s_w[kk][1];
+            const uint32_t w[LIN_ROWS] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+            for (int r = 0; r < LIN_ROWS; ++r) {
+                acc[r][0] = __dp4a(y0, w[r], acc[r][0]);
+                acc[r][1] = __dp4a(y1, w[r], acc[r][1]);
+                acc[r][2] = __dp4a(y2, w[r], acc[r][2]);
+                acc[r][3] = __dp4a(y3, w[r], acc[r][3]);
+            }
+        }
+    }
+    if (!active) return;
+    const uint32_t d = col / P.Bp;
+#pragma unroll
+    for (int r = 0; r < LIN_ROWS; ++r) {
+        const uint32_t v = vg * LIN_ROWS + r;
+        if (v >= P.M) break;
+        const uint32_t cst = __ldg(P.cst[j] + (uint64_t)v * m.nc + d);
+        uint32_t o = 0;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) o |= ((acc[r][c] + cst) % m.q) << (8 * c);
+        *reinterpret_cast<uint32_t*>(P.out[j] + ((uint64_t)v * P.npix + pix) * rowlen + col) = o;
+    }
+}
+
+cudaError_t launch_linear(const LinearParams& p, cudaStream_t s) {
+    uint32_t max_cols = 0;
+    for (int j = 0; j < p.k; ++j) max_cols = max(max_cols, p.mod[j].nc * p.Bp);
+    const uint32_t nvg = (p.M + LIN_ROWS - 1) / LIN_ROWS;
+    dim3 grid((max_cols / 4 + LIN_THREADS - 1) / LIN_THREADS, p.npix * nvg, p.k);
+    k_linear<<<grid, LIN_THREADS, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
+/* -------------------------------------------------------- projection */
+/* GarbledProjection::cuda_evaluate / eval_proj (layer/garbled_projection.h:
+ * 168-194, misc/cuda_util.h:297-317): out = digits(ciphers[e][colour] -
+ * H(compress(in))). */
+__global__ void __launch_bounds__(128) k_projection(const __grid_constant__ ProjParams P) {
+    __shared__ AesSmem aes;
+    aes_smem_load(aes);
+    const int j = blockIdx.y;
+    const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P.n * P.batch) return;
+    const uint32_t b = (uint32_t)(idx % P.batch);
+    const uint64_t e = idx / P.batch;
+    uint32_t colour;
+    const u128 key = load_compress(P.in[j], P.min[j], e, b, P.Bp, colour);
+    const u128 h = hash(aes, key);
+    const u128 row = ldg128(P.ciphers[j] + e * P.min[j].q + colour);
+    store_digits(P.out[j], P.mout[j], e, b, P.Bp, gc::sub128(row, h));
+}
+
+cudaError_t launch_projection(const ProjParams& p, cudaStream_t s) {
+    const uint64_t total = p.n * p.batch;
+    dim3 grid((unsigned)((total + 127) / 128), p.k);
+    k_projection<<<grid, 128, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
+/* ------------------------------------------------- sign gadget / ReLU */
+/* digit-wise accumulation of a compressed label into acc[] (no reduction:
+ * at most k+1 digits below 2^11 are summed) */
+__device__ __forceinline__ void accumulate(u128 x, const ModInfo& m, uint16_t* acc) {
+    gc::for_each_digit(x, m, [&](uint32_t d, uint32_t v) { acc[d] = (uint16_t)(acc[d] + v); });
+}
+
+/* compress(acc mod q) and the colour of the sum */
+__device__ __forceinline__ u128 compress_acc(const uint16_t* acc, const ModInfo& m, uint32_t& colour) {
+    gc::Compressor c(m);
+    uint32_t dg = 0;
+    for (int d = (int)m.nc - 1; d >= 0; --d) {
+        dg = gc::mod_q(acc[d], m);
+        c.push(dg);
+    }
+    colour = dg;
+    return c.value();
+}
+
+/*
+ * Fused approximate-sign gadget, optionally followed by the ReLU's mixed-
+ * modulus half gates.  Replaces eval_approx_res_gadget + mrs_sum_most_sig +
+ * eval_sign (gadgets/sign_gadget.h:41-213,737-795) and eval_sign_mult
+ * (layer/garbled_relu.h:19-38,258-294) -- three kernels, three device
+ * syncs, device-side new/delete -- and follows SignGadget::cpu_evaluate
+ * (gadgets/sign_gadget.h:583-671) + MixedModHalfGate::cpu_evaluate
+ * (gates/mixed_mod_half_gate.h:91-104) bit for bit.
+ *
+ * Hash reuse (results identical, fewer AES blocks than the reference):
+ * the n_mrs approximate-residue projections of residue j and its garbler
+ * half gate all key on H(x_j); the evaluator half gate and the mini gate of
+ * every modulus key on H(s); the sign projections of every out modulus key
+ * on H(top sum).  The per-digit sums of digits i >= 1 (mrs_sum, :615-622)
+ * are never read by the reference and are not formed.
+ */
+template <bool RELU>
+__global__ void __launch_bounds__(128) k_sign(const __grid_constant__ SignParams P) {
+    __shared__ AesSmem aes;
+    aes_smem_load(aes);
+    const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P.n * P.batch) return;
+    const uint32_t b = (uint32_t)(idx % P.batch);
+    const uint64_t e = idx / P.batch;
+    const int k = P.k;
+    const int nm = P.n_mrs;
+
+    /* Step 1a: key and hash every CRT residue label once */
+    u128 h[MAXK];
+    uint32_t col[MAXK];
+#pragma unroll 1
+    for (int j = 0; j < k; ++j) {
+        const u128 key = load_compress(P.in[j], P.crt[j], e, b, P.Bp, col[j]);
+        h[j] = hash(aes, key);
+    }
+
+    /* Step 2: mixed-radix addition from the least significant digit */
+    uint16_t acc[128];
+    u128 carry = P.carry0;
+    const u128* approx_e = P.approx + e * (uint64_t)nm * P.S;
+    uint64_t cnt1 = e * (uint64_t)(k + 1) * P.Mp, cnt2 = cnt1;
+#pragma unroll 1
+    for (int i = nm - 1; i >= 1; --i) {
+        const ModInfo& M = P.mrs[i];
+        const ModInfo& C = P.cast[i];
+        for (uint32_t d = 0; d < C.nc; ++d) acc[d] = 0;
+#pragma unroll 1
+        for (int j = 0; j <= k; ++j) {
+            /* Step 1b: approx. MRS digit i of residue j (j == k: the carry) */
+            u128 lab = carry;
+            if (j < k)
+                lab = gc::sub128(ldg128(approx_e + (uint64_t)nm * P.prefix[j] + (uint64_t)i * P.crt[j].q + col[j]),
+                                 h[j]);
+            /* Step 2.2: cast to modulus (k+1)*m_i */
+            const u128 hl = hash(aes, lab);
+            const uint32_t c0 = gc::colour_of(lab, M);
+            accumulate(gc::sub128(ldg128(P.cast1 + cnt1 + (uint64_t)j * M.q + c0), hl), C, acc);
+        }
+        cnt1 += (uint64_t)(k + 1) * M.q;
+        /* Step 2.3 / 2.4: sum of the casts -> carry into digit i-1 */
+        uint32_t c2;
+        const u128 sum2 = compress_acc(acc, C, c2);
+        carry = gc::sub128(ldg128(P.cast2 + cnt2 + c2), hash(aes, sum2));
+        cnt2 += C.q;
+    }
+    /* most significant digit: sum = carry + sum_j digit_{j,0} */
+    const ModInfo& M0 = P.mrs[0];
+    for (uint32_t d = 0; d < M0.nc; ++d) acc[d] = 0;
+#pragma unroll 1
+    for (int j = 0; j <= k; ++j) {
+        u128 lab = carry;
+        if (j < k) lab = gc::sub128(ldg128(approx_e + (uint64_t)nm * P.prefix[j] + col[j]), h[j]);
+        accumulate(lab, M0, acc);
+    }
+    uint32_t ctop;
+    const u128 top = compress_acc(acc, M0, ctop);
+    const u128 htop = hash(aes, top);
+
+    /* Step 3: sign projection(s) */
+    const u128* sign_e = P.sign + e * (uint64_t)P.n_out * M0.q;
+    if (!RELU) {
+#pragma unroll 1
+        for (int j = 0; j < P.n_out; ++j)
+            store_digits(P.out[j], P.outm[j], e, b, P.Bp,
+                         gc::sub128(ldg128(sign_e + (uint64_t)j * M0.q + ctop), htop));
+        return;
+    }
+    /* Step 4 (ReLU): out_j = E_j + (y+r)*x_j - G_j  (mod p_j) */
+    const u128 s = gc::sub128(ldg128(sign_e + ctop), htop); /* sign label, modulus 2 */
+    const u128 hs = hash(aes, s);
+    const uint32_t cs = (uint32_t)s.lo & 1u;
+#pragma unroll 1
+    for (int j = 0; j < k; ++j) {
+        const ModInfo& Pm = P.crt[j];
+        const u128 G = gc::sub128(ldg128(P.garbler + e * (uint64_t)P.S + P.prefix[j] + col[j]), h[j]);
+        const u128* ev = P.evaluator + (e * (uint64_t)k + j) * 3;
+        const u128 E = gc::sub128(ldg128(ev + cs), hs);
+        /* mini gate: int16 row `cs` of the packed slot minus the low 16 hash
+         * bits (gates/projection_gate_mini.h:45-56) */
+        const u128 mini = ldg128(ev + 2);
+        const int16_t row16 = (int16_t)((mini.lo >> (16 * cs)) & 0xffff);
+        const int16_t t16 = (int16_t)(row16 - (int16_t)(hs.lo & 0xffff));
+        int tt = (int)t16 % (int)Pm.q;
+        if (tt < 0) tt += (int)Pm.q;
+        const uint64_t off = e * (uint64_t)Pm.nc * P.Bp + b;
+        const uint8_t* xin = P.in[j] + off;
+        uint8_t* xout = P.out[j] + off;
+        gc::for_each_digit2(E, G, Pm, [&](uint32_t d, uint32_t de, uint32_t dg) {
+            const uint32_t x = xin[d * P.Bp];
+            xout[d * P.Bp] = (uint8_t)gc::mod_q(de + (uint32_t)tt * x + Pm.q - dg, Pm);
+        });
+    }
+}
+
+cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s) {
+    const uint64_t total = p.n * p.batch;
+    const unsigned grid = (unsigned)((total + 127) / 128);
+    if (relu)
+        k_sign<true><<<grid, 128, 0, s>>>(p);
+    else
+        k_sign<false><<<grid, 128, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
+/* ------------------------------------------------------------ rescale */
+/*
+ * General-factor rescale with base extension, one thread per (element,
+ * inference), all k residues' digits in a per-thread workspace.  CPU-only
+ * in the reference ("Not yet implemented" on the GPU:
+ * gadgets/base_extension_gadget.h:297-315; rescale_gadget.h:364); follows
+ * RescaleGadget::cpu_evaluate (gadgets/rescale_gadget.h:244-362) and
+ * BaseExtensionGadget::cpu_evaluate (gadgets/base_extension_gadget.h:
+ * 197-295).  Each source label is hashed once for all the projections that
+ * key on it.  With P.legacy the kernel stops after step 2.3; the legacy
+ * variant's sign gadget (k_sign) and downshift (k_add_label) follow.
+ */
+__global__ void __launch_bounds__(128) k_rescale(const __grid_constant__ RescaleParams P) {
+    __shared__ AesSmem aes;
+    aes_smem_load(aes);
+    const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P.n * P.batch) return;
+    const uint32_t b = (uint32_t)(idx % P.batch);
+    const uint64_t e = idx / P.batch;
+    const int k = P.k;
+    uint8_t lw[LW_MAX];
+
+    /* Step 1: upshift */
+    for (int j = 0; j < k; ++j) {
+        const ModInfo& m = P.crt[j];
+        const uint8_t* p = P.in[j] + e * (uint64_t)m.nc * P.Bp + b;
+        uint8_t* w = lw + P.loff[j];
+        for (uint32_t d = 0; d < m.nc; ++d) {
+            uint32_t v = (uint32_t)p[d * P.Bp] + __ldg(P.up[j] + d);
+            w[d] = (uint8_t)(v >= m.q ? v - m.q : v);
+        }
+    }
+    /* Step 2: divide by every factor */
+    for (int i = 0; i < P.nf; ++i) {
+        const int f = P.fidx[i];
+        const ModInfo& mf = P.crt[f];
+        gc::Compressor c(mf);
+        for (int d = (int)mf.nc - 1; d >= 0; --d) c.push(lw[P.loff[f] + d]);
+        const uint32_t colour = lw[P.loff[f]];
+        const u128 hf = hash(aes, c.value());
+        for (int j = 0; j < k; ++j) {
+            if (P.tm_off[i][j] == ~0ull) continue; /* ignored modulus */
+            const ModInfo& m = P.crt[j];
+            const u128 pr = gc::sub128(ldg128(P.tm + P.tm_off[i][j] + e * (uint64_t)P.factor[i] + colour), hf);
+            uint8_t* w = lw + P.loff[j];
+            const uint32_t inv = P.inv_f[i][j];
+            gc::for_each_digit(pr, m, [&](uint32_t d, uint32_t v) {
+                w[d] = (uint8_t)gc::mod_q(((uint32_t)w[d] + m.q - v) * inv, m);
+            });
+        }
+    }
+    /* Step 2.3: zero label on the factors' residues */
+    for (int i = 0; i < P.nf; ++i) {
+        const int f = P.fidx[i];
+        for (uint32_t d = 0; d < P.crt[f].nc; ++d) lw[P.loff[f] + d] = __ldg(P.zero[f] + d);
+    }
+    /* store residue j (after the downshift of step 4, unless legacy, where
+     * the sign gadget and k_add_label follow) */
+    auto store_residue = [&](int j) {
+        const ModInfo& m = P.crt[j];
+        uint8_t* p = P.out[j] + e * (uint64_t)m.nc * P.Bp + b;
+        const uint8_t* w = lw + P.loff[j];
+        for (uint32_t d = 0; d < m.nc; ++d) {
+            uint32_t v = w[d];
+            if (!P.legacy) {
+                v = v + m.q - __ldg(P.down[j] + d);
+                if (v >= m.q) v -= m.q;
+            }
+            p[d * P.Bp] = (uint8_t)v;
+        }
+    };
+    if (P.legacy) {
+        for (int j = 0; j < k; ++j) store_residue(j);
+        return;
+    }
+    /* The base extension only changes the factors' residues
+     * (base_extension_gadget.h:253-294): the others leave now, their
+     * workspace copies are consumed by the elimination below. */
+    for (int t = 0; t < P.non_ext; ++t) store_residue(P.perm[t]);
+    /* Step 3: base extension (garbled mixed-radix conversion) */
+    for (int i = 0; i < P.non_ext; ++i) {
+        const int ji = P.perm[i];
+        const ModInfo& mi = P.crt[ji];
+        gc::Compressor c(mi);
+        for (int d = (int)mi.nc - 1; d >= 0; --d) c.push(lw[P.loff[ji] + d]);
+        const uint32_t colour = lw[P.loff[ji]];
+        const u128 hi = hash(aes, c.value());
+        for (int t = i + 1; t < k; ++t) {
+            const int jt = P.perm[t];
+            const ModInfo& mt = P.crt[jt];
+            const u128 pr = gc::sub128(ldg128(P.be + P.be_off[i][t] + e * (uint64_t)mi.q + colour), hi);
+            uint8_t* w = lw + P.loff[jt];
+            const uint32_t inv = P.inv_partial[i][t];
+            gc::for_each_digit(pr, mt, [&](uint32_t d, uint32_t v) {
+                w[d] = (uint8_t)gc::mod_q(((uint32_t)w[d] + mt.q - v) * inv, mt);
+            });
+        }
+    }
+    for (int x = 0; x < P.nf; ++x) {
+        /* the extended residue is the last mixed-radix digit times -invv */
+        const int j = P.extra_idx[x];
+        const ModInfo& m = P.crt[j];
+        uint8_t* w = lw + P.loff[j];
+        for (uint32_t d = 0; d < m.nc; ++d) w[d] = (uint8_t)gc::mod_q((uint32_t)w[d] * P.neg_invv[x], m);
+        store_residue(j);
+    }
+}
+
+cudaError_t launch_rescale(const RescaleParams& p, cudaStream_t s) {
+    const uint64_t total = p.n * p.batch;
+    k_rescale<<<(unsigned)((total + 127) / 128), 128, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
+/* AddLabel / SubLabel (misc/cuda_util.h:54-76): add or subtract one
+ * broadcast label on every label of every plane. */
+__global__ void k_add_label(const __grid_constant__ AddLabelParams P) {
+    const int j = blockIdx.y;
+    const ModInfo& m = P.crt[j];
+    const uint64_t total = P.n * m.nc * (uint64_t)P.Bp;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t d = (uint32_t)((i / P.Bp) % m.nc);
+        const uint32_t l = __ldg(P.label[j] + d);
+        uint32_t v = P.plane[j][i];
+        v = P.subtract ? v + m.q - l : v + l;
+        if (v >= m.q) v -= m.q;
+        P.plane[j][i] = (uint8_t)v;
+    }
+}
+
+cudaError_t launch_add_label(const AddLabelParams& p, cudaStream_t s) {
+    uint64_t mx = 0;
+    for (int j = 0; j < p.k; ++j) mx = max(mx, p.n * p.crt[j].nc * (uint64_t)p.Bp);
+    uint64_t want = (mx + 255) / 256;
+    unsigned gx = (unsigned)(want < 148 * 16 ? want : 148 * 16);
+    dim3 grid(gx ? gx : 1, p.k);
+    k_add_label<<<grid, 256, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
+/* ------------------------------------------------------------- decode */
+/* decode_outputs (garbling/garbled_circuit_interface.h:422-467): hash each
+ * output label, find the residue whose decoding hash matches, CRT-combine,
+ * map to the signed range.  One thread per (output, inference). */
+__global__ void __launch_bounds__(128) k_decode(const __grid_constant__ DecodeParams P) {
+    __shared__ AesSmem aes;
+    aes_smem_load(aes);
+    const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P.n * P.batch) return;
+    const uint32_t b = (uint32_t)(idx % P.batch);
+    const uint64_t e = idx / P.batch;
+    unsigned __int128 sum = 0;
+    bool good = true;
+    for (int j = 0; j < P.k; ++j) {
+        uint32_t colour;
+        const u128 hh = hash(aes, load_compress(P.in[j], P.crt[j], e, b, P.Bp, colour));
+        int found = -1;
+        for (uint32_t r = 0; r < P.crt[j].q; ++r) {
+            const u128 dref = ldg128(P.dec[j] + (uint64_t)r * P.n + e);
+            if (dref.lo == hh.lo && dref.hi == hh.hi) found = (int)r;
+        }
+        if (found < 0) {
+            good = false;
+            found = 0;
+        }
+        /* util::chinese_remainder (misc/util.h:116-141) term by term */
+        const unsigned __int128 prod = (unsigned __int128)(uint64_t)P.prod;
+        sum += (((unsigned __int128)(uint64_t)found * (uint64_t)P.inv[j]) % prod * (uint64_t)P.pdiv[j]) % prod;
+    }
+    int64_t v = (int64_t)(uint64_t)(sum % (uint64_t)P.prod);
+    if (v >= P.crt_modulus / 2) v -= P.crt_modulus;
+    P.values[(uint64_t)b * P.n + e] = v;
+    if (!good) P.ok[b] = 0;
+}
+
+cudaError_t launch_decode(const DecodeParams& p, cudaStream_t s) {
+    const uint64_t total = p.n * p.batch;
+    k_decode<<<(unsigned)((total + 127) / 128), 128, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace dashb

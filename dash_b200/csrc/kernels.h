@@ -1,0 +1,132 @@
+/*
+ * kernels.h -- host-side launch interface of the sm_100a kernels
+ * (kernels.cu) used by the C-ABI layer (dashb_api.cu).
+ *
+ * Device layout of a label tensor ("residue-major digit planes"): one plane
+ * per CRT modulus j, u8 digits,
+ *     plane_j[element e][digit d][batch b]   at  e*nc_j*Bp + d*Bp + b,
+ * Bp = batch rounded up to 16, so every (element, digit) row is 16-byte
+ * aligned and the whole plane is the K x N (N = nc_j*Bp) row-major operand
+ * of the linear kernels as it stands.
+ */
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "gc_common.cuh"
+
+namespace dashb {
+
+constexpr int MAXK = 12;   /* CRT moduli */
+constexpr int MAXM = 12;   /* MRS digits */
+constexpr int MAXF = 4;    /* rescale factors */
+constexpr int LW_MAX = 640; /* sum of nc over the CRT base that a rescale thread keeps */
+
+struct LinearParams {
+    const uint8_t* in[MAXK];
+    uint8_t* out[MAXK];
+    const uint32_t* w4[MAXK];  /* [ceil(M/8)][Kp/4][8] packed weights mod q_j */
+    const uint8_t* cst[MAXK];  /* [M][nc_j] bias + zero-weight constant label */
+    gc::ModInfo mod[MAXK];
+    const int32_t* koff;       /* [Kp] input element offset of tap k */
+    uint32_t M, K, Kp;
+    uint32_t npix, ow;         /* output pixels per filter, output width */
+    uint32_t step_x, step_y;   /* element offset per output x / y step */
+    uint32_t Bp;
+    int k;
+};
+
+struct SignParams {
+    const uint8_t* in[MAXK];
+    uint8_t* out[MAXK];
+    gc::ModInfo crt[MAXK];
+    gc::ModInfo mrs[MAXM];
+    gc::ModInfo cast[MAXM];  /* modulus (k+1)*m_i, i >= 1 */
+    gc::ModInfo outm[MAXK];  /* sign layer: out moduli */
+    const gc::u128 *approx, *cast1, *cast2, *sign, *garbler, *evaluator;
+    gc::u128 carry0;         /* compressed zero label of m_{n_mrs-1} */
+    uint64_t n;
+    uint32_t prefix[MAXK];
+    uint32_t S, Mp;
+    uint32_t batch, Bp;
+    int k, n_mrs, n_out;
+};
+
+struct ProjParams {
+    const uint8_t* in[MAXK];
+    uint8_t* out[MAXK];
+    gc::ModInfo min[MAXK], mout[MAXK];
+    const gc::u128* ciphers[MAXK];
+    uint64_t n;
+    uint32_t batch, Bp;
+    int k;
+};
+
+struct RescaleParams {
+    const uint8_t* in[MAXK];
+    uint8_t* out[MAXK];
+    gc::ModInfo crt[MAXK];
+    const uint8_t* up[MAXK];    /* upshift label digits (u8[nc_j]) */
+    const uint8_t* down[MAXK];  /* downshift label digits */
+    const uint8_t* zero[MAXK];  /* zero label digits */
+    uint32_t loff[MAXK];        /* offset of residue j in the thread's digit workspace */
+    const gc::u128* tm;
+    const gc::u128* be;
+    uint64_t tm_off[MAXF][MAXK]; /* row offset of block (factor i, modulus j) */
+    uint16_t inv_f[MAXF][MAXK];  /* factor_i^-1 mod p_j */
+    uint32_t factor[MAXF];
+    int fidx[MAXF];
+    int perm[MAXK];              /* swapped order -> CRT index */
+    uint64_t be_off[MAXK][MAXK]; /* row offset of BE block (i, t) in swapped order */
+    uint16_t inv_partial[MAXK][MAXK];
+    uint16_t neg_invv[MAXF];     /* (-invv) mod extra modulus */
+    int extra_idx[MAXF];         /* CRT index of extra modulus x */
+    int extra_pos[MAXF];         /* its position in the swapped order */
+    uint64_t n;
+    uint32_t batch, Bp;
+    int k, nf, non_ext;
+    int legacy;                  /* 1: stop after step 2.3 (sign gadget and downshift follow) */
+};
+
+struct AddLabelParams {
+    uint8_t* plane[MAXK];
+    const uint8_t* label[MAXK]; /* u8[nc_j] */
+    gc::ModInfo crt[MAXK];
+    uint64_t n;
+    uint32_t Bp;
+    int k;
+    int subtract;
+};
+
+struct DecodeParams {
+    const uint8_t* in[MAXK];
+    gc::ModInfo crt[MAXK];
+    const gc::u128* dec[MAXK]; /* [p_j][n] */
+    int64_t inv[MAXK];         /* mul_inv(prod / p_j, p_j) mod prod */
+    int64_t pdiv[MAXK];        /* prod / p_j */
+    int64_t prod, crt_modulus;
+    int64_t* values;           /* [batch][n] */
+    uint8_t* ok;               /* [batch] */
+    uint64_t n;
+    uint32_t batch, Bp;
+    int k;
+};
+
+/* uploads T-tables / S-box / round keys of key 00..0f to the device */
+cudaError_t upload_aes_tables();
+/* host copies of the tables for dashb_hostcheck_* */
+void host_aes_tables(const uint32_t** te0, const uint32_t** te1, const uint32_t** te2, const uint32_t** te3,
+                     const uint8_t** sbox, const uint32_t** rk);
+
+cudaError_t launch_ingest(const int16_t* src, uint8_t* plane, uint64_t rows /* n*nc */, uint32_t batch, uint32_t Bp,
+                          cudaStream_t s);
+cudaError_t launch_egress(const uint8_t* plane, int16_t* dst, uint64_t rows, uint32_t batch, uint32_t Bp,
+                          cudaStream_t s);
+cudaError_t launch_linear(const LinearParams& p, cudaStream_t s);
+cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s);
+cudaError_t launch_projection(const ProjParams& p, cudaStream_t s);
+cudaError_t launch_rescale(const RescaleParams& p, cudaStream_t s);
+cudaError_t launch_add_label(const AddLabelParams& p, cudaStream_t s);
+cudaError_t launch_decode(const DecodeParams& p, cudaStream_t s);
+
+}  // namespace dashb

@@ -1,0 +1,80 @@
+"""Generates the golden fixtures in this directory with the UNMODIFIED
+reference (oracle/_ref/libdash_ref.so, built from /root/reference by
+oracle/Makefile).  Run in the build container only:
+
+    python tests/golden/make_golden.py
+
+For every unit circuit: <name>.gcm (garbled material, seeded garbling) and
+<name>.npz with integer inputs `x`, the reference's input labels `in<j>`,
+the output labels of every garbled layer `l<layer>_<j>` as computed by the
+reference's own cpu_evaluate, and the decoded outputs `dec`.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "..", ".."))
+
+import workloads as W  # noqa: E402
+from oracle import refbind as R  # noqa: E402
+
+GOLDEN = ["SIGN_TINY", "RELU_99", "RESCALE_LEGACY", "RESCALE_2", "RESCALE_2_3", "RESCALE_OPT", "PROJECTION",
+          "MLP_TINY", "CONV_UNIT", "RELU_EDGE"]
+
+# extra unit circuits only used as fixtures
+W.MODELS["CONV_UNIT"] = dict(  # stride 2, two channels, three filters (cf. test_conv2d.h:133-261)
+    input=(5, 5, 2), layers=[("conv", 3, 3, 2), ("relu",), ("flatten",), ("dense", 2)],
+    quant=("simple", 0.05), crt=[2, 3, 5, 7, 11], mrs=[54, 4, 3], max_modulus=0)
+W.MODELS["RELU_EDGE"] = dict(  # test_relu.h:144-225: crt {2,3,5}, mrs {26,6,3,2}
+    input=(14, 1, 1), layers=[("flatten",), ("relu",)], quant=("simple", 1.0), crt=[2, 3, 5], mrs=[26, 6, 3, 2],
+    max_modulus=0)
+
+BATCH = 3
+
+
+def inputs_for(name, spec, n):
+    if name == "RELU_EDGE":
+        P = 30  # 0, +-1, +-mid, +-extremes of the signed range (-P/2, P/2)
+        row = np.array([0, 1, -1, 7, -7, 14, -14, 2, -2, 13, -13, 5, -5, 3], dtype=np.int64)
+        return np.stack([row, -row, np.roll(row, 3)])[:, :n]
+    if name in ("RESCALE_LEGACY", "RESCALE_2", "RESCALE_2_3"):
+        rng = np.random.default_rng(3)
+        return rng.integers(-1000, 1000, size=(BATCH, n), dtype=np.int64)
+    return W.synthetic_inputs(spec, BATCH, seed=11)
+
+
+def main():
+    for name in GOLDEN:
+        spec = W.MODELS[name]
+        c = W.build_reference_circuit(spec, seed=1234, weight_seed=7)
+        c.export(os.path.join(HERE, name + ".gcm"))
+        X = inputs_for(name, spec, c.input_size)
+        out = {"x": X}
+        ins = [[] for _ in range(c.k)]
+        lay = {}
+        dec = []
+        for x in X:
+            lab = c.garble_inputs(x)
+            for j in range(c.k):
+                ins[j].append(lab[j])
+            for l in range(c.n_layers):
+                o = c.cpu_evaluate_layer(lab, l, 1)
+                for j in range(c.k):
+                    lay.setdefault((l, j), []).append(o[j])
+            final, _ = c.cpu_evaluate(lab, 1)
+            if all(q == p for q, p in zip(c.out_moduli, c.crt)):
+                dec.append(c.decode_outputs(final))
+        for j in range(c.k):
+            out["in%d" % j] = np.stack(ins[j])
+        for (l, j), v in lay.items():
+            out["l%d_%d" % (l, j)] = np.stack(v)
+        if dec:
+            out["dec"] = np.stack(dec)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+        print(name, "layers", c.n_layers, "gcm KB", os.path.getsize(os.path.join(HERE, name + ".gcm")) >> 10)
+
+
+if __name__ == "__main__":
+    main()
