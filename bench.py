@@ -1,0 +1,325 @@
+#!/usr/bin/env python
+"""bench.py -- online garbled-evaluation throughput of the B200 evaluator.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference]
+
+One "step" = one pass of the hot path (every garbled layer of the model)
+over one batch of synthetic inferences.  Workload at N=1: BASELINE.json
+configs[1], the MNIST LeNet-5-style CNN (MODEL_B_POOL_REPL), batch 256 per
+GPU; N>1 shards independent inferences (weak scaling, no data-path
+collective).  Prints ONE JSON line on rank 0; see DESIGN.md "Measurement".
+
+The garbled material and the input labels are *inputs* of the path: they are
+produced outside the timed region by the reference's own garbler
+(oracle/_ref, test infrastructure) with a fixed seed and cached under
+$DASHB_CACHE.  The reference arm (--impl reference) and the cpu_baseline leg
+time the reference's own CPU evaluator on the same material.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import workloads as W  # noqa: E402
+
+METRIC = "online garbled-eval inferences/s"
+CACHE = os.environ.get("DASHB_CACHE", "/tmp/dashb_cache")
+SEED = 42
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def material_paths(model):
+    os.makedirs(CACHE, exist_ok=True)
+    return os.path.join(CACHE, "%s_s%d.gcm" % (model, SEED)), os.path.join(CACHE, "%s_s%d_in.npz" % (model, SEED))
+
+
+def build_material(model, n_inputs, want_ref=False):
+    """Garbles `model` with the reference (seeded) and encodes n_inputs
+    synthetic inputs.  Returns (gcm path, labels [k][n_inputs][n][nc], ref)."""
+    from oracle import refbind
+
+    gcm, npz = material_paths(model)
+    spec = W.MODELS[model]
+    ref = None
+    have = os.path.exists(gcm) and os.path.exists(npz)
+    if have:
+        z = np.load(npz)
+        labels = [z["in%d" % j] for j in range(len(spec["crt"]))]
+        have = labels[0].shape[0] >= n_inputs
+    if not have or want_ref:
+        if not refbind.available():
+            raise RuntimeError("oracle/_ref/libdash_ref.so missing: build it where /root/reference exists (make -C oracle ref)")
+        ref = W.build_reference_circuit(spec, seed=SEED, weight_seed=SEED)
+    if not have:
+        ref.export(gcm + ".tmp")
+        os.replace(gcm + ".tmp", gcm)
+        X = W.synthetic_inputs(spec, n_inputs, seed=SEED)
+        per = [ref.garble_inputs(x) for x in X]
+        labels = [np.stack([p[j] for p in per]) for j in range(ref.k)]
+        np.savez(npz + ".tmp.npz", x=X, **{"in%d" % j: labels[j] for j in range(ref.k)})
+        os.replace(npz + ".tmp.npz", npz)
+    return gcm, [l[:n_inputs] for l in labels], ref
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.stop_flag = threading.Event()
+        self.samples = []
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            self.stop_flag.wait(0.1)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(s[0]) for s in self.samples)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i] == "Active" for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][1]), "reasons": reasons,
+                "samples": len(self.samples)}
+
+
+def run_reference(args, rank):
+    """Reference arm: the reference's own CPU evaluator (oracle/_ref) with all
+    host threads on the same model; a step is a bounded sample of inferences."""
+    if rank != 0:
+        return
+    threads = host_threads()
+    per_step = args.ref_inferences
+    n = per_step * (args.steps + args.warmup)
+    gcm, labels, ref = build_material(args.model, max(n, 1), want_ref=True)
+    times = []
+    idx = 0
+    for s in range(args.steps + args.warmup):
+        t0 = time.perf_counter()
+        for _ in range(per_step):
+            ref.cpu_evaluate([l[idx % labels[0].shape[0]] for l in labels], threads, want_output=False)
+            idx += 1
+        if s >= args.warmup:
+            times.append(time.perf_counter() - t0)
+    total = sum(times)
+    value = per_step * args.steps / total
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "inferences/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "%s garbled online evaluation (BASELINE.json configs[1]), reference CPU evaluator" % args.model,
+                   "batch": per_step},
+        "cpu_baseline": {"value": value, "unit": "inferences/s", "cores": threads, "kind": "reference",
+                         "sample": "%d inferences per step, GarbledCircuitInterface::cpu_evaluate, %d threads" % (per_step, threads)},
+        "e2e": {"value": value, "unit": "inferences/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--model", default="MODEL_B_POOL_REPL")
+    ap.add_argument("--batch", type=int, default=256, help="inferences per GPU per step")
+    ap.add_argument("--ref-inferences", type=int, default=2, help="reference arm: inferences per step")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="cpu_baseline leg budget")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if args.warmup < 3:
+        args.warmup = 3
+
+    import torch
+    import torch.distributed as dist
+
+    from dash_b200 import api
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    # ---- inputs of the path (outside the timed region) -------------------
+    B = args.batch
+    if rank == 0:
+        gcm, labels, _ = build_material(args.model, B)
+    barrier()
+    if rank != 0:
+        gcm, labels, _ = build_material(args.model, B)
+    api.init(local_rank)
+    circ = api.Circuit.load(gcm, max_batch=B)
+    stream = torch.cuda.ExternalStream(api.stream_handle())
+
+    # pinned host buffers: what a caller hands to the C ABI
+    pinned_in = []
+    for l in labels:
+        t = torch.empty(l.shape, dtype=torch.int16).pin_memory()
+        t.numpy()[...] = l
+        pinned_in.append(t)
+    in_np = [t.numpy() for t in pinned_in]
+    h2d = sum(l.nbytes for l in in_np)
+    out_t = [torch.empty((B, circ.output_size, api.nr_comps(q)), dtype=torch.int16).pin_memory() for q in circ.out_moduli]
+    out_np = [t.numpy() for t in out_t]
+    d2h = sum(o.nbytes for o in out_np)
+    in_ptrs = api._ptr_array(in_np)
+    out_ptrs = api._ptr_array(out_np)
+    L = circ.L
+
+    circ.move_inputs(in_np)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def step_device():
+        api._check(L.dashb_evaluate_device(circ.h))
+
+    def step_e2e():
+        api._check(L.dashb_evaluate(circ.h, in_ptrs, B, out_ptrs))
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        barrier()
+        torch.cuda.synchronize()
+        ms = 0.0
+        for _ in range(steps):
+            flush.zero_()  # L2 flush between timed iterations (not timed)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            fn()
+            e1.record(stream)
+            e1.synchronize()
+            ms += e0.elapsed_time(e1)
+        torch.cuda.synchronize()
+        barrier()
+        if world > 1:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    circ.set_layer_timing(True)
+    ms_dev = timed(step_device, args.steps, args.warmup)
+    layer_ms = circ.layer_times_ms()  # last timed step
+    launches = circ.launch_count()
+    circ.set_layer_timing(False)
+    ms_e2e = timed(step_e2e, args.steps, args.warmup)
+    sampler.stop_flag.set()
+    sampler.join()
+
+    total_inf = B * world * args.steps
+    value = total_inf / (ms_dev / 1e3)
+    e2e_value = total_inf / (ms_e2e / 1e3)
+
+    # ---- roofline of the dominant kernel (the fused sign/ReLU gadget) -----
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    relu_ms = sum(ms for (name, ms) in layer_ms if name == "approx_relu")
+    relu_layers = [i for i in range(circ.n_layers) if circ.layer_type(i) == 3]
+    relu_bytes = sum(circ.algorithmic_bytes(i) for i in relu_layers) * B
+    relu_aes = sum(circ.aes_blocks(i) for i in relu_layers) * B
+    achieved = relu_bytes / (relu_ms / 1e3) / 1e9 if relu_ms > 0 else 0.0
+    step_ms = sum(ms for (_, ms) in layer_ms)
+    by_type = {}
+    for name, ms in layer_ms:
+        by_type[name] = by_type.get(name, 0.0) + ms
+    roofline = {
+        "bound": "hbm", "kernel": "k_sign<relu> (fused sign gadget + half gates)", "achieved": achieved, "peak": peak,
+        "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+        "launches_per_step": len(relu_layers), "avg_launch_ms": relu_ms / max(1, len(relu_layers)),
+        "share_of_step": relu_ms / step_ms if step_ms else None,
+        "aes_blocks_per_s": relu_aes / (relu_ms / 1e3) if relu_ms > 0 else 0.0,
+        "note": "compute-bound on AES + base-q digit arithmetic, not on HBM (see DESIGN.md)",
+        "whole_step_algorithmic_GBps": circ.algorithmic_bytes(-1) * B / (step_ms / 1e3) / 1e9 if step_ms else None,
+        "layer_ms": by_type,
+    }
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "inferences/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "%s garbled online evaluation (BASELINE.json configs[1]): conv2d + ReLU projections + dense, k=%d CRT moduli" % (args.model, circ.k),
+                   "batch_per_gpu": B, "global_batch": B * world, "parallelism": "batch-sharded x%d" % world,
+                   "cache": "L2 flushed (256 MiB write) between timed iterations; per-step working set also exceeds L2",
+                   "material": "reference garbler, seed %d, tables shared by the batch" % SEED},
+        "e2e": {"value": e2e_value, "unit": "inferences/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": ms_e2e / args.steps,
+                "api": "dashb_evaluate (int16 LabelTensor layout in pinned host memory -> output labels)"},
+        "gpu_launches": int(launches * args.steps),
+        "clocks": sampler.summary(),
+        "roofline": roofline,
+    }
+
+    # ---- cpu_baseline + parity on a bounded sample (rank 0, N=1) ----------
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import refbind
+
+        if refbind.available():
+            _, _, ref = build_material(args.model, B, want_ref=True)
+            threads = host_threads()
+            gpu_out = [o.copy() for o in out_np]
+            t_used, n_done, equal = 0.0, 0, True
+            ref.cpu_evaluate([l[0] for l in labels], threads)  # warm-up (table init)
+            while n_done < B and (n_done < 2 or t_used < args.cpu_seconds):
+                t0 = time.perf_counter()
+                ro, _ = ref.cpu_evaluate([l[n_done] for l in labels], threads)
+                t_used += time.perf_counter() - t0
+                equal = equal and all(np.array_equal(ro[j], gpu_out[j][n_done]) for j in range(ref.k))
+                n_done += 1
+            line["cpu_baseline"] = {"value": n_done / t_used, "unit": "inferences/s", "cores": threads, "kind": "reference",
+                                    "sample": "%d inferences of the same batch, GarbledCircuitInterface::cpu_evaluate (oracle/_ref), %d threads" % (n_done, threads)}
+            line["parity"] = {"inferences_checked": n_done, "bit_exact_output_labels": bool(equal)}
+        else:
+            line["cpu_baseline"] = {"value": None, "unit": "inferences/s", "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

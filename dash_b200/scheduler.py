@@ -1,0 +1,61 @@
+"""Batch scheduler: shards independent inferences across the GPUs of one box.
+
+One process per GPU (torch.distributed, NCCL over NVLink on the GPU box,
+gloo in the CPU tests).  Inferences are independent, weights and ciphertext
+tables are replicated once per GPU, so evaluation needs no collective at
+all; the only exchange is the final gather of the output labels
+(k * output_size * nc int16 per inference).  The reference has no
+counterpart: it evaluates one inference per call on one GPU
+(garbling/garbled_circuit_interface.h:603-612).
+"""
+import numpy as np
+
+
+def shard_range(total, world_size, rank):
+    """[begin, end) of the inferences rank `rank` evaluates: contiguous,
+    sizes differing by at most one, empty shards allowed."""
+    if world_size < 1 or not (0 <= rank < world_size):
+        raise ValueError("bad world_size/rank")
+    base, extra = divmod(total, world_size)
+    begin = rank * base + min(rank, extra)
+    return begin, begin + base + (1 if rank < extra else 0)
+
+
+class BatchShardedEvaluator:
+    """Evaluates a global batch: every rank runs `evaluate_fn` on its shard
+    and the output labels of all ranks are gathered on every rank."""
+
+    def __init__(self, evaluate_fn, out_shapes, device=None):
+        """evaluate_fn(list of k int16 arrays [b][n_in][nc]) -> list of k
+        int16 arrays [b][n_out][nc_out]; out_shapes = [(n_out, nc_out_j)]."""
+        import torch.distributed as dist
+
+        self.dist = dist
+        self.evaluate_fn = evaluate_fn
+        self.out_shapes = out_shapes
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.device = device
+
+    def evaluate(self, labels):
+        import torch
+
+        total = labels[0].shape[0]
+        b, e = shard_range(total, self.world, self.rank)
+        local = self.evaluate_fn([l[b:e] for l in labels]) if e > b else [
+            np.zeros((0, n, nc), dtype=np.int16) for (n, nc) in self.out_shapes]
+        if self.world == 1:
+            return local
+        out = []
+        for j, (n, nc) in enumerate(self.out_shapes):
+            sizes = [shard_range(total, self.world, r) for r in range(self.world)]
+            mx = max(hi - lo for lo, hi in sizes)
+            pad = np.zeros((mx, n, nc), dtype=np.int16)
+            pad[: e - b] = local[j]
+            t = torch.from_numpy(pad)
+            if self.device is not None:
+                t = t.to(self.device)
+            parts = [torch.empty_like(t) for _ in range(self.world)]
+            self.dist.all_gather(parts, t)
+            out.append(np.concatenate([p.cpu().numpy()[: hi - lo] for p, (lo, hi) in zip(parts, sizes)], axis=0))
+        return out
