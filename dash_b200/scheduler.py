@@ -52,10 +52,13 @@ class BatchShardedEvaluator:
             mx = max(hi - lo for lo, hi in sizes)
             pad = np.zeros((mx, n, nc), dtype=np.int16)
             pad[: e - b] = local[j]
-            t = torch.from_numpy(pad)
+            # gathered as raw bytes: int16 is not a collective dtype on every backend
+            t = torch.from_numpy(pad.view(np.uint8).reshape(-1))
             if self.device is not None:
                 t = t.to(self.device)
             parts = [torch.empty_like(t) for _ in range(self.world)]
             self.dist.all_gather(parts, t)
-            out.append(np.concatenate([p.cpu().numpy()[: hi - lo] for p, (lo, hi) in zip(parts, sizes)], axis=0))
+            out.append(np.concatenate(
+                [p.cpu().numpy().view(np.int16).reshape(mx, n, nc)[: hi - lo] for p, (lo, hi) in zip(parts, sizes)],
+                axis=0))
         return out

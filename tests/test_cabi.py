@@ -1,0 +1,78 @@
+"""The C-ABI library loads, exports every symbol include/dash_b200.h
+declares, fails loudly without a GPU, and its device primitives -- run on
+the host through the dashb_hostcheck_* hooks -- agree with the oracle.
+CPU only: no compute call needs a device."""
+import ctypes
+import os
+import random
+import re
+
+import pytest
+
+from helpers import ROOT
+from oracle import oraclebind as O
+
+
+@pytest.fixture(scope="module")
+def api():
+    from dash_b200 import api as a
+
+    a.lib()
+    return a
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "dash_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(dashb_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol(api):
+    L = api.lib()
+    syms = declared_symbols()
+    assert len(syms) >= 25
+    for s in syms:
+        assert hasattr(L, s), "libdash_b200.so does not export " + s
+
+
+def test_no_gpu_fails_loudly(api):
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(api.DashB200Error) as e:
+        api.init(0)
+    assert "no CUDA device" in str(e.value) or "CPU" in str(e.value)
+    # nothing can be built or evaluated either
+    h = ctypes.c_void_p()
+    rc = api.lib().dashb_circuit_load(ctypes.byref(h), os.fsencode(os.path.join(ROOT, "tests", "golden", "MLP_TINY.gcm")))
+    assert rc == -2 and not h  # DASHB_ENODEV
+
+
+def test_product_does_not_link_the_oracle():
+    import subprocess
+
+    from dash_b200 import build
+
+    out = subprocess.run(["nm", "-D", build.LIB], capture_output=True, text=True).stdout
+    assert "oracle_" not in out and "ref_" not in out.replace("deref", "")
+
+
+def test_device_primitives_on_host_match_oracle(api):
+    rng = random.Random(11)
+    pt = int.from_bytes(bytes.fromhex("00112233445566778899aabbccddeeff"), "little")
+    assert api.hostcheck_hash(pt).to_bytes(16, "little").hex() == "69c4e0d86a7b0430d8cdb78070b4c55a"
+    for q in [2, 3, 5, 7, 8, 9, 11, 13, 17, 19, 23, 32, 45, 63, 72, 81, 91, 97, 98, 107, 126, 138, 167, 173, 255, 256, 882]:
+        nc = O.nr_comps(q)
+        assert api.nr_comps(q) == nc
+        for t in range(60):
+            d = [rng.randrange(q) for _ in range(nc)]
+            c = O.compress(q, d)
+            assert api.hostcheck_compress(q, d) == c
+            assert list(api.hostcheck_digits(q, c)) == d
+            assert api.hostcheck_colour(q, c) == d[0]
+            x = rng.getrandbits(128)
+            assert api.hostcheck_hash(x) == O.hash128(x)
+            assert api.hostcheck_colour(q, x) == x % q
+            if q <= 181:  # out-of-range payloads: identical digits as long as the top quotient fits int16
+                assert list(api.hostcheck_digits(q, x)) == list(O.decompress(q, x))
