@@ -70,14 +70,29 @@ ModInfo make_modinfo(uint32_t q) {
     m.Q = (uint32_t)Q;
     m.nchunks = (m.nc + t - 1) / t;
     m.top_len = m.nc - (m.nchunks - 1) * t;
-    m.MQ = ~0ull / Q;
     if ((q & (q - 1)) == 0) {
-        m.shift = 0;
-        while ((1u << m.shift) < q) ++m.shift;
-        m.mq = 0;
+        m.mq = (uint32_t)((1ull << 32) / q);
+        m.lim = 0xffffffffu;
     } else {
-        m.shift = 0;
         m.mq = (uint32_t)((1ull << 32) / q) + 1;
+        m.lim = 0xffffffffu / q;
+    }
+    m.s = (uint32_t)__builtin_clz(m.Q);
+    m.dn = m.Q << m.s;
+    m.v = (uint32_t)(~0ull / m.dn - (1ull << 32));
+    /* significant limbs of the running quotient before division c: it is
+     * below 2^128 / Q^c for every 128-bit payload */
+    unsigned __int128 bound = ~(unsigned __int128)0;
+    m.limbs = 0;
+    for (uint32_t c = 0; c + 1 < m.nchunks && c < 16; ++c) {
+        uint32_t l = 1;
+        for (int i = 3; i >= 1; --i)
+            if ((uint32_t)(bound >> (32 * i)) != 0) {
+                l = (uint32_t)i + 1;
+                break;
+            }
+        m.limbs |= (l - 1) << (2 * c);
+        bound /= Q;
     }
     return m;
 }
@@ -120,9 +135,9 @@ struct DevMem {
     }
 };
 
-/* int16 label digits -> u8 */
+/* int16 label digits -> u8, zero padded to a multiple of 4 digits */
 std::vector<uint8_t> to_u8(const int16_t* d, size_t n) {
-    std::vector<uint8_t> v(n);
+    std::vector<uint8_t> v((n + 3) & ~(size_t)3, 0);
     for (size_t i = 0; i < n; ++i) v[i] = (uint8_t)d[i];
     return v;
 }
@@ -142,7 +157,7 @@ struct Tensor {
 
 size_t tensor_bytes(uint64_t n, int k, const int* q, uint32_t Bp) {
     size_t total = 0;
-    for (int j = 0; j < k; ++j) total += ((size_t)n * nr_comps(q[j]) * Bp + 255) & ~(size_t)255;
+    for (int j = 0; j < k; ++j) total += ((size_t)n * ((nr_comps(q[j]) + 3) & ~3) * Bp + 255) & ~(size_t)255;
     return total;
 }
 
@@ -153,7 +168,7 @@ void carve(Tensor& t, uint8_t* base, uint64_t n, int k, const int* q, uint32_t B
     for (int j = 0; j < k; ++j) {
         t.q[j] = q[j];
         t.plane[j] = base + off;
-        off += ((size_t)n * nr_comps(q[j]) * Bp + 255) & ~(size_t)255;
+        off += ((size_t)n * ((nr_comps(q[j]) + 3) & ~3) * Bp + 255) & ~(size_t)255;
     }
 }
 
@@ -237,7 +252,8 @@ int prep_linear(dashb_circuit* c, Layer& L, const std::vector<int64_t>& wrow /* 
     for (int j = 0; j < c->k; ++j) {
         const uint32_t q = (uint32_t)c->crt[j], nc = c->crt_mi[j].nc;
         std::vector<uint32_t> w4((size_t)nvg * k4 * 8, 0);
-        std::vector<uint8_t> cst((size_t)M * nc);
+        const uint32_t ncp = (nc + 3) & ~3u; /* rows padded to whole words */
+        std::vector<uint8_t> cst((size_t)M * ncp, 0);
         const int16_t* z = c->zero[q - 2].data();
         for (uint64_t r = 0; r < M; ++r) {
             uint64_t nz = 0;
@@ -248,7 +264,7 @@ int prep_linear(dashb_circuit* c, Layer& L, const std::vector<int64_t>& wrow /* 
                 w4[((size_t)(r / 8) * k4 + kk / 4) * 8 + (r % 8)] |= (uint32_t)w << (8 * (kk % 4));
             }
             for (uint32_t d = 0; d < nc; ++d)
-                cst[r * nc + d] = (uint8_t)(((uint64_t)bias_labels[j][r * nc + d] + (nz % q) * (uint64_t)z[d]) % q);
+                cst[r * ncp + d] = (uint8_t)(((uint64_t)bias_labels[j][r * nc + d] + (nz % q) * (uint64_t)z[d]) % q);
         }
         CU(L.w4[j].upload(w4.data(), w4.size() * 4));
         CU(L.cst[j].upload(cst.data(), cst.size()));
@@ -540,7 +556,7 @@ static int fill_rescale_static(dashb_circuit* c, Layer& L, uint64_t n, const int
     for (int j = 0; j < k; ++j) {
         p.crt[j] = c->crt_mi[j];
         p.loff[j] = off;
-        off += c->crt_mi[j].nc;
+        off += (c->crt_mi[j].nc + 3) & ~3u;
     }
     if (off > LW_MAX) return fail(DASHB_EINVAL, "rescale: CRT base too wide for the per-thread workspace");
     /* Step 2 bookkeeping: sequential cipher counter over (factor, modulus) */
@@ -756,7 +772,7 @@ int dashb_move_inputs(dashb_circuit* c, const int16_t* const* in, uint64_t batch
         const size_t bytes = (size_t)batch * rows * 2;
         int16_t* st = (int16_t*)((char*)c->stage_in.p + off);
         CU(cudaMemcpyAsync(st, in[j], bytes, cudaMemcpyHostToDevice, g_stream));
-        CU(launch_ingest(st, c->t_in.plane[j], rows, c->batch, c->Bp, g_stream));
+        CU(launch_ingest(st, c->t_in.plane[j], c->input_size, c->crt_mi[j].nc, c->batch, c->Bp, g_stream));
         off += bytes;
     }
     c->t_last = c->t_in;
@@ -919,7 +935,7 @@ static int copy_out(dashb_circuit* c, const Tensor& t, int16_t* const* out) {
         const uint64_t rows = t.n * (uint64_t)nr_comps(t.q[j]);
         const size_t bytes = (size_t)c->batch * rows * 2;
         int16_t* st = (int16_t*)((char*)c->stage_out.p + off);
-        CU(launch_egress(t.plane[j], st, rows, c->batch, c->Bp, g_stream));
+        CU(launch_egress(t.plane[j], st, t.n, (uint32_t)nr_comps(t.q[j]), c->batch, c->Bp, g_stream));
         CU(cudaMemcpyAsync(out[j], st, bytes, cudaMemcpyDeviceToHost, g_stream));
         off += bytes;
     }

@@ -75,6 +75,8 @@ GC_HD u128 muladd_small(u128 x, uint32_t m, uint32_t a) {
  * A label's nc digits are cut into chunks of t digits from the least
  * significant end; Q = q^t with q^(t+1) <= 2^32, so that a chunk value fits
  * 32 bits and r/q for r < Q is exact with the 32-bit reciprocal mq.
+ * The 128-bit value is divided by Q limb by limb (32-bit limbs) with the
+ * Moeller-Granlund 2-by-1 step on the normalised divisor dn = Q << s.
  */
 struct ModInfo {
     uint32_t q;        /* modulus */
@@ -82,45 +84,67 @@ struct ModInfo {
     uint32_t t;        /* digits per chunk */
     uint32_t nchunks;  /* ceil(nc / t) */
     uint32_t Q;        /* q^t */
-    uint32_t mq;       /* floor(2^32 / q) + 1 (0 when q is a power of two) */
-    uint32_t shift;    /* log2 q when q is a power of two, else 0 */
+    uint32_t mq;       /* 2^32/q for powers of two, else floor(2^32 / q) + 1 */
+    uint32_t lim;      /* r / q == mulhi(r, mq) for every r <= lim */
     uint32_t top_len;  /* digits in the most significant chunk */
-    uint64_t MQ;       /* floor((2^64 - 1) / Q) */
+    uint32_t s;        /* clz(Q) */
+    uint32_t dn;       /* Q << s */
+    uint32_t v;        /* floor((2^64 - 1) / dn) - 2^32 */
+    uint32_t limbs;    /* 2 bits per chunk c: (significant 32-bit limbs before division c) - 1 */
 };
 
-/* r / q for r < 2^32 / q (true for every chunk value and its quotients). */
-GC_HD uint32_t div_q(uint32_t r, const ModInfo& m) {
-    return m.shift ? (r >> m.shift) : mulhi32(r, m.mq);
+/* r / q for r <= m.lim (true for every chunk value and its quotients). */
+GC_HD uint32_t div_q(uint32_t r, const ModInfo& m) { return mulhi32(r, m.mq); }
+
+/* r / q for any 32-bit r */
+GC_HD uint32_t div_q_any(uint32_t r, const ModInfo& m) { return r <= m.lim ? mulhi32(r, m.mq) : r / m.q; }
+
+/* a mod q for small a (a <= m.lim): digit sums before reduction. */
+GC_HD uint32_t mod_q(uint32_t a, const ModInfo& m) { return a - div_q(a, m) * m.q; }
+
+GC_HD uint32_t funnel_hi(uint32_t lo, uint32_t sh) {
+    /* (lo >> (32 - sh)), 0 for sh == 0 */
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_l(lo, 0u, sh);
+#else
+    return sh ? (lo >> (32 - sh)) : 0u;
+#endif
 }
 
-/* a mod q for small a (a < 2^32 / q): digit sums before reduction. */
-GC_HD uint32_t mod_q(uint32_t a, const ModInfo& m) {
-    return a - div_q(a, m) * m.q;
+/* One step of the long division by Q: (rs:w) / dn with rs the running
+ * remainder in the shifted domain (rem << s).  Returns the quotient limb,
+ * updates rs.  Moeller & Granlund, "Improved division by invariant
+ * integers", Alg. 4. */
+GC_HD uint32_t div_step(uint32_t& rs, uint32_t w, const ModInfo& m) {
+    const uint32_t u1 = rs | funnel_hi(w, m.s);
+    const uint32_t u0 = w << m.s;
+    const uint64_t qq = (uint64_t)m.v * u1 + (((uint64_t)u1 << 32) | u0);
+    uint32_t q1 = (uint32_t)(qq >> 32) + 1u;
+    const uint32_t q0 = (uint32_t)qq;
+    uint32_t r = u0 - q1 * m.dn;
+    /* the two corrections, branch-free */
+    const uint32_t dec = r > q0 ? 1u : 0u;
+    q1 -= dec;
+    r += dec ? m.dn : 0u;
+    const uint32_t inc = r >= m.dn ? 1u : 0u;
+    q1 += inc;
+    r -= inc ? m.dn : 0u;
+    rs = r;
+    return q1;
 }
 
-/* x = x / Q, returns x mod Q.  Long division over four 32-bit limbs with the
- * 64-bit reciprocal MQ; limbs known to be zero are skipped by the caller's
- * `limbs` (number of significant 32-bit limbs, 1..4). */
-GC_HD uint32_t divmod_Q(u128& x, const ModInfo& m, int limbs = 4) {
-    uint32_t w[4] = {(uint32_t)x.lo, (uint32_t)(x.lo >> 32), (uint32_t)x.hi, (uint32_t)(x.hi >> 32)};
-    uint64_t rem = 0;
-#pragma unroll
-    for (int i = 3; i >= 0; --i) {
-        if (i >= limbs) continue;
-        uint64_t cur = (rem << 32) | w[i];
-        uint64_t qd = mulhi64(cur, m.MQ);
-        uint64_t r = cur - qd * m.Q;
-        while (r >= m.Q) {
-            r -= m.Q;
-            ++qd;
-        }
-        w[i] = (uint32_t)qd;
-        rem = r;
-    }
-    x.lo = (uint64_t)w[0] | ((uint64_t)w[1] << 32);
-    x.hi = (uint64_t)w[2] | ((uint64_t)w[3] << 32);
-    return (uint32_t)rem;
+/* x = x / Q, returns x mod Q; `limbs` = number of 32-bit limbs of x that can
+ * be non-zero (1..4). */
+GC_HD uint32_t divmod_Q(uint32_t (&w)[4], const ModInfo& m, uint32_t limbs) {
+    uint32_t rs = 0;
+    if (limbs > 3) w[3] = div_step(rs, w[3], m);
+    if (limbs > 2) w[2] = div_step(rs, w[2], m);
+    if (limbs > 1) w[1] = div_step(rs, w[1], m);
+    w[0] = div_step(rs, w[0], m);
+    return rs >> m.s;
 }
+
+GC_HD uint32_t limbs_before(const ModInfo& m, uint32_t c) { return ((m.limbs >> (2 * c)) & 3u) + 1u; }
 
 /*
  * Calls f(d, digit) for d = 0..nc-1 with the base-q digits of x, least
@@ -132,65 +156,61 @@ GC_HD uint32_t divmod_Q(u128& x, const ModInfo& m, int limbs = 4) {
  */
 template <typename F>
 GC_HD void for_each_digit(u128 x, const ModInfo& m, F&& f) {
+    uint32_t w[4] = {(uint32_t)x.lo, (uint32_t)(x.lo >> 32), (uint32_t)x.hi, (uint32_t)(x.hi >> 32)};
     uint32_t d = 0;
     for (uint32_t c = 0; c + 1 < m.nchunks; ++c) {
-        uint32_t r = divmod_Q(x, m);
+        uint32_t r = divmod_Q(w, m, limbs_before(m, c));
         for (uint32_t i = 0; i < m.t; ++i) {
-            uint32_t qd = div_q(r, m);
+            const uint32_t qd = div_q(r, m);
             f(d++, r - qd * m.q);
             r = qd;
         }
     }
     /* most significant chunk: what is left of x (fits 32 bits, see
-     * DESIGN.md); plain division because an out-of-range payload can push
-     * it past the reciprocal's exact range */
-    uint32_t r = (uint32_t)x.lo;
-    for (uint32_t i = 0; i + 1 < m.top_len; ++i) {
-        uint32_t qd = r / m.q;
+     * DESIGN.md); an out-of-range payload can push it past the reciprocal's
+     * exact range, hence div_q_any */
+    uint32_t r = w[0];
+    for (uint32_t i = 0; i < m.top_len; ++i) {
+        const uint32_t qd = div_q_any(r, m);
         f(d++, r - qd * m.q);
         r = qd;
     }
-    f(d, r % m.q);
 }
 
 /* Same, for two labels of the same modulus in lockstep: f(d, dx, dy). */
 template <typename F>
 GC_HD void for_each_digit2(u128 x, u128 y, const ModInfo& m, F&& f) {
+    uint32_t wx[4] = {(uint32_t)x.lo, (uint32_t)(x.lo >> 32), (uint32_t)x.hi, (uint32_t)(x.hi >> 32)};
+    uint32_t wy[4] = {(uint32_t)y.lo, (uint32_t)(y.lo >> 32), (uint32_t)y.hi, (uint32_t)(y.hi >> 32)};
     uint32_t d = 0;
     for (uint32_t c = 0; c + 1 < m.nchunks; ++c) {
-        uint32_t rx = divmod_Q(x, m);
-        uint32_t ry = divmod_Q(y, m);
+        const uint32_t L = limbs_before(m, c);
+        uint32_t rx = divmod_Q(wx, m, L);
+        uint32_t ry = divmod_Q(wy, m, L);
         for (uint32_t i = 0; i < m.t; ++i) {
-            uint32_t qx = div_q(rx, m), qy = div_q(ry, m);
+            const uint32_t qx = div_q(rx, m), qy = div_q(ry, m);
             f(d++, rx - qx * m.q, ry - qy * m.q);
             rx = qx;
             ry = qy;
         }
     }
-    uint32_t rx = (uint32_t)x.lo, ry = (uint32_t)y.lo;
-    for (uint32_t i = 0; i + 1 < m.top_len; ++i) {
-        uint32_t qx = rx / m.q, qy = ry / m.q;
+    uint32_t rx = wx[0], ry = wy[0];
+    for (uint32_t i = 0; i < m.top_len; ++i) {
+        const uint32_t qx = div_q_any(rx, m), qy = div_q_any(ry, m);
         f(d++, rx - qx * m.q, ry - qy * m.q);
         rx = qx;
         ry = qy;
     }
-    f(d, rx % m.q, ry % m.q);
 }
 
 /* Colour digit of a compressed label: x mod q (q divides Q). */
 GC_HD uint32_t colour_of(u128 x, const ModInfo& m) {
-    if (m.shift) return (uint32_t)x.lo & (m.q - 1);
-    uint32_t w[4] = {(uint32_t)x.lo, (uint32_t)(x.lo >> 32), (uint32_t)x.hi, (uint32_t)(x.hi >> 32)};
-    uint64_t rem = 0;
-#pragma unroll
-    for (int i = 3; i >= 0; --i) {
-        uint64_t cur = (rem << 32) | w[i];
-        uint64_t qd = mulhi64(cur, m.MQ);
-        uint64_t r = cur - qd * m.Q;
-        while (r >= m.Q) r -= m.Q;
-        rem = r;
-    }
-    return mod_q((uint32_t)rem, m);
+    uint32_t rs = 0;
+    (void)div_step(rs, (uint32_t)(x.hi >> 32), m);
+    (void)div_step(rs, (uint32_t)x.hi, m);
+    (void)div_step(rs, (uint32_t)(x.lo >> 32), m);
+    (void)div_step(rs, (uint32_t)x.lo, m);
+    return mod_q(rs >> m.s, m);
 }
 
 /*
@@ -239,7 +259,10 @@ GC_HD u128 aes128_encrypt(u128 in, const T32* te0, const T32* te1, const T32* te
     uint32_t s1 = bswap32((uint32_t)(in.lo >> 32)) ^ rk[1];
     uint32_t s2 = bswap32((uint32_t)in.hi) ^ rk[2];
     uint32_t s3 = bswap32((uint32_t)(in.hi >> 32)) ^ rk[3];
-#pragma unroll
+    /* rolled on purpose: the nine middle rounds are one ~1 KB loop body that
+     * stays in the SM's L0 instruction cache; unrolled (9.6 KB) every call
+     * streamed through it (ncu: stall_no_inst 24 %) */
+#pragma unroll 1
     for (int r = 1; r < 10; ++r) {
         uint32_t t0 = te0[s0 >> 24] ^ te1[(s1 >> 16) & 0xff] ^ te2[(s2 >> 8) & 0xff] ^ te3[s3 & 0xff] ^ rk[4 * r];
         uint32_t t1 = te0[s1 >> 24] ^ te1[(s2 >> 16) & 0xff] ^ te2[(s3 >> 8) & 0xff] ^ te3[s0 & 0xff] ^ rk[4 * r + 1];

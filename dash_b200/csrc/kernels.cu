@@ -112,7 +112,20 @@ __device__ __forceinline__ void aes_smem_load(AesSmem& a) {
     __syncthreads();
 }
 
-__device__ __forceinline__ u128 hash(const AesSmem& a, u128 x) {
+/* Copies a ModInfo out of the (dynamically indexed) kernel-parameter bank
+ * into registers and hides its origin from the compiler, which would
+ * otherwise re-read the constant bank (4 instructions) at every use. */
+__device__ __forceinline__ ModInfo pin(const ModInfo& src) {
+    ModInfo m = src;
+    asm volatile("" : "+r"(m.q), "+r"(m.nc), "+r"(m.t), "+r"(m.nchunks), "+r"(m.Q), "+r"(m.mq));
+    asm volatile("" : "+r"(m.lim), "+r"(m.top_len), "+r"(m.s), "+r"(m.dn), "+r"(m.v), "+r"(m.limbs));
+    return m;
+}
+
+/* One copy of the cipher per kernel (not inlined at its ~8 call sites): the
+ * gadget kernels then fit the instruction cache (ncu: 24 % stall_no_inst
+ * with the inlined version). */
+__device__ __noinline__ u128 hash(const AesSmem& a, u128 x) {
     return gc::aes128_encrypt(x, a.te0, a.te1, a.te2, a.te3, a.sbox, c_rk);
 }
 
@@ -124,78 +137,108 @@ __device__ __forceinline__ u128 ldg128(const u128* p) {
     return r;
 }
 
+/* Plane addressing (see kernels.h): digits are stored four to a 32-bit
+ * word, word (e, d/4, b) at e*row + (d/4)*4*Bp + 4*b, so a thread reads or
+ * writes 4 digits per access and a warp 128 contiguous bytes. */
+__device__ __forceinline__ uint32_t nc4_of(const ModInfo& m) { return (m.nc + 3) >> 2; }
+__device__ __forceinline__ uint64_t plane_off(const ModInfo& m, uint64_t e, uint32_t b, uint32_t Bp) {
+    return (e * nc4_of(m) * (uint64_t)Bp + b) * 4;
+}
+
 /* compress the label (element e, inference b) of a digit plane */
 __device__ __forceinline__ u128 load_compress(const uint8_t* plane, const ModInfo& m, uint64_t e, uint32_t b,
                                                uint32_t Bp, uint32_t& colour) {
-    const uint8_t* p = plane + e * (uint64_t)m.nc * Bp + b;
+    const uint8_t* p = plane + plane_off(m, e, b, Bp);
     gc::Compressor c(m);
-    uint32_t dg = 0;
-    for (int d = (int)m.nc - 1; d >= 0; --d) {
-        dg = p[(uint32_t)d * Bp];
-        c.push(dg);
+    uint32_t w = 0;
+    uint32_t valid = m.nc - 4 * (nc4_of(m) - 1); /* digits in the top word */
+    for (int d4 = (int)nc4_of(m) - 1; d4 >= 0; --d4) {
+        w = *reinterpret_cast<const uint32_t*>(p + (uint64_t)d4 * 4 * Bp);
+        if (valid > 3) c.push(w >> 24);
+        if (valid > 2) c.push((w >> 16) & 0xff);
+        if (valid > 1) c.push((w >> 8) & 0xff);
+        c.push(w & 0xff);
+        valid = 4;
     }
-    colour = dg;
+    colour = w & 0xff;
     return c.value();
 }
 
 /* write the digits of compressed label x into a plane */
 __device__ __forceinline__ void store_digits(uint8_t* plane, const ModInfo& m, uint64_t e, uint32_t b, uint32_t Bp,
                                              u128 x) {
-    uint8_t* p = plane + e * (uint64_t)m.nc * Bp + b;
-    gc::for_each_digit(x, m, [&](uint32_t d, uint32_t v) { p[d * Bp] = (uint8_t)v; });
+    uint8_t* p = plane + plane_off(m, e, b, Bp);
+    uint32_t w = 0;
+    const uint32_t last = m.nc - 1;
+    gc::for_each_digit(x, m, [&](uint32_t d, uint32_t v) {
+        w |= v << (8 * (d & 3));
+        if ((d & 3) == 3 || d == last) {
+            *reinterpret_cast<uint32_t*>(p + (uint64_t)(d >> 2) * 4 * Bp) = w;
+            w = 0;
+        }
+    });
 }
 
 /* --------------------------------------------------- ingest / egress */
-/* Host layout int16 [batch][rows] (rows = labels*nc, LabelTensor order,
- * garbling/label_tensor.h:238-246) <-> device plane u8 [rows][Bp].
- * Replaces the per-modulus cudaMemcpy of cuda_move_inputs /
+/* Host layout int16 [batch][label][nc] (LabelTensor order,
+ * garbling/label_tensor.h:238-246) <-> device plane.  One CTA moves one
+ * label of 32 inferences through a shared-memory tile so that both sides are
+ * coalesced.  Replaces the per-modulus cudaMemcpy of cuda_move_inputs /
  * cuda_move_outputs (garbled_circuit_interface.h:551-565,733-736). */
-__global__ void k_ingest(const int16_t* __restrict__ src, uint8_t* __restrict__ plane, uint64_t rows, uint32_t batch,
-                         uint32_t Bp) {
-    __shared__ uint8_t tile[32][33];
-    const uint64_t r0 = (uint64_t)blockIdx.x * 32;
+__global__ void __launch_bounds__(128) k_ingest(const int16_t* __restrict__ src, uint8_t* __restrict__ plane,
+                                                uint64_t n, uint32_t nc, uint32_t batch, uint32_t Bp) {
+    __shared__ uint32_t tile[32][33]; /* [b][d4] */
+    const uint64_t e = blockIdx.x;
     const uint32_t b0 = blockIdx.y * 32;
-    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-        uint32_t b = b0 + i;
-        uint64_t r = r0 + threadIdx.x;
-        tile[i][threadIdx.x] = (b < batch && r < rows) ? (uint8_t)src[(uint64_t)b * rows + r] : 0;
+    const uint32_t nc4 = (nc + 3) >> 2;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t i = warp; i < 32; i += 4) {
+        const uint32_t b = b0 + i;
+        const int16_t* row = src + ((uint64_t)b * n + e) * nc;
+        for (uint32_t d4 = lane; d4 < nc4; d4 += 32) {
+            uint32_t w = 0;
+            if (b < batch)
+                for (uint32_t t = 0; t < 4 && 4 * d4 + t < nc; ++t) w |= (uint32_t)(uint8_t)row[4 * d4 + t] << (8 * t);
+            tile[i][d4] = w;
+        }
     }
     __syncthreads();
-    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-        uint64_t r = r0 + i;
-        uint32_t b = b0 + threadIdx.x;
-        if (r < rows && b < Bp) plane[r * Bp + b] = tile[threadIdx.x][i];
+    for (uint32_t d4 = warp; d4 < nc4; d4 += 4) {
+        const uint32_t b = b0 + lane;
+        if (b < Bp) *reinterpret_cast<uint32_t*>(plane + ((e * nc4 + d4) * (uint64_t)Bp + b) * 4) = tile[lane][d4];
     }
 }
 
-__global__ void k_egress(const uint8_t* __restrict__ plane, int16_t* __restrict__ dst, uint64_t rows, uint32_t batch,
-                         uint32_t Bp) {
-    __shared__ uint8_t tile[32][33];
-    const uint64_t r0 = (uint64_t)blockIdx.x * 32;
+__global__ void __launch_bounds__(128) k_egress(const uint8_t* __restrict__ plane, int16_t* __restrict__ dst,
+                                                uint64_t n, uint32_t nc, uint32_t batch, uint32_t Bp) {
+    __shared__ uint32_t tile[32][33];
+    const uint64_t e = blockIdx.x;
     const uint32_t b0 = blockIdx.y * 32;
-    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-        uint64_t r = r0 + i;
-        uint32_t b = b0 + threadIdx.x;
-        tile[i][threadIdx.x] = (r < rows && b < Bp) ? plane[r * Bp + b] : 0;
+    const uint32_t nc4 = (nc + 3) >> 2;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t d4 = warp; d4 < nc4; d4 += 4) {
+        const uint32_t b = b0 + lane;
+        tile[lane][d4] = b < Bp ? *reinterpret_cast<const uint32_t*>(plane + ((e * nc4 + d4) * (uint64_t)Bp + b) * 4) : 0;
     }
     __syncthreads();
-    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
-        uint32_t b = b0 + i;
-        uint64_t r = r0 + threadIdx.x;
-        if (b < batch && r < rows) dst[(uint64_t)b * rows + r] = (int16_t)tile[threadIdx.x][i];
+    for (uint32_t i = warp; i < 32; i += 4) {
+        const uint32_t b = b0 + i;
+        if (b >= batch) continue;
+        int16_t* row = dst + ((uint64_t)b * n + e) * nc;
+        for (uint32_t d = lane; d < nc; d += 32) row[d] = (int16_t)((tile[i][d >> 2] >> (8 * (d & 3))) & 0xff);
     }
 }
 
-cudaError_t launch_ingest(const int16_t* src, uint8_t* plane, uint64_t rows, uint32_t batch, uint32_t Bp,
+cudaError_t launch_ingest(const int16_t* src, uint8_t* plane, uint64_t n, uint32_t nc, uint32_t batch, uint32_t Bp,
                           cudaStream_t s) {
-    dim3 grid((unsigned)((rows + 31) / 32), (Bp + 31) / 32), block(32, 8);
-    k_ingest<<<grid, block, 0, s>>>(src, plane, rows, batch, Bp);
+    dim3 grid((unsigned)n, (Bp + 31) / 32);
+    k_ingest<<<grid, 128, 0, s>>>(src, plane, n, nc, batch, Bp);
     return cudaGetLastError();
 }
-cudaError_t launch_egress(const uint8_t* plane, int16_t* dst, uint64_t rows, uint32_t batch, uint32_t Bp,
+cudaError_t launch_egress(const uint8_t* plane, int16_t* dst, uint64_t n, uint32_t nc, uint32_t batch, uint32_t Bp,
                           cudaStream_t s) {
-    dim3 grid((unsigned)((rows + 31) / 32), (Bp + 31) / 32), block(32, 8);
-    k_egress<<<grid, block, 0, s>>>(plane, dst, rows, batch, Bp);
+    dim3 grid((unsigned)n, (Bp + 31) / 32);
+    k_egress<<<grid, 128, 0, s>>>(plane, dst, n, nc, batch, Bp);
     return cudaGetLastError();
 }
 
@@ -221,8 +264,8 @@ __global__ void __launch_bounds__(LIN_THREADS) k_linear(const __grid_constant__ 
     __shared__ uint4 s_w[LIN_KC / 4][2];  /* [k/4][8 rows] packed weights */
     __shared__ int32_t s_koff[LIN_KC];
     const int j = blockIdx.z;
-    const ModInfo m = P.mod[j];
-    const uint32_t ncols = m.nc * P.Bp;
+    const ModInfo m = pin(P.mod[j]);
+    const uint32_t ncols = ((m.nc + 3) & ~3u) * P.Bp; /* nc4 words of 4 digits per inference */
     const uint32_t col = (blockIdx.x * LIN_THREADS + threadIdx.x) * 4;
     const uint32_t nvg = (P.M + LIN_ROWS - 1) / LIN_ROWS;
     const uint32_t vg = blockIdx.y % nvg;
@@ -269,22 +312,24 @@ __global__ void __launch_bounds__(LIN_THREADS) k_linear(const __grid_constant__ 
         }
     }
     if (!active) return;
-    const uint32_t d = col / P.Bp;
+    /* the thread's 4 columns are digits 4*d4 .. 4*d4+3 of one inference */
+    const uint32_t d4 = col / (4 * P.Bp);
+    const uint32_t nc4 = (m.nc + 3) >> 2;
 #pragma unroll
     for (int r = 0; r < LIN_ROWS; ++r) {
         const uint32_t v = vg * LIN_ROWS + r;
         if (v >= P.M) break;
-        const uint32_t cst = __ldg(P.cst[j] + (uint64_t)v * m.nc + d);
+        const uint32_t cst = __ldg(reinterpret_cast<const uint32_t*>(P.cst[j]) + (uint64_t)v * nc4 + d4);
         uint32_t o = 0;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) o |= ((acc[r][c] + cst) % m.q) << (8 * c);
+        for (int c = 0; c < 4; ++c) o |= ((acc[r][c] + ((cst >> (8 * c)) & 0xff)) % m.q) << (8 * c);
         *reinterpret_cast<uint32_t*>(P.out[j] + ((uint64_t)v * P.npix + pix) * rowlen + col) = o;
     }
 }
 
 cudaError_t launch_linear(const LinearParams& p, cudaStream_t s) {
     uint32_t max_cols = 0;
-    for (int j = 0; j < p.k; ++j) max_cols = max(max_cols, p.mod[j].nc * p.Bp);
+    for (int j = 0; j < p.k; ++j) max_cols = max(max_cols, ((p.mod[j].nc + 3) & ~3u) * p.Bp);
     const uint32_t nvg = (p.M + LIN_ROWS - 1) / LIN_ROWS;
     dim3 grid((max_cols / 4 + LIN_THREADS - 1) / LIN_THREADS, p.npix * nvg, p.k);
     k_linear<<<grid, LIN_THREADS, 0, s>>>(p);
@@ -304,10 +349,11 @@ __global__ void __launch_bounds__(128) k_projection(const __grid_constant__ Proj
     const uint32_t b = (uint32_t)(idx % P.batch);
     const uint64_t e = idx / P.batch;
     uint32_t colour;
-    const u128 key = load_compress(P.in[j], P.min[j], e, b, P.Bp, colour);
+    const ModInfo mi = pin(P.min[j]), mo = pin(P.mout[j]);
+    const u128 key = load_compress(P.in[j], mi, e, b, P.Bp, colour);
     const u128 h = hash(aes, key);
-    const u128 row = ldg128(P.ciphers[j] + e * P.min[j].q + colour);
-    store_digits(P.out[j], P.mout[j], e, b, P.Bp, gc::sub128(row, h));
+    const u128 row = ldg128(P.ciphers[j] + e * mi.q + colour);
+    store_digits(P.out[j], mo, e, b, P.Bp, gc::sub128(row, h));
 }
 
 cudaError_t launch_projection(const ProjParams& p, cudaStream_t s) {
@@ -318,10 +364,16 @@ cudaError_t launch_projection(const ProjParams& p, cudaStream_t s) {
 }
 
 /* ------------------------------------------------- sign gadget / ReLU */
-/* digit-wise accumulation of a compressed label into acc[] (no reduction:
- * at most k+1 digits below 2^11 are summed) */
+/* Per-thread digit accumulators live in shared memory, digit-major
+ * (acc[d * blockDim + tid]) so that a warp's accesses are conflict-free. */
+constexpr int SIGN_THREADS = 128;
+
+/* digit-wise accumulation of a compressed label (no reduction: at most k+1
+ * digits below 2^11 are summed) */
 __device__ __forceinline__ void accumulate(u128 x, const ModInfo& m, uint16_t* acc) {
-    gc::for_each_digit(x, m, [&](uint32_t d, uint32_t v) { acc[d] = (uint16_t)(acc[d] + v); });
+    gc::for_each_digit(x, m, [&](uint32_t d, uint32_t v) {
+        acc[d * SIGN_THREADS] = (uint16_t)(acc[d * SIGN_THREADS] + v);
+    });
 }
 
 /* compress(acc mod q) and the colour of the sum */
@@ -329,7 +381,7 @@ __device__ __forceinline__ u128 compress_acc(const uint16_t* acc, const ModInfo&
     gc::Compressor c(m);
     uint32_t dg = 0;
     for (int d = (int)m.nc - 1; d >= 0; --d) {
-        dg = gc::mod_q(acc[d], m);
+        dg = gc::mod_q(acc[d * SIGN_THREADS], m);
         c.push(dg);
     }
     colour = dg;
@@ -353,8 +405,9 @@ __device__ __forceinline__ u128 compress_acc(const uint16_t* acc, const ModInfo&
  * are never read by the reference and are not formed.
  */
 template <bool RELU>
-__global__ void __launch_bounds__(128) k_sign(const __grid_constant__ SignParams P) {
+__global__ void __launch_bounds__(SIGN_THREADS) k_sign(const __grid_constant__ SignParams P) {
     __shared__ AesSmem aes;
+    extern __shared__ uint16_t s_acc[]; /* [acc_digits][SIGN_THREADS] */
     aes_smem_load(aes);
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P.n * P.batch) return;
@@ -368,20 +421,23 @@ __global__ void __launch_bounds__(128) k_sign(const __grid_constant__ SignParams
     uint32_t col[MAXK];
 #pragma unroll 1
     for (int j = 0; j < k; ++j) {
-        const u128 key = load_compress(P.in[j], P.crt[j], e, b, P.Bp, col[j]);
+        const ModInfo Pm = pin(P.crt[j]);
+        const u128 key = load_compress(P.in[j], Pm, e, b, P.Bp, col[j]);
         h[j] = hash(aes, key);
     }
 
     /* Step 2: mixed-radix addition from the least significant digit */
-    uint16_t acc[128];
+    uint16_t* acc = s_acc + threadIdx.x;
     u128 carry = P.carry0;
     const u128* approx_e = P.approx + e * (uint64_t)nm * P.S;
     uint64_t cnt1 = e * (uint64_t)(k + 1) * P.Mp, cnt2 = cnt1;
 #pragma unroll 1
     for (int i = nm - 1; i >= 1; --i) {
-        const ModInfo& M = P.mrs[i];
-        const ModInfo& C = P.cast[i];
-        for (uint32_t d = 0; d < C.nc; ++d) acc[d] = 0;
+        /* by value: keeps the fields in registers instead of re-reading the
+         * dynamically indexed parameter bank at every use */
+        const ModInfo M = pin(P.mrs[i]);
+        const ModInfo C = pin(P.cast[i]);
+        for (uint32_t d = 0; d < C.nc; ++d) acc[d * SIGN_THREADS] = 0;
 #pragma unroll 1
         for (int j = 0; j <= k; ++j) {
             /* Step 1b: approx. MRS digit i of residue j (j == k: the carry) */
@@ -402,8 +458,8 @@ __global__ void __launch_bounds__(128) k_sign(const __grid_constant__ SignParams
         cnt2 += C.q;
     }
     /* most significant digit: sum = carry + sum_j digit_{j,0} */
-    const ModInfo& M0 = P.mrs[0];
-    for (uint32_t d = 0; d < M0.nc; ++d) acc[d] = 0;
+    const ModInfo M0 = pin(P.mrs[0]);
+    for (uint32_t d = 0; d < M0.nc; ++d) acc[d * SIGN_THREADS] = 0;
 #pragma unroll 1
     for (int j = 0; j <= k; ++j) {
         u128 lab = carry;
@@ -418,9 +474,10 @@ __global__ void __launch_bounds__(128) k_sign(const __grid_constant__ SignParams
     const u128* sign_e = P.sign + e * (uint64_t)P.n_out * M0.q;
     if (!RELU) {
 #pragma unroll 1
-        for (int j = 0; j < P.n_out; ++j)
-            store_digits(P.out[j], P.outm[j], e, b, P.Bp,
-                         gc::sub128(ldg128(sign_e + (uint64_t)j * M0.q + ctop), htop));
+        for (int j = 0; j < P.n_out; ++j) {
+            const ModInfo mo = pin(P.outm[j]);
+            store_digits(P.out[j], mo, e, b, P.Bp, gc::sub128(ldg128(sign_e + (uint64_t)j * M0.q + ctop), htop));
+        }
         return;
     }
     /* Step 4 (ReLU): out_j = E_j + (y+r)*x_j - G_j  (mod p_j) */
@@ -429,7 +486,7 @@ __global__ void __launch_bounds__(128) k_sign(const __grid_constant__ SignParams
     const uint32_t cs = (uint32_t)s.lo & 1u;
 #pragma unroll 1
     for (int j = 0; j < k; ++j) {
-        const ModInfo& Pm = P.crt[j];
+        const ModInfo Pm = pin(P.crt[j]);
         const u128 G = gc::sub128(ldg128(P.garbler + e * (uint64_t)P.S + P.prefix[j] + col[j]), h[j]);
         const u128* ev = P.evaluator + (e * (uint64_t)k + j) * 3;
         const u128 E = gc::sub128(ldg128(ev + cs), hs);
@@ -440,23 +497,33 @@ __global__ void __launch_bounds__(128) k_sign(const __grid_constant__ SignParams
         const int16_t t16 = (int16_t)(row16 - (int16_t)(hs.lo & 0xffff));
         int tt = (int)t16 % (int)Pm.q;
         if (tt < 0) tt += (int)Pm.q;
-        const uint64_t off = e * (uint64_t)Pm.nc * P.Bp + b;
+        const uint64_t off = plane_off(Pm, e, b, P.Bp);
         const uint8_t* xin = P.in[j] + off;
         uint8_t* xout = P.out[j] + off;
+        uint32_t xw = 0, ow = 0;
+        const uint32_t last = Pm.nc - 1;
         gc::for_each_digit2(E, G, Pm, [&](uint32_t d, uint32_t de, uint32_t dg) {
-            const uint32_t x = xin[d * P.Bp];
-            xout[d * P.Bp] = (uint8_t)gc::mod_q(de + (uint32_t)tt * x + Pm.q - dg, Pm);
+            if ((d & 3) == 0) xw = *reinterpret_cast<const uint32_t*>(xin + (uint64_t)(d >> 2) * 4 * P.Bp);
+            const uint32_t x = (xw >> (8 * (d & 3))) & 0xff;
+            ow |= gc::mod_q(de + (uint32_t)tt * x + Pm.q - dg, Pm) << (8 * (d & 3));
+            if ((d & 3) == 3 || d == last) {
+                *reinterpret_cast<uint32_t*>(xout + (uint64_t)(d >> 2) * 4 * P.Bp) = ow;
+                ow = 0;
+            }
         });
     }
 }
 
 cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s) {
     const uint64_t total = p.n * p.batch;
-    const unsigned grid = (unsigned)((total + 127) / 128);
+    const unsigned grid = (unsigned)((total + SIGN_THREADS - 1) / SIGN_THREADS);
+    uint32_t acc_digits = p.mrs[0].nc;
+    for (int i = 1; i < p.n_mrs; ++i) acc_digits = max(acc_digits, p.cast[i].nc);
+    const size_t smem = (size_t)acc_digits * SIGN_THREADS * sizeof(uint16_t);
     if (relu)
-        k_sign<true><<<grid, 128, 0, s>>>(p);
+        k_sign<true><<<grid, SIGN_THREADS, smem, s>>>(p);
     else
-        k_sign<false><<<grid, 128, 0, s>>>(p);
+        k_sign<false><<<grid, SIGN_THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }
 
@@ -484,25 +551,29 @@ __global__ void __launch_bounds__(128) k_rescale(const __grid_constant__ Rescale
 
     /* Step 1: upshift */
     for (int j = 0; j < k; ++j) {
-        const ModInfo& m = P.crt[j];
-        const uint8_t* p = P.in[j] + e * (uint64_t)m.nc * P.Bp + b;
+        const ModInfo m = pin(P.crt[j]);
+        const uint8_t* p = P.in[j] + plane_off(m, e, b, P.Bp);
         uint8_t* w = lw + P.loff[j];
-        for (uint32_t d = 0; d < m.nc; ++d) {
-            uint32_t v = (uint32_t)p[d * P.Bp] + __ldg(P.up[j] + d);
-            w[d] = (uint8_t)(v >= m.q ? v - m.q : v);
+        for (uint32_t d4 = 0; d4 < nc4_of(m); ++d4) {
+            const uint32_t xw = *reinterpret_cast<const uint32_t*>(p + (uint64_t)d4 * 4 * P.Bp);
+            const uint32_t uw = __ldg(reinterpret_cast<const uint32_t*>(P.up[j]) + d4);
+            for (uint32_t t = 0; t < 4; ++t) {
+                uint32_t v = ((xw >> (8 * t)) & 0xff) + ((uw >> (8 * t)) & 0xff);
+                w[4 * d4 + t] = (uint8_t)(v >= m.q ? v - m.q : v);
+            }
         }
     }
     /* Step 2: divide by every factor */
     for (int i = 0; i < P.nf; ++i) {
         const int f = P.fidx[i];
-        const ModInfo& mf = P.crt[f];
+        const ModInfo mf = pin(P.crt[f]);
         gc::Compressor c(mf);
         for (int d = (int)mf.nc - 1; d >= 0; --d) c.push(lw[P.loff[f] + d]);
         const uint32_t colour = lw[P.loff[f]];
         const u128 hf = hash(aes, c.value());
         for (int j = 0; j < k; ++j) {
             if (P.tm_off[i][j] == ~0ull) continue; /* ignored modulus */
-            const ModInfo& m = P.crt[j];
+            const ModInfo m = pin(P.crt[j]);
             const u128 pr = gc::sub128(ldg128(P.tm + P.tm_off[i][j] + e * (uint64_t)P.factor[i] + colour), hf);
             uint8_t* w = lw + P.loff[j];
             const uint32_t inv = P.inv_f[i][j];
@@ -519,16 +590,22 @@ __global__ void __launch_bounds__(128) k_rescale(const __grid_constant__ Rescale
     /* store residue j (after the downshift of step 4, unless legacy, where
      * the sign gadget and k_add_label follow) */
     auto store_residue = [&](int j) {
-        const ModInfo& m = P.crt[j];
-        uint8_t* p = P.out[j] + e * (uint64_t)m.nc * P.Bp + b;
+        const ModInfo m = pin(P.crt[j]);
+        uint8_t* p = P.out[j] + plane_off(m, e, b, P.Bp);
         const uint8_t* w = lw + P.loff[j];
-        for (uint32_t d = 0; d < m.nc; ++d) {
-            uint32_t v = w[d];
-            if (!P.legacy) {
-                v = v + m.q - __ldg(P.down[j] + d);
-                if (v >= m.q) v -= m.q;
+        for (uint32_t d4 = 0; d4 < nc4_of(m); ++d4) {
+            const uint32_t dw = __ldg(reinterpret_cast<const uint32_t*>(P.down[j]) + d4);
+            uint32_t ow = 0;
+            for (uint32_t t = 0; t < 4; ++t) {
+                const uint32_t d = 4 * d4 + t;
+                uint32_t v = d < m.nc ? w[d] : 0;
+                if (!P.legacy && d < m.nc) {
+                    v = v + m.q - ((dw >> (8 * t)) & 0xff);
+                    if (v >= m.q) v -= m.q;
+                }
+                ow |= v << (8 * t);
             }
-            p[d * P.Bp] = (uint8_t)v;
+            *reinterpret_cast<uint32_t*>(p + (uint64_t)d4 * 4 * P.Bp) = ow;
         }
     };
     if (P.legacy) {
@@ -542,14 +619,14 @@ __global__ void __launch_bounds__(128) k_rescale(const __grid_constant__ Rescale
     /* Step 3: base extension (garbled mixed-radix conversion) */
     for (int i = 0; i < P.non_ext; ++i) {
         const int ji = P.perm[i];
-        const ModInfo& mi = P.crt[ji];
+        const ModInfo mi = pin(P.crt[ji]);
         gc::Compressor c(mi);
         for (int d = (int)mi.nc - 1; d >= 0; --d) c.push(lw[P.loff[ji] + d]);
         const uint32_t colour = lw[P.loff[ji]];
         const u128 hi = hash(aes, c.value());
         for (int t = i + 1; t < k; ++t) {
             const int jt = P.perm[t];
-            const ModInfo& mt = P.crt[jt];
+            const ModInfo mt = pin(P.crt[jt]);
             const u128 pr = gc::sub128(ldg128(P.be + P.be_off[i][t] + e * (uint64_t)mi.q + colour), hi);
             uint8_t* w = lw + P.loff[jt];
             const uint32_t inv = P.inv_partial[i][t];
@@ -561,7 +638,7 @@ __global__ void __launch_bounds__(128) k_rescale(const __grid_constant__ Rescale
     for (int x = 0; x < P.nf; ++x) {
         /* the extended residue is the last mixed-radix digit times -invv */
         const int j = P.extra_idx[x];
-        const ModInfo& m = P.crt[j];
+        const ModInfo m = pin(P.crt[j]);
         uint8_t* w = lw + P.loff[j];
         for (uint32_t d = 0; d < m.nc; ++d) w[d] = (uint8_t)gc::mod_q((uint32_t)w[d] * P.neg_invv[x], m);
         store_residue(j);
@@ -579,11 +656,12 @@ cudaError_t launch_rescale(const RescaleParams& p, cudaStream_t s) {
 __global__ void k_add_label(const __grid_constant__ AddLabelParams P) {
     const int j = blockIdx.y;
     const ModInfo& m = P.crt[j];
-    const uint64_t total = P.n * m.nc * (uint64_t)P.Bp;
+    const uint32_t nc4 = (m.nc + 3) >> 2;
+    const uint64_t total = P.n * nc4 * 4 * (uint64_t)P.Bp;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (uint64_t)gridDim.x * blockDim.x) {
-        const uint32_t d = (uint32_t)((i / P.Bp) % m.nc);
-        const uint32_t l = __ldg(P.label[j] + d);
+        const uint32_t d = (uint32_t)((i / (4 * P.Bp)) % nc4) * 4 + (uint32_t)(i & 3);
+        const uint32_t l = __ldg(P.label[j] + d); /* labels are zero-padded to 4*nc4 digits */
         uint32_t v = P.plane[j][i];
         v = P.subtract ? v + m.q - l : v + l;
         if (v >= m.q) v -= m.q;
@@ -593,7 +671,7 @@ __global__ void k_add_label(const __grid_constant__ AddLabelParams P) {
 
 cudaError_t launch_add_label(const AddLabelParams& p, cudaStream_t s) {
     uint64_t mx = 0;
-    for (int j = 0; j < p.k; ++j) mx = max(mx, p.n * p.crt[j].nc * (uint64_t)p.Bp);
+    for (int j = 0; j < p.k; ++j) mx = max(mx, p.n * ((p.crt[j].nc + 3) & ~3u) * (uint64_t)p.Bp);
     uint64_t want = (mx + 255) / 256;
     unsigned gx = (unsigned)(want < 148 * 16 ? want : 148 * 16);
     dim3 grid(gx ? gx : 1, p.k);

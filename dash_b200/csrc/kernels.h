@@ -3,11 +3,14 @@
  * (kernels.cu) used by the C-ABI layer (dashb_api.cu).
  *
  * Device layout of a label tensor ("residue-major digit planes"): one plane
- * per CRT modulus j, u8 digits,
- *     plane_j[element e][digit d][batch b]   at  e*nc_j*Bp + d*Bp + b,
- * Bp = batch rounded up to 16, so every (element, digit) row is 16-byte
- * aligned and the whole plane is the K x N (N = nc_j*Bp) row-major operand
- * of the linear kernels as it stands.
+ * per CRT modulus j, u8 digits packed four to a 32-bit word,
+ *     plane_j[element e][d/4][batch b][d%4]
+ *         at  ((e*nc4_j + d/4)*Bp + b)*4 + d%4,   nc4_j = ceil(nc_j / 4),
+ * Bp = batch rounded up to 16 (digits >= nc_j of the last word are zero).
+ * A gadget thread (one element, one inference) moves 4 digits per 32-bit
+ * access and a warp of 32 inferences 128 contiguous bytes; every element row
+ * is 64-byte aligned and the whole plane is the K x N (N = 4*nc4_j*Bp)
+ * row-major operand of the linear kernels as it stands.
  */
 #pragma once
 #include <cuda_runtime.h>
@@ -26,7 +29,7 @@ struct LinearParams {
     const uint8_t* in[MAXK];
     uint8_t* out[MAXK];
     const uint32_t* w4[MAXK];  /* [ceil(M/8)][Kp/4][8] packed weights mod q_j */
-    const uint8_t* cst[MAXK];  /* [M][nc_j] bias + zero-weight constant label */
+    const uint8_t* cst[MAXK];  /* [M][4*nc4_j] bias + zero-weight constant label, zero padded */
     gc::ModInfo mod[MAXK];
     const int32_t* koff;       /* [Kp] input element offset of tap k */
     uint32_t M, K, Kp;
@@ -66,7 +69,7 @@ struct RescaleParams {
     const uint8_t* in[MAXK];
     uint8_t* out[MAXK];
     gc::ModInfo crt[MAXK];
-    const uint8_t* up[MAXK];    /* upshift label digits (u8[nc_j]) */
+    const uint8_t* up[MAXK];    /* upshift label digits (u8[4*nc4_j], zero padded) */
     const uint8_t* down[MAXK];  /* downshift label digits */
     const uint8_t* zero[MAXK];  /* zero label digits */
     uint32_t loff[MAXK];        /* offset of residue j in the thread's digit workspace */
@@ -90,7 +93,7 @@ struct RescaleParams {
 
 struct AddLabelParams {
     uint8_t* plane[MAXK];
-    const uint8_t* label[MAXK]; /* u8[nc_j] */
+    const uint8_t* label[MAXK]; /* u8[4*nc4_j], zero padded */
     gc::ModInfo crt[MAXK];
     uint64_t n;
     uint32_t Bp;
@@ -118,9 +121,9 @@ cudaError_t upload_aes_tables();
 void host_aes_tables(const uint32_t** te0, const uint32_t** te1, const uint32_t** te2, const uint32_t** te3,
                      const uint8_t** sbox, const uint32_t** rk);
 
-cudaError_t launch_ingest(const int16_t* src, uint8_t* plane, uint64_t rows /* n*nc */, uint32_t batch, uint32_t Bp,
+cudaError_t launch_ingest(const int16_t* src, uint8_t* plane, uint64_t n, uint32_t nc, uint32_t batch, uint32_t Bp,
                           cudaStream_t s);
-cudaError_t launch_egress(const uint8_t* plane, int16_t* dst, uint64_t rows, uint32_t batch, uint32_t Bp,
+cudaError_t launch_egress(const uint8_t* plane, int16_t* dst, uint64_t n, uint32_t nc, uint32_t batch, uint32_t Bp,
                           cudaStream_t s);
 cudaError_t launch_linear(const LinearParams& p, cudaStream_t s);
 cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s);
