@@ -79,6 +79,7 @@ ModInfo make_modinfo(uint32_t q) {
     }
     m.s = (uint32_t)__builtin_clz(m.Q);
     m.dn = m.Q << m.s;
+    m.pow2s = 1u << m.s;
     m.v = (uint32_t)(~0ull / m.dn - (1ull << 32));
     /* significant limbs of the running quotient before division c: it is
      * below 2^128 / Q^c for every 128-bit payload */

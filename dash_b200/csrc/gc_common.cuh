@@ -91,6 +91,7 @@ struct ModInfo {
     uint32_t dn;       /* Q << s */
     uint32_t v;        /* floor((2^64 - 1) / dn) - 2^32 */
     uint32_t limbs;    /* 2 bits per chunk c: (significant 32-bit limbs before division c) - 1 */
+    uint32_t pow2s;    /* 1 << s */
 };
 
 /* r / q for r <= m.lim (true for every chunk value and its quotients). */
@@ -116,8 +117,10 @@ GC_HD uint32_t funnel_hi(uint32_t lo, uint32_t sh) {
  * updates rs.  Moeller & Granlund, "Improved division by invariant
  * integers", Alg. 4. */
 GC_HD uint32_t div_step(uint32_t& rs, uint32_t w, const ModInfo& m) {
-    const uint32_t u1 = rs | funnel_hi(w, m.s);
-    const uint32_t u0 = w << m.s;
+    /* (rs:0) + (w << s) as two words; written with multiplies by 2^s so that
+     * the shifts run on the FMA pipe (the ALU pipe is the busy one, ncu) */
+    const uint32_t u1 = mulhi32(w, m.pow2s) + rs;
+    const uint32_t u0 = w * m.pow2s;
     const uint64_t qq = (uint64_t)m.v * u1 + (((uint64_t)u1 << 32) | u0);
     uint32_t q1 = (uint32_t)(qq >> 32) + 1u;
     const uint32_t q0 = (uint32_t)qq;
@@ -252,6 +255,20 @@ GC_HD uint32_t bswap32(uint32_t x) {
 #endif
 }
 
+/* byte i (0 = least significant) of s, times 4: the T-table byte offset.
+ * (Writing the shifts as mul.hi by a power of two moves them to the FMA pipe
+ * but measured slower on B200: IMAD.HI is not full rate.) */
+GC_HD uint32_t tt_off3(uint32_t s) {
+    return (s >> 22) & 0x3fcu;
+}
+GC_HD uint32_t tt_off2(uint32_t s) {
+    return (s >> 14) & 0x3fcu;
+}
+GC_HD uint32_t tt_off1(uint32_t s) {
+    return (s >> 6) & 0x3fcu;
+}
+GC_HD uint32_t tt_off0(uint32_t s) { return (s << 2) & 0x3fcu; }
+
 template <typename T32, typename T8, typename K32>
 GC_HD u128 aes128_encrypt(u128 in, const T32* te0, const T32* te1, const T32* te2, const T32* te3, const T8* sbox,
                           const K32* rk) {
@@ -264,10 +281,10 @@ GC_HD u128 aes128_encrypt(u128 in, const T32* te0, const T32* te1, const T32* te
      * streamed through it (ncu: stall_no_inst 24 %) */
 #pragma unroll 1
     for (int r = 1; r < 10; ++r) {
-        uint32_t t0 = te0[s0 >> 24] ^ te1[(s1 >> 16) & 0xff] ^ te2[(s2 >> 8) & 0xff] ^ te3[s3 & 0xff] ^ rk[4 * r];
-        uint32_t t1 = te0[s1 >> 24] ^ te1[(s2 >> 16) & 0xff] ^ te2[(s3 >> 8) & 0xff] ^ te3[s0 & 0xff] ^ rk[4 * r + 1];
-        uint32_t t2 = te0[s2 >> 24] ^ te1[(s3 >> 16) & 0xff] ^ te2[(s0 >> 8) & 0xff] ^ te3[s1 & 0xff] ^ rk[4 * r + 2];
-        uint32_t t3 = te0[s3 >> 24] ^ te1[(s0 >> 16) & 0xff] ^ te2[(s1 >> 8) & 0xff] ^ te3[s2 & 0xff] ^ rk[4 * r + 3];
+        uint32_t t0 = te0[tt_off3(s0) >> 2] ^ te1[tt_off2(s1) >> 2] ^ te2[tt_off1(s2) >> 2] ^ te3[tt_off0(s3) >> 2] ^ rk[4 * r];
+        uint32_t t1 = te0[tt_off3(s1) >> 2] ^ te1[tt_off2(s2) >> 2] ^ te2[tt_off1(s3) >> 2] ^ te3[tt_off0(s0) >> 2] ^ rk[4 * r + 1];
+        uint32_t t2 = te0[tt_off3(s2) >> 2] ^ te1[tt_off2(s3) >> 2] ^ te2[tt_off1(s0) >> 2] ^ te3[tt_off0(s1) >> 2] ^ rk[4 * r + 2];
+        uint32_t t3 = te0[tt_off3(s3) >> 2] ^ te1[tt_off2(s0) >> 2] ^ te2[tt_off1(s1) >> 2] ^ te3[tt_off0(s2) >> 2] ^ rk[4 * r + 3];
         s0 = t0;
         s1 = t1;
         s2 = t2;

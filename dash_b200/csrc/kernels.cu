@@ -118,7 +118,7 @@ __device__ __forceinline__ void aes_smem_load(AesSmem& a) {
 __device__ __forceinline__ ModInfo pin(const ModInfo& src) {
     ModInfo m = src;
     asm volatile("" : "+r"(m.q), "+r"(m.nc), "+r"(m.t), "+r"(m.nchunks), "+r"(m.Q), "+r"(m.mq));
-    asm volatile("" : "+r"(m.lim), "+r"(m.top_len), "+r"(m.s), "+r"(m.dn), "+r"(m.v), "+r"(m.limbs));
+    asm volatile("" : "+r"(m.lim), "+r"(m.top_len), "+r"(m.s), "+r"(m.dn), "+r"(m.v), "+r"(m.limbs), "+r"(m.pow2s));
     return m;
 }
 
