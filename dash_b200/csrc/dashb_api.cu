@@ -332,6 +332,21 @@ void push_layer(dashb_circuit* c, std::unique_ptr<Layer> L) {
 
 }  // namespace
 
+namespace dashb {
+gc::ModInfo modinfo_for(uint32_t q) { return make_modinfo(q); }
+int report_error(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+cudaStream_t library_stream() { return g_stream; }
+int initialised_device() { return g_device; }
+}  // namespace dashb
+
 extern "C" {
 
 const char* dashb_last_error(void) { return g_err.c_str(); }

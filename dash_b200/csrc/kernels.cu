@@ -10,6 +10,9 @@
  */
 #include <cuda_runtime.h>
 
+#include <cstring>
+
+#include "../../include/dash_b200.h"
 #include "kernels.h"
 
 namespace dashb {
@@ -362,6 +365,90 @@ cudaError_t launch_projection(const ProjParams& p, cudaStream_t s) {
     k_projection<<<grid, 128, 0, s>>>(p);
     return cudaGetLastError();
 }
+
+/* ---------------------------------------- projection, allocation-free */
+/*
+ * The digit planes of dashb_projection_static.  This is the only device
+ * memory that entry point uses besides the caller's own buffers; it is part
+ * of the library image, so every GPU that loads the library carries these
+ * 8 MiB until the process ends.  In host code the name below is only a
+ * stand-in for the symbol: the address kernels may dereference comes from
+ * cudaGetSymbolAddress (static_scratch_address).
+ */
+static __device__ __align__(256) unsigned char s_static_scratch[DASHB_STATIC_SCRATCH_BYTES];
+
+constexpr int MAX_DEVICES = 64;
+static unsigned char* g_static_scratch_addr[MAX_DEVICES]; /* device address per device, 0 = not looked up yet */
+
+/* One-off per device, with that device current. */
+static cudaError_t static_scratch_address(int device, unsigned char** out) {
+    if (!g_static_scratch_addr[device]) {
+        unsigned char* ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&ptr, s_static_scratch);
+        if (e != cudaSuccess) return e;
+        g_static_scratch_addr[device] = ptr;
+    }
+    *out = g_static_scratch_addr[device];
+    return cudaSuccess;
+}
+
+}  // namespace dashb
+
+/* See include/dash_b200.h.  Same three kernels as the allocated path
+ * (k_ingest -> k_projection -> k_egress); only the planes in between live in
+ * s_static_scratch instead of cudaMalloc'ed buffers. */
+extern "C" int dashb_projection_static(const int16_t* d_in, const dashb_u128* d_ciphers, int16_t* d_out, uint64_t n,
+                                       uint64_t batch, int q_in, int q_out, void* stream) {
+    using namespace dashb;
+    if (!d_in || !d_ciphers || !d_out) return report_error(DASHB_EINVAL, "dashb_projection_static: null device pointer");
+    if (q_in < 2 || q_in > 256 || q_out < 2 || q_out > 256)
+        return report_error(DASHB_EINVAL, "dashb_projection_static: moduli must lie in [2,256] (got %d -> %d)", q_in, q_out);
+    if (n == 0 || batch == 0 || batch > (1u << 24) || n > (1u << 30))
+        return report_error(DASHB_EINVAL, "dashb_projection_static: empty or oversized problem");
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return report_error(DASHB_ECUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+    if (initialised_device() < 0 || dev != initialised_device() || dev >= MAX_DEVICES)
+        return report_error(DASHB_ENODEV, "dashb_projection_static: call dashb_init() on the current device first");
+    const ModInfo mi = modinfo_for((uint32_t)q_in), mo = modinfo_for((uint32_t)q_out);
+    const uint64_t Bp = (batch + 15) & ~15ull;
+    const uint64_t in_bytes = n * ((mi.nc + 3) / 4) * 4 * Bp;
+    const uint64_t out_bytes = n * ((mo.nc + 3) / 4) * 4 * Bp;
+    if (in_bytes + out_bytes > DASHB_STATIC_SCRATCH_BYTES)
+        return report_error(DASHB_EINVAL,
+                            "dashb_projection_static: %llu gates x %llu inferences need %llu bytes of digit planes, "
+                            "the static scratch holds %u; split the call",
+                            (unsigned long long)n, (unsigned long long)batch,
+                            (unsigned long long)(in_bytes + out_bytes), (unsigned)DASHB_STATIC_SCRATCH_BYTES);
+    unsigned char* scratch = nullptr;
+    e = static_scratch_address(dev, &scratch);
+    if (e != cudaSuccess) return report_error(DASHB_ECUDA, "cudaGetSymbolAddress(static scratch): %s", cudaGetErrorString(e));
+    cudaStream_t s = stream ? (cudaStream_t)stream : library_stream();
+    unsigned char* plane_in = scratch;
+    unsigned char* plane_out = scratch + in_bytes; /* in_bytes is a multiple of 64 */
+    /* the array still holds the previous call's planes: start from zeros */
+    e = cudaMemsetAsync(scratch, 0, in_bytes + out_bytes, s);
+    if (e == cudaSuccess) e = launch_ingest(d_in, plane_in, n, mi.nc, (uint32_t)batch, (uint32_t)Bp, s);
+    if (e == cudaSuccess) {
+        ProjParams p;
+        memset(&p, 0, sizeof(p));
+        p.k = 1;
+        p.n = n;
+        p.batch = (uint32_t)batch;
+        p.Bp = (uint32_t)Bp;
+        p.in[0] = plane_in;
+        p.out[0] = plane_out;
+        p.min[0] = mi;
+        p.mout[0] = mo;
+        p.ciphers[0] = reinterpret_cast<const gc::u128*>(d_ciphers);
+        e = launch_projection(p, s);
+    }
+    if (e == cudaSuccess) e = launch_egress(plane_out, d_out, n, mo.nc, (uint32_t)batch, (uint32_t)Bp, s);
+    if (e != cudaSuccess) return report_error(DASHB_ECUDA, "dashb_projection_static: %s", cudaGetErrorString(e));
+    return DASHB_OK;
+}
+
+namespace dashb {
 
 /* ------------------------------------------------- sign gadget / ReLU */
 /* Per-thread digit accumulators live in shared memory, digit-major

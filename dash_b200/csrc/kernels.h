@@ -115,6 +115,13 @@ struct DecodeParams {
     int k;
 };
 
+/* small services of dashb_api.cu for entry points that live next to their
+ * kernels (dashb_projection_static) */
+gc::ModInfo modinfo_for(uint32_t q);
+int report_error(int code, const char* fmt, ...);
+cudaStream_t library_stream();
+int initialised_device();
+
 /* uploads T-tables / S-box / round keys of key 00..0f to the device */
 cudaError_t upload_aes_tables();
 /* host copies of the tables for dashb_hostcheck_* */

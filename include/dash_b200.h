@@ -158,6 +158,43 @@ int dashb_add_projection(dashb_circuit* c, uint64_t n,
                          const int32_t* in_moduli, const int32_t* out_moduli,
                          const dashb_u128* const* ciphers);
 
+/* Projection gates without any allocation.  No counterpart in the
+ * reference.
+ *
+ * For hosts that must not allocate while they evaluate: a server that gave
+ * its whole device-memory budget to its own arena at start-up, the untrusted
+ * half of Dash's SGX split where every cudaMalloc is an ocall round trip out
+ * of the enclave (sgx/Enclave/Enclave.edl, ocall_cudaMalloc), or a latency-
+ * critical loop in which cudaMalloc/cudaFree would stall the whole device.
+ * Such a caller keeps its labels and tables in device memory it already owns
+ * and passes plain device pointers; the digit planes the kernels need in
+ * between live in one fixed array inside the library image
+ * (DASHB_STATIC_SCRATCH_BYTES, resident on every GPU that loads the library
+ * until the process exits).  The call itself performs no cudaMalloc, no
+ * cudaFree and calls no allocating library routine.
+ *
+ * Evaluates n projection gates of one modulus pair for `batch` inferences:
+ *   d_in      device int16 [batch][n][nc(q_in)]   (LabelTensor digit order)
+ *   d_ciphers device 16-byte rows [n][q_in]
+ *   d_out     device int16 [batch][n][nc(q_out)]
+ * i.e. GarbledProjection / eval_proj semantics, identical to what
+ * dashb_evaluate computes for a projection layer.  q_in, q_out in [2,256].
+ * Work is enqueued on `stream` (a cudaStream_t; NULL = dashb_stream()) and
+ * is asynchronous.  Fails with DASHB_EINVAL, touching nothing, when
+ *   4*Bp*n*(ceil(nc(q_in)/4) + ceil(nc(q_out)/4)) > DASHB_STATIC_SCRATCH_BYTES
+ * (Bp = batch rounded up to 16).
+ *
+ * The first call on a device looks up the array's device address (one-off
+ * set-up); make that first call before you start any stream capture.
+ * All calls share the one array and it keeps whatever the previous call left:
+ * the part a call uses is cleared at its start, so results never depend on
+ * earlier calls, but two calls that overlap in time on the GPU (different
+ * streams, or several host threads) race on it -- serialise them.
+ * Requires dashb_init() on the current device. */
+#define DASHB_STATIC_SCRATCH_BYTES (8u << 20)
+int dashb_projection_static(const int16_t* d_in, const dashb_u128* d_ciphers, int16_t* d_out, uint64_t n,
+                            uint64_t batch, int q_in, int q_out, void* stream);
+
 /* Decoding information (gen_decoding_information,
  * garbled_circuit_interface.h:386-415): dec[j] = [p_j][output_size] hashes.
  * Optional; needed only for dashb_decode_outputs. */
