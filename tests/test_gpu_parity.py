@@ -36,3 +36,67 @@ def test_golden_every_layer(gpu, name):
         _check(c.L.dashb_layer_outputs(c.h, l, _ptr_array(out)))
         assert_labels_equal(out, want, "%s layer %d" % (name, l))
     c.close()
+
+
+# ---- circuits garbled on the box by the reference build (oracle/_ref) -----
+def _live(name, gpu, tmp_path, batch, seed=77):
+    import workloads as W
+    from oracle import oraclebind as O
+    from oracle import refbind as R
+
+    if not R.available():
+        pytest.skip("oracle/_ref not present on this box")
+    spec = W.MODELS[name]
+    ref = W.build_reference_circuit(spec, seed=seed, weight_seed=seed)
+    path = str(tmp_path / (name + ".gcm"))
+    ref.export(path)
+    X = W.synthetic_inputs(spec, batch, seed=seed)
+    per = [ref.garble_inputs(x) for x in X]
+    labels = [np.stack([p[j] for p in per]) for j in range(ref.k)]
+    c = gpu.Circuit.load(path, max_batch=batch)
+    got = c.evaluate(labels)
+    return ref, O.OracleCircuit(path), labels, c, got
+
+
+@pytest.mark.parametrize("name,batch", [("MNIST_TINY_CNN", 33), ("CIFAR_TINY_SCALE", 20), ("SIGN_TINY", 64),
+                                        ("MODEL_E_30", 5), ("RESCALE_LEGACY", 48)])
+def test_live_reference_circuits(gpu, tmp_path, name, batch):
+    ref, oc, labels, c, got = _live(name, gpu, tmp_path, batch)
+    vals, ok = c.decode_outputs()
+    assert ok.all()
+    for b in range(0, batch, max(1, batch // 6)):
+        lab = [l[b] for l in labels]
+        want, _ = ref.cpu_evaluate(lab, 4)              # the reference itself
+        assert_labels_equal([g[b] for g in got], want, "%s inference %d vs reference" % (name, b))
+        assert_labels_equal(oc.evaluate(lab, threads=4), want, "%s oracle vs reference" % name)
+        assert np.array_equal(vals[b], ref.decode_outputs(want))
+    c.close()
+
+
+def test_full_size_model_b_batch_256(gpu, tmp_path):
+    """BASELINE.json configs[1] at its full size: MODEL_B_POOL_REPL, batch 256.
+    Bit-exact against the reference on a sample of the batch, plus size-
+    independent properties: an inference's labels do not depend on its
+    position or neighbours in the batch, and every output decodes."""
+    import bench
+    from oracle import refbind as R
+
+    if not R.available():
+        pytest.skip("oracle/_ref not present on this box")
+    B = 256
+    gcm, labels, ref = bench.build_material("MODEL_B_POOL_REPL", B, want_ref=True)
+    c = gpu.Circuit.load(gcm, max_batch=B)
+    got = c.evaluate(labels)
+    vals, ok = c.decode_outputs()
+    assert ok.all()
+    for b in (0, 1, 31, 32, 100, 255):
+        want, _ = ref.cpu_evaluate([l[b] for l in labels], 8)
+        assert_labels_equal([g[b] for g in got], want, "MODEL_B inference %d" % b)
+        assert np.array_equal(vals[b], ref.decode_outputs(want))
+    # permutation property: reverse the batch, outputs reverse with it
+    rev = c.evaluate([l[::-1].copy() for l in labels])
+    assert_labels_equal([r[::-1] for r in rev], got, "batch permutation")
+    # a smaller, ragged batch reproduces the same labels
+    sub = c.evaluate([l[:37].copy() for l in labels])
+    assert_labels_equal(sub, [g[:37] for g in got], "ragged batch 37")
+    c.close()
