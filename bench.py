@@ -20,7 +20,6 @@ import json
 import os
 import subprocess
 import sys
-import threading
 import time
 
 import numpy as np
@@ -75,29 +74,39 @@ def build_material(model, n_inputs, want_ref=False):
     return gcm, [l[:n_inputs] for l in labels], ref
 
 
-class ClockSampler(threading.Thread):
-    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region
+    (one background `nvidia-smi -lms 50` process)."""
 
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        super().__init__(daemon=True)
         self.index = index
-        self.stop_flag = threading.Event()
+        self.proc = None
         self.samples = []
 
-    def run(self):
-        while not self.stop_flag.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                f = [x.strip() for x in out.strip().split(",")]
-                if len(f) >= 6:
-                    self.samples.append(f)
-            except Exception:
-                pass
-            self.stop_flag.wait(0.1)
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) >= 6 and f[0].replace(".", "").isdigit():
+                self.samples.append(f)
 
     def summary(self):
         if not self.samples:
@@ -145,7 +154,7 @@ def run_reference(args, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--model", default="MODEL_B_POOL_REPL")
@@ -239,14 +248,26 @@ def main():
 
     sampler = ClockSampler(local_rank)
     sampler.start()
-    circ.set_layer_timing(True)
+    time.sleep(0.2)
     ms_dev = timed(step_device, args.steps, args.warmup)
-    layer_ms = circ.layer_times_ms()  # last timed step
     launches = circ.launch_count()
-    circ.set_layer_timing(False)
     ms_e2e = timed(step_e2e, args.steps, args.warmup)
-    sampler.stop_flag.set()
-    sampler.join()
+    # per-kernel durations for the roofline: same steps with the sub-batch
+    # lanes serialised on one stream and a CUDA event pair around every layer
+    circ.set_layer_timing(True)
+    prof_steps = min(args.steps, 20)
+    acc = None
+    for _ in range(3 + prof_steps):
+        flush.zero_()
+        torch.cuda.synchronize()
+        step_device()
+        lm = circ.layer_times_ms()
+        if _ >= 3:
+            acc = lm if acc is None else [(n, a + b) for (n, a), (_n, b) in zip(acc, lm)]
+    layer_ms = [(n, v / prof_steps) for n, v in acc]
+    circ.set_layer_timing(False)
+    time.sleep(0.1)
+    sampler.stop()
 
     total_inf = B * world * args.steps
     value = total_inf / (ms_dev / 1e3)
@@ -270,7 +291,9 @@ def main():
     roofline = {
         "bound": "hbm", "kernel": "k_sign<relu> (fused sign gadget + half gates)", "achieved": achieved, "peak": peak,
         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-        "launches_per_step": len(relu_layers), "avg_launch_ms": relu_ms / max(1, len(relu_layers)),
+        "launches_per_step": len(relu_layers) * circ.L.dashb_num_lanes(circ.h) if hasattr(circ.L, "dashb_num_lanes") else len(relu_layers),
+        "avg_layer_ms": relu_ms / max(1, len(relu_layers)),
+        "timing": "CUDA events around every layer, sub-batch lanes serialised on the library stream, %d steps after the timed region" % prof_steps,
         "share_of_step": relu_ms / step_ms if step_ms else None,
         "aes_blocks_per_s": relu_aes / (relu_ms / 1e3) if relu_ms > 0 else 0.0,
         "note": "compute-bound on AES + base-q digit arithmetic, not on HBM (see DESIGN.md)",

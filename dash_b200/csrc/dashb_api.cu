@@ -8,9 +8,11 @@
  */
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -196,6 +198,19 @@ struct Layer {
     float ms{0};
 };
 
+/* One sub-batch pipeline: its own stream, staging and activation buffers.
+ * A batch is cut into contiguous slices, one per lane; the lanes' copies and
+ * kernels overlap (H2D of lane i+1 under the kernels of lane i, the small
+ * late layers of one lane under the big early layers of another). */
+struct Lane {
+    cudaStream_t s{nullptr};
+    cudaEvent_t done{nullptr}, in_done{nullptr}, ing_done{nullptr};
+    DevMem buf_in, buf_a, buf_b, stage_in, stage_out;
+    Tensor t_in, t_cur;
+    int which{0};
+    uint32_t b0{0}, batch{0}, Bp{0};
+};
+
 }  // namespace
 
 struct dashb_circuit {
@@ -213,17 +228,32 @@ struct dashb_circuit {
     uint64_t cur_size{0}; /* their count */
     bool finalized{false};
     uint64_t max_batch{0};
-    uint32_t Bp{0}, batch{0};
-    DevMem buf_in, buf_a, buf_b, stage_in, stage_out;
+    uint32_t batch{0};
+    std::vector<std::unique_ptr<Lane>> lanes;
+    int lanes_used{0};
+    uint32_t lane_cap{0};
+    cudaEvent_t ev_fork{nullptr};
+    cudaStream_t copy_s{nullptr};   /* H2D copies of the pipelined dashb_evaluate */
+    cudaStream_t ingest_s{nullptr}; /* its ingest kernels (highest priority) */
     DevMem dec[MAXK];
     bool has_dec{false};
     DevMem d_values, d_ok;
-    Tensor t_in, t_last;
+    uint64_t out_n{0};   /* labels per inference in the lanes' current tensors */
+    int out_q[MAXK];     /* their moduli */
     uint64_t launches{0};
     bool timing{false};
     std::vector<cudaEvent_t> ev;
     ~dashb_circuit() {
         for (auto e : ev) cudaEventDestroy(e);
+        if (ev_fork) cudaEventDestroy(ev_fork);
+        if (copy_s) cudaStreamDestroy(copy_s);
+        if (ingest_s) cudaStreamDestroy(ingest_s);
+        for (auto& l : lanes) {
+            if (l->done) cudaEventDestroy(l->done);
+            if (l->in_done) cudaEventDestroy(l->in_done);
+            if (l->ing_done) cudaEventDestroy(l->ing_done);
+            if (l->s) cudaStreamDestroy(l->s);
+        }
     }
 };
 
@@ -745,27 +775,48 @@ int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
     if (rc) return rc;
     if (max_batch == 0 || max_batch > (1u << 24)) return fail(DASHB_EINVAL, "bad max_batch");
     c->max_batch = max_batch;
-    const uint32_t Bp = (uint32_t)((max_batch + 15) & ~15ull);
+    int n_lanes = max_batch >= 128 ? 4 : (max_batch >= 64 ? 2 : 1);
+    if (const char* env = getenv("DASHB_LANES")) {
+        int v = atoi(env);
+        if (v >= 1 && v <= 16) n_lanes = v;
+    }
+    c->lane_cap = (uint32_t)((((max_batch + n_lanes - 1) / n_lanes) + 15) & ~15ull);
+    const uint32_t Bp = c->lane_cap;
     size_t in_bytes = tensor_bytes(c->input_size, c->k, c->crt, Bp);
     size_t act_bytes = 256;
     size_t stage_in = 0, stage_out = 0;
-    for (int j = 0; j < c->k; ++j) stage_in += (size_t)max_batch * c->input_size * c->crt_mi[j].nc * 2;
+    for (int j = 0; j < c->k; ++j) stage_in += (size_t)Bp * c->input_size * c->crt_mi[j].nc * 2;
     for (auto& L : c->layers) {
         size_t b = tensor_bytes(L->out_size, c->k, L->out_q, Bp);
         if (b > act_bytes) act_bytes = b;
         size_t so = 0;
-        for (int j = 0; j < c->k; ++j) so += (size_t)max_batch * L->out_size * nr_comps(L->out_q[j]) * 2;
+        for (int j = 0; j < c->k; ++j) so += (size_t)Bp * L->out_size * nr_comps(L->out_q[j]) * 2;
         if (so > stage_out) stage_out = so;
     }
     if (stage_in > stage_out) stage_out = stage_in; /* zero-layer circuits echo the input */
-    CU(c->buf_in.alloc(in_bytes));
-    CU(c->buf_a.alloc(act_bytes));
-    CU(c->buf_b.alloc(act_bytes));
-    CU(c->stage_in.alloc(stage_in));
-    CU(c->stage_out.alloc(stage_out));
-    CU(cudaMemset(c->buf_in.p, 0, in_bytes));
-    CU(cudaMemset(c->buf_a.p, 0, act_bytes));
-    CU(cudaMemset(c->buf_b.p, 0, act_bytes));
+    for (int i = 0; i < n_lanes; ++i) {
+        auto ln = std::make_unique<Lane>();
+        CU(cudaStreamCreateWithFlags(&ln->s, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&ln->done, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&ln->in_done, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&ln->ing_done, cudaEventDisableTiming));
+        CU(ln->buf_in.alloc(in_bytes));
+        CU(ln->buf_a.alloc(act_bytes));
+        CU(ln->buf_b.alloc(act_bytes));
+        CU(ln->stage_in.alloc(stage_in));
+        CU(ln->stage_out.alloc(stage_out));
+        CU(cudaMemset(ln->buf_in.p, 0, in_bytes));
+        CU(cudaMemset(ln->buf_a.p, 0, act_bytes));
+        CU(cudaMemset(ln->buf_b.p, 0, act_bytes));
+        c->lanes.push_back(std::move(ln));
+    }
+    CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    CU(cudaStreamCreateWithFlags(&c->copy_s, cudaStreamNonBlocking));
+    {
+        int lo = 0, hi = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CU(cudaStreamCreateWithPriority(&c->ingest_s, cudaStreamNonBlocking, hi));
+    }
     CU(c->d_values.alloc((size_t)max_batch * c->cur_size * 8));
     CU(c->d_ok.alloc(max_batch));
     c->ev.resize(c->layers.size() + 1);
@@ -774,161 +825,253 @@ int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
     return DASHB_OK;
 }
 
-int dashb_move_inputs(dashb_circuit* c, const int16_t* const* in, uint64_t batch) {
-    if (!c || !in) return fail(DASHB_EINVAL, "null argument");
-    if (!c->finalized) return fail(DASHB_ESTATE, "circuit not finalized");
-    if (batch == 0 || batch > c->max_batch) return fail(DASHB_EINVAL, "batch %llu outside 1..%llu", (unsigned long long)batch, (unsigned long long)c->max_batch);
-    c->batch = (uint32_t)batch;
-    c->Bp = (uint32_t)((batch + 15) & ~15ull);
-    carve(c->t_in, (uint8_t*)c->buf_in.p, c->input_size, c->k, c->crt, c->Bp);
-    size_t off = 0;
-    for (int j = 0; j < c->k; ++j) {
-        if (!in[j]) return fail(DASHB_EINVAL, "input labels %d missing", j);
-        const uint64_t rows = c->input_size * c->crt_mi[j].nc;
-        const size_t bytes = (size_t)batch * rows * 2;
-        int16_t* st = (int16_t*)((char*)c->stage_in.p + off);
-        CU(cudaMemcpyAsync(st, in[j], bytes, cudaMemcpyHostToDevice, g_stream));
-        CU(launch_ingest(st, c->t_in.plane[j], c->input_size, c->crt_mi[j].nc, c->batch, c->Bp, g_stream));
-        off += bytes;
+/* lane streams start after everything already enqueued on the library stream */
+static int fork_lanes(dashb_circuit* c) {
+    CU(cudaEventRecord(c->ev_fork, g_stream));
+    for (int i = 0; i < c->lanes_used; ++i) CU(cudaStreamWaitEvent(c->lanes[i]->s, c->ev_fork, 0));
+    CU(cudaStreamWaitEvent(c->copy_s, c->ev_fork, 0));
+    CU(cudaStreamWaitEvent(c->ingest_s, c->ev_fork, 0));
+    return DASHB_OK;
+}
+/* ... and the library stream continues after all of them */
+static int join_lanes(dashb_circuit* c) {
+    for (int i = 0; i < c->lanes_used; ++i) {
+        CU(cudaEventRecord(c->lanes[i]->done, c->lanes[i]->s));
+        CU(cudaStreamWaitEvent(g_stream, c->lanes[i]->done, 0));
     }
-    c->t_last = c->t_in;
     return DASHB_OK;
 }
 
-static int run_layers(dashb_circuit* c, int upto) {
-    Tensor cur = c->t_in;
-    uint8_t* bufs[2] = {(uint8_t*)c->buf_a.p, (uint8_t*)c->buf_b.p};
-    int which = 0;
-    c->launches = 0;
-    const uint32_t B = c->batch, Bp = c->Bp;
-    if (c->timing) CU(cudaEventRecord(c->ev[0], g_stream));
-    for (int li = 0; li <= upto; ++li) {
-        Layer& L = *c->layers[li];
-        Tensor out;
-        carve(out, bufs[which], L.out_size, c->k, L.out_q, Bp);
-        which ^= 1;
-        switch (L.type) {
-            case DASHB_LAYER_DENSE:
-            case DASHB_LAYER_CONV2D: {
-                LinearParams p;
-                memset(&p, 0, sizeof(p));
-                p.k = c->k;
-                for (int j = 0; j < c->k; ++j) {
-                    p.in[j] = cur.plane[j];
-                    p.out[j] = out.plane[j];
-                    p.w4[j] = (const uint32_t*)L.w4[j].p;
-                    p.cst[j] = (const uint8_t*)L.cst[j].p;
-                    p.mod[j] = c->crt_mi[j];
-                }
-                p.koff = (const int32_t*)L.koff.p;
-                p.M = (uint32_t)L.M;
-                p.K = (uint32_t)L.K;
-                p.Kp = L.Kp;
-                p.npix = L.npix;
-                p.ow = L.ow;
-                p.step_x = L.step_x;
-                p.step_y = L.step_y;
-                p.Bp = Bp;
-                CU(launch_linear(p, g_stream));
-                c->launches += 1;
-                break;
-            }
-            case DASHB_LAYER_RELU:
-            case DASHB_LAYER_SIGN: {
-                const bool relu = L.type == DASHB_LAYER_RELU;
-                SignParams p;
-                fill_sign_params(c, p, L.in_size, relu ? 1 : c->k);
-                for (int j = 0; j < c->k; ++j) {
-                    p.in[j] = cur.plane[j];
-                    p.out[j] = out.plane[j];
-                    p.outm[j] = c->crt_mi[j];
-                }
-                p.approx = (const u128*)L.approx.p;
-                p.cast1 = (const u128*)L.cast1.p;
-                p.cast2 = (const u128*)L.cast2.p;
-                p.sign = (const u128*)L.sign.p;
-                p.garbler = (const u128*)L.garbler.p;
-                p.evaluator = (const u128*)L.evaluator.p;
-                p.batch = B;
-                p.Bp = Bp;
-                CU(launch_sign(p, relu, g_stream));
-                c->launches += 1;
-                break;
-            }
-            case DASHB_LAYER_RESCALE:
-            case DASHB_LAYER_RESCALE_LEGACY: {
-                const bool legacy = L.type == DASHB_LAYER_RESCALE_LEGACY;
-                const int iters = legacy ? L.l_iter : 1;
-                for (int it = 0; it < iters; ++it) {
-                    RescaleParams p = L.rp;
-                    for (int j = 0; j < c->k; ++j) {
-                        p.in[j] = it == 0 ? cur.plane[j] : out.plane[j];
-                        p.out[j] = out.plane[j];
-                        p.up[j] = (const uint8_t*)c->d_up[j].p;
-                        p.down[j] = (const uint8_t*)L.down[j].p;
-                        p.zero[j] = (const uint8_t*)c->d_zero[j].p;
-                    }
-                    p.tm = (const u128*)(legacy ? L.it_tables[5 * it]->p : L.tm.p);
-                    p.be = (const u128*)L.be.p;
-                    p.batch = B;
-                    p.Bp = Bp;
-                    CU(launch_rescale(p, g_stream));
-                    c->launches += 1;
-                    if (legacy) {
-                        /* base extension by sign gadget: regenerates residue 0 in place */
-                        SignParams sp;
-                        fill_sign_params(c, sp, L.in_size, 1);
-                        for (int j = 0; j < c->k; ++j) sp.in[j] = out.plane[j];
-                        sp.out[0] = out.plane[0];
-                        sp.outm[0] = c->crt_mi[0];
-                        sp.approx = (const u128*)L.it_tables[5 * it + 1]->p;
-                        sp.cast1 = (const u128*)L.it_tables[5 * it + 2]->p;
-                        sp.cast2 = (const u128*)L.it_tables[5 * it + 3]->p;
-                        sp.sign = (const u128*)L.it_tables[5 * it + 4]->p;
-                        sp.batch = B;
-                        sp.Bp = Bp;
-                        CU(launch_sign(sp, false, g_stream));
-                        AddLabelParams ap;
-                        memset(&ap, 0, sizeof(ap));
-                        ap.k = c->k;
-                        ap.n = L.in_size;
-                        ap.Bp = Bp;
-                        ap.subtract = 1;
-                        for (int j = 0; j < c->k; ++j) {
-                            ap.plane[j] = out.plane[j];
-                            ap.label[j] = (const uint8_t*)L.down[j].p;
-                            ap.crt[j] = c->crt_mi[j];
-                        }
-                        CU(launch_add_label(ap, g_stream));
-                        c->launches += 2;
-                    }
-                }
-                break;
-            }
-            case DASHB_LAYER_PROJECTION: {
-                ProjParams p;
-                memset(&p, 0, sizeof(p));
-                p.k = c->k;
-                p.n = L.in_size;
-                p.batch = B;
-                p.Bp = Bp;
-                for (int j = 0; j < c->k; ++j) {
-                    p.in[j] = cur.plane[j];
-                    p.out[j] = out.plane[j];
-                    p.min[j] = make_modinfo((uint32_t)L.in_q[j]);
-                    p.mout[j] = make_modinfo((uint32_t)L.out_q[j]);
-                    p.ciphers[j] = (const u128*)L.proj[j].p;
-                }
-                CU(launch_projection(p, g_stream));
-                c->launches += 1;
-                break;
-            }
-            default: return fail(DASHB_EINVAL, "unknown layer type");
-        }
-        if (c->timing) CU(cudaEventRecord(c->ev[li + 1], g_stream));
-        cur = out;
+static int split_batch(dashb_circuit* c, uint64_t batch) {
+    if (batch == 0 || batch > c->max_batch)
+        return fail(DASHB_EINVAL, "batch %llu outside 1..%llu", (unsigned long long)batch, (unsigned long long)c->max_batch);
+    const int n_lanes = (int)c->lanes.size();
+    uint32_t per = (uint32_t)((((batch + n_lanes - 1) / n_lanes) + 15) & ~15ull);
+    if (per > c->lane_cap) per = c->lane_cap;
+    c->batch = (uint32_t)batch;
+    c->lanes_used = (int)((batch + per - 1) / per);
+    for (int i = 0; i < c->lanes_used; ++i) {
+        Lane& ln = *c->lanes[i];
+        ln.b0 = (uint32_t)i * per;
+        ln.batch = (uint32_t)std::min<uint64_t>(per, batch - ln.b0);
+        ln.Bp = (ln.batch + 15) & ~15u;
+        carve(ln.t_in, (uint8_t*)ln.buf_in.p, c->input_size, c->k, c->crt, ln.Bp);
+        ln.t_cur = ln.t_in;
+        ln.which = 0;
     }
-    c->t_last = cur;
+    c->out_n = c->input_size;
+    for (int j = 0; j < c->k; ++j) c->out_q[j] = c->crt[j];
+    return DASHB_OK;
+}
+
+/* H2D copies of one lane's slice into its staging area (stream cs), then the
+ * layout-changing ingest kernels (stream s).  With cs != s the copies of
+ * all lanes run back to back on the copy engine while earlier lanes compute;
+ * s waits for the lane's last copy. */
+static int enqueue_inputs(dashb_circuit* c, Lane& ln, const int16_t* const* in, cudaStream_t cs, cudaStream_t s) {
+    size_t off = 0;
+    for (int j = 0; j < c->k; ++j) {
+        const uint64_t rows = c->input_size * c->crt_mi[j].nc;
+        const size_t bytes = (size_t)ln.batch * rows * 2;
+        CU(cudaMemcpyAsync((char*)ln.stage_in.p + off, in[j] + (size_t)ln.b0 * rows, bytes, cudaMemcpyHostToDevice, cs));
+        off += bytes;
+    }
+    /* the ingest kernels are short; in the pipelined path they run on a
+     * high-priority stream so that they are not queued behind the thousands
+     * of CTAs of the lanes that already compute */
+    cudaStream_t is = (cs != s) ? c->ingest_s : s;
+    if (cs != s) {
+        CU(cudaEventRecord(ln.in_done, cs));
+        CU(cudaStreamWaitEvent(is, ln.in_done, 0));
+    }
+    off = 0;
+    for (int j = 0; j < c->k; ++j) {
+        const uint64_t rows = c->input_size * c->crt_mi[j].nc;
+        CU(launch_ingest((const int16_t*)((char*)ln.stage_in.p + off), ln.t_in.plane[j], c->input_size, c->crt_mi[j].nc,
+                         ln.batch, ln.Bp, is));
+        off += (size_t)ln.batch * rows * 2;
+    }
+    if (is != s) {
+        CU(cudaEventRecord(ln.ing_done, is));
+        CU(cudaStreamWaitEvent(s, ln.ing_done, 0));
+    }
+    ln.t_cur = ln.t_in;
+    ln.which = 0;
+    return DASHB_OK;
+}
+
+int dashb_move_inputs(dashb_circuit* c, const int16_t* const* in, uint64_t batch) {
+    if (!c || !in) return fail(DASHB_EINVAL, "null argument");
+    if (!c->finalized) return fail(DASHB_ESTATE, "circuit not finalized");
+    for (int j = 0; j < c->k; ++j)
+        if (!in[j]) return fail(DASHB_EINVAL, "input labels %d missing", j);
+    int rc = split_batch(c, batch);
+    if (rc) return rc;
+    if ((rc = fork_lanes(c))) return rc;
+    for (int i = 0; i < c->lanes_used; ++i)
+        if ((rc = enqueue_inputs(c, *c->lanes[i], in, c->lanes[i]->s, c->lanes[i]->s))) return rc;
+    return join_lanes(c);
+}
+
+/* enqueues layer li of one lane on stream s; input = the lane's current tensor */
+static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
+    Layer& L = *c->layers[li];
+    const Tensor cur = ln.t_cur;
+    uint8_t* bufs[2] = {(uint8_t*)ln.buf_a.p, (uint8_t*)ln.buf_b.p};
+    const uint32_t B = ln.batch, Bp = ln.Bp;
+    Tensor out;
+    carve(out, bufs[ln.which], L.out_size, c->k, L.out_q, Bp);
+    ln.which ^= 1;
+    switch (L.type) {
+        case DASHB_LAYER_DENSE:
+        case DASHB_LAYER_CONV2D: {
+            LinearParams p;
+            memset(&p, 0, sizeof(p));
+            p.k = c->k;
+            for (int j = 0; j < c->k; ++j) {
+                p.in[j] = cur.plane[j];
+                p.out[j] = out.plane[j];
+                p.w4[j] = (const uint32_t*)L.w4[j].p;
+                p.cst[j] = (const uint8_t*)L.cst[j].p;
+                p.mod[j] = c->crt_mi[j];
+            }
+            p.koff = (const int32_t*)L.koff.p;
+            p.M = (uint32_t)L.M;
+            p.K = (uint32_t)L.K;
+            p.Kp = L.Kp;
+            p.npix = L.npix;
+            p.ow = L.ow;
+            p.step_x = L.step_x;
+            p.step_y = L.step_y;
+            p.Bp = Bp;
+            CU(launch_linear(p, s));
+            c->launches += 1;
+            break;
+        }
+        case DASHB_LAYER_RELU:
+        case DASHB_LAYER_SIGN: {
+            const bool relu = L.type == DASHB_LAYER_RELU;
+            SignParams p;
+            fill_sign_params(c, p, L.in_size, relu ? 1 : c->k);
+            for (int j = 0; j < c->k; ++j) {
+                p.in[j] = cur.plane[j];
+                p.out[j] = out.plane[j];
+                p.outm[j] = c->crt_mi[j];
+            }
+            p.approx = (const u128*)L.approx.p;
+            p.cast1 = (const u128*)L.cast1.p;
+            p.cast2 = (const u128*)L.cast2.p;
+            p.sign = (const u128*)L.sign.p;
+            p.garbler = (const u128*)L.garbler.p;
+            p.evaluator = (const u128*)L.evaluator.p;
+            p.batch = B;
+            p.Bp = Bp;
+            CU(launch_sign(p, relu, s));
+            c->launches += 1;
+            break;
+        }
+        case DASHB_LAYER_RESCALE:
+        case DASHB_LAYER_RESCALE_LEGACY: {
+            const bool legacy = L.type == DASHB_LAYER_RESCALE_LEGACY;
+            const int iters = legacy ? L.l_iter : 1;
+            for (int it = 0; it < iters; ++it) {
+                RescaleParams p = L.rp;
+                for (int j = 0; j < c->k; ++j) {
+                    p.in[j] = it == 0 ? cur.plane[j] : out.plane[j];
+                    p.out[j] = out.plane[j];
+                    p.up[j] = (const uint8_t*)c->d_up[j].p;
+                    p.down[j] = (const uint8_t*)L.down[j].p;
+                    p.zero[j] = (const uint8_t*)c->d_zero[j].p;
+                }
+                p.tm = (const u128*)(legacy ? L.it_tables[5 * it]->p : L.tm.p);
+                p.be = (const u128*)L.be.p;
+                p.batch = B;
+                p.Bp = Bp;
+                CU(launch_rescale(p, s));
+                c->launches += 1;
+                if (legacy) {
+                    /* base extension by sign gadget: regenerates residue 0 in place */
+                    SignParams sp;
+                    fill_sign_params(c, sp, L.in_size, 1);
+                    for (int j = 0; j < c->k; ++j) sp.in[j] = out.plane[j];
+                    sp.out[0] = out.plane[0];
+                    sp.outm[0] = c->crt_mi[0];
+                    sp.approx = (const u128*)L.it_tables[5 * it + 1]->p;
+                    sp.cast1 = (const u128*)L.it_tables[5 * it + 2]->p;
+                    sp.cast2 = (const u128*)L.it_tables[5 * it + 3]->p;
+                    sp.sign = (const u128*)L.it_tables[5 * it + 4]->p;
+                    sp.batch = B;
+                    sp.Bp = Bp;
+                    CU(launch_sign(sp, false, s));
+                    AddLabelParams ap;
+                    memset(&ap, 0, sizeof(ap));
+                    ap.k = c->k;
+                    ap.n = L.in_size;
+                    ap.Bp = Bp;
+                    ap.subtract = 1;
+                    for (int j = 0; j < c->k; ++j) {
+                        ap.plane[j] = out.plane[j];
+                        ap.label[j] = (const uint8_t*)L.down[j].p;
+                        ap.crt[j] = c->crt_mi[j];
+                    }
+                    CU(launch_add_label(ap, s));
+                    c->launches += 2;
+                }
+            }
+            break;
+        }
+        case DASHB_LAYER_PROJECTION: {
+            ProjParams p;
+            memset(&p, 0, sizeof(p));
+            p.k = c->k;
+            p.n = L.in_size;
+            p.batch = B;
+            p.Bp = Bp;
+            for (int j = 0; j < c->k; ++j) {
+                p.in[j] = cur.plane[j];
+                p.out[j] = out.plane[j];
+                p.min[j] = make_modinfo((uint32_t)L.in_q[j]);
+                p.mout[j] = make_modinfo((uint32_t)L.out_q[j]);
+                p.ciphers[j] = (const u128*)L.proj[j].p;
+            }
+            CU(launch_projection(p, s));
+            c->launches += 1;
+            break;
+        }
+        default: return fail(DASHB_EINVAL, "unknown layer type");
+    }
+    ln.t_cur = out;
+    return DASHB_OK;
+}
+
+/* Layers 0..upto for every lane, layer-major so that the lanes' launches of
+ * one layer sit next to each other.  With per-layer timing everything runs
+ * on the library stream (serialised) so that event pairs delimit a layer. */
+static int run_layers(dashb_circuit* c, int upto) {
+    int rc;
+    c->launches = 0;
+    for (int i = 0; i < c->lanes_used; ++i) {
+        c->lanes[i]->t_cur = c->lanes[i]->t_in;
+        c->lanes[i]->which = 0;
+    }
+    if (c->timing) {
+        CU(cudaEventRecord(c->ev[0], g_stream));
+        for (int li = 0; li <= upto; ++li) {
+            for (int i = 0; i < c->lanes_used; ++i)
+                if ((rc = run_layer(c, *c->lanes[i], li, g_stream))) return rc;
+            CU(cudaEventRecord(c->ev[li + 1], g_stream));
+        }
+    } else {
+        if ((rc = fork_lanes(c))) return rc;
+        for (int li = 0; li <= upto; ++li)
+            for (int i = 0; i < c->lanes_used; ++i)
+                if ((rc = run_layer(c, *c->lanes[i], li, c->lanes[i]->s))) return rc;
+        if ((rc = join_lanes(c))) return rc;
+    }
+    if (upto >= 0) {
+        c->out_n = c->layers[upto]->out_size;
+        for (int j = 0; j < c->k; ++j) c->out_q[j] = c->layers[upto]->out_q[j];
+    }
     return DASHB_OK;
 }
 
@@ -944,17 +1087,28 @@ int dashb_evaluate_device(dashb_circuit* c) {
     return DASHB_OK;
 }
 
-static int copy_out(dashb_circuit* c, const Tensor& t, int16_t* const* out) {
+static int enqueue_outputs(dashb_circuit* c, Lane& ln, int16_t* const* out, cudaStream_t s) {
     size_t off = 0;
     for (int j = 0; j < c->k; ++j) {
-        if (!out[j]) return fail(DASHB_EINVAL, "output buffer %d missing", j);
-        const uint64_t rows = t.n * (uint64_t)nr_comps(t.q[j]);
-        const size_t bytes = (size_t)c->batch * rows * 2;
-        int16_t* st = (int16_t*)((char*)c->stage_out.p + off);
-        CU(launch_egress(t.plane[j], st, t.n, (uint32_t)nr_comps(t.q[j]), c->batch, c->Bp, g_stream));
-        CU(cudaMemcpyAsync(out[j], st, bytes, cudaMemcpyDeviceToHost, g_stream));
+        const uint32_t nc = (uint32_t)nr_comps(ln.t_cur.q[j]);
+        const uint64_t rows = ln.t_cur.n * (uint64_t)nc;
+        const size_t bytes = (size_t)ln.batch * rows * 2;
+        int16_t* st = (int16_t*)((char*)ln.stage_out.p + off);
+        CU(launch_egress(ln.t_cur.plane[j], st, ln.t_cur.n, nc, ln.batch, ln.Bp, s));
+        CU(cudaMemcpyAsync(out[j] + (size_t)ln.b0 * rows, st, bytes, cudaMemcpyDeviceToHost, s));
         off += bytes;
     }
+    return DASHB_OK;
+}
+
+static int copy_out(dashb_circuit* c, int16_t* const* out) {
+    for (int j = 0; j < c->k; ++j)
+        if (!out[j]) return fail(DASHB_EINVAL, "output buffer %d missing", j);
+    int rc = fork_lanes(c);
+    if (rc) return rc;
+    for (int i = 0; i < c->lanes_used; ++i)
+        if ((rc = enqueue_outputs(c, *c->lanes[i], out, c->lanes[i]->s))) return rc;
+    if ((rc = join_lanes(c))) return rc;
     CU(cudaStreamSynchronize(g_stream));
     return DASHB_OK;
 }
@@ -962,14 +1116,66 @@ static int copy_out(dashb_circuit* c, const Tensor& t, int16_t* const* out) {
 int dashb_move_outputs(dashb_circuit* c, int16_t* const* out) {
     if (!c || !out) return fail(DASHB_EINVAL, "null argument");
     if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "nothing evaluated");
-    return copy_out(c, c->t_last, out);
+    return copy_out(c, out);
 }
 
+/* cuda_move_inputs + cuda_evaluate + cuda_move_outputs as one pipelined
+ * pass: every lane copies its slice in, runs all layers and copies its
+ * outputs back on its own stream. */
 int dashb_evaluate(dashb_circuit* c, const int16_t* const* in, uint64_t batch, int16_t* const* out) {
-    int rc = dashb_move_inputs(c, in, batch);
+    if (!c || !in || !out) return fail(DASHB_EINVAL, "null argument");
+    if (!c->finalized) return fail(DASHB_ESTATE, "circuit not finalized");
+    if (c->timing) { /* serialised, per-layer events */
+        int rc = dashb_move_inputs(c, in, batch);
+        if (rc) return rc;
+        if ((rc = dashb_evaluate_device(c))) return rc;
+        return dashb_move_outputs(c, out);
+    }
+    for (int j = 0; j < c->k; ++j)
+        if (!in[j] || !out[j]) return fail(DASHB_EINVAL, "label buffer %d missing", j);
+    int rc = split_batch(c, batch);
     if (rc) return rc;
-    if ((rc = dashb_evaluate_device(c))) return rc;
-    return dashb_move_outputs(c, out);
+    c->launches = 0;
+    static const bool trace = getenv("DASHB_TRACE") != nullptr;
+    cudaEvent_t tr[1 + 3 * 16];
+    if (trace) {
+        for (auto& e : tr) cudaEventCreate(&e);
+        cudaEventRecord(tr[0], g_stream);
+    }
+    if ((rc = fork_lanes(c))) return rc;
+    for (int i = 0; i < c->lanes_used; ++i) {
+        /* all H2D copies go through one copy stream, lane after lane, so that
+         * lane i-1 computes while lane i still transfers */
+        if ((rc = enqueue_inputs(c, *c->lanes[i], in, c->copy_s, c->lanes[i]->s))) return rc;
+        if (trace) cudaEventRecord(tr[1 + 3 * i], c->lanes[i]->s);
+    }
+    const int nl = (int)c->layers.size();
+    for (int li = 0; li < nl; ++li)
+        for (int i = 0; i < c->lanes_used; ++i) {
+            if ((rc = run_layer(c, *c->lanes[i], li, c->lanes[i]->s))) return rc;
+            if (trace && li == nl - 1) cudaEventRecord(tr[2 + 3 * i], c->lanes[i]->s);
+        }
+    if (nl > 0) {
+        c->out_n = c->layers[nl - 1]->out_size;
+        for (int j = 0; j < c->k; ++j) c->out_q[j] = c->layers[nl - 1]->out_q[j];
+    }
+    for (int i = 0; i < c->lanes_used; ++i) {
+        if ((rc = enqueue_outputs(c, *c->lanes[i], out, c->lanes[i]->s))) return rc;
+        if (trace) cudaEventRecord(tr[3 + 3 * i], c->lanes[i]->s);
+    }
+    if ((rc = join_lanes(c))) return rc;
+    CU(cudaStreamSynchronize(g_stream));
+    if (trace) {
+        for (int i = 0; i < c->lanes_used; ++i) {
+            float a = 0, b = 0, d = 0;
+            cudaEventElapsedTime(&a, tr[0], tr[1 + 3 * i]);
+            cudaEventElapsedTime(&b, tr[0], tr[2 + 3 * i]);
+            cudaEventElapsedTime(&d, tr[0], tr[3 + 3 * i]);
+            fprintf(stderr, "[dashb trace] lane %d: inputs done %.2f ms, layers done %.2f ms, outputs done %.2f ms\n", i, a, b, d);
+        }
+        for (auto& e : tr) cudaEventDestroy(e);
+    }
+    return DASHB_OK;
 }
 
 int dashb_layer_outputs(dashb_circuit* c, int layer, int16_t* const* out) {
@@ -981,7 +1187,7 @@ int dashb_layer_outputs(dashb_circuit* c, int layer, int16_t* const* out) {
     int rc = run_layers(c, layer);
     c->timing = t;
     if (rc) return rc;
-    return copy_out(c, c->t_last, out);
+    return copy_out(c, out);
 }
 
 int dashb_decode_outputs(dashb_circuit* c, int64_t* values, uint8_t* ok) {
@@ -989,13 +1195,11 @@ int dashb_decode_outputs(dashb_circuit* c, int64_t* values, uint8_t* ok) {
     if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "nothing evaluated");
     if (!c->has_dec) return fail(DASHB_ESTATE, "no decoding information");
     for (int j = 0; j < c->k; ++j)
-        if (c->t_last.q[j] != c->crt[j]) return fail(DASHB_EINVAL, "outputs are not in the CRT base");
+        if (c->out_q[j] != c->crt[j]) return fail(DASHB_EINVAL, "outputs are not in the CRT base");
     DecodeParams p;
     memset(&p, 0, sizeof(p));
     p.k = c->k;
-    p.n = c->t_last.n;
-    p.batch = c->batch;
-    p.Bp = c->Bp;
+    p.n = c->out_n;
     /* util::chinese_remainder accumulates `prod` in an int (misc/util.h:123) */
     int prod_i = 1;
     long long crt_modulus = 1;
@@ -1007,18 +1211,23 @@ int dashb_decode_outputs(dashb_circuit* c, int64_t* values, uint8_t* ok) {
     p.prod = prod_i;
     p.crt_modulus = crt_modulus;
     for (int j = 0; j < c->k; ++j) {
-        p.in[j] = c->t_last.plane[j];
         p.crt[j] = c->crt_mi[j];
         p.dec[j] = (const u128*)c->dec[j].p;
         p.pdiv[j] = prod_i / c->crt[j];
         p.inv[j] = (int64_t)(mul_inv((unsigned __int128)p.pdiv[j], (uint16_t)c->crt[j]) % (uint64_t)prod_i);
     }
-    p.values = (int64_t*)c->d_values.p;
-    p.ok = (uint8_t*)c->d_ok.p;
-    CU(cudaMemsetAsync(p.ok, 1, c->batch, g_stream));
-    CU(launch_decode(p, g_stream));
-    CU(cudaMemcpyAsync(values, p.values, (size_t)c->batch * p.n * 8, cudaMemcpyDeviceToHost, g_stream));
-    if (ok) CU(cudaMemcpyAsync(ok, p.ok, c->batch, cudaMemcpyDeviceToHost, g_stream));
+    CU(cudaMemsetAsync(c->d_ok.p, 1, c->batch, g_stream));
+    for (int i = 0; i < c->lanes_used; ++i) {
+        Lane& ln = *c->lanes[i];
+        for (int j = 0; j < c->k; ++j) p.in[j] = ln.t_cur.plane[j];
+        p.batch = ln.batch;
+        p.Bp = ln.Bp;
+        p.values = (int64_t*)c->d_values.p + (size_t)ln.b0 * p.n;
+        p.ok = (uint8_t*)c->d_ok.p + ln.b0;
+        CU(launch_decode(p, g_stream));
+    }
+    CU(cudaMemcpyAsync(values, c->d_values.p, (size_t)c->batch * p.n * 8, cudaMemcpyDeviceToHost, g_stream));
+    if (ok) CU(cudaMemcpyAsync(ok, c->d_ok.p, c->batch, cudaMemcpyDeviceToHost, g_stream));
     CU(cudaStreamSynchronize(g_stream));
     return DASHB_OK;
 }
