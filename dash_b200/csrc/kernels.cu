@@ -263,7 +263,9 @@ constexpr int LIN_THREADS = 128;
 constexpr int LIN_ROWS = 8;
 constexpr int LIN_KC = 1024; /* taps staged in shared memory per chunk */
 
-__global__ void __launch_bounds__(LIN_THREADS) k_linear(const __grid_constant__ LinearParams P) {
+constexpr int LIN_PIXC = 4; /* output pixels a CTA walks through with one staging of the weights */
+
+__global__ void __launch_bounds__(LIN_THREADS, 8) k_linear(const __grid_constant__ LinearParams P) {
     __shared__ uint4 s_w[LIN_KC / 4][2];  /* [k/4][8 rows] packed weights */
     __shared__ int32_t s_koff[LIN_KC];
     const int j = blockIdx.z;
@@ -272,61 +274,82 @@ __global__ void __launch_bounds__(LIN_THREADS) k_linear(const __grid_constant__ 
     const uint32_t col = (blockIdx.x * LIN_THREADS + threadIdx.x) * 4;
     const uint32_t nvg = (P.M + LIN_ROWS - 1) / LIN_ROWS;
     const uint32_t vg = blockIdx.y % nvg;
-    const uint32_t pix = blockIdx.y / nvg;
-    const uint64_t base = (uint64_t)(pix / P.ow) * P.step_y + (uint64_t)(pix % P.ow) * P.step_x;
+    const uint32_t pix0 = (blockIdx.y / nvg) * LIN_PIXC;
+    const uint32_t pix1 = min(pix0 + LIN_PIXC, P.npix);
     const uint64_t rowlen = ncols;
     const bool active = col < ncols;
-    const uint8_t* in = P.in[j] + base * rowlen + col;
-
-    uint32_t acc[LIN_ROWS][4];
-#pragma unroll
-    for (int r = 0; r < LIN_ROWS; ++r)
-#pragma unroll
-        for (int c = 0; c < 4; ++c) acc[r][c] = 0;
-
     const uint32_t k4_total = P.Kp / 4;
-    for (uint32_t k4_0 = 0; k4_0 < k4_total; k4_0 += LIN_KC / 4) {
-        const uint32_t k4_n = min((uint32_t)(LIN_KC / 4), k4_total - k4_0);
-        __syncthreads();
-        const uint4* wsrc = reinterpret_cast<const uint4*>(P.w4[j]) + ((uint64_t)vg * k4_total + k4_0) * 2;
-        for (uint32_t i = threadIdx.x; i < k4_n * 2; i += LIN_THREADS) (&s_w[0][0])[i] = __ldg(wsrc + i);
-        for (uint32_t i = threadIdx.x; i < k4_n * 4; i += LIN_THREADS) s_koff[i] = __ldg(P.koff + k4_0 * 4 + i);
-        __syncthreads();
-        if (!active) continue;
-        for (uint32_t kk = 0; kk < k4_n; ++kk) {
-            const uint32_t x0 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 0] * rowlen));
-            const uint32_t x1 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 1] * rowlen));
-            const uint32_t x2 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 2] * rowlen));
-            const uint32_t x3 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 3] * rowlen));
-            /* 4x4 byte transpose: y_c = (x0.c, x1.c, x2.c, x3.c) */
-            const uint32_t t0 = __byte_perm(x0, x1, 0x5140), t1 = __byte_perm(x0, x1, 0x7362);
-            const uint32_t u0 = __byte_perm(x2, x3, 0x5140), u1 = __byte_perm(x2, x3, 0x7362);
-            const uint32_t y0 = __byte_perm(t0, u0, 0x5410), y1 = __byte_perm(t0, u0, 0x7632);
-            const uint32_t y2 = __byte_perm(t1, u1, 0x5410), y3 = __byte_perm(t1, u1, 0x7632);
-            const uint4 wa = s_w[kk][0], wb = s_w[kk][1];
-            const uint32_t w[LIN_ROWS] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
-#pragma unroll
-            for (int r = 0; r < LIN_ROWS; ++r) {
-                acc[r][0] = __dp4a(y0, w[r], acc[r][0]);
-                acc[r][1] = __dp4a(y1, w[r], acc[r][1]);
-                acc[r][2] = __dp4a(y2, w[r], acc[r][2]);
-                acc[r][3] = __dp4a(y3, w[r], acc[r][3]);
-            }
-        }
-    }
-    if (!active) return;
+    const bool one_chunk = k4_total <= LIN_KC / 4;
     /* the thread's 4 columns are digits 4*d4 .. 4*d4+3 of one inference */
     const uint32_t d4 = col / (4 * P.Bp);
     const uint32_t nc4 = (m.nc + 3) >> 2;
+
+    auto stage = [&](uint32_t k4_0, uint32_t k4_n) {
+        const uint4* wsrc = reinterpret_cast<const uint4*>(P.w4[j]) + ((uint64_t)vg * k4_total + k4_0) * 2;
+        for (uint32_t i = threadIdx.x; i < k4_n * 2; i += LIN_THREADS) (&s_w[0][0])[i] = __ldg(wsrc + i);
+        for (uint32_t i = threadIdx.x; i < k4_n * 4; i += LIN_THREADS) s_koff[i] = __ldg(P.koff + k4_0 * 4 + i);
+    };
+    if (one_chunk) {
+        stage(0, k4_total);
+        __syncthreads();
+    }
+    for (uint32_t pix = pix0; pix < pix1; ++pix) {
+        const uint64_t base = (uint64_t)(pix / P.ow) * P.step_y + (uint64_t)(pix % P.ow) * P.step_x;
+        const uint8_t* in = P.in[j] + base * rowlen + col;
+        uint32_t acc[LIN_ROWS][4];
 #pragma unroll
-    for (int r = 0; r < LIN_ROWS; ++r) {
-        const uint32_t v = vg * LIN_ROWS + r;
-        if (v >= P.M) break;
-        const uint32_t cst = __ldg(reinterpret_cast<const uint32_t*>(P.cst[j]) + (uint64_t)v * nc4 + d4);
-        uint32_t o = 0;
+        for (int r = 0; r < LIN_ROWS; ++r)
 #pragma unroll
-        for (int c = 0; c < 4; ++c) o |= ((acc[r][c] + ((cst >> (8 * c)) & 0xff)) % m.q) << (8 * c);
-        *reinterpret_cast<uint32_t*>(P.out[j] + ((uint64_t)v * P.npix + pix) * rowlen + col) = o;
+            for (int c = 0; c < 4; ++c) acc[r][c] = 0;
+
+        for (uint32_t k4_0 = 0; k4_0 < k4_total; k4_0 += LIN_KC / 4) {
+            const uint32_t k4_n = min((uint32_t)(LIN_KC / 4), k4_total - k4_0);
+            if (!one_chunk) {
+                __syncthreads();
+                stage(k4_0, k4_n);
+                __syncthreads();
+            }
+            if (!active) continue;
+#pragma unroll 1
+            for (uint32_t kk = 0; kk < k4_n; ++kk) {
+                const uint32_t x0 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 0] * rowlen));
+                const uint32_t x1 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 1] * rowlen));
+                const uint32_t x2 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 2] * rowlen));
+                const uint32_t x3 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 3] * rowlen));
+                /* 4x4 byte transpose: y_c = (x0.c, x1.c, x2.c, x3.c) */
+                const uint32_t t0 = __byte_perm(x0, x1, 0x5140), t1 = __byte_perm(x0, x1, 0x7362);
+                const uint32_t u0 = __byte_perm(x2, x3, 0x5140), u1 = __byte_perm(x2, x3, 0x7362);
+                const uint32_t y0 = __byte_perm(t0, u0, 0x5410), y1 = __byte_perm(t0, u0, 0x7632);
+                const uint32_t y2 = __byte_perm(t1, u1, 0x5410), y3 = __byte_perm(t1, u1, 0x7632);
+                const uint4 wa = s_w[kk][0], wb = s_w[kk][1];
+                const uint32_t w[LIN_ROWS] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+                for (int r = 0; r < LIN_ROWS; ++r) {
+                    acc[r][0] = __dp4a(y0, w[r], acc[r][0]);
+                    acc[r][1] = __dp4a(y1, w[r], acc[r][1]);
+                    acc[r][2] = __dp4a(y2, w[r], acc[r][2]);
+                    acc[r][3] = __dp4a(y3, w[r], acc[r][3]);
+                }
+            }
+        }
+        if (!active) continue;
+#pragma unroll
+        for (int r = 0; r < LIN_ROWS; ++r) {
+            const uint32_t v = vg * LIN_ROWS + r;
+            if (v >= P.M) break;
+            const uint32_t cst = __ldg(reinterpret_cast<const uint32_t*>(P.cst[j]) + (uint64_t)v * nc4 + d4);
+            uint32_t o = 0;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                /* x mod q for any 32-bit x: the reciprocal over-estimates the
+                 * quotient by at most one */
+                uint32_t x = acc[r][c] + ((cst >> (8 * c)) & 0xff);
+                x -= gc::mulhi32(x, m.mq) * m.q;
+                if ((int32_t)x < 0) x += m.q;
+                o |= x << (8 * c);
+            }
+            *reinterpret_cast<uint32_t*>(P.out[j] + ((uint64_t)v * P.npix + pix) * rowlen + col) = o;
+        }
     }
 }
 
@@ -334,7 +357,7 @@ cudaError_t launch_linear(const LinearParams& p, cudaStream_t s) {
     uint32_t max_cols = 0;
     for (int j = 0; j < p.k; ++j) max_cols = max(max_cols, ((p.mod[j].nc + 3) & ~3u) * p.Bp);
     const uint32_t nvg = (p.M + LIN_ROWS - 1) / LIN_ROWS;
-    dim3 grid((max_cols / 4 + LIN_THREADS - 1) / LIN_THREADS, p.npix * nvg, p.k);
+    dim3 grid((max_cols / 4 + LIN_THREADS - 1) / LIN_THREADS, ((p.npix + LIN_PIXC - 1) / LIN_PIXC) * nvg, p.k);
     k_linear<<<grid, LIN_THREADS, 0, s>>>(p);
     return cudaGetLastError();
 }
