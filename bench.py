@@ -71,6 +71,7 @@ def build_material(model, n_inputs, want_ref=False):
         labels = [np.stack([p[j] for p in per]) for j in range(ref.k)]
         np.savez(npz + ".tmp.npz", x=X, **{"in%d" % j: labels[j] for j in range(ref.k)})
         os.replace(npz + ".tmp.npz", npz)
+    build_material.x = np.load(npz)["x"][:n_inputs]
     return gcm, [l[:n_inputs] for l in labels], ref
 
 
@@ -246,12 +247,27 @@ def main():
             ms = float(t.item())
         return ms
 
+    # plaintext values in -> decoded values out (garble_inputs + evaluate +
+    # decode_outputs all on the device): the reference user's whole call chain
+    xs = torch.empty((B, circ.input_size), dtype=torch.int64).pin_memory()
+    xs.numpy()[...] = build_material.x[:B]
+    vals_t = torch.empty((B, circ.output_size), dtype=torch.int64).pin_memory()
+    ok_t = torch.empty((B,), dtype=torch.uint8).pin_memory()
+
+    def step_values():
+        api._check(L.dashb_garble_inputs(circ.h, xs.data_ptr(), B))
+        api._check(L.dashb_evaluate_device(circ.h))
+        api._check(L.dashb_decode_outputs(circ.h, vals_t.data_ptr(), ok_t.data_ptr()))
+
     sampler = ClockSampler(local_rank)
     sampler.start()
     time.sleep(0.2)
     ms_dev = timed(step_device, args.steps, args.warmup)
     launches = circ.launch_count()
     ms_e2e = timed(step_e2e, args.steps, args.warmup)
+    ms_val = timed(step_values, args.steps, args.warmup)
+    values_ok = bool(ok_t.numpy().all())
+    circ.move_inputs(in_np)  # restore the label inputs for the profiling pass
     # per-kernel durations for the roofline: same steps with the sub-batch
     # lanes serialised on one stream and a CUDA event pair around every layer
     circ.set_layer_timing(True)
@@ -312,6 +328,10 @@ def main():
         "e2e": {"value": e2e_value, "unit": "inferences/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / args.steps,
                 "api": "dashb_evaluate (int16 LabelTensor layout in pinned host memory -> output labels)"},
+        "e2e_values": {"value": total_inf / (ms_val / 1e3), "unit": "inferences/s", "ms_per_step": ms_val / args.steps,
+                       "h2d_bytes_per_step": int(xs.numel() * 8), "d2h_bytes_per_step": int(vals_t.numel() * 8 + B),
+                       "all_outputs_decoded": values_ok,
+                       "api": "dashb_garble_inputs + dashb_evaluate_device + dashb_decode_outputs (int64 values in, int64 values out)"},
         "gpu_launches": int(launches * args.steps),
         "clocks": sampler.summary(),
         "roofline": roofline,

@@ -44,6 +44,7 @@ def lib():
         L.dashb_finalize.argtypes = [C.c_void_p, C.c_uint64]
         L.dashb_move_inputs.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
         L.dashb_evaluate_device.argtypes = [C.c_void_p]
+        L.dashb_garble_inputs.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
         L.dashb_move_outputs.argtypes = [C.c_void_p, C.c_void_p]
         L.dashb_evaluate.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.dashb_layer_outputs.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
@@ -144,6 +145,16 @@ class Circuit:
         _check(self.L.dashb_move_inputs(self.h, _ptr_array(labels), batch))
         self.batch = batch
         self._keep = labels
+
+    def garble_inputs(self, values):
+        """garble_inputs on the device: values int64 [batch][input_size]
+        (needs a material file that carries the garbler's input encoding)."""
+        v = np.ascontiguousarray(values, dtype=np.int64)
+        if v.ndim != 2 or v.shape[1] != self.input_size:
+            raise ValueError("values must be [batch][input_size]")
+        _check(self.L.dashb_garble_inputs(self.h, v.ctypes.data, v.shape[0]))
+        self.batch = v.shape[0]
+        self._keep = v
 
     def evaluate_device(self):
         _check(self.L.dashb_evaluate_device(self.h))

@@ -205,7 +205,7 @@ struct Layer {
 struct Lane {
     cudaStream_t s{nullptr};
     cudaEvent_t done{nullptr}, in_done{nullptr}, ing_done{nullptr};
-    DevMem buf_in, buf_a, buf_b, stage_in, stage_out;
+    DevMem buf_in, buf_a, buf_b, stage_in, stage_out, xvals;
     Tensor t_in, t_cur;
     int which{0};
     uint32_t b0{0}, batch{0}, Bp{0};
@@ -237,6 +237,8 @@ struct dashb_circuit {
     cudaStream_t ingest_s{nullptr}; /* its ingest kernels (highest priority) */
     DevMem dec[MAXK];
     bool has_dec{false};
+    DevMem in_base[MAXK], in_off[MAXK];
+    bool has_ginp{false};
     DevMem d_values, d_ok;
     uint64_t out_n{0};   /* labels per inference in the lanes' current tensors */
     int out_q[MAXK];     /* their moduli */
@@ -770,6 +772,25 @@ int dashb_set_decoding_info(dashb_circuit* c, const dashb_u128* const* dec) {
     return DASHB_OK;
 }
 
+int dashb_set_input_encoding(dashb_circuit* c, const int16_t* const* base_labels,
+                             const int16_t* const* offset_labels) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if (!base_labels || !offset_labels) return fail(DASHB_EINVAL, "null argument");
+    for (int j = 0; j < c->k; ++j) {
+        if (!base_labels[j] || !offset_labels[j]) return fail(DASHB_EINVAL, "input encoding %d missing", j);
+        const uint32_t nc = c->crt_mi[j].nc, ncp = (nc + 3) & ~3u;
+        std::vector<uint8_t> b((size_t)c->input_size * ncp, 0);
+        for (uint64_t e = 0; e < c->input_size; ++e)
+            for (uint32_t d = 0; d < nc; ++d) b[e * ncp + d] = (uint8_t)base_labels[j][e * nc + d];
+        CU(c->in_base[j].upload(b.data(), b.size()));
+        auto o = to_u8(offset_labels[j], nc);
+        CU(c->in_off[j].upload(o.data(), o.size()));
+    }
+    c->has_ginp = true;
+    return DASHB_OK;
+}
+
 int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
     int rc = check_building(c);
     if (rc) return rc;
@@ -805,6 +826,7 @@ int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
         CU(ln->buf_b.alloc(act_bytes));
         CU(ln->stage_in.alloc(stage_in));
         CU(ln->stage_out.alloc(stage_out));
+        if (c->has_ginp) CU(ln->xvals.alloc((size_t)Bp * c->input_size * 8));
         CU(cudaMemset(ln->buf_in.p, 0, in_bytes));
         CU(cudaMemset(ln->buf_a.p, 0, act_bytes));
         CU(cudaMemset(ln->buf_b.p, 0, act_bytes));
@@ -910,6 +932,35 @@ int dashb_move_inputs(dashb_circuit* c, const int16_t* const* in, uint64_t batch
     if ((rc = fork_lanes(c))) return rc;
     for (int i = 0; i < c->lanes_used; ++i)
         if ((rc = enqueue_inputs(c, *c->lanes[i], in, c->lanes[i]->s, c->lanes[i]->s))) return rc;
+    return join_lanes(c);
+}
+
+int dashb_garble_inputs(dashb_circuit* c, const int64_t* values, uint64_t batch) {
+    if (!c || !values) return fail(DASHB_EINVAL, "null argument");
+    if (!c->finalized) return fail(DASHB_ESTATE, "circuit not finalized");
+    if (!c->has_ginp) return fail(DASHB_ESTATE, "no input encoding (dashb_set_input_encoding)");
+    int rc = split_batch(c, batch);
+    if (rc) return rc;
+    if ((rc = fork_lanes(c))) return rc;
+    for (int i = 0; i < c->lanes_used; ++i) {
+        Lane& ln = *c->lanes[i];
+        CU(cudaMemcpyAsync(ln.xvals.p, values + (size_t)ln.b0 * c->input_size, (size_t)ln.batch * c->input_size * 8,
+                           cudaMemcpyHostToDevice, ln.s));
+        GarbleInParams p;
+        memset(&p, 0, sizeof(p));
+        p.x = (const int64_t*)ln.xvals.p;
+        p.n = c->input_size;
+        p.batch = ln.batch;
+        p.Bp = ln.Bp;
+        p.k = c->k;
+        for (int j = 0; j < c->k; ++j) {
+            p.out[j] = ln.t_in.plane[j];
+            p.base[j] = (const uint8_t*)c->in_base[j].p;
+            p.off[j] = (const uint8_t*)c->in_off[j].p;
+            p.crt[j] = c->crt_mi[j];
+        }
+        CU(launch_garble_inputs(p, ln.s));
+    }
     return join_lanes(c);
 }
 

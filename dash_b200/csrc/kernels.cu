@@ -789,6 +789,47 @@ cudaError_t launch_add_label(const AddLabelParams& p, cudaStream_t s) {
     return cudaGetLastError();
 }
 
+/* ------------------------------------------------------ garble_inputs */
+/* GarbledCircuitInterface::garble_inputs (garbling/
+ * garbled_circuit_interface.h:325-343), batched and on the device:
+ * label_j[e] = (x[e] mod p_j) * R_{p_j} + base_j[e], digit-wise mod p_j
+ * (util::crt_reduce gives the non-negative residue, misc/util.h:143-156).
+ * One thread per (input, inference) and modulus; writes the plane words. */
+__global__ void __launch_bounds__(128) k_garble_inputs(const __grid_constant__ GarbleInParams P) {
+    const int j = blockIdx.y;
+    const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P.n * P.batch) return;
+    const uint32_t b = (uint32_t)(idx % P.batch);
+    const uint64_t e = idx / P.batch;
+    const ModInfo m = pin(P.crt[j]);
+    const int64_t q = (int64_t)m.q;
+    int64_t r64 = P.x[(uint64_t)b * P.n + e] % q;
+    if (r64 < 0) r64 += q;
+    const uint32_t r = (uint32_t)r64;
+    const uint32_t nc4 = nc4_of(m);
+    const uint32_t* base = reinterpret_cast<const uint32_t*>(P.base[j]) + e * nc4;
+    const uint32_t* off = reinterpret_cast<const uint32_t*>(P.off[j]);
+    uint8_t* out = P.out[j] + plane_off(m, e, b, P.Bp);
+    for (uint32_t d4 = 0; d4 < nc4; ++d4) {
+        const uint32_t bw = __ldg(base + d4), ow = __ldg(off + d4);
+        uint32_t w = 0;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+            const uint32_t d = 4 * d4 + t;
+            const uint32_t v = gc::mod_q(r * ((ow >> (8 * t)) & 0xff) + ((bw >> (8 * t)) & 0xff), m);
+            w |= (d < m.nc ? v : 0u) << (8 * t);
+        }
+        *reinterpret_cast<uint32_t*>(out + (uint64_t)d4 * 4 * P.Bp) = w;
+    }
+}
+
+cudaError_t launch_garble_inputs(const GarbleInParams& p, cudaStream_t s) {
+    const uint64_t total = p.n * p.batch;
+    dim3 grid((unsigned)((total + 127) / 128), p.k);
+    k_garble_inputs<<<grid, 128, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
 /* ------------------------------------------------------------- decode */
 /* decode_outputs (garbling/garbled_circuit_interface.h:422-467): hash each
  * output label, find the residue whose decoding hash matches, CRT-combine,

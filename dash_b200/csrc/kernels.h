@@ -101,6 +101,17 @@ struct AddLabelParams {
     int subtract;
 };
 
+struct GarbleInParams {
+    const int64_t* x;           /* [batch][n] plaintext inputs of this sub-batch */
+    uint8_t* out[MAXK];
+    const uint8_t* base[MAXK];  /* base labels u8 [n][4*nc4_j], zero padded */
+    const uint8_t* off[MAXK];   /* offset label R_{p_j} u8 [4*nc4_j] */
+    gc::ModInfo crt[MAXK];
+    uint64_t n;
+    uint32_t batch, Bp;
+    int k;
+};
+
 struct DecodeParams {
     const uint8_t* in[MAXK];
     gc::ModInfo crt[MAXK];
@@ -138,5 +149,6 @@ cudaError_t launch_projection(const ProjParams& p, cudaStream_t s);
 cudaError_t launch_rescale(const RescaleParams& p, cudaStream_t s);
 cudaError_t launch_add_label(const AddLabelParams& p, cudaStream_t s);
 cudaError_t launch_decode(const DecodeParams& p, cudaStream_t s);
+cudaError_t launch_garble_inputs(const GarbleInParams& p, cudaStream_t s);
 
 }  // namespace dashb

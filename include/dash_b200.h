@@ -200,6 +200,15 @@ int dashb_projection_static(const int16_t* d_in, const dashb_u128* d_ciphers, in
  * Optional; needed only for dashb_decode_outputs. */
 int dashb_set_decoding_info(dashb_circuit* c, const dashb_u128* const* dec);
 
+/* Garbler-side input encoding for deployments where the evaluating process
+ * also encodes the inputs (benchmarks, single-party tests): base_labels[j] =
+ * int16 [input_size][nc(p_j)] (get_base_label(),
+ * garbled_circuit_interface.h:771) and offset_labels[j] = int16 [nc(p_j)],
+ * the global offset R_{p_j} (get_label_offset, :762-767).  Optional; needed
+ * only for dashb_garble_inputs.  Call before dashb_finalize. */
+int dashb_set_input_encoding(dashb_circuit* c, const int16_t* const* base_labels,
+                             const int16_t* const* offset_labels);
+
 /* Uploads weights and tables, re-lays them for the kernels and sizes the
  * activation buffers for up to max_batch concurrent inferences. */
 int dashb_finalize(dashb_circuit* c, uint64_t max_batch);
@@ -210,6 +219,13 @@ int dashb_finalize(dashb_circuit* c, uint64_t max_batch);
  * in[j] = int16 [batch][input_size][nc(p_j)]. */
 int dashb_move_inputs(dashb_circuit* c, const int16_t* const* in,
                       uint64_t batch);
+/* garble_inputs (garbled_circuit_interface.h:325-343) on the device,
+ * batched: label_j[e] = (x[e] mod p_j) * R_{p_j} + base_j[e] digit-wise mod
+ * p_j, written straight into the input planes; values = host int64
+ * [batch][input_size].  Replaces garble_inputs + cuda_move_inputs: only
+ * 8 bytes per input value cross PCIe.  Needs dashb_set_input_encoding. */
+int dashb_garble_inputs(dashb_circuit* c, const int64_t* values, uint64_t batch);
+
 /* cuda_evaluate (garbled_circuit_interface.h:603-612): runs every layer on
  * the labels left by dashb_move_inputs; asynchronous on dashb_stream(). */
 int dashb_evaluate_device(dashb_circuit* c);

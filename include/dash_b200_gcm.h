@@ -127,6 +127,14 @@ static inline int dashb_circuit_from_gcm(const gcm_circuit* g, dashb_circuit** o
         for (int j = 0; j < k; ++j) dec[j] = (const dashb_u128*)g->dec[j].data;
         rc = dashb_set_decoding_info(c, dec);
     }
+    if (rc == DASHB_OK && g->has_ginp) {
+        const int16_t *base[32], *off[32];
+        for (int j = 0; j < k; ++j) {
+            base[j] = (const int16_t*)g->in_base[j].data;
+            off[j] = (const int16_t*)g->in_offset[j].data;
+        }
+        rc = dashb_set_input_encoding(c, base, off);
+    }
     if (rc != DASHB_OK) {
         dashb_circuit_destroy(c);
         *out = NULL;

@@ -13,7 +13,7 @@
  *
  * Section order: HEAD, ZERO, [UPSH], then per layer LAYR followed by its
  * ARRY sections in the fixed order listed at gcm_layer below, [DECI arrays],
- * ENDF.  All label arrays are int16 digits in the reference's
+ * [GINB/GINO arrays: the garbler-side input encoding, see gcm_circuit], ENDF.  All label arrays are int16 digits in the reference's
  * [label][digit] order; all ciphertext arrays are 16-byte little-endian
  * integers in the order the reference's garbler filled them (see
  * include/dash_b200.h for every table's layout and citation).
@@ -35,6 +35,8 @@
 #define GCM_TAG_LAYR GCM_TAG('L', 'A', 'Y', 'R')
 #define GCM_TAG_ARRY GCM_TAG('A', 'R', 'R', 'Y')
 #define GCM_TAG_DECI GCM_TAG('D', 'E', 'C', 'I')
+#define GCM_TAG_GINB GCM_TAG('G', 'I', 'N', 'B')
+#define GCM_TAG_GINO GCM_TAG('G', 'I', 'N', 'O')
 #define GCM_TAG_ENDF GCM_TAG('E', 'N', 'D', 'F')
 
 #define GCM_MAX_PARAMS 32
@@ -87,6 +89,12 @@ typedef struct gcm_circuit {
     gcm_layer* layers;
     int has_dec;
     gcm_array dec[32]; /* per CRT modulus u128 [p_j][output_size]           */
+    /* Garbler-side input encoding (garble_inputs,
+     * garbled_circuit_interface.h:325-343); optional -- an evaluator-only
+     * deployment never holds it. */
+    int has_ginp;
+    gcm_array in_base[32];   /* per CRT modulus int16 [input_size][nc(p_j)] */
+    gcm_array in_offset[32]; /* per CRT modulus int16 [nc(p_j)]: R_{p_j}    */
     int owns_data;     /* set by gcm_load: arrays are malloc'd              */
 } gcm_circuit;
 
@@ -134,6 +142,11 @@ static inline int gcm_save(const gcm_circuit* c, const char* path) {
     if (c->has_dec)
         for (int j = 0; j < c->k; ++j)
             rc |= gcm__wr(f, GCM_TAG_DECI, (uint32_t)j, c->dec[j].data, c->dec[j].nbytes);
+    if (c->has_ginp)
+        for (int j = 0; j < c->k; ++j) {
+            rc |= gcm__wr(f, GCM_TAG_GINB, (uint32_t)j, c->in_base[j].data, c->in_base[j].nbytes);
+            rc |= gcm__wr(f, GCM_TAG_GINO, (uint32_t)j, c->in_offset[j].data, c->in_offset[j].nbytes);
+        }
     rc |= gcm__wr(f, GCM_TAG_ENDF, 0, NULL, 0);
     if (fclose(f)) rc = -1;
     return rc;
@@ -162,7 +175,11 @@ static inline void gcm_free(gcm_circuit* c) {
         free((void*)c->upshift.data);
         for (int l = 0; l < c->n_layers; ++l)
             for (int a = 0; a < c->layers[l].n_arrays; ++a) free((void*)c->layers[l].a[a].data);
-        for (int j = 0; j < 32; ++j) free((void*)c->dec[j].data);
+        for (int j = 0; j < 32; ++j) {
+            free((void*)c->dec[j].data);
+            free((void*)c->in_base[j].data);
+            free((void*)c->in_offset[j].data);
+        }
     }
     free(c->layers);
     memset(c, 0, sizeof(*c));
@@ -238,6 +255,16 @@ static inline int gcm_load(gcm_circuit* c, const char* path) {
             } else {
                 c->dec[aux].data = p;
                 c->dec[aux].nbytes = n;
+            }
+        } else if (tag == GCM_TAG_GINB || tag == GCM_TAG_GINO) {
+            if (aux >= 32) {
+                rc = -1;
+                free(p);
+            } else {
+                gcm_array* a = tag == GCM_TAG_GINB ? &c->in_base[aux] : &c->in_offset[aux];
+                a->data = p;
+                a->nbytes = n;
+                c->has_ginp = 1;
             }
         } else if (tag == GCM_TAG_ENDF) {
             free(p);

@@ -272,6 +272,20 @@ inline void dash_view_from_circuit(GarbledCircuit* gc, DashMaterialView& v, bool
     }
 }
 
+/* Adds the garbler-side input encoding (base labels and offset labels) to the
+ * view, for deployments where the party that evaluates also encodes inputs
+ * (benchmarks, tests).  The arrays are borrowed from the circuit. */
+inline void dash_view_add_input_encoding(GarbledCircuit* gc, DashMaterialView& v) {
+    const size_t k = gc->get_crt_base().size();
+    v.c.has_ginp = 1;
+    for (size_t j = 0; j < k; ++j) {
+        auto* base = gc->get_base_label().at(j);
+        v.c.in_base[j] = dash_adapter_detail::arr(base->get_components(), base->size() * sizeof(crt_val_t));
+        LabelSlice off = gc->get_label_offset(gc->get_crt_base().at(j));
+        v.c.in_offset[j] = dash_adapter_detail::arr(off.get_components(), off.get_nr_comps() * sizeof(crt_val_t));
+    }
+}
+
 inline int dash_view_save(const DashMaterialView& v, const char* path) {
     gcm_circuit c = v.c;
     c.layers = const_cast<gcm_layer*>(v.layers.data());

@@ -22,8 +22,11 @@ def build():
 def lib():
     global _lib
     if _lib is None:
-        if not os.path.exists(ORACLE_SO):
+        try:  # make is a no-op when the library is newer than its sources
             build()
+        except Exception:
+            if not os.path.exists(ORACLE_SO):
+                raise
         L = C.CDLL(ORACLE_SO)
         L.oracle_load.restype = C.c_void_p
         L.oracle_load.argtypes = [C.c_char_p]

@@ -216,6 +216,7 @@ int ref_export(void* hv, const char* path) {
     try {
         DashMaterialView v;
         dash_view_from_circuit(h->gc, v);
+        dash_view_add_input_encoding(h->gc, v);
         return dash_view_save(v, path);
     } catch (const std::exception& e) {
         h->err = e.what();

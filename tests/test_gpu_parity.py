@@ -100,3 +100,22 @@ def test_full_size_model_b_batch_256(gpu, tmp_path):
     sub = c.evaluate([l[:37].copy() for l in labels])
     assert_labels_equal(sub, [g[:37] for g in got], "ragged batch 37")
     c.close()
+
+
+@pytest.mark.parametrize("name", ["MLP_TINY", "CONV_UNIT", "RESCALE_2_3", "RELU_EDGE"])
+@pytest.mark.parametrize("batch", [3, 70])
+def test_device_garble_inputs(gpu, name, batch):
+    """garble_inputs on the device (garbled_circuit_interface.h:325-343):
+    plaintext inputs -> labels -> evaluation gives the same output labels and
+    decoded values as feeding the reference's own input labels."""
+    g = Golden(name)
+    c = gpu.Circuit.load(g.gcm, max_batch=batch)
+    x = tile_batch([g.x], batch)[0]
+    c.garble_inputs(x)
+    c.evaluate_device()
+    got = c.move_outputs()
+    assert_labels_equal(got, tile_batch(g.layers[-1], batch), "%s via device garble_inputs" % name)
+    if g.dec is not None:
+        vals, ok = c.decode_outputs()
+        assert ok.all() and np.array_equal(vals, tile_batch([g.dec], batch)[0])
+    c.close()
