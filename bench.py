@@ -304,10 +304,18 @@ def main():
     by_type = {}
     for name, ms in layer_ms:
         by_type[name] = by_type.get(name, 0.0) + ms
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    if os.path.exists(tpath) and args.model == "MODEL_B_POOL_REPL" and B == 256:
+        tj = json.load(open(tpath))
+        traffic = tj["k_sign_relu_dram_bytes_per_step"] / tj["k_sign_relu_launches_per_step"]
+    n_lanes = 4 if B >= 128 else (2 if B >= 64 else 1)
+    n_lanes = int(os.environ.get("DASHB_LANES", n_lanes))
     roofline = {
         "bound": "hbm", "kernel": "k_sign<relu> (fused sign gadget + half gates)", "achieved": achieved, "peak": peak,
-        "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-        "launches_per_step": len(relu_layers) * circ.L.dashb_num_lanes(circ.h) if hasattr(circ.L, "dashb_num_lanes") else len(relu_layers),
+        "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+        "algorithmic_bytes_per_launch": relu_bytes / max(1, len(relu_layers) * n_lanes),
+        "launches_per_step": len(relu_layers) * n_lanes,
         "avg_layer_ms": relu_ms / max(1, len(relu_layers)),
         "timing": "CUDA events around every layer, sub-batch lanes serialised on the library stream, %d steps after the timed region" % prof_steps,
         "share_of_step": relu_ms / step_ms if step_ms else None,
