@@ -59,6 +59,10 @@ def lib():
         for f in (L.dashb_algorithmic_bytes, L.dashb_aes_blocks, L.dashb_reference_aes_blocks):
             f.restype = C.c_double
             f.argtypes = [C.c_void_p, C.c_int]
+        L.dashb_set_shard.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.dashb_evaluate_layers.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.dashb_current_plane.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.dashb_layer_slice.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.dashb_set_layer_timing.argtypes = [C.c_void_p, C.c_int]
         L.dashb_layer_time_ms.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float)]
         L.dashb_circuit_destroy.argtypes = [C.c_void_p]
@@ -111,13 +115,38 @@ class Circuit:
         self.in_moduli = None
 
     @classmethod
-    def load(cls, path, max_batch=1):
-        """Reads a DGCM material file and moves the circuit to the device."""
+    def load(cls, path, max_batch=1, shard=None):
+        """Reads a DGCM material file and moves the circuit to the device.
+        shard=(rank, world) makes it one rank of an output-channel-sharded
+        evaluation (see dash_b200.scheduler.ChannelShardedEvaluator)."""
         L = lib()
         h = C.c_void_p()
         _check(L.dashb_circuit_load(C.byref(h), os.fsencode(path)))
+        if shard is not None:
+            _check(L.dashb_set_shard(h, int(shard[0]), int(shard[1])))
         _check(L.dashb_finalize(h, int(max_batch)))
         return cls(h, max_batch)
+
+    # ---- channel sharding -------------------------------------------------
+    def evaluate_layers(self, first, last):
+        _check(self.L.dashb_evaluate_layers(self.h, int(first), int(last)))
+
+    def current_plane(self, j):
+        """(device pointer, bytes per element, elements) of plane j of the
+        tensor the last evaluated layer produced."""
+        ptr, bpe, n = C.c_void_p(), C.c_uint64(), C.c_uint64()
+        _check(self.L.dashb_current_plane(self.h, j, C.byref(ptr), C.byref(bpe), C.byref(n)))
+        return ptr.value, bpe.value, n.value
+
+    def layer_slice(self, layer, rank):
+        e0, e1 = C.c_uint64(), C.c_uint64()
+        _check(self.L.dashb_layer_slice(self.h, layer, rank, C.byref(e0), C.byref(e1)))
+        return e0.value, e1.value
+
+    def sync(self):
+        import torch
+
+        torch.cuda.ExternalStream(stream_handle()).synchronize()
 
     def close(self):
         if self.h:

@@ -193,6 +193,9 @@ struct Layer {
     /* projection */
     int in_q[MAXK];
     DevMem proj[MAXK];
+    /* channel sharding: output elements [e0, e1) / linear rows [v0, v1) of this rank */
+    uint64_t e0{0}, e1{0};
+    uint32_t v0{0}, v1{0};
     /* accounting */
     double label_bytes{0}, weight_bytes{0}, aes{0}, ref_aes{0};
     float ms{0};
@@ -231,6 +234,7 @@ struct dashb_circuit {
     uint32_t batch{0};
     std::vector<std::unique_ptr<Lane>> lanes;
     int lanes_used{0};
+    int shard_rank{0}, shard_world{1};
     uint32_t lane_cap{0};
     cudaEvent_t ev_fork{nullptr};
     cudaStream_t copy_s{nullptr};   /* H2D copies of the pipelined dashb_evaluate */
@@ -791,15 +795,54 @@ int dashb_set_input_encoding(dashb_circuit* c, const int16_t* const* base_labels
     return DASHB_OK;
 }
 
+/* Output slice of `rank` for every layer: a linear layer splits its rows
+ * (dense rows / conv filters) evenly, the element-wise layers after it keep
+ * the same elements. */
+static void layer_slice(const dashb_circuit* c, int layer, int rank, uint64_t* e0, uint64_t* e1, uint32_t* v0, uint32_t* v1) {
+    const int W = c->shard_world;
+    uint64_t a = 0, b = 0;
+    uint32_t r0 = 0, r1 = 0;
+    for (int li = 0; li <= layer; ++li) {
+        const Layer& L = *c->layers[li];
+        if (L.type == DASHB_LAYER_DENSE || L.type == DASHB_LAYER_CONV2D) {
+            r0 = (uint32_t)(L.M * (uint64_t)rank / W);
+            r1 = (uint32_t)(L.M * (uint64_t)(rank + 1) / W);
+            a = (uint64_t)r0 * L.npix;
+            b = (uint64_t)r1 * L.npix;
+        } else if (li == 0) {
+            a = L.in_size * (uint64_t)rank / W;
+            b = L.in_size * (uint64_t)(rank + 1) / W;
+        }
+    }
+    *e0 = a;
+    *e1 = b;
+    *v0 = r0;
+    *v1 = r1;
+}
+
+int dashb_set_shard(dashb_circuit* c, int rank, int world) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if (world < 1 || rank < 0 || rank >= world) return fail(DASHB_EINVAL, "bad shard %d of %d", rank, world);
+    c->shard_rank = rank;
+    c->shard_world = world;
+    return DASHB_OK;
+}
+
 int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
     int rc = check_building(c);
     if (rc) return rc;
     if (max_batch == 0 || max_batch > (1u << 24)) return fail(DASHB_EINVAL, "bad max_batch");
     c->max_batch = max_batch;
+    for (int li = 0; li < (int)c->layers.size(); ++li) {
+        Layer& L = *c->layers[li];
+        layer_slice(c, li, c->shard_rank, &L.e0, &L.e1, &L.v0, &L.v1);
+    }
     int n_lanes = max_batch >= 128 ? 4 : (max_batch >= 64 ? 2 : 1);
+    if (c->shard_world > 1) n_lanes = 1; /* the channel-sharded path exchanges whole planes */
     if (const char* env = getenv("DASHB_LANES")) {
         int v = atoi(env);
-        if (v >= 1 && v <= 16) n_lanes = v;
+        if (v >= 1 && v <= 16 && c->shard_world == 1) n_lanes = v;
     }
     c->lane_cap = (uint32_t)((((max_batch + n_lanes - 1) / n_lanes) + 15) & ~15ull);
     const uint32_t Bp = c->lane_cap;
@@ -988,6 +1031,8 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
             }
             p.koff = (const int32_t*)L.koff.p;
             p.M = (uint32_t)L.M;
+            p.v0 = L.v0;
+            p.v1 = L.v1;
             p.K = (uint32_t)L.K;
             p.Kp = L.Kp;
             p.npix = L.npix;
@@ -1003,7 +1048,8 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
         case DASHB_LAYER_SIGN: {
             const bool relu = L.type == DASHB_LAYER_RELU;
             SignParams p;
-            fill_sign_params(c, p, L.in_size, relu ? 1 : c->k);
+            fill_sign_params(c, p, L.e1 - L.e0, relu ? 1 : c->k);
+            p.e0 = L.e0;
             for (int j = 0; j < c->k; ++j) {
                 p.in[j] = cur.plane[j];
                 p.out[j] = out.plane[j];
@@ -1036,6 +1082,8 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
                 }
                 p.tm = (const u128*)(legacy ? L.it_tables[5 * it]->p : L.tm.p);
                 p.be = (const u128*)L.be.p;
+                p.e0 = L.e0;
+                p.n = L.e1 - L.e0;
                 p.batch = B;
                 p.Bp = Bp;
                 CU(launch_rescale(p, s));
@@ -1043,7 +1091,8 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
                 if (legacy) {
                     /* base extension by sign gadget: regenerates residue 0 in place */
                     SignParams sp;
-                    fill_sign_params(c, sp, L.in_size, 1);
+                    fill_sign_params(c, sp, L.e1 - L.e0, 1);
+                    sp.e0 = L.e0;
                     for (int j = 0; j < c->k; ++j) sp.in[j] = out.plane[j];
                     sp.out[0] = out.plane[0];
                     sp.outm[0] = c->crt_mi[0];
@@ -1057,7 +1106,8 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
                     AddLabelParams ap;
                     memset(&ap, 0, sizeof(ap));
                     ap.k = c->k;
-                    ap.n = L.in_size;
+                    ap.n = L.e1 - L.e0;
+                    ap.e0 = L.e0;
                     ap.Bp = Bp;
                     ap.subtract = 1;
                     for (int j = 0; j < c->k; ++j) {
@@ -1075,7 +1125,8 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
             ProjParams p;
             memset(&p, 0, sizeof(p));
             p.k = c->k;
-            p.n = L.in_size;
+            p.n = L.e1 - L.e0;
+            p.e0 = L.e0;
             p.batch = B;
             p.Bp = Bp;
             for (int j = 0; j < c->k; ++j) {
@@ -1126,9 +1177,54 @@ static int run_layers(dashb_circuit* c, int upto) {
     return DASHB_OK;
 }
 
+/* Channel-sharded evaluation: layers first..last on this rank's slices,
+ * continuing from the current tensors (first == 0 restarts from the inputs).
+ * The caller gathers the slices of all ranks (dashb_current_plane) before a
+ * layer that needs every input element. */
+int dashb_evaluate_layers(dashb_circuit* c, int first, int last) {
+    if (!c) return fail(DASHB_EINVAL, "null circuit");
+    if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "no inputs moved");
+    if (first < 0 || last < first || last >= (int)c->layers.size()) return fail(DASHB_EINVAL, "bad layer range");
+    if (c->lanes_used != 1) return fail(DASHB_ESTATE, "dashb_evaluate_layers needs a single lane (sharded circuit or DASHB_LANES=1)");
+    Lane& ln = *c->lanes[0];
+    if (first == 0) {
+        ln.t_cur = ln.t_in;
+        ln.which = 0;
+        c->launches = 0;
+    }
+    for (int li = first; li <= last; ++li) {
+        int rc = run_layer(c, ln, li, g_stream);
+        if (rc) return rc;
+    }
+    c->out_n = c->layers[last]->out_size;
+    for (int j = 0; j < c->k; ++j) c->out_q[j] = c->layers[last]->out_q[j];
+    return DASHB_OK;
+}
+
+int dashb_current_plane(dashb_circuit* c, int j, void** dev_ptr, uint64_t* bytes_per_element, uint64_t* n_elements) {
+    if (!c || !dev_ptr || !bytes_per_element || !n_elements) return fail(DASHB_EINVAL, "null argument");
+    if (!c->finalized || c->batch == 0 || c->lanes_used != 1) return fail(DASHB_ESTATE, "no single-lane evaluation in flight");
+    if (j < 0 || j >= c->k) return fail(DASHB_EINVAL, "bad modulus index");
+    Lane& ln = *c->lanes[0];
+    *dev_ptr = ln.t_cur.plane[j];
+    *bytes_per_element = (uint64_t)((nr_comps(ln.t_cur.q[j]) + 3) & ~3) * ln.Bp;
+    *n_elements = ln.t_cur.n;
+    return DASHB_OK;
+}
+
+int dashb_layer_slice(const dashb_circuit* c, int layer, int rank, uint64_t* e0, uint64_t* e1) {
+    if (!c || !e0 || !e1 || layer < 0 || layer >= (int)c->layers.size() || rank < 0 || rank >= c->shard_world)
+        return fail(DASHB_EINVAL, "bad argument");
+    uint32_t v0, v1;
+    layer_slice(c, layer, rank, e0, e1, &v0, &v1);
+    return DASHB_OK;
+}
+
 int dashb_evaluate_device(dashb_circuit* c) {
     if (!c) return fail(DASHB_EINVAL, "null circuit");
     if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "no inputs moved");
+    if (c->shard_world > 1)
+        return fail(DASHB_ESTATE, "channel-sharded circuit: use dashb_evaluate_layers and gather between layer groups");
     int rc = run_layers(c, (int)c->layers.size() - 1);
     if (rc) return rc;
     if (c->timing) {

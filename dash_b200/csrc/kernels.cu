@@ -272,8 +272,10 @@ __global__ void __launch_bounds__(LIN_THREADS, 8) k_linear(const __grid_constant
     const ModInfo m = pin(P.mod[j]);
     const uint32_t ncols = ((m.nc + 3) & ~3u) * P.Bp; /* nc4 words of 4 digits per inference */
     const uint32_t col = (blockIdx.x * LIN_THREADS + threadIdx.x) * 4;
-    const uint32_t nvg = (P.M + LIN_ROWS - 1) / LIN_ROWS;
-    const uint32_t vg = blockIdx.y % nvg;
+    /* groups of 8 rows that overlap [v0, v1) */
+    const uint32_t vg_first = P.v0 / LIN_ROWS;
+    const uint32_t nvg = (P.v1 + LIN_ROWS - 1) / LIN_ROWS - vg_first;
+    const uint32_t vg = vg_first + blockIdx.y % nvg;
     const uint32_t pix0 = (blockIdx.y / nvg) * LIN_PIXC;
     const uint32_t pix1 = min(pix0 + LIN_PIXC, P.npix);
     const uint64_t rowlen = ncols;
@@ -336,7 +338,8 @@ __global__ void __launch_bounds__(LIN_THREADS, 8) k_linear(const __grid_constant
 #pragma unroll
         for (int r = 0; r < LIN_ROWS; ++r) {
             const uint32_t v = vg * LIN_ROWS + r;
-            if (v >= P.M) break;
+            if (v >= P.v1) break;
+            if (v < P.v0) continue;
             const uint32_t cst = __ldg(reinterpret_cast<const uint32_t*>(P.cst[j]) + (uint64_t)v * nc4 + d4);
             uint32_t o = 0;
 #pragma unroll
@@ -356,7 +359,8 @@ __global__ void __launch_bounds__(LIN_THREADS, 8) k_linear(const __grid_constant
 cudaError_t launch_linear(const LinearParams& p, cudaStream_t s) {
     uint32_t max_cols = 0;
     for (int j = 0; j < p.k; ++j) max_cols = max(max_cols, ((p.mod[j].nc + 3) & ~3u) * p.Bp);
-    const uint32_t nvg = (p.M + LIN_ROWS - 1) / LIN_ROWS;
+    if (p.v1 <= p.v0) return cudaSuccess; /* this rank owns no row of the layer */
+    const uint32_t nvg = (p.v1 + LIN_ROWS - 1) / LIN_ROWS - p.v0 / LIN_ROWS;
     dim3 grid((max_cols / 4 + LIN_THREADS - 1) / LIN_THREADS, ((p.npix + LIN_PIXC - 1) / LIN_PIXC) * nvg, p.k);
     k_linear<<<grid, LIN_THREADS, 0, s>>>(p);
     return cudaGetLastError();
@@ -373,7 +377,7 @@ __global__ void __launch_bounds__(128) k_projection(const __grid_constant__ Proj
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P.n * P.batch) return;
     const uint32_t b = (uint32_t)(idx % P.batch);
-    const uint64_t e = idx / P.batch;
+    const uint64_t e = P.e0 + idx / P.batch;
     uint32_t colour;
     const ModInfo mi = pin(P.min[j]), mo = pin(P.mout[j]);
     const u128 key = load_compress(P.in[j], mi, e, b, P.Bp, colour);
@@ -383,6 +387,7 @@ __global__ void __launch_bounds__(128) k_projection(const __grid_constant__ Proj
 }
 
 cudaError_t launch_projection(const ProjParams& p, cudaStream_t s) {
+    if (p.n == 0) return cudaSuccess;
     const uint64_t total = p.n * p.batch;
     dim3 grid((unsigned)((total + 127) / 128), p.k);
     k_projection<<<grid, 128, 0, s>>>(p);
@@ -522,7 +527,7 @@ __global__ void __launch_bounds__(SIGN_THREADS) k_sign(const __grid_constant__ S
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P.n * P.batch) return;
     const uint32_t b = (uint32_t)(idx % P.batch);
-    const uint64_t e = idx / P.batch;
+    const uint64_t e = P.e0 + idx / P.batch;
     const int k = P.k;
     const int nm = P.n_mrs;
 
@@ -625,6 +630,7 @@ __global__ void __launch_bounds__(SIGN_THREADS) k_sign(const __grid_constant__ S
 }
 
 cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s) {
+    if (p.n == 0) return cudaSuccess;
     const uint64_t total = p.n * p.batch;
     const unsigned grid = (unsigned)((total + SIGN_THREADS - 1) / SIGN_THREADS);
     uint32_t acc_digits = p.mrs[0].nc;
@@ -655,7 +661,7 @@ __global__ void __launch_bounds__(128) k_rescale(const __grid_constant__ Rescale
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P.n * P.batch) return;
     const uint32_t b = (uint32_t)(idx % P.batch);
-    const uint64_t e = idx / P.batch;
+    const uint64_t e = P.e0 + idx / P.batch;
     const int k = P.k;
     uint8_t lw[LW_MAX];
 
@@ -756,6 +762,7 @@ __global__ void __launch_bounds__(128) k_rescale(const __grid_constant__ Rescale
 }
 
 cudaError_t launch_rescale(const RescaleParams& p, cudaStream_t s) {
+    if (p.n == 0) return cudaSuccess;
     const uint64_t total = p.n * p.batch;
     k_rescale<<<(unsigned)((total + 127) / 128), 128, 0, s>>>(p);
     return cudaGetLastError();
@@ -767,8 +774,9 @@ __global__ void k_add_label(const __grid_constant__ AddLabelParams P) {
     const int j = blockIdx.y;
     const ModInfo& m = P.crt[j];
     const uint32_t nc4 = (m.nc + 3) >> 2;
-    const uint64_t total = P.n * nc4 * 4 * (uint64_t)P.Bp;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+    const uint64_t first = P.e0 * nc4 * 4 * (uint64_t)P.Bp;
+    const uint64_t total = first + P.n * nc4 * 4 * (uint64_t)P.Bp;
+    for (uint64_t i = first + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
          i += (uint64_t)gridDim.x * blockDim.x) {
         const uint32_t d = (uint32_t)((i / (4 * P.Bp)) % nc4) * 4 + (uint32_t)(i & 3);
         const uint32_t l = __ldg(P.label[j] + d); /* labels are zero-padded to 4*nc4 digits */
@@ -780,6 +788,7 @@ __global__ void k_add_label(const __grid_constant__ AddLabelParams P) {
 }
 
 cudaError_t launch_add_label(const AddLabelParams& p, cudaStream_t s) {
+    if (p.n == 0) return cudaSuccess;
     uint64_t mx = 0;
     for (int j = 0; j < p.k; ++j) mx = max(mx, p.n * ((p.crt[j].nc + 3) & ~3u) * (uint64_t)p.Bp);
     uint64_t want = (mx + 255) / 256;

@@ -33,6 +33,7 @@ struct LinearParams {
     gc::ModInfo mod[MAXK];
     const int32_t* koff;       /* [Kp] input element offset of tap k */
     uint32_t M, K, Kp;
+    uint32_t v0, v1;           /* output rows [v0, v1) this launch computes (channel sharding) */
     uint32_t npix, ow;         /* output pixels per filter, output width */
     uint32_t step_x, step_y;   /* element offset per output x / y step */
     uint32_t Bp;
@@ -48,7 +49,8 @@ struct SignParams {
     gc::ModInfo outm[MAXK];  /* sign layer: out moduli */
     const gc::u128 *approx, *cast1, *cast2, *sign, *garbler, *evaluator;
     gc::u128 carry0;         /* compressed zero label of m_{n_mrs-1} */
-    uint64_t n;
+    uint64_t n;   /* elements this launch processes ... */
+    uint64_t e0;  /* ... starting at this element (channel sharding) */
     uint32_t prefix[MAXK];
     uint32_t S, Mp;
     uint32_t batch, Bp;
@@ -60,7 +62,8 @@ struct ProjParams {
     uint8_t* out[MAXK];
     gc::ModInfo min[MAXK], mout[MAXK];
     const gc::u128* ciphers[MAXK];
-    uint64_t n;
+    uint64_t n;   /* elements this launch processes ... */
+    uint64_t e0;  /* ... starting at this element (channel sharding) */
     uint32_t batch, Bp;
     int k;
 };
@@ -85,7 +88,8 @@ struct RescaleParams {
     uint16_t neg_invv[MAXF];     /* (-invv) mod extra modulus */
     int extra_idx[MAXF];         /* CRT index of extra modulus x */
     int extra_pos[MAXF];         /* its position in the swapped order */
-    uint64_t n;
+    uint64_t n;   /* elements this launch processes ... */
+    uint64_t e0;  /* ... starting at this element (channel sharding) */
     uint32_t batch, Bp;
     int k, nf, non_ext;
     int legacy;                  /* 1: stop after step 2.3 (sign gadget and downshift follow) */
@@ -95,7 +99,8 @@ struct AddLabelParams {
     uint8_t* plane[MAXK];
     const uint8_t* label[MAXK]; /* u8[4*nc4_j], zero padded */
     gc::ModInfo crt[MAXK];
-    uint64_t n;
+    uint64_t n;   /* elements this launch processes ... */
+    uint64_t e0;  /* ... starting at this element (channel sharding) */
     uint32_t Bp;
     int k;
     int subtract;

@@ -62,3 +62,76 @@ class BatchShardedEvaluator:
                 [p.cpu().numpy().view(np.int16).reshape(mx, n, nc)[: hi - lo] for p, (lo, hi) in zip(parts, sizes)],
                 axis=0))
         return out
+
+
+LINEAR_TYPES = (1, 2)  # DASHB_LAYER_DENSE, DASHB_LAYER_CONV2D
+
+
+def layer_groups(layer_types):
+    """Cuts a layer list into groups that can run on a rank's slice without
+    communication: a linear layer (dense / conv2d) needs every input element,
+    so each one starts a new group; the element-wise gadget layers after it
+    stay with it.  Returns [(first, last)]."""
+    groups = []
+    start = 0
+    for i, t in enumerate(layer_types):
+        if t in LINEAR_TYPES and i > start:
+            groups.append((start, i - 1))
+            start = i
+    if layer_types:
+        groups.append((start, len(layer_types) - 1))
+    return groups
+
+
+class _DeviceBytes:
+    """Wraps raw device memory for torch.as_tensor (CUDA array interface)."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
+
+
+class ChannelShardedEvaluator:
+    """Output-channel sharding of ONE batch across the GPUs of a box (config
+    C4): every rank owns a block of each linear layer's output rows and the
+    same elements of the gadget layers behind it; after each group of layers
+    the ranks' slices of the activation planes are exchanged in place with
+    NCCL broadcasts over NVLink (one per rank and CRT modulus, straight on
+    the device planes).  Weights and tables are replicated."""
+
+    def __init__(self, circuit, rank, world, dist=None, as_tensor=None):
+        self.c = circuit
+        self.rank = rank
+        self.world = world
+        self.dist = dist
+        self.as_tensor = as_tensor
+        self.groups = layer_groups([circuit.layer_type(i) for i in range(circuit.n_layers)])
+        self.bytes_exchanged = 0
+
+    def _gather(self, layer):
+        import torch
+
+        self.c.sync()
+        for j in range(self.c.k):
+            ptr, bpe, n = self.c.current_plane(j)
+            if self.as_tensor is not None:
+                plane = self.as_tensor(ptr, bpe * n)
+            else:
+                plane = torch.as_tensor(_DeviceBytes(ptr, bpe * n), device="cuda")
+            for r in range(self.world):
+                e0, e1 = self.c.layer_slice(layer, r)
+                if e1 > e0:
+                    self.dist.broadcast(plane[e0 * bpe:e1 * bpe], src=r)
+                    if r != self.rank:
+                        self.bytes_exchanged += (e1 - e0) * bpe
+        if self.as_tensor is None:
+            torch.cuda.synchronize()
+
+    def evaluate(self, labels):
+        """labels: the whole batch on every rank.  Returns the output labels
+        (identical on every rank)."""
+        self.c.move_inputs(labels)
+        for first, last in self.groups:
+            self.c.evaluate_layers(first, last)
+            if self.world > 1:
+                self._gather(last)
+        return self.c.move_outputs()

@@ -245,6 +245,28 @@ int dashb_layer_outputs(dashb_circuit* c, int layer, int16_t* const* out);
  * matched its decoding information. */
 int dashb_decode_outputs(dashb_circuit* c, int64_t* values, uint8_t* ok);
 
+/* ---- output-channel sharding across GPUs (no counterpart in the reference,
+ *      which is single-GPU) ----------------------
+ * Every rank (one process per GPU) builds the same circuit, calls
+ * dashb_set_shard(rank, world) before dashb_finalize and then owns, for each
+ * linear layer, a contiguous block of output rows (dense rows / conv
+ * filters) and, for the element-wise gadget layers that follow, the same
+ * elements.  Weights and tables are replicated; only activations are
+ * exchanged.  A rank evaluates a group of layers with
+ * dashb_evaluate_layers(first, last) on its slices; before the next layer
+ * that needs every input element (the next dense/conv, or the end) the
+ * caller all-gathers the ranks' slices of the current planes -- plane j of
+ * the current tensor is dashb_current_plane(): a device pointer to
+ * n_elements rows of bytes_per_element bytes, rank r's slice of layer L's
+ * output being elements dashb_layer_slice(L, r).  dash_b200/scheduler.py
+ * does this with NCCL broadcasts over NVLink.  The exchange happens on the
+ * digit planes as they are (no staging).  Sharded circuits run one lane. */
+int dashb_set_shard(dashb_circuit* c, int rank, int world);
+int dashb_evaluate_layers(dashb_circuit* c, int first, int last);
+int dashb_current_plane(dashb_circuit* c, int j, void** dev_ptr, uint64_t* bytes_per_element,
+                        uint64_t* n_elements);
+int dashb_layer_slice(const dashb_circuit* c, int layer, int rank, uint64_t* e0, uint64_t* e1);
+
 /* ---- introspection ---------------------------------------------------- */
 uint64_t dashb_input_size(const dashb_circuit* c);
 uint64_t dashb_output_size(const dashb_circuit* c);

@@ -60,3 +60,14 @@ def test_batch_sharded_gather_world2(total):
     for p in procs:
         p.join(timeout=60)
     assert sorted(res) == [(0, True), (1, True)]
+
+
+def test_layer_groups():
+    from dash_b200.scheduler import layer_groups
+
+    D, C2, R, S, RS, P = 1, 2, 3, 4, 5, 7
+    assert layer_groups([C2, R, C2, R, D, R, D]) == [(0, 1), (2, 3), (4, 5), (6, 6)]
+    assert layer_groups([R, D]) == [(0, 0), (1, 1)]
+    assert layer_groups([C2, RS, R, C2, RS]) == [(0, 2), (3, 4)]
+    assert layer_groups([D]) == [(0, 0)]
+    assert layer_groups([]) == []
