@@ -119,3 +119,23 @@ def test_device_garble_inputs(gpu, name, batch):
         vals, ok = c.decode_outputs()
         assert ok.all() and np.array_equal(vals, tile_batch([g.dec], batch)[0])
     c.close()
+
+
+def test_inprocess_cpp_example(gpu):
+    """integration/example_inprocess.cpp: a Dash program (reference classes,
+    compiled from the unmodified headers) that hands its garbled circuit to
+    the B200 evaluator through integration/dash_adapter.h + the C ABI and
+    decodes the result with the reference's own decode_outputs."""
+    import os
+    import subprocess
+
+    from helpers import ROOT
+
+    exe = os.path.join(ROOT, "oracle", "_ref", "example_inprocess")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/example_inprocess not built")
+    res = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0, res.stdout + res.stderr
+    line = [l for l in res.stdout.splitlines() if l.startswith("b200:")][0]
+    b200, cpu = line.split("cpu:")
+    assert b200.replace("b200:", "").split() == cpu.split() == ["3", "3"]
