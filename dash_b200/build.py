@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdash_b200.so")
-SOURCES = ["kernels.cu", "dashb_api.cu"]
+SOURCES = ["kernels.cu", "dense_tc.cu", "dashb_api.cu"]
 HEADERS = ["kernels.h", "gc_common.cuh", "../../include/dash_b200.h", "../../include/dash_b200_gcm.h",
            "../../include/dash_gcm_format.h"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
@@ -24,7 +24,8 @@ def needs_build():
 def build(force=False, verbose=False):
     if not force and not needs_build():
         return LIB
-    cmd = [NVCC] + FLAGS + ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES] + ["-lcudart"]
+    extra = os.environ.get("DASHB_NVCC_EXTRA", "").split()
+    cmd = [NVCC] + FLAGS + extra + ["-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES] + ["-lcudart"]
     res = subprocess.run(cmd, capture_output=True, text=True)
     with open(os.path.join(HERE, "build.log"), "w") as f:
         f.write(" ".join(cmd) + "\n" + res.stdout + res.stderr)

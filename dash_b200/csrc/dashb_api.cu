@@ -183,6 +183,10 @@ struct Layer {
     uint64_t M{0}, K{0};
     uint32_t Kp{0}, npix{1}, ow{1}, step_x{0}, step_y{0};
     DevMem w4[MAXK], cst[MAXK], koff;
+    /* tensor-core dense path: row-major u8 weights [M][Kp16] and their TMA maps */
+    DevMem wrm[MAXK];
+    TensorMapBlob map_a[MAXK];
+    bool use_tc{false};
     /* gadget tables */
     DevMem approx, cast1, cast2, sign, garbler, evaluator;
     /* rescale */
@@ -484,6 +488,24 @@ int dashb_add_dense(dashb_circuit* c, uint64_t M, uint64_t K, int channel_tf, co
         koff[kk] = channel_tf ? (int32_t)(kk / channel_tf + (kk % channel_tf) * (K / channel_tf)) : (int32_t)kk;
     }
     CU(L->koff.upload(koff.data(), koff.size() * 4));
+    /* tcgen05 path: plain input order, exact s32 accumulation, worth a 128-row tile */
+    static const bool tc_off = getenv("DASHB_NO_TC") != nullptr;
+    if (!tc_off && channel_tf == 0 && K * 65025ull < (1ull << 31) && M >= 16 && K >= 32) {
+        const uint64_t Kp16 = (K + 15) & ~15ull;
+        for (int j = 0; j < c->k; ++j) {
+            const int64_t q = c->crt[j];
+            std::vector<uint8_t> wr((size_t)M * Kp16, 0);
+            for (uint64_t r = 0; r < M; ++r)
+                for (uint64_t kk = 0; kk < K; ++kk) {
+                    int64_t wv = weights[r * K + kk] % q;
+                    if (wv < 0) wv += q;
+                    wr[r * Kp16 + kk] = (uint8_t)wv;
+                }
+            CU(L->wrm[j].upload(wr.data(), wr.size()));
+            CU(dense_tc_make_map(&L->map_a[j], L->wrm[j].p, Kp16, M));
+        }
+        L->use_tc = true;
+    }
     push_layer(c, std::move(L));
     return DASHB_OK;
 }
@@ -1019,6 +1041,28 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
     switch (L.type) {
         case DASHB_LAYER_DENSE:
         case DASHB_LAYER_CONV2D: {
+            if (L.use_tc) {
+                DenseTcMaps maps;
+                DenseTcParams tp;
+                memset(&tp, 0, sizeof(tp));
+                tp.k = c->k;
+                tp.M = (uint32_t)L.M;
+                tp.K = (uint32_t)L.K;
+                tp.Bp = Bp;
+                tp.v0 = L.v0;
+                tp.v1 = L.v1;
+                for (int j = 0; j < c->k; ++j) {
+                    maps.a[j] = L.map_a[j];
+                    const uint64_t Nj = (uint64_t)((c->crt_mi[j].nc + 3) & ~3u) * Bp;
+                    CU(dense_tc_make_map(&maps.b[j], cur.plane[j], Nj, L.K));
+                    tp.out[j] = out.plane[j];
+                    tp.cst[j] = (const uint8_t*)L.cst[j].p;
+                    tp.mod[j] = c->crt_mi[j];
+                }
+                CU(launch_dense_tc(maps, tp, s));
+                c->launches += 1;
+                break;
+            }
             LinearParams p;
             memset(&p, 0, sizeof(p));
             p.k = c->k;

@@ -1,0 +1,249 @@
+/*
+ * dense_tc.cu -- garbled dense layer on the 5th-generation tensor cores.
+ *
+ *   out_j[m][n] = ( sum_k Wq_j[m][k] * in_j[k][n] + cst_j[m][d(n)] ) mod p_j
+ *
+ * for every CRT modulus j in one launch.  The digit planes are already the
+ * row-major K x N operand (N = 4*nc4_j*Bp bytes per element row), so they are
+ * consumed as they are: TMA (cp.async.bulk.tensor, SWIZZLE_128B) stages
+ * 128 x 128-byte tiles of the weights (K-major) and of the plane (N-major =
+ * "MN-major" B operand) in shared memory, one elected thread issues
+ * tcgen05.mma.kind::i8 (u8 x u8 -> s32, accumulator in TMEM), four epilogue
+ * warps read the accumulator back with tcgen05.ld, add the constant label,
+ * reduce mod p_j and store bytes.  Exact while K * 255^2 < 2^31 (checked by
+ * the caller).  Replaces MatMulModAddZero (misc/cuda_util.h:95-114) /
+ * LabelTensor::matvecmul (garbling/label_tensor.h:783-818); same
+ * reformulation of the zero-weight rule as k_linear (kernels.cu).
+ *
+ * Warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer +
+ * TMEM allocation, warps 2..5 = epilogue (TMEM sub-partition = warp % 4).
+ * A 4-stage shared-memory ring (full/empty mbarriers) decouples them.
+ */
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+
+#include "kernels.h"
+
+namespace dashb {
+
+using gc::ModInfo;
+
+constexpr int TC_BM = 128, TC_BN = 128, TC_BK = 128; /* u8: bytes == elements */
+constexpr int TC_STAGES = 4;
+constexpr int TC_THREADS = 192;
+constexpr uint32_t TC_STAGE_BYTES = TC_BM * TC_BK + TC_BK * TC_BN;
+constexpr uint32_t TC_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+/* bounded wait: a protocol error traps instead of hanging the GPU */
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t it = 0; it < (1u << 26); ++it) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+        if (done) return;
+    }
+    __trap();
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+            smem_u32(dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+/* shared-memory matrix descriptor: SWIZZLE_128B, version 1 (sm_100) */
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3fff);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ DenseTcParams P) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t bar_full[TC_STAGES], bar_empty[TC_STAGES], bar_acc;
+    __shared__ uint32_t tmem_base_s;
+    const int j = blockIdx.z;
+    const ModInfo m = P.mod[j];
+    const uint32_t nc4 = (m.nc + 3) >> 2;
+    const uint32_t Nj = nc4 * 4 * P.Bp;
+    const uint32_t n0 = blockIdx.x * TC_BN;
+    if (n0 >= Nj) return; /* uniform per CTA: planes of small moduli have fewer columns */
+    const uint32_t m0 = P.v0 + blockIdx.y * TC_BM;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t nkb = (P.K + TC_BK - 1) / TC_BK;
+
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(TC_BN));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < TC_STAGES; ++s) {
+            mbar_init(&bar_full[s], 1);
+            mbar_init(&bar_empty[s], 1);
+        }
+        mbar_init(&bar_acc, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;");
+        asm volatile("fence.proxy.async.shared::cta;");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const uint32_t tmem_base = tmem_base_s;
+
+    if (warp == 0) {
+        /* ===== TMA producer ===== */
+        if (lane == 0) {
+            for (uint32_t kb = 0; kb < nkb; ++kb) {
+                const uint32_t s = kb % TC_STAGES, round = kb / TC_STAGES;
+                if (round > 0) mbar_wait(&bar_empty[s], (round - 1) & 1);
+                uint8_t* sA = smem + s * TC_STAGE_BYTES;
+                uint8_t* sB = sA + TC_BM * TC_BK;
+                mbar_expect_tx(&bar_full[s], TC_STAGE_BYTES);
+                tma_load_2d(sA, reinterpret_cast<const CUtensorMap*>(&maps.a[j]), &bar_full[s], (int)(kb * TC_BK), (int)m0);  /* {k, m} */
+                tma_load_2d(sB, reinterpret_cast<const CUtensorMap*>(&maps.b[j]), &bar_full[s], (int)n0, (int)(kb * TC_BK));  /* {n, k} */
+            }
+        }
+    } else if (warp == 1) {
+        /* ===== MMA issuer ===== */
+        if (lane == 0) {
+            /* S32 accumulator, U8 x U8, A K-major, B MN-major, M = 128, N = 128 */
+            const uint32_t idesc = (2u << 4) | (1u << 16) | ((uint32_t)(TC_BN >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+            for (uint32_t kb = 0; kb < nkb; ++kb) {
+                const uint32_t s = kb % TC_STAGES, round = kb / TC_STAGES;
+                mbar_wait(&bar_full[s], round & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;");
+                const uint32_t aA = smem_u32(smem + s * TC_STAGE_BYTES);
+                const uint32_t aB = aA + TC_BM * TC_BK;
+#pragma unroll
+                for (int k4 = 0; k4 < TC_BK / 32; ++k4) {
+                    const uint64_t da = umma_desc(aA + k4 * 32, 16, 1024);         /* +32 B inside the swizzled row */
+                    const uint64_t db = umma_desc(aB + k4 * 32 * TC_BN, 16, 1024); /* +32 k-rows of 128 B */
+                    const uint32_t acc = (kb | (uint32_t)k4) ? 1u : 0u;
+                    asm volatile(
+                        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}" ::"r"(tmem_base),
+                        "l"(da), "l"(db), "r"(idesc), "r"(acc), "r"(0), "r"(0), "r"(0), "r"(0)
+                        : "memory");
+                }
+                /* frees the stage when the MMAs that read it are done */
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                                 smem_u32(&bar_empty[s]))
+                             : "memory");
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar_acc))
+                         : "memory");
+        }
+    } else {
+        /* ===== epilogue: TMEM -> registers -> (+cst) mod q -> bytes ===== */
+        mbar_wait(&bar_acc, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        const uint32_t sub = (uint32_t)warp & 3u; /* TMEM lanes 32*sub .. 32*sub+31 */
+        const uint32_t row = m0 + sub * 32 + lane;
+        const bool row_ok = row < P.v1;
+        const uint32_t* cst = reinterpret_cast<const uint32_t*>(P.cst[j]) + (uint64_t)(row_ok ? row : 0) * nc4;
+        uint8_t* orow = P.out[j] + (uint64_t)(row_ok ? row : 0) * Nj + n0;
+        for (int c0 = 0; c0 < TC_BN; c0 += 32) {
+            uint32_t v[32];
+            const uint32_t taddr = tmem_base + ((sub * 32u) << 16) + (uint32_t)c0;
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                  "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                  "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (row_ok && n0 + c0 < Nj) {
+                uint32_t w[8];
+#pragma unroll
+                for (int g = 0; g < 8; ++g) {
+                    /* 4 columns = digits 4*d4..4*d4+3 of one inference */
+                    const uint32_t d4 = (n0 + c0 + 4 * g) / (4 * P.Bp);
+                    const uint32_t cw = __ldg(cst + d4);
+                    uint32_t o = 0;
+#pragma unroll
+                    for (int t = 0; t < 4; ++t) {
+                        uint32_t x = v[4 * g + t] + ((cw >> (8 * t)) & 0xff);
+                        x -= gc::mulhi32(x, m.mq) * m.q; /* reciprocal over-estimates by at most one */
+                        if ((int32_t)x < 0) x += m.q;
+                        o |= x << (8 * t);
+                    }
+                    w[g] = o;
+                }
+                /* Nj is a multiple of 64, tiles of 32 columns never straddle it */
+                *reinterpret_cast<uint4*>(orow + c0) = make_uint4(w[0], w[1], w[2], w[3]);
+                *reinterpret_cast<uint4*>(orow + c0 + 16) = make_uint4(w[4], w[5], w[6], w[7]);
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_BN));
+}
+
+/* ---- host side: tensor maps ---- */
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+
+/* u8 row-major [outer][inner] (inner = contiguous bytes, multiple of 16), 128 x 128 boxes, zero fill out of bounds */
+cudaError_t dense_tc_make_map(void* map_out, const void* ptr, uint64_t inner, uint64_t outer) {
+    if (!g_encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+        if (e != cudaSuccess) return e;
+        if (!fn) return cudaErrorNotSupported;
+        g_encode = (EncodeTiledFn)fn;
+    }
+    cuuint64_t dims[2] = {inner, outer};
+    cuuint64_t strides[1] = {inner};
+    cuuint32_t box[2] = {128, 128};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode((CUtensorMap*)map_out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(ptr), dims, strides, box,
+                          estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
+cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p, cudaStream_t s) {
+    if (p.v1 <= p.v0) return cudaSuccess;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(k_dense_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    uint32_t max_cols = 0;
+    for (int j = 0; j < p.k; ++j) max_cols = max(max_cols, ((p.mod[j].nc + 3) & ~3u) * p.Bp);
+    dim3 grid((max_cols + TC_BN - 1) / TC_BN, (p.v1 - p.v0 + TC_BM - 1) / TC_BM, p.k);
+    k_dense_tc<<<grid, TC_THREADS, TC_SMEM_BYTES, s>>>(maps, p);
+    return cudaGetLastError();
+}
+
+}  // namespace dashb

@@ -481,7 +481,10 @@ namespace dashb {
 /* ------------------------------------------------- sign gadget / ReLU */
 /* Per-thread digit accumulators live in shared memory, digit-major
  * (acc[d * blockDim + tid]) so that a warp's accesses are conflict-free. */
-constexpr int SIGN_THREADS = 128;
+#ifndef DASHB_SIGN_THREADS
+#define DASHB_SIGN_THREADS 128
+#endif
+constexpr int SIGN_THREADS = DASHB_SIGN_THREADS;
 
 /* digit-wise accumulation of a compressed label (no reduction: at most k+1
  * digits below 2^11 are summed) */

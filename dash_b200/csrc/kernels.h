@@ -40,6 +40,24 @@ struct LinearParams {
     int k;
 };
 
+/* tcgen05 dense path (dense_tc.cu).  A tensor map is CUtensorMap's 128 opaque
+ * bytes; kept opaque here so that this header does not need <cuda.h>. */
+struct alignas(64) TensorMapBlob {
+    uint64_t v[16];
+};
+struct DenseTcMaps {
+    TensorMapBlob a[MAXK]; /* Wq_j  u8 [M][Kp16]            (K-major A)  */
+    TensorMapBlob b[MAXK]; /* plane_j u8 [K][4*nc4_j*Bp]    (N-major B)  */
+};
+struct DenseTcParams {
+    uint8_t* out[MAXK];
+    const uint8_t* cst[MAXK];
+    gc::ModInfo mod[MAXK];
+    uint32_t M, K, Bp;
+    uint32_t v0, v1;
+    int k;
+};
+
 struct SignParams {
     const uint8_t* in[MAXK];
     uint8_t* out[MAXK];
@@ -149,6 +167,8 @@ cudaError_t launch_ingest(const int16_t* src, uint8_t* plane, uint64_t n, uint32
 cudaError_t launch_egress(const uint8_t* plane, int16_t* dst, uint64_t n, uint32_t nc, uint32_t batch, uint32_t Bp,
                           cudaStream_t s);
 cudaError_t launch_linear(const LinearParams& p, cudaStream_t s);
+cudaError_t dense_tc_make_map(void* map_out, const void* ptr, uint64_t inner, uint64_t outer);
+cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p, cudaStream_t s);
 cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s);
 cudaError_t launch_projection(const ProjParams& p, cudaStream_t s);
 cudaError_t launch_rescale(const RescaleParams& p, cudaStream_t s);

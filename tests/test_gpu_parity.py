@@ -139,3 +139,30 @@ def test_inprocess_cpp_example(gpu):
     line = [l for l in res.stdout.splitlines() if l.startswith("b200:")][0]
     b200, cpu = line.split("cpu:")
     assert b200.replace("b200:", "").split() == cpu.split() == ["3", "3"]
+
+
+@pytest.mark.parametrize("M,K", [(16, 33), (50, 100), (130, 257), (128, 128), (200, 640)])
+@pytest.mark.parametrize("batch", [1, 17, 40])
+def test_dense_tensor_core_path(gpu, tmp_path, M, K, batch):
+    """Dense layers large enough for the tcgen05 kind::i8 kernel (dense_tc.cu):
+    odd shapes (rows/taps not multiples of the 128-wide tiles, ragged batch),
+    followed by a ReLU so that a wrong digit anywhere would also break the
+    hashes.  Bit-exact against the reference."""
+    import workloads as W
+    from oracle import refbind as R
+
+    if not R.available():
+        pytest.skip("oracle/_ref not present on this box")
+    spec = dict(input=(K, 1, 1), layers=[("flatten",), ("dense", M), ("relu",)], quant=("simple", 0.02), **W.cpm(8, 99.0))
+    ref = W.build_reference_circuit(spec, seed=K, weight_seed=M)
+    path = str(tmp_path / "dense.gcm")
+    ref.export(path)
+    X = W.synthetic_inputs(spec, batch, seed=3)
+    per = [ref.garble_inputs(x) for x in X]
+    labels = [np.stack([p[j] for p in per]) for j in range(ref.k)]
+    c = gpu.Circuit.load(path, max_batch=batch)
+    got = c.evaluate(labels)
+    for b in sorted({0, batch // 2, batch - 1}):
+        want, _ = ref.cpu_evaluate([l[b] for l in labels], 4)
+        assert_labels_equal([g[b] for g in got], want, "dense %dx%d inference %d" % (M, K, b))
+    c.close()

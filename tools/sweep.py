@@ -106,6 +106,11 @@ def main():
             run_case(name, W.MODELS[name], bs)
     elif what == "gnnp":
         run_case("MODEL_F_GNNP_POOL_REPL", W.MODELS["MODEL_F_GNNP_POOL_REPL"], [16], steps=3, cpu_reps=1, check=1)
+    elif what == "dense":
+        for dim in (128, 512, 2048):
+            run_case("dense_%d" % dim, dict(input=(dim, 1, 1), layers=[("flatten",), ("dense", dim)],
+                                            quant=("simple", 0.02), crt=W.PRIMES[:8], mrs=[], max_modulus=0), [1, 16, 256])
+        run_case("MODEL_A", W.MODELS["MODEL_A"], [256])
     elif what == "micro":
         # benchmarks/micro_benchmarks/non_sgx/main.cpp:577-683 grids (subset that garbles in seconds)
         for n in (128, 1024, 4096):
