@@ -187,6 +187,8 @@ struct Layer {
     DevMem wrm[MAXK];
     TensorMapBlob map_a[MAXK];
     bool use_tc{false};
+    /* tensor-core convolution: geometry for the im2col TMA box, cb channels per 128-column K block */
+    uint32_t cv_w{0}, cv_h{0}, cv_c{0}, cv_fw{0}, cv_fh{0}, cv_sw{0}, cv_sh{0}, cv_cb{0}, tc_nkb{0};
     /* gadget tables */
     DevMem approx, cast1, cast2, sign, garbler, evaluator;
     /* rescale */
@@ -505,6 +507,7 @@ int dashb_add_dense(dashb_circuit* c, uint64_t M, uint64_t K, int channel_tf, co
             CU(dense_tc_make_map(&L->map_a[j], L->wrm[j].p, Kp16, M));
         }
         L->use_tc = true;
+        L->tc_nkb = (uint32_t)((K + 127) / 128);
     }
     push_layer(c, std::move(L));
     return DASHB_OK;
@@ -549,6 +552,33 @@ int dashb_add_conv2d(dashb_circuit* c, uint64_t in_w, uint64_t in_h, uint64_t ch
     L->step_y = (uint32_t)(s_h * in_w);
     if ((uint64_t)L->npix * ((filters + 7) / 8) > 65535) return fail(DASHB_EINVAL, "conv2d: output grid too large");
     CU(L->koff.upload(koff.data(), koff.size() * 4));
+    /* tcgen05 path (dense_tc.cu): one GEMM per output pixel, im2col by a 4-D
+     * TMA box of cb channels; weights regrouped into 128-column K blocks of
+     * cb*fs taps each, zero padded */
+    static const bool tc_off = getenv("DASHB_NO_TC") != nullptr;
+    if (!tc_off && filters >= 16 && K >= 64 && fs <= 128 && f_w <= 256 && f_h <= 256 && K * 65025ull < (1ull << 31) &&
+        ow * oh * ((filters + 127) / 128) <= 65535) {
+        const uint64_t cb = std::min<uint64_t>(128 / fs, channels);
+        const uint64_t nkb = (channels + cb - 1) / cb, Kpad = nkb * 128;
+        for (int j = 0; j < c->k; ++j) {
+            const int64_t q = c->crt[j];
+            std::vector<uint8_t> wr((size_t)filters * Kpad, 0);
+            for (uint64_t v = 0; v < filters; ++v)
+                for (uint64_t w = 0; w < channels; ++w)
+                    for (uint64_t t = 0; t < fs; ++t) {
+                        int64_t wv = wrow[v * K + w * fs + t] % q;
+                        if (wv < 0) wv += q;
+                        wr[v * Kpad + (w / cb) * 128 + (w % cb) * fs + t] = (uint8_t)wv;
+                    }
+            CU(L->wrm[j].upload(wr.data(), wr.size()));
+            CU(dense_tc_make_map(&L->map_a[j], L->wrm[j].p, Kpad, filters));
+        }
+        L->use_tc = true;
+        L->tc_nkb = (uint32_t)nkb;
+        L->cv_w = (uint32_t)in_w, L->cv_h = (uint32_t)in_h, L->cv_c = (uint32_t)channels;
+        L->cv_fw = (uint32_t)f_w, L->cv_fh = (uint32_t)f_h, L->cv_sw = (uint32_t)s_w, L->cv_sh = (uint32_t)s_h;
+        L->cv_cb = (uint32_t)cb;
+    }
     push_layer(c, std::move(L));
     return DASHB_OK;
 }
@@ -1051,10 +1081,22 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
                 tp.Bp = Bp;
                 tp.v0 = L.v0;
                 tp.v1 = L.v1;
+                tp.nkb = L.tc_nkb;
+                const bool conv = L.type == DASHB_LAYER_CONV2D;
+                tp.conv = conv;
+                tp.npix = L.npix;
+                tp.ow = L.ow;
+                tp.sx = L.cv_sw;
+                tp.sy = L.cv_sh;
+                tp.cb = L.cv_cb;
+                tp.b_box_bytes = conv ? 128u * L.cv_fw * L.cv_fh * L.cv_cb : 128u * 128u;
                 for (int j = 0; j < c->k; ++j) {
                     maps.a[j] = L.map_a[j];
                     const uint64_t Nj = (uint64_t)((c->crt_mi[j].nc + 3) & ~3u) * Bp;
-                    CU(dense_tc_make_map(&maps.b[j], cur.plane[j], Nj, L.K));
+                    if (conv)
+                        CU(conv_tc_make_map(&maps.b[j], cur.plane[j], Nj, L.cv_w, L.cv_h, L.cv_c, L.cv_fw, L.cv_fh, L.cv_cb));
+                    else
+                        CU(dense_tc_make_map(&maps.b[j], cur.plane[j], Nj, L.K));
                     tp.out[j] = out.plane[j];
                     tp.cst[j] = (const uint8_t*)L.cst[j].p;
                     tp.mod[j] = c->crt_mi[j];

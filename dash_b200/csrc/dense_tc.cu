@@ -17,7 +17,18 @@
  *
  * Warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer +
  * TMEM allocation, warps 2..5 = epilogue (TMEM sub-partition = warp % 4).
- * A 4-stage shared-memory ring (full/empty mbarriers) decouples them.
+ * A shared-memory ring (full/empty mbarriers) decouples them.
+ *
+ * Convolution (CONV = true) is the same GEMM per output pixel: M = filters,
+ * K = taps (channel, filter row, filter column), N = the pixel's plane row.
+ * The im2col gather is done by TMA itself: the input plane is described as a
+ * 4-D tensor {plane bytes, column, row, channel} and one box {128, f_w, f_h,
+ * Cb} lands in shared memory as Cb*f_h*f_w consecutive 128-byte K rows --
+ * exactly the N-major B tile of the dense case.  The weights are laid out to
+ * match (Cb channels per 128-column K block, zero padded), so the rows of a
+ * K block that the box does not fill meet zero weights.  Replaces
+ * Conv2dModZero (misc/cuda_util.h:209-268) / LabelTensor::conv2d
+ * (garbling/label_tensor.h:920-1002) for layers wide enough to fill a tile.
  */
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -32,10 +43,11 @@ namespace dashb {
 using gc::ModInfo;
 
 constexpr int TC_BM = 128, TC_BN = 128, TC_BK = 128; /* u8: bytes == elements */
-constexpr int TC_STAGES = 4;
+constexpr int TC_STAGES_DENSE = 4; /* long K loops: deep ring, one CTA per SM */
+constexpr int TC_STAGES_CONV = 2;  /* few K blocks per tile: three CTAs per SM overlap MMA and epilogue */
 constexpr int TC_THREADS = 192;
 constexpr uint32_t TC_STAGE_BYTES = TC_BM * TC_BK + TC_BK * TC_BN;
-constexpr uint32_t TC_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024;
+constexpr uint32_t tc_smem_bytes(int stages) { return (uint32_t)stages * TC_STAGE_BYTES + 1024; }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -67,6 +79,13 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
         "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
         : "memory");
 }
+__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+            smem_u32(dst)),
+        "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
 /* shared-memory matrix descriptor: SWIZZLE_128B, version 1 (sm_100) */
 __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
     uint64_t d = 0;
@@ -78,6 +97,7 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes
     return d;
 }
 
+template <bool CONV, int TC_STAGES>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ DenseTcParams P) {
     extern __shared__ uint8_t smem_raw[];
@@ -90,9 +110,11 @@ k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ Den
     const uint32_t Nj = nc4 * 4 * P.Bp;
     const uint32_t n0 = blockIdx.x * TC_BN;
     if (n0 >= Nj) return; /* uniform per CTA: planes of small moduli have fewer columns */
-    const uint32_t m0 = P.v0 + blockIdx.y * TC_BM;
+    /* conv: blockIdx.y = filter block * npix + output pixel */
+    const uint32_t pix = CONV ? blockIdx.y % P.npix : 0u;
+    const uint32_t m0 = P.v0 + (CONV ? blockIdx.y / P.npix : blockIdx.y) * TC_BM;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t nkb = (P.K + TC_BK - 1) / TC_BK;
+    const uint32_t nkb = P.nkb;
 
     if (warp == 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(TC_BN));
@@ -120,9 +142,13 @@ k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ Den
                 if (round > 0) mbar_wait(&bar_empty[s], (round - 1) & 1);
                 uint8_t* sA = smem + s * TC_STAGE_BYTES;
                 uint8_t* sB = sA + TC_BM * TC_BK;
-                mbar_expect_tx(&bar_full[s], TC_STAGE_BYTES);
+                mbar_expect_tx(&bar_full[s], TC_BM * TC_BK + P.b_box_bytes);
                 tma_load_2d(sA, reinterpret_cast<const CUtensorMap*>(&maps.a[j]), &bar_full[s], (int)(kb * TC_BK), (int)m0);  /* {k, m} */
-                tma_load_2d(sB, reinterpret_cast<const CUtensorMap*>(&maps.b[j]), &bar_full[s], (int)n0, (int)(kb * TC_BK));  /* {n, k} */
+                if (CONV)
+                    tma_load_4d(sB, reinterpret_cast<const CUtensorMap*>(&maps.b[j]), &bar_full[s], (int)n0,
+                                (int)((pix % P.ow) * P.sx), (int)((pix / P.ow) * P.sy), (int)(kb * P.cb)); /* {n, x, y, c} */
+                else
+                    tma_load_2d(sB, reinterpret_cast<const CUtensorMap*>(&maps.b[j]), &bar_full[s], (int)n0, (int)(kb * TC_BK));  /* {n, k} */
             }
         }
     } else if (warp == 1) {
@@ -163,7 +189,7 @@ k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ Den
         const uint32_t row = m0 + sub * 32 + lane;
         const bool row_ok = row < P.v1;
         const uint32_t* cst = reinterpret_cast<const uint32_t*>(P.cst[j]) + (uint64_t)(row_ok ? row : 0) * nc4;
-        uint8_t* orow = P.out[j] + (uint64_t)(row_ok ? row : 0) * Nj + n0;
+        uint8_t* orow = P.out[j] + ((uint64_t)(row_ok ? row : 0) * (CONV ? P.npix : 1u) + pix) * Nj + n0;
         for (int c0 = 0; c0 < TC_BN; c0 += 32) {
             uint32_t v[32];
             const uint32_t taddr = tmem_base + ((sub * 32u) << 16) + (uint32_t)c0;
@@ -211,8 +237,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 static EncodeTiledFn g_encode = nullptr;
 
-/* u8 row-major [outer][inner] (inner = contiguous bytes, multiple of 16), 128 x 128 boxes, zero fill out of bounds */
-cudaError_t dense_tc_make_map(void* map_out, const void* ptr, uint64_t inner, uint64_t outer) {
+static cudaError_t load_encode() {
     if (!g_encode) {
         void* fn = nullptr;
         cudaDriverEntryPointQueryResult q;
@@ -221,6 +246,13 @@ cudaError_t dense_tc_make_map(void* map_out, const void* ptr, uint64_t inner, ui
         if (!fn) return cudaErrorNotSupported;
         g_encode = (EncodeTiledFn)fn;
     }
+    return cudaSuccess;
+}
+
+/* u8 row-major [outer][inner] (inner = contiguous bytes, multiple of 16), 128 x 128 boxes, zero fill out of bounds */
+cudaError_t dense_tc_make_map(void* map_out, const void* ptr, uint64_t inner, uint64_t outer) {
+    cudaError_t e = load_encode();
+    if (e != cudaSuccess) return e;
     cuuint64_t dims[2] = {inner, outer};
     cuuint64_t strides[1] = {inner};
     cuuint32_t box[2] = {128, 128};
@@ -231,18 +263,43 @@ cudaError_t dense_tc_make_map(void* map_out, const void* ptr, uint64_t inner, ui
     return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
+/* input plane of a convolution: u8 [channel][row][column][row_bytes], boxes {128, f_w, f_h, cb} */
+cudaError_t conv_tc_make_map(void* map_out, const void* ptr, uint64_t row_bytes, uint64_t in_w, uint64_t in_h,
+                             uint64_t channels, uint32_t f_w, uint32_t f_h, uint32_t cb) {
+    cudaError_t e = load_encode();
+    if (e != cudaSuccess) return e;
+    cuuint64_t dims[4] = {row_bytes, in_w, in_h, channels};
+    cuuint64_t strides[3] = {row_bytes, row_bytes * in_w, row_bytes * in_w * in_h};
+    cuuint32_t box[4] = {128, f_w, f_h, cb};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = g_encode((CUtensorMap*)map_out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<void*>(ptr), dims, strides, box,
+                          estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
 cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p, cudaStream_t s) {
     if (p.v1 <= p.v0) return cudaSuccess;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_dense_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM_BYTES);
+        cudaError_t e = cudaFuncSetAttribute(k_dense_tc<false, TC_STAGES_DENSE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)tc_smem_bytes(TC_STAGES_DENSE));
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(k_dense_tc<true, TC_STAGES_CONV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)tc_smem_bytes(TC_STAGES_CONV));
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
     uint32_t max_cols = 0;
     for (int j = 0; j < p.k; ++j) max_cols = max(max_cols, ((p.mod[j].nc + 3) & ~3u) * p.Bp);
-    dim3 grid((max_cols + TC_BN - 1) / TC_BN, (p.v1 - p.v0 + TC_BM - 1) / TC_BM, p.k);
-    k_dense_tc<<<grid, TC_THREADS, TC_SMEM_BYTES, s>>>(maps, p);
+    const uint32_t mblocks = (p.v1 - p.v0 + TC_BM - 1) / TC_BM;
+    if (p.npix > 1 || p.conv) {
+        dim3 grid((max_cols + TC_BN - 1) / TC_BN, mblocks * p.npix, p.k);
+        k_dense_tc<true, TC_STAGES_CONV><<<grid, TC_THREADS, tc_smem_bytes(TC_STAGES_CONV), s>>>(maps, p);
+    } else {
+        dim3 grid((max_cols + TC_BN - 1) / TC_BN, mblocks, p.k);
+        k_dense_tc<false, TC_STAGES_DENSE><<<grid, TC_THREADS, tc_smem_bytes(TC_STAGES_DENSE), s>>>(maps, p);
+    }
     return cudaGetLastError();
 }
 

@@ -55,6 +55,10 @@ struct DenseTcParams {
     gc::ModInfo mod[MAXK];
     uint32_t M, K, Bp;
     uint32_t v0, v1;
+    uint32_t nkb;          /* 128-column K blocks of the weight matrix */
+    uint32_t b_box_bytes;  /* bytes one B box brings in (dense: 128*128) */
+    /* convolution: per output pixel one GEMM; box {128, f_w, f_h, cb} at {n, x*sx, y*sy, kb*cb} */
+    uint32_t conv, npix, ow, sx, sy, cb;
     int k;
 };
 
@@ -168,6 +172,8 @@ cudaError_t launch_egress(const uint8_t* plane, int16_t* dst, uint64_t n, uint32
                           cudaStream_t s);
 cudaError_t launch_linear(const LinearParams& p, cudaStream_t s);
 cudaError_t dense_tc_make_map(void* map_out, const void* ptr, uint64_t inner, uint64_t outer);
+cudaError_t conv_tc_make_map(void* map_out, const void* ptr, uint64_t row_bytes, uint64_t in_w, uint64_t in_h,
+                             uint64_t channels, uint32_t f_w, uint32_t f_h, uint32_t cb);
 cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p, cudaStream_t s);
 cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s);
 cudaError_t launch_projection(const ProjParams& p, cudaStream_t s);

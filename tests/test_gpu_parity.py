@@ -166,3 +166,37 @@ def test_dense_tensor_core_path(gpu, tmp_path, M, K, batch):
         want, _ = ref.cpu_evaluate([l[b] for l in labels], 4)
         assert_labels_equal([g[b] for g in got], want, "dense %dx%d inference %d" % (M, K, b))
     c.close()
+
+
+@pytest.mark.parametrize("geom", [
+    # (width, height, channels, filters, filter size, stride)
+    (8, 8, 8, 16, 3, 1),     # K = 72: one K block, 14 channels would fit
+    (10, 9, 20, 40, 3, 1),   # 20 channels = 14 + 6: second box partly out of bounds
+    (12, 12, 16, 32, 2, 2),  # 2x2/2 "pool replacement", K = 64
+    (9, 9, 33, 130, 2, 1),   # two filter blocks (130 > 128), 33 channels = 32 + 1
+    (7, 7, 3, 16, 5, 2),     # 5x5 filter: 5 channels per block, only 3 present
+])
+@pytest.mark.parametrize("batch", [1, 19])
+def test_conv_tensor_core_path(gpu, tmp_path, geom, batch):
+    """Convolutions wide enough for the tcgen05 kernel (im2col by a 4-D TMA
+    box, dense_tc.cu), followed by a ReLU; bit-exact against the reference
+    and against the dp4a kernel's result for the same circuit."""
+    import workloads as W
+    from oracle import refbind as R
+
+    if not R.available():
+        pytest.skip("oracle/_ref not present on this box")
+    w, h, ch, filters, f, stride = geom
+    spec = dict(input=(w, h, ch), layers=[("conv", filters, f, stride), ("relu",)], quant=("simple", 0.02), **W.cpm(8, 99.0))
+    ref = W.build_reference_circuit(spec, seed=w * h, weight_seed=filters)
+    path = str(tmp_path / "conv.gcm")
+    ref.export(path)
+    X = W.synthetic_inputs(spec, batch, seed=5)
+    per = [ref.garble_inputs(x) for x in X]
+    labels = [np.stack([p[j] for p in per]) for j in range(ref.k)]
+    c = gpu.Circuit.load(path, max_batch=batch)
+    got = c.evaluate(labels)
+    for b in sorted({0, batch - 1}):
+        want, _ = ref.cpu_evaluate([l[b] for l in labels], 4)
+        assert_labels_equal([g[b] for g in got], want, "conv %s inference %d" % (geom, b))
+    c.close()

@@ -111,6 +111,16 @@ def main():
             run_case("dense_%d" % dim, dict(input=(dim, 1, 1), layers=[("flatten",), ("dense", dim)],
                                             quant=("simple", 0.02), crt=W.PRIMES[:8], mrs=[], max_modulus=0), [1, 16, 256])
         run_case("MODEL_A", W.MODELS["MODEL_A"], [256])
+    elif what == "conv":
+        # the convolution shapes of MODEL_F_GNNP / MINIONN (32x32 CIFAR models), one layer each
+        for name, (w, h, ch, f, fs, st) in (("conv_30x30x32_32f3", (30, 30, 32, 32, 3, 1)),
+                                            ("conv_28x28x32_32f2s2", (28, 28, 32, 32, 2, 2)),
+                                            ("conv_14x14x32_64f3", (14, 14, 32, 64, 3, 1)),
+                                            ("conv_12x12x64_64f3", (12, 12, 64, 64, 3, 1)),
+                                            ("conv_5x5x64_128f3", (5, 5, 64, 128, 3, 1))):
+            run_case(name, dict(input=(w, h, ch), layers=[("conv", f, fs, st)], quant=("simple", 0.02),
+                                crt=[32, 3, 5, 7, 11, 13, 17], mrs=[], max_modulus=32), [16, 64])
+        run_case("MODEL_D_POOL_REPL", W.MODELS["MODEL_D_POOL_REPL"], [256])
     elif what == "micro":
         # benchmarks/micro_benchmarks/non_sgx/main.cpp:577-683 grids (subset that garbles in seconds)
         for n in (128, 1024, 4096):
