@@ -662,7 +662,6 @@ static int fill_rescale_static(dashb_circuit* c, Layer& L, uint64_t n, const int
         p.loff[j] = off;
         off += (c->crt_mi[j].nc + 3) & ~3u;
     }
-    if (off > LW_MAX) return fail(DASHB_EINVAL, "rescale: CRT base too wide for the per-thread workspace");
     /* Step 2 bookkeeping: sequential cipher counter over (factor, modulus) */
     bool ignored[MAXK] = {false};
     uint64_t cnt = 0;
@@ -688,6 +687,30 @@ static int fill_rescale_static(dashb_circuit* c, Layer& L, uint64_t n, const int
             p.inv_f[i][j] = (uint16_t)inv;
         }
     }
+    /* lazy-reduction form of step 2 (k_rescale): for residue j the updates
+     * w <- (w - p_i) * inv_i over its factors i collapse to w0*a1 + sum p_i*b1 */
+    for (int j = 0; j < k; ++j) {
+        const uint64_t q = (uint64_t)c->crt[j];
+        if ((uint64_t)(k + 1) * (q - 1) * (q - 1) >= 65536) p.wide = 1;
+        uint64_t suffix = 1; /* product of inv_f[i'][j] over the valid i' >= i */
+        for (int i = nf - 1; i >= 0; --i) {
+            if (p.tm_off[i][j] == ~0ull) continue;
+            suffix = suffix * p.inv_f[i][j] % q;
+            p.b1[i][j] = (uint16_t)((q - suffix) % q);
+        }
+        p.a1[j] = (uint16_t)suffix;
+    }
+    for (int i = 0; i < nf; ++i) { /* factor i's own residue: only the factors before it */
+        const int j = p.fidx[i];
+        const uint64_t q = (uint64_t)c->crt[j];
+        uint64_t suffix = 1;
+        for (int i2 = i - 1; i2 >= 0; --i2) {
+            if (p.tm_off[i2][j] == ~0ull) continue;
+            suffix = suffix * p.inv_f[i2][j] % q;
+            p.b1f[i][i2] = (uint16_t)((q - suffix) % q);
+        }
+        p.a1f[i] = (uint16_t)suffix;
+    }
     if (legacy) return DASHB_OK;
     /* base extension constants (base_extension_gadget.h:334-377) */
     int perm[MAXK], swapped[MAXK];
@@ -708,6 +731,16 @@ static int fill_rescale_static(dashb_circuit* c, Layer& L, uint64_t n, const int
             bcnt += n * (uint64_t)swapped[i];
             p.inv_partial[i][t] = (uint16_t)(int16_t)mul_inv((unsigned __int128)swapped[i], (uint16_t)swapped[t]);
         }
+    for (int t = 0; t < k; ++t) { /* lazy-reduction form of the eliminations into target t */
+        const uint64_t q = (uint64_t)swapped[t];
+        const int ni = t < p.non_ext ? t : p.non_ext;
+        uint64_t suffix = 1;
+        for (int i = ni - 1; i >= 0; --i) {
+            suffix = suffix * (p.inv_partial[i][t] % q) % q;
+            p.b2[i][t] = (uint16_t)((q - suffix) % q);
+        }
+        p.a2[t] = (uint16_t)suffix;
+    }
     for (int x = 0; x < nf; ++x) {
         int acc_i = 1; /* std::accumulate with an int accumulator (:351) */
         for (int j = 0; j < p.non_ext; ++j) acc_i = (int)((unsigned long)(long)acc_i * (unsigned long)swapped[j]);

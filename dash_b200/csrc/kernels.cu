@@ -23,7 +23,9 @@ using gc::u128;
 /* ------------------------------------------------------------ AES tables */
 /* Round keys of the fixed key 00..0f (crypto/cpu_aes_engine.h:23-25) as
  * big-endian words; uniform across a warp -> constant cache. */
-__constant__ uint32_t c_rk[44];
+__constant__ __align__(16) uint32_t c_rk[44];
+/* the number 4, kept where the compiler cannot fold it (see te_at) */
+__constant__ uint32_t c_four;
 /* T-table Te0 and the S-box; copied into shared memory by every CTA that
  * hashes (cuda_aes_engine.h:27-32 keeps four tables in __constant__, which
  * serialises divergent lookups). */
@@ -92,6 +94,9 @@ cudaError_t upload_aes_tables() {
     build_host_tables();
     cudaError_t e = cudaMemcpyToSymbol(c_rk, h_rk, sizeof(h_rk));
     if (e != cudaSuccess) return e;
+    const uint32_t four = 4;
+    e = cudaMemcpyToSymbol(c_four, &four, sizeof(four));
+    if (e != cudaSuccess) return e;
     e = cudaMemcpyToSymbol(g_te0, h_te[0], sizeof(h_te[0]));
     if (e != cudaSuccess) return e;
     return cudaMemcpyToSymbol(g_sbox, h_sbox, sizeof(h_sbox));
@@ -125,11 +130,52 @@ __device__ __forceinline__ ModInfo pin(const ModInfo& src) {
     return m;
 }
 
-/* One copy of the cipher per kernel (not inlined at its ~8 call sites): the
- * gadget kernels then fit the instruction cache (ncu: 24 % stall_no_inst
- * with the inlined version). */
+/* Te<TAB>[byte I of s].  The byte comes out with one PRMT (ALU pipe); the
+ * scaling to a table offset is a multiply by a constant the compiler cannot
+ * see (c_four, constant bank) so that it stays an IMAD on the FMA pipe: the
+ * ALU pipe is the busy one in the gadget kernels (ncu), and the usual
+ * shift+mask form puts two ALU operations on every one of the 160 lookups. */
+template <int TAB, int I>
+__device__ __forceinline__ uint32_t te_at(const AesSmem& a, uint32_t s, uint32_t four) {
+    const uint32_t byte = I == 0 ? (s & 0xffu) : __byte_perm(s, 0, 0x4440 + I);
+    const char* tab = reinterpret_cast<const char*>(TAB == 0 ? a.te0 : TAB == 1 ? a.te1 : TAB == 2 ? a.te2 : a.te3);
+    return *reinterpret_cast<const uint32_t*>(tab + byte * four);
+}
+
+template <int I>
+__device__ __forceinline__ uint32_t sbox_at(const AesSmem& a, uint32_t s) {
+    return a.sbox[I == 0 ? (s & 0xffu) : __byte_perm(s, 0, 0x4440 + I)];
+}
+
+/* H(x): AES-128 under the fixed key of x as 16 little-endian bytes
+ * (crypto/cpu_aes_engine.h:23-40).  Same function as gc::aes128_encrypt,
+ * which stays the host-checkable statement of the cipher.  One copy per
+ * kernel (not inlined at its ~8 call sites) with rolled rounds: the gadget
+ * kernels then fit the instruction cache (ncu: 24 % stall_no_inst when
+ * inlined and unrolled). */
 __device__ __noinline__ u128 hash(const AesSmem& a, u128 x) {
-    return gc::aes128_encrypt(x, a.te0, a.te1, a.te2, a.te3, a.sbox, c_rk);
+    const uint32_t four = c_four;
+    uint32_t s0 = gc::bswap32((uint32_t)x.lo) ^ c_rk[0];
+    uint32_t s1 = gc::bswap32((uint32_t)(x.lo >> 32)) ^ c_rk[1];
+    uint32_t s2 = gc::bswap32((uint32_t)x.hi) ^ c_rk[2];
+    uint32_t s3 = gc::bswap32((uint32_t)(x.hi >> 32)) ^ c_rk[3];
+#pragma unroll 1
+    for (int r = 1; r < 10; ++r) {
+        const uint4 k4 = reinterpret_cast<const uint4*>(c_rk)[r];
+        const uint32_t t0 = te_at<0, 3>(a, s0, four) ^ te_at<1, 2>(a, s1, four) ^ te_at<2, 1>(a, s2, four) ^ te_at<3, 0>(a, s3, four) ^ k4.x;
+        const uint32_t t1 = te_at<0, 3>(a, s1, four) ^ te_at<1, 2>(a, s2, four) ^ te_at<2, 1>(a, s3, four) ^ te_at<3, 0>(a, s0, four) ^ k4.y;
+        const uint32_t t2 = te_at<0, 3>(a, s2, four) ^ te_at<1, 2>(a, s3, four) ^ te_at<2, 1>(a, s0, four) ^ te_at<3, 0>(a, s1, four) ^ k4.z;
+        const uint32_t t3 = te_at<0, 3>(a, s3, four) ^ te_at<1, 2>(a, s0, four) ^ te_at<2, 1>(a, s1, four) ^ te_at<3, 0>(a, s2, four) ^ k4.w;
+        s0 = t0, s1 = t1, s2 = t2, s3 = t3;
+    }
+    const uint32_t o0 = (sbox_at<3>(a, s0) << 24) ^ (sbox_at<2>(a, s1) << 16) ^ (sbox_at<1>(a, s2) << 8) ^ sbox_at<0>(a, s3) ^ c_rk[40];
+    const uint32_t o1 = (sbox_at<3>(a, s1) << 24) ^ (sbox_at<2>(a, s2) << 16) ^ (sbox_at<1>(a, s3) << 8) ^ sbox_at<0>(a, s0) ^ c_rk[41];
+    const uint32_t o2 = (sbox_at<3>(a, s2) << 24) ^ (sbox_at<2>(a, s3) << 16) ^ (sbox_at<1>(a, s0) << 8) ^ sbox_at<0>(a, s1) ^ c_rk[42];
+    const uint32_t o3 = (sbox_at<3>(a, s3) << 24) ^ (sbox_at<2>(a, s0) << 16) ^ (sbox_at<1>(a, s1) << 8) ^ sbox_at<0>(a, s2) ^ c_rk[43];
+    u128 out;
+    out.lo = (uint64_t)gc::bswap32(o0) | ((uint64_t)gc::bswap32(o1) << 32);
+    out.hi = (uint64_t)gc::bswap32(o2) | ((uint64_t)gc::bswap32(o3) << 32);
+    return out;
 }
 
 __device__ __forceinline__ u128 ldg128(const u128* p) {
@@ -649,125 +695,233 @@ cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s) {
 /* ------------------------------------------------------------ rescale */
 /*
  * General-factor rescale with base extension, one thread per (element,
- * inference), all k residues' digits in a per-thread workspace.  CPU-only
- * in the reference ("Not yet implemented" on the GPU:
+ * inference).  CPU-only in the reference ("Not yet implemented" on the GPU:
  * gadgets/base_extension_gadget.h:297-315; rescale_gadget.h:364); follows
  * RescaleGadget::cpu_evaluate (gadgets/rescale_gadget.h:244-362) and
  * BaseExtensionGadget::cpu_evaluate (gadgets/base_extension_gadget.h:
  * 197-295).  Each source label is hashed once for all the projections that
  * key on it.  With P.legacy the kernel stops after step 2.3; the legacy
  * variant's sign gadget (k_sign) and downshift (k_add_label) follow.
+ *
+ * Two rearrangements of the reference's arithmetic, results identical:
+ *
+ * (1) Column order.  The reference eliminates row by row (for every source
+ *     residue, update all later residues), which needs the digits of all k
+ *     residues at once.  Here one target residue at a time takes all the
+ *     updates it will ever get, then is hashed (it becomes a source) or
+ *     stored; a thread keeps one residue's digits plus the 16-byte hashes.
+ *
+ * (2) Lazy reduction.  A chain of updates w <- (w - p_i) * inv_i (mod q) is
+ *     the linear form w0*A + sum_i p_i*B_i with A = prod inv_i and
+ *     B_i = -prod_{i' >= i} inv_i' (host constants, RescaleParams::a1..b2).
+ *     The digits of every projected label are multiplied by B_i and added
+ *     to an unreduced accumulator (shared memory, [digit][thread]); one
+ *     reduction mod q per digit at the end of the chain replaces one per
+ *     update.  16-bit accumulators where (k+1)(q-1)^2 < 2^16, else 32-bit.
  */
-__global__ void __launch_bounds__(128) k_rescale(const __grid_constant__ RescaleParams P) {
+constexpr int RS_THREADS = 128;
+
+/* acc[d] = ((x_j[d] + upshift_j[d]) mod q) * a   (step 1, pre-multiplied) */
+template <typename A>
+__device__ __forceinline__ void rs_init(A* acc, const uint8_t* plane, const uint8_t* up, const ModInfo& m, uint64_t e,
+                                        uint32_t b, uint32_t Bp, uint32_t a) {
+    const uint8_t* p = plane + plane_off(m, e, b, Bp);
+    for (uint32_t d4 = 0; d4 < nc4_of(m); ++d4) {
+        const uint32_t xw = *reinterpret_cast<const uint32_t*>(p + (uint64_t)d4 * 4 * Bp);
+        const uint32_t uw = __ldg(reinterpret_cast<const uint32_t*>(up) + d4);
+#pragma unroll
+        for (uint32_t t = 0; t < 4; ++t) {
+            if (4 * d4 + t >= m.nc) break;
+            uint32_t v = ((xw >> (8 * t)) & 0xff) + ((uw >> (8 * t)) & 0xff);
+            v = v >= m.q ? v - m.q : v;
+            acc[(4 * d4 + t) * RS_THREADS] = (A)(v * a);
+        }
+    }
+}
+
+/* acc[d] = label[d] * a for a broadcast label (zero padded u8[4*nc4]) */
+template <typename A>
+__device__ __forceinline__ void rs_set(A* acc, const uint8_t* label, const ModInfo& m, uint32_t a) {
+    for (uint32_t d = 0; d < m.nc; ++d) acc[d * RS_THREADS] = (A)(__ldg(label + d) * a);
+}
+
+/* acc[d] += digit_d(pr) * bcoef.  Not inlined (and the modulus by value, in
+ * registers): its three call sites share one copy of the long division, the
+ * kernel's hot loop then stays in the instruction cache (ncu showed
+ * stall_no_instruction 4.5 per issue with the inlined copies). */
+template <typename A>
+__device__ __noinline__ void rs_accumulate(A* acc, u128 pr, const ModInfo m, uint32_t bcoef) {
+    /* gc::for_each_digit with the digit loop unrolled by two and the
+     * accumulator pointer stepped instead of indexed */
+    uint32_t w[4] = {(uint32_t)pr.lo, (uint32_t)(pr.lo >> 32), (uint32_t)pr.hi, (uint32_t)(pr.hi >> 32)};
+    auto digits = [&](uint32_t r, uint32_t n, bool exact) {
+        uint32_t i = 0;
+        for (; i + 1 < n; i += 2) {
+            const uint32_t q1 = exact ? gc::div_q(r, m) : gc::div_q_any(r, m);
+            const uint32_t q2 = gc::div_q(q1, m);
+            acc[0] = (A)(acc[0] + (r - q1 * m.q) * bcoef);
+            acc[RS_THREADS] = (A)(acc[RS_THREADS] + (q1 - q2 * m.q) * bcoef);
+            acc += 2 * RS_THREADS;
+            r = q2;
+        }
+        if (i < n) {
+            const uint32_t q1 = exact ? gc::div_q(r, m) : gc::div_q_any(r, m);
+            acc[0] = (A)(acc[0] + (r - q1 * m.q) * bcoef);
+            acc += RS_THREADS;
+        }
+    };
+#pragma unroll 1
+    for (uint32_t c = 0; c + 1 < m.nchunks; ++c) digits(gc::divmod_Q(w, m, gc::limbs_before(m, c)), m.t, true);
+    /* most significant chunk: what is left of the value; an out-of-range
+     * payload can push it past the reciprocal's exact range on its first
+     * division (see gc::for_each_digit) */
+    digits(w[0], m.top_len, false);
+}
+
+/* reduce, compress and return the colour digit */
+template <typename A>
+__device__ __forceinline__ u128 rs_finish_compress(const A* acc, const ModInfo& m, uint32_t& colour) {
+    gc::Compressor c(m);
+    uint32_t dg = 0;
+    for (int d = (int)m.nc - 1; d >= 0; --d) {
+        dg = gc::mod_q(acc[d * RS_THREADS], m);
+        c.push(dg);
+    }
+    colour = dg;
+    return c.value();
+}
+
+/* plane <- ((acc mod q) * mul - down) mod q; mul == 1 / down == nullptr skip
+ * that step.  With next_a != 0 the accumulator restarts at (acc mod q) *
+ * next_a for the next chain. */
+template <typename A>
+__device__ __forceinline__ void rs_finish_store(A* acc, uint8_t* plane, const uint8_t* down, uint32_t mul, uint32_t next_a,
+                                                const ModInfo& m, uint64_t e, uint32_t b, uint32_t Bp) {
+    uint8_t* p = plane + plane_off(m, e, b, Bp);
+    for (uint32_t d4 = 0; d4 < nc4_of(m); ++d4) {
+        const uint32_t dw = down ? __ldg(reinterpret_cast<const uint32_t*>(down) + d4) : 0u;
+        uint32_t ow = 0;
+#pragma unroll
+        for (uint32_t t = 0; t < 4; ++t) {
+            const uint32_t d = 4 * d4 + t;
+            if (d >= m.nc) break;
+            uint32_t v = gc::mod_q(acc[d * RS_THREADS], m);
+            if (next_a) acc[d * RS_THREADS] = (A)(v * next_a);
+            if (mul != 1) v = gc::mod_q(v * mul, m);
+            if (down) {
+                v = v + m.q - ((dw >> (8 * t)) & 0xff);
+                v = v >= m.q ? v - m.q : v;
+            }
+            ow |= v << (8 * t);
+        }
+        *reinterpret_cast<uint32_t*>(p + (uint64_t)d4 * 4 * Bp) = ow;
+    }
+}
+
+template <typename A>
+__device__ __forceinline__ void rescale_body(const RescaleParams& P, const AesSmem& aes, A* acc, uint64_t e, uint32_t b) {
+    const int k = P.k;
+    /* Steps 1-2 for the factors' own residues: the hash each factor's
+     * trans-modulus projections key on (rescale_gadget.h:271-300).  A later
+     * factor's residue has first been divided by the earlier factors. */
+    u128 hf[MAXF];
+    uint32_t fcol[MAXF];
+#pragma unroll 1
+    for (int i = 0; i < P.nf; ++i) {
+        const int j = P.fidx[i];
+        const ModInfo m = pin(P.crt[j]);
+        rs_init(acc, P.in[j], P.up[j], m, e, b, P.Bp, P.a1f[i]);
+#pragma unroll 1
+        for (int i2 = 0; i2 < i; ++i2) {
+            if (P.tm_off[i2][j] == ~0ull) continue;
+            const u128 pr = gc::sub128(ldg128(P.tm + P.tm_off[i2][j] + e * (uint64_t)P.factor[i2] + fcol[i2]), hf[i2]);
+            rs_accumulate(acc, pr, m, P.b1f[i][i2]);
+        }
+        uint32_t colour;
+        const u128 key = rs_finish_compress(acc, m, colour);
+        hf[i] = hash(aes, key);
+        fcol[i] = colour;
+    }
+
+    /* every residue in turn, in the base extension's swapped order
+     * (base_extension_gadget.h:206-224: the factors' residues last) */
+    u128 h[MAXK];
+    uint32_t col[MAXK];
+#pragma unroll 1
+    for (int t = 0; t < k; ++t) {
+        const int jt = P.legacy ? t : P.perm[t];
+        const ModInfo m = pin(P.crt[jt]);
+        int x = -1; /* index among the factors, -1 for the others */
+        for (int i = 0; i < P.nf; ++i)
+            if (P.fidx[i] == jt) x = i;
+        if (x < 0) {
+            /* steps 1-2: upshift, then divide by every factor */
+            rs_init(acc, P.in[jt], P.up[jt], m, e, b, P.Bp, P.a1[jt]);
+#pragma unroll 1
+            for (int i = 0; i < P.nf; ++i) {
+                if (P.tm_off[i][jt] == ~0ull) continue;
+                const u128 pr = gc::sub128(ldg128(P.tm + P.tm_off[i][jt] + e * (uint64_t)P.factor[i] + fcol[i]), hf[i]);
+                rs_accumulate(acc, pr, m, P.b1[i][jt]);
+            }
+            /* step 4 for this residue (the base extension below only changes
+             * the factors' residues, base_extension_gadget.h:253-294); the
+             * accumulator restarts as the elimination's target */
+            rs_finish_store(acc, P.out[jt], P.legacy ? nullptr : P.down[jt], 1, P.legacy ? 0u : (uint32_t)P.a2[t], m, e, b, P.Bp);
+        } else if (P.legacy) {
+            /* step 2.3: the factor's residue is the zero label */
+            rs_set(acc, P.zero[jt], m, 1);
+            rs_finish_store(acc, P.out[jt], nullptr, 1, 0, m, e, b, P.Bp);
+        } else {
+            rs_set(acc, P.zero[jt], m, P.a2[t]);
+        }
+        if (P.legacy) continue;
+        /* step 3: garbled mixed-radix conversion, all eliminations of this target */
+        const int ni = t < P.non_ext ? t : P.non_ext;
+#pragma unroll 1
+        for (int i = 0; i < ni; ++i) {
+            const u128 pr = gc::sub128(ldg128(P.be + P.be_off[i][t] + e * (uint64_t)P.crt[P.perm[i]].q + col[i]), h[i]);
+            rs_accumulate(acc, pr, m, P.b2[i][t]);
+        }
+        if (x < 0) {
+            uint32_t colour;
+            const u128 key = rs_finish_compress(acc, m, colour);
+            h[t] = hash(aes, key);
+            col[t] = colour;
+        } else {
+            /* the extended residue is the last mixed-radix digit times -invv, then the downshift */
+            rs_finish_store(acc, P.out[jt], P.down[jt], P.neg_invv[x], 0, m, e, b, P.Bp);
+        }
+    }
+}
+
+template <typename A>
+__global__ void __launch_bounds__(RS_THREADS) k_rescale(const __grid_constant__ RescaleParams P) {
     __shared__ AesSmem aes;
+    extern __shared__ uint32_t s_rs[]; /* A [max nc][RS_THREADS] */
     aes_smem_load(aes);
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P.n * P.batch) return;
-    const uint32_t b = (uint32_t)(idx % P.batch);
-    const uint64_t e = P.e0 + idx / P.batch;
-    const int k = P.k;
-    uint8_t lw[LW_MAX];
-
-    /* Step 1: upshift */
-    for (int j = 0; j < k; ++j) {
-        const ModInfo m = pin(P.crt[j]);
-        const uint8_t* p = P.in[j] + plane_off(m, e, b, P.Bp);
-        uint8_t* w = lw + P.loff[j];
-        for (uint32_t d4 = 0; d4 < nc4_of(m); ++d4) {
-            const uint32_t xw = *reinterpret_cast<const uint32_t*>(p + (uint64_t)d4 * 4 * P.Bp);
-            const uint32_t uw = __ldg(reinterpret_cast<const uint32_t*>(P.up[j]) + d4);
-            for (uint32_t t = 0; t < 4; ++t) {
-                uint32_t v = ((xw >> (8 * t)) & 0xff) + ((uw >> (8 * t)) & 0xff);
-                w[4 * d4 + t] = (uint8_t)(v >= m.q ? v - m.q : v);
-            }
-        }
-    }
-    /* Step 2: divide by every factor */
-    for (int i = 0; i < P.nf; ++i) {
-        const int f = P.fidx[i];
-        const ModInfo mf = pin(P.crt[f]);
-        gc::Compressor c(mf);
-        for (int d = (int)mf.nc - 1; d >= 0; --d) c.push(lw[P.loff[f] + d]);
-        const uint32_t colour = lw[P.loff[f]];
-        const u128 hf = hash(aes, c.value());
-        for (int j = 0; j < k; ++j) {
-            if (P.tm_off[i][j] == ~0ull) continue; /* ignored modulus */
-            const ModInfo m = pin(P.crt[j]);
-            const u128 pr = gc::sub128(ldg128(P.tm + P.tm_off[i][j] + e * (uint64_t)P.factor[i] + colour), hf);
-            uint8_t* w = lw + P.loff[j];
-            const uint32_t inv = P.inv_f[i][j];
-            gc::for_each_digit(pr, m, [&](uint32_t d, uint32_t v) {
-                w[d] = (uint8_t)gc::mod_q(((uint32_t)w[d] + m.q - v) * inv, m);
-            });
-        }
-    }
-    /* Step 2.3: zero label on the factors' residues */
-    for (int i = 0; i < P.nf; ++i) {
-        const int f = P.fidx[i];
-        for (uint32_t d = 0; d < P.crt[f].nc; ++d) lw[P.loff[f] + d] = __ldg(P.zero[f] + d);
-    }
-    /* store residue j (after the downshift of step 4, unless legacy, where
-     * the sign gadget and k_add_label follow) */
-    auto store_residue = [&](int j) {
-        const ModInfo m = pin(P.crt[j]);
-        uint8_t* p = P.out[j] + plane_off(m, e, b, P.Bp);
-        const uint8_t* w = lw + P.loff[j];
-        for (uint32_t d4 = 0; d4 < nc4_of(m); ++d4) {
-            const uint32_t dw = __ldg(reinterpret_cast<const uint32_t*>(P.down[j]) + d4);
-            uint32_t ow = 0;
-            for (uint32_t t = 0; t < 4; ++t) {
-                const uint32_t d = 4 * d4 + t;
-                uint32_t v = d < m.nc ? w[d] : 0;
-                if (!P.legacy && d < m.nc) {
-                    v = v + m.q - ((dw >> (8 * t)) & 0xff);
-                    if (v >= m.q) v -= m.q;
-                }
-                ow |= v << (8 * t);
-            }
-            *reinterpret_cast<uint32_t*>(p + (uint64_t)d4 * 4 * P.Bp) = ow;
-        }
-    };
-    if (P.legacy) {
-        for (int j = 0; j < k; ++j) store_residue(j);
-        return;
-    }
-    /* The base extension only changes the factors' residues
-     * (base_extension_gadget.h:253-294): the others leave now, their
-     * workspace copies are consumed by the elimination below. */
-    for (int t = 0; t < P.non_ext; ++t) store_residue(P.perm[t]);
-    /* Step 3: base extension (garbled mixed-radix conversion) */
-    for (int i = 0; i < P.non_ext; ++i) {
-        const int ji = P.perm[i];
-        const ModInfo mi = pin(P.crt[ji]);
-        gc::Compressor c(mi);
-        for (int d = (int)mi.nc - 1; d >= 0; --d) c.push(lw[P.loff[ji] + d]);
-        const uint32_t colour = lw[P.loff[ji]];
-        const u128 hi = hash(aes, c.value());
-        for (int t = i + 1; t < k; ++t) {
-            const int jt = P.perm[t];
-            const ModInfo mt = pin(P.crt[jt]);
-            const u128 pr = gc::sub128(ldg128(P.be + P.be_off[i][t] + e * (uint64_t)mi.q + colour), hi);
-            uint8_t* w = lw + P.loff[jt];
-            const uint32_t inv = P.inv_partial[i][t];
-            gc::for_each_digit(pr, mt, [&](uint32_t d, uint32_t v) {
-                w[d] = (uint8_t)gc::mod_q(((uint32_t)w[d] + mt.q - v) * inv, mt);
-            });
-        }
-    }
-    for (int x = 0; x < P.nf; ++x) {
-        /* the extended residue is the last mixed-radix digit times -invv */
-        const int j = P.extra_idx[x];
-        const ModInfo m = pin(P.crt[j]);
-        uint8_t* w = lw + P.loff[j];
-        for (uint32_t d = 0; d < m.nc; ++d) w[d] = (uint8_t)gc::mod_q((uint32_t)w[d] * P.neg_invv[x], m);
-        store_residue(j);
-    }
+    rescale_body<A>(P, aes, reinterpret_cast<A*>(s_rs) + threadIdx.x, P.e0 + idx / P.batch, (uint32_t)(idx % P.batch));
 }
 
 cudaError_t launch_rescale(const RescaleParams& p, cudaStream_t s) {
     if (p.n == 0) return cudaSuccess;
     const uint64_t total = p.n * p.batch;
-    k_rescale<<<(unsigned)((total + 127) / 128), 128, 0, s>>>(p);
+    const unsigned grid = (unsigned)((total + RS_THREADS - 1) / RS_THREADS);
+    uint32_t nc = 0;
+    for (int j = 0; j < p.k; ++j) nc = max(nc, p.crt[j].nc);
+    if (p.wide) {
+        static bool opted_in[MAX_DEVICES];
+        const int dev = initialised_device();
+        if (dev >= 0 && dev < MAX_DEVICES && !opted_in[dev]) { /* 128 digits x 128 threads x 4 B */
+            cudaError_t e = cudaFuncSetAttribute(k_rescale<uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * RS_THREADS * 4);
+            if (e != cudaSuccess) return e;
+            opted_in[dev] = true;
+        }
+        k_rescale<uint32_t><<<grid, RS_THREADS, (size_t)nc * RS_THREADS * 4, s>>>(p);
+    } else {
+        k_rescale<uint16_t><<<grid, RS_THREADS, (size_t)nc * RS_THREADS * 2, s>>>(p);
+    }
     return cudaGetLastError();
 }
 

@@ -23,7 +23,6 @@ namespace dashb {
 constexpr int MAXK = 12;   /* CRT moduli */
 constexpr int MAXM = 12;   /* MRS digits */
 constexpr int MAXF = 4;    /* rescale factors */
-constexpr int LW_MAX = 640; /* sum of nc over the CRT base that a rescale thread keeps */
 
 struct LinearParams {
     const uint8_t* in[MAXK];
@@ -97,7 +96,7 @@ struct RescaleParams {
     const uint8_t* up[MAXK];    /* upshift label digits (u8[4*nc4_j], zero padded) */
     const uint8_t* down[MAXK];  /* downshift label digits */
     const uint8_t* zero[MAXK];  /* zero label digits */
-    uint32_t loff[MAXK];        /* offset of residue j in the thread's digit workspace */
+    uint32_t loff[MAXK];        /* (unused by the kernel) running offset of residue j's digits */
     const gc::u128* tm;
     const gc::u128* be;
     uint64_t tm_off[MAXF][MAXK]; /* row offset of block (factor i, modulus j) */
@@ -115,6 +114,15 @@ struct RescaleParams {
     uint32_t batch, Bp;
     int k, nf, non_ext;
     int legacy;                  /* 1: stop after step 2.3 (sign gadget and downshift follow) */
+    /* lazy-reduction constants (see k_rescale): a chain of updates
+     * w <- (w - p_i) * inv_i is w0*a + sum_i p_i*b_i (mod q) */
+    uint16_t a1[MAXK];           /* step 2 on residue j: product of the factors' inverses */
+    uint16_t b1[MAXF][MAXK];     /* coefficient of factor i's projection into residue j */
+    uint16_t a1f[MAXF];          /* same for factor i's own residue (earlier factors only) */
+    uint16_t b1f[MAXF][MAXF];
+    uint16_t a2[MAXK];           /* base extension, target t (swapped order) */
+    uint16_t b2[MAXK][MAXK];     /* coefficient of source i's projection into target t */
+    int wide;                    /* 1: some (k+1)(q-1)^2 >= 2^16, use 32-bit accumulators */
 };
 
 struct AddLabelParams {

@@ -59,7 +59,8 @@ def _live(name, gpu, tmp_path, batch, seed=77):
 
 
 @pytest.mark.parametrize("name,batch", [("MNIST_TINY_CNN", 33), ("CIFAR_TINY_SCALE", 20), ("SIGN_TINY", 64),
-                                        ("MODEL_E_30", 5), ("RESCALE_LEGACY", 48)])
+                                        ("MODEL_E_30", 5), ("RESCALE_LEGACY", 48), ("RESCALE_2_3", 37),
+                                        ("RESCALE_OPT", 9)])
 def test_live_reference_circuits(gpu, tmp_path, name, batch):
     ref, oc, labels, c, got = _live(name, gpu, tmp_path, batch)
     vals, ok = c.decode_outputs()
@@ -70,6 +71,31 @@ def test_live_reference_circuits(gpu, tmp_path, name, batch):
         assert_labels_equal([g[b] for g in got], want, "%s inference %d vs reference" % (name, b))
         assert_labels_equal(oc.evaluate(lab, threads=4), want, "%s oracle vs reference" % name)
         assert np.array_equal(vals[b], ref.decode_outputs(want))
+    c.close()
+
+
+def test_rescale_wide_accumulators(gpu, tmp_path):
+    """CRT base {2,3,251}: (k+1)(q-1)^2 >= 2^16, so k_rescale runs with its
+    32-bit accumulators.  Labels only: this base is outside the range where
+    the reference's own decode finds a match."""
+    import workloads as W
+    from oracle import refbind as R
+
+    if not R.available():
+        pytest.skip("oracle/_ref not present on this box")
+    spec = W.MODELS["RESCALE_WIDE"]
+    ref = W.build_reference_circuit(spec, seed=77, weight_seed=77)
+    path = str(tmp_path / "rw.gcm")
+    ref.export(path)
+    batch = 21
+    X = W.synthetic_inputs(spec, batch, seed=77)
+    per = [ref.garble_inputs(x) for x in X]
+    labels = [np.stack([p[j] for p in per]) for j in range(ref.k)]
+    c = gpu.Circuit.load(path, max_batch=batch)
+    got = c.evaluate(labels)
+    for b in range(batch):
+        want, _ = ref.cpu_evaluate([l[b] for l in labels], 2)
+        assert_labels_equal([g[b] for g in got], want, "RESCALE_WIDE inference %d" % b)
     c.close()
 
 

@@ -22,6 +22,7 @@
 #include <vector>
 #include <cuda_runtime.h>
 
+static int g_reps = 10, g_warm = 3;
 static uint8_t h_sbox[256];
 static uint32_t h_te[4][256];
 static uint32_t h_rk[44];
@@ -235,9 +236,9 @@ static int run_rep(int total_threads, int chain, uint4* d_out) {
     CK(cudaEventCreate(&e1));
     const int ctas = total_threads / THREADS;
     CK(cudaFuncSetAttribute(k_chain_rep<THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32768));
-    for (int w = 0; w < 3; ++w) k_chain_rep<THREADS><<<ctas, THREADS, 32768>>>(d_out, chain, 128);
+    for (int w = 0; w < g_warm; ++w) k_chain_rep<THREADS><<<ctas, THREADS, 32768>>>(d_out, chain, 128);
     CK(cudaDeviceSynchronize());
-    const int reps = 10;
+    const int reps = g_reps;
     CK(cudaEventRecord(e0));
     for (int r = 0; r < reps; ++r) k_chain_rep<THREADS><<<ctas, THREADS, 32768>>>(d_out, chain, 128);
     CK(cudaEventRecord(e1));
@@ -259,9 +260,9 @@ static int run(int ctas, int chain, uint4* d_out, double* rate) {
     cudaEvent_t e0, e1;
     CK(cudaEventCreate(&e0));
     CK(cudaEventCreate(&e1));
-    for (int w = 0; w < 3; ++w) k_chain<V><<<ctas, 128>>>(d_out, chain, 4);
+    for (int w = 0; w < g_warm; ++w) k_chain<V><<<ctas, 128>>>(d_out, chain, 4);
     CK(cudaDeviceSynchronize());
-    const int reps = 10;
+    const int reps = g_reps;
     CK(cudaEventRecord(e0));
     for (int r = 0; r < reps; ++r) k_chain<V><<<ctas, 128>>>(d_out, chain, 4);
     CK(cudaEventRecord(e1));
@@ -282,6 +283,7 @@ static int run(int ctas, int chain, uint4* d_out, double* rate) {
 int main(int argc, char** argv) {
     build_tables();
     const int chain = argc > 1 ? atoi(argv[1]) : 88;
+    if (argc > 2) g_reps = atoi(argv[2]), g_warm = 0; /* for a profiler: no warm-up, few launches */
     int sms = 148;
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, 0));

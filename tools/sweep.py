@@ -121,6 +121,16 @@ def main():
             run_case(name, dict(input=(w, h, ch), layers=[("conv", f, fs, st)], quant=("simple", 0.02),
                                 crt=[32, 3, 5, 7, 11, 13, 17], mrs=[], max_modulus=32), [16, 64])
         run_case("MODEL_D_POOL_REPL", W.MODELS["MODEL_D_POOL_REPL"], [256])
+    elif what == "rescale1":  # one case, for a profiler
+        run_case("rescale32_n16384", dict(input=(16384, 1, 1), layers=[("flatten",), ("rescale", (32,))], quant=("simple", 1.0),
+                                          crt=W.SCALE_CRT, mrs=W.SCALE_MRS, max_modulus=32), [64], steps=2, cpu_reps=1, check=1)
+    elif what == "rescale":
+        # C3/C4 scaling gadget: factor 32 on the {32,3,5,7,11,13,17} base, and the k=8 prime base with factor 2
+        for n in (1024, 16384):
+            run_case("rescale32_n%d" % n, dict(input=(n, 1, 1), layers=[("flatten",), ("rescale", (32,))], quant=("simple", 1.0),
+                                               crt=W.SCALE_CRT, mrs=W.SCALE_MRS, max_modulus=32), [16, 256] if n == 1024 else [64])
+        run_case("rescale2_n4096", dict(input=(4096, 1, 1), layers=[("flatten",), ("rescale", (2,))],
+                                        quant=("simple", 1.0), **W.cpm(8)), [256])
     elif what == "micro":
         # benchmarks/micro_benchmarks/non_sgx/main.cpp:577-683 grids (subset that garbles in seconds)
         for n in (128, 1024, 4096):

@@ -104,6 +104,9 @@ MODELS = {
                         **cpm(6)),
     "RESCALE_OPT": dict(input=(4, 1, 1), layers=[("flatten",), ("dense", 3), ("rescale", (32,)), ("relu",)],
                         quant=("simple", 0.05), crt=[32, 97, 107], mrs=[22, 19, 15, 13], max_modulus=107),
+    # a modulus large enough for k_rescale's 32-bit accumulators ((k+1)(q-1)^2 >= 2^16)
+    "RESCALE_WIDE": dict(input=(6, 1, 1), layers=[("flatten",), ("rescale", (2,))], quant=("simple", 1.0),
+                         crt=[2, 3, 251], mrs=[], max_modulus=255),
     "PROJECTION": dict(input=(4, 1, 1), layers=[("flatten",), ("projection", [19], [91], 0),
                                                 ("projection", [91], [19], 0)],
                        quant=("simple", 1.0), crt=[19], mrs=[], max_modulus=100),   # test_projection.h:18-50
