@@ -206,15 +206,28 @@ GC_HD void for_each_digit2(u128 x, u128 y, const ModInfo& m, F&& f) {
     }
 }
 
-/* Colour digit of a compressed label: x mod q (q divides Q). */
-GC_HD uint32_t colour_of(u128 x, const ModInfo& m) {
-    uint32_t rs = 0;
-    (void)div_step(rs, (uint32_t)(x.hi >> 32), m);
-    (void)div_step(rs, (uint32_t)x.hi, m);
-    (void)div_step(rs, (uint32_t)(x.lo >> 32), m);
-    (void)div_step(rs, (uint32_t)x.lo, m);
-    return mod_q(rs >> m.s, m);
+/* Colour digit of a compressed label: x mod q, from the residues of the
+ * limb weights 2^32, 2^64, 2^96 mod q (a dozen multiply-adds instead of a
+ * four-limb long division).  The constants depend on the modulus only. */
+struct ColourConsts {
+    uint32_t c16, c32, c64, c96; /* 2^16, 2^32, 2^64, 2^96 mod q */
+};
+GC_HD ColourConsts colour_consts(const ModInfo& m) {
+    ColourConsts c;
+    c.c16 = mod_q(65536u, m);
+    c.c32 = mod_q(c.c16 * c.c16, m);
+    c.c64 = mod_q(c.c32 * c.c32, m);
+    c.c96 = mod_q(c.c64 * c.c32, m);
+    return c;
 }
+GC_HD uint32_t colour_of(u128 x, const ModInfo& m, const ColourConsts& c) {
+    const uint64_t s = (uint64_t)(uint32_t)x.lo + (uint64_t)(uint32_t)(x.lo >> 32) * c.c32 + (uint64_t)(uint32_t)x.hi * c.c64 +
+                       (uint64_t)(uint32_t)(x.hi >> 32) * c.c96; /* < 2^42 */
+    const uint32_t sl = (uint32_t)s, sh = (uint32_t)(s >> 32);
+    const uint32_t r1 = mod_q((sl >> 16) * c.c16 + (sl & 0xffffu), m); /* < 2^24 + 2^16 <= lim */
+    return mod_q(sh * c.c32 + r1, m);
+}
+GC_HD uint32_t colour_of(u128 x, const ModInfo& m) { return colour_of(x, m, colour_consts(m)); }
 
 /*
  * Horner accumulation of digits fed most significant first, chunk-wise:

@@ -533,11 +533,29 @@ namespace dashb {
 constexpr int SIGN_THREADS = DASHB_SIGN_THREADS;
 
 /* digit-wise accumulation of a compressed label (no reduction: at most k+1
- * digits below 2^11 are summed) */
-__device__ __forceinline__ void accumulate(u128 x, const ModInfo& m, uint16_t* acc) {
-    gc::for_each_digit(x, m, [&](uint32_t d, uint32_t v) {
-        acc[d * SIGN_THREADS] = (uint16_t)(acc[d * SIGN_THREADS] + v);
-    });
+ * digits below 2^11 are summed).  One copy per kernel, digit loop unrolled
+ * by two, accumulator pointer stepped (see rs_accumulate). */
+__device__ __noinline__ void accumulate(u128 x, const ModInfo m, uint16_t* acc) {
+    uint32_t w[4] = {(uint32_t)x.lo, (uint32_t)(x.lo >> 32), (uint32_t)x.hi, (uint32_t)(x.hi >> 32)};
+    auto digits = [&](uint32_t r, uint32_t n, bool exact) {
+        uint32_t i = 0;
+        for (; i + 1 < n; i += 2) {
+            const uint32_t q1 = exact ? gc::div_q(r, m) : gc::div_q_any(r, m);
+            const uint32_t q2 = gc::div_q(q1, m);
+            acc[0] = (uint16_t)(acc[0] + (r - q1 * m.q));
+            acc[SIGN_THREADS] = (uint16_t)(acc[SIGN_THREADS] + (q1 - q2 * m.q));
+            acc += 2 * SIGN_THREADS;
+            r = q2;
+        }
+        if (i < n) {
+            const uint32_t q1 = exact ? gc::div_q(r, m) : gc::div_q_any(r, m);
+            acc[0] = (uint16_t)(acc[0] + (r - q1 * m.q));
+            acc += SIGN_THREADS;
+        }
+    };
+#pragma unroll 1
+    for (uint32_t c = 0; c + 1 < m.nchunks; ++c) digits(gc::divmod_Q(w, m, gc::limbs_before(m, c)), m.t, true);
+    digits(w[0], m.top_len, false);
 }
 
 /* compress(acc mod q) and the colour of the sum */
@@ -601,6 +619,7 @@ __global__ void __launch_bounds__(SIGN_THREADS) k_sign(const __grid_constant__ S
          * dynamically indexed parameter bank at every use */
         const ModInfo M = pin(P.mrs[i]);
         const ModInfo C = pin(P.cast[i]);
+        const gc::ColourConsts cc = gc::colour_consts(M);
         for (uint32_t d = 0; d < C.nc; ++d) acc[d * SIGN_THREADS] = 0;
 #pragma unroll 1
         for (int j = 0; j <= k; ++j) {
@@ -611,7 +630,7 @@ __global__ void __launch_bounds__(SIGN_THREADS) k_sign(const __grid_constant__ S
                                  h[j]);
             /* Step 2.2: cast to modulus (k+1)*m_i */
             const u128 hl = hash(aes, lab);
-            const uint32_t c0 = gc::colour_of(lab, M);
+            const uint32_t c0 = gc::colour_of(lab, M, cc);
             accumulate(gc::sub128(ldg128(P.cast1 + cnt1 + (uint64_t)j * M.q + c0), hl), C, acc);
         }
         cnt1 += (uint64_t)(k + 1) * M.q;
