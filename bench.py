@@ -320,6 +320,9 @@ def main():
         "timing": "CUDA events around every layer, sub-batch lanes serialised on the library stream, %d steps after the timed region" % prof_steps,
         "share_of_step": relu_ms / step_ms if step_ms else None,
         "aes_blocks_per_s": relu_aes / (relu_ms / 1e3) if relu_ms > 0 else 0.0,
+        "aes_blocks_per_s_in_step": circ.aes_blocks(-1) * B * args.steps / (ms_dev / 1e3),
+        "aes_only_kernel_peak_blocks_per_s": 19.1e9,
+        "aes_peak_source": "tools/aes_probe.cu on a B200, same 4 KB shared-memory T-table layout (profiles/r1_aes_probe.md)",
         "note": "compute-bound on AES + base-q digit arithmetic, not on HBM (see DESIGN.md)",
         "whole_step_algorithmic_GBps": circ.algorithmic_bytes(-1) * B / (step_ms / 1e3) / 1e9 if step_ms else None,
         "layer_ms": by_type,

@@ -106,6 +106,9 @@ def main():
             run_case(name, W.MODELS[name], bs)
     elif what == "gnnp":
         run_case("MODEL_F_GNNP_POOL_REPL", W.MODELS["MODEL_F_GNNP_POOL_REPL"], [16], steps=3, cpu_reps=1, check=1)
+    elif what == "dense1":  # one case, for a profiler
+        run_case("dense_2048", dict(input=(2048, 1, 1), layers=[("flatten",), ("dense", 2048)],
+                                    quant=("simple", 0.02), crt=W.PRIMES[:8], mrs=[], max_modulus=0), [256], steps=2, cpu_reps=1, check=1)
     elif what == "dense":
         for dim in (128, 512, 2048):
             run_case("dense_%d" % dim, dict(input=(dim, 1, 1), layers=[("flatten",), ("dense", dim)],
