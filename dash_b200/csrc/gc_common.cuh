@@ -42,6 +42,13 @@ GC_HD u128 sub128(u128 a, u128 b) {
     return r;
 }
 
+GC_HD u128 add128(u128 a, u128 b) {
+    u128 r;
+    r.lo = a.lo + b.lo;
+    r.hi = a.hi + b.hi + (r.lo < a.lo ? 1u : 0u);
+    return r;
+}
+
 GC_HD uint64_t mulhi64(uint64_t a, uint64_t b) {
 #if defined(__CUDA_ARCH__)
     return __umul64hi(a, b);

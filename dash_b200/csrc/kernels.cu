@@ -1057,3 +1057,5 @@ cudaError_t launch_decode(const DecodeParams& p, cudaStream_t s) {
 }
 
 }  // namespace dashb
+
+#include "garble_kernels.cuh"

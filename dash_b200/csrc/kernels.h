@@ -161,6 +161,56 @@ struct DecodeParams {
     int k;
 };
 
+/* ---- GPU garbler (garble_kernels.cuh, garbler.cu) ---- */
+constexpr uint32_t GB_NONE = 0xffffffffu;
+enum { GB_TERM_PLANE = 1, GB_TERM_CONST = 2, GB_TERM_PRF = 3 };
+enum { GB_F_ID = 0, GB_F_LOOKUP, GB_F_DIV, GB_F_SIGN, GB_F_MULR, GB_F_NEGSUM, GB_F_ADDR };
+enum { GB_MODE_PROJ = 0, GB_MODE_MINI = 1, GB_MODE_DEC = 2 };
+constexpr int GB_MAXTERMS = 14;
+
+/* one summand of a label: coef * (label of input plane `arg` | constant label
+ * at byte offset `arg` of GarbleParams::labels | PRF label with tag `arg`) */
+struct GateTerm {
+    uint32_t kind, coef;
+    uint64_t arg;
+};
+
+/* one projection gate (or, with q_in == 0, just an output label) per element */
+struct GateDesc {
+    uint32_t q_in, q_out;
+    uint32_t n_in, n_out;
+    GateTerm in[GB_MAXTERMS];   /* the gate's input base label, modulus q_in */
+    GateTerm out[GB_MAXTERMS];  /* its output base label, modulus q_out */
+    uint32_t off_plane;         /* payload offset label: GB_NONE = R_{q_out}, else that input plane's label */
+    uint32_t r_plane;           /* r = colour digit of that input plane's label (half gates), GB_NONE: 0 */
+    uint32_t f;                 /* GB_F_* */
+    int32_t fa, fb, fc;
+    uint64_t flut;              /* GB_F_LOOKUP: device pointer, value of v at flut[v * flut_stride] */
+    uint32_t flut_stride;
+    uint32_t mode;              /* GB_MODE_* */
+    uint32_t table;             /* index into GarbleParams::tables */
+    int32_t out_plane;          /* >= 0: store the output label to that output plane */
+    uint64_t table_off, table_stride; /* rows at table_off + element * table_stride (+ colour) */
+};
+
+struct GarbleParams {
+    const GateDesc* desc;
+    uint32_t n_desc;
+    uint32_t nc_max;            /* longest label (digits) any descriptor touches */
+    uint64_t n;                 /* elements */
+    const uint8_t* in[MAXK];    /* input base labels, u8 [element][4*nc4] */
+    uint32_t in_nc[MAXK];
+    uint8_t* out[MAXK];         /* output base labels, same layout */
+    gc::u128* tables[16];
+    const gc::ModInfo* mods;    /* indexed by modulus */
+    const uint8_t* labels;      /* constant labels: u8 digits, addressed by byte offset */
+    const uint32_t* r_off;      /* byte offset of the offset label R_q, indexed by modulus */
+    uint64_t layer_tag;
+};
+
+cudaError_t garbler_set_prf_key(const uint32_t rk[44]);
+cudaError_t launch_garble_gates(const GarbleParams& p, cudaStream_t s);
+
 /* small services of dashb_api.cu for entry points that live next to their
  * kernels (dashb_projection_static) */
 gc::ModInfo modinfo_for(uint32_t q);

@@ -1,0 +1,60 @@
+"""ctypes front end of dashb_garble_to_file (include/dash_b200_garble.h): the
+offline phase on the GPU.  A plaintext circuit is a list of layer dicts:
+
+    {"type": "dense", "M": m, "K": k, "channel_tf": 0, "weights": int64 [M][K], "biases": int64 [M]}
+    {"type": "conv2d", "geom": (in_w, in_h, channels, filters, f_w, f_h, s_w, s_h),
+     "weights": int64 (reference order), "biases": int64 [filters]}
+    {"type": "relu"} | {"type": "sign"} | {"type": "rescale", "factors": (32,)}
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import api
+
+TYPES = {"dense": 1, "conv2d": 2, "relu": 3, "sign": 4, "rescale": 5}
+
+
+class PlainLayer(C.Structure):
+    _fields_ = [("p", C.c_int64 * 16), ("weights", C.c_void_p), ("biases", C.c_void_p)]
+
+
+class GarbleStats(C.Structure):
+    _fields_ = [("kernel_ms", C.c_double), ("total_ms", C.c_double), ("gates", C.c_uint64), ("rows", C.c_uint64),
+                ("table_bytes", C.c_uint64)]
+
+
+def garble_to_file(crt, mrs, input_size, layers, path, seed=b"dash-b200-garble", max_modulus=0):
+    """Garbles `layers` on the current device and writes the DGCM material to
+    `path`.  Returns the statistics as a dict."""
+    L = api.lib()
+    L.dashb_garble_to_file.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_int,
+                                       C.c_char_p, C.c_char_p, C.c_void_p]
+    arr = (PlainLayer * len(layers))()
+    keep = []
+    for i, l in enumerate(layers):
+        t = TYPES[l["type"]]
+        arr[i].p[0] = t
+        if t == 1:
+            arr[i].p[1], arr[i].p[2], arr[i].p[3] = int(l["M"]), int(l["K"]), int(l.get("channel_tf", 0))
+        elif t == 2:
+            for x, v in enumerate(l["geom"]):
+                arr[i].p[1 + x] = int(v)
+        elif t == 5:
+            arr[i].p[2] = len(l["factors"])
+            for x, v in enumerate(l["factors"]):
+                arr[i].p[3 + x] = int(v)
+        if t in (1, 2):
+            w = np.ascontiguousarray(l["weights"], dtype=np.int64).ravel()
+            b = np.ascontiguousarray(l["biases"], dtype=np.int64).ravel()
+            keep += [w, b]
+            arr[i].weights = w.ctypes.data
+            arr[i].biases = b.ctypes.data
+    crt_a = np.ascontiguousarray(crt, dtype=np.int32)
+    mrs_a = np.ascontiguousarray(mrs if len(mrs) else [0], dtype=np.int32)
+    seed = (bytes(seed) + b"\0" * 16)[:16]
+    st = GarbleStats()
+    api._check(L.dashb_garble_to_file(crt_a.ctypes.data, len(crt), mrs_a.ctypes.data, len(mrs), int(max_modulus),
+                                      int(input_size), C.byref(arr), len(layers), seed, os.fsencode(path), C.byref(st)))
+    return {f: getattr(st, f) for f, _ in GarbleStats._fields_}

@@ -1,0 +1,88 @@
+"""The GPU garbler (include/dash_b200_garble.h): material
+garbled on the B200 must evaluate -- on the pinned CPU oracle and on the GPU
+evaluator -- to exactly the values the reference-garbled circuit decodes to
+for the same plaintext inputs, and must have the reference's structure."""
+import numpy as np
+import pytest
+
+from helpers import assert_labels_equal
+
+pytestmark = pytest.mark.gpu
+
+CASES = [("MLP_TINY", 9), ("MNIST_TINY_CNN", 7), ("CIFAR_TINY_SCALE", 6), ("SIGN_TINY", 11), ("RESCALE_2_3", 5),
+         ("RESCALE_OPT", 4), ("RELU_99", 8), ("RESCALE_2", 3)]
+
+
+@pytest.mark.parametrize("name,batch", CASES)
+def test_gpu_garbled_circuit_evaluates_like_the_reference(gpu, tmp_path, name, batch):
+    import workloads as W
+    from dash_b200 import garble, gcm
+    from oracle import oraclebind as O
+    from oracle import refbind as R
+
+    if not R.available():
+        pytest.skip("oracle/_ref not present on this box")
+    spec = W.MODELS[name]
+    ref = W.build_reference_circuit(spec, seed=5, weight_seed=5)
+    ref_path = str(tmp_path / "ref.gcm")
+    ref.export(ref_path)
+    gref = gcm.read_gcm(ref_path)
+    plain = gcm.plain_circuit(gref)
+
+    gpu_path = str(tmp_path / "gpu.gcm")
+    stats = garble.garble_to_file(gref["crt"], gref["mrs"], gref["input_size"], plain, gpu_path, seed=b"seed-%s" % name.encode(),
+                                  max_modulus=gref["max_modulus"])
+    assert stats["gates"] > 0 or all(l["type"] in ("dense", "conv2d") for l in plain)
+    ggpu = gcm.read_gcm(gpu_path)
+    # same structure as the reference's material: layer types, parameters, size of every table
+    assert len(ggpu["layers"]) == len(gref["layers"])
+    for a, b in zip(ggpu["layers"], gref["layers"]):
+        assert list(a["p"][:12]) == list(b["p"][:12])
+        assert [len(x) for x in a["arrays"]] == [len(x) for x in b["arrays"]]
+    assert {j: len(v) for j, v in ggpu["dec"].items()} == {j: len(v) for j, v in gref["dec"].items()}
+
+    X = W.synthetic_inputs(spec, batch, seed=9)
+    want = []
+    for x in X:
+        lab = ref.garble_inputs(x)
+        out, _ = ref.cpu_evaluate(lab, 2)
+        want.append(ref.decode_outputs(out))
+    want = np.array(want)
+
+    c = gpu.Circuit.load(gpu_path, max_batch=batch)
+    c.garble_inputs(np.asarray(X, dtype=np.int64).reshape(batch, -1))
+    c.evaluate_device()
+    got_labels = c.move_outputs()
+    vals, ok = c.decode_outputs()
+    assert ok.all(), "outputs of the GPU-garbled circuit do not decode"
+    assert np.array_equal(vals, want.reshape(vals.shape))
+
+    oc = O.OracleCircuit(gpu_path)
+    for b in range(batch):
+        lab = gcm.encode_inputs(ggpu, X[b])
+        out = oc.evaluate(lab, threads=2)
+        assert_labels_equal([g[b] for g in got_labels], out, "%s: oracle vs GPU evaluator on GPU-garbled material, inference %d" % (name, b))
+        v, missing = oc.decode(out)
+        assert missing == 0 and np.array_equal(v, want[b].ravel())
+    c.close()
+
+
+def test_same_seed_same_circuit_other_seed_other_labels(gpu, tmp_path):
+    import workloads as W
+    from dash_b200 import garble, gcm
+    from oracle import refbind as R
+
+    if not R.available():
+        pytest.skip("oracle/_ref not present on this box")
+    spec = W.MODELS["MLP_TINY"]
+    ref = W.build_reference_circuit(spec, seed=5, weight_seed=5)
+    ref.export(str(tmp_path / "ref.gcm"))
+    gref = gcm.read_gcm(str(tmp_path / "ref.gcm"))
+    plain = gcm.plain_circuit(gref)
+    paths = []
+    for i, seed in enumerate((b"one", b"one", b"two")):
+        p = str(tmp_path / ("g%d.gcm" % i))
+        garble.garble_to_file(gref["crt"], gref["mrs"], gref["input_size"], plain, p, seed=seed, max_modulus=gref["max_modulus"])
+        paths.append(open(p, "rb").read())
+    assert paths[0] == paths[1]
+    assert paths[0] != paths[2] and len(paths[0]) == len(paths[2])
