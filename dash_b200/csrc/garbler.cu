@@ -780,8 +780,9 @@ extern "C" int dashb_garble_to_file(const int32_t* crt_base, int k, const int32_
         G.P *= G.crt[j];
     }
     for (int i = 0; i < n_mrs; ++i) need = std::max(need, i == 0 ? G.mrs[0] : (k + 1) * G.mrs[i]);
-    if (max_modulus == 0) max_modulus = need;
-    if (max_modulus < need || max_modulus > 1024) return report_error(DASHB_EINVAL, "garbler: max_modulus %d does not cover the gadget moduli (need %d)", max_modulus, need);
+    /* a given max_modulus only ever raises the computed one (garbled_circuit_interface.h:128-135) */
+    if (max_modulus < need) max_modulus = need;
+    if (max_modulus > 1024) return report_error(DASHB_EINVAL, "garbler: max_modulus %d too large", max_modulus);
     if (need > 256) return report_error(DASHB_EINVAL, "garbler: gadget modulus %d above 256", need);
     G.max_modulus = max_modulus;
     G.mods.resize(max_modulus + 1);

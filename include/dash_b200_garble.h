@@ -59,8 +59,9 @@ typedef struct dashb_garble_stats {
 
 /*
  * Garbles the circuit and writes the material, the decoding information and
- * the input encoding (GINB/GINO sections) to `path`.  max_modulus = 0 picks
- * the smallest value that covers every modulus the gadgets use.  Needs
+ * the input encoding (GINB/GINO sections) to `path`.  max_modulus is raised
+ * to the smallest value that covers every modulus the gadgets use (as the
+ * reference's constructors do, garbled_circuit_interface.h:128-135).  Needs
  * dashb_init() on the current device.  Returns DASHB_OK or a DASHB_E* code
  * (dashb_last_error() has the text).
  */

@@ -174,6 +174,51 @@ def build_reference_circuit(spec, seed=42, weight_seed=42):
     return c
 
 
+def plain_layers(spec, weight_seed=42, wmax=7):
+    """The circuit of `spec` as plaintext layer dicts for the GPU garbler
+    (dash_b200.garble.garble_to_file), with synthetic quantised weights
+    U[-wmax, wmax]: same layer structure build_reference_circuit gives the
+    reference (a rescale after every linear layer for the scaling quantisers),
+    no reference code involved.  Returns (layers, input_size)."""
+    rng = np.random.default_rng(weight_seed)
+    qname, qval = spec["quant"]
+    w, h, ch = spec["input"]
+    flat = None
+    out = []
+
+    def after_linear():
+        if qname == "scaleplus":
+            out.append({"type": "rescale", "factors": (int(qval),)})
+        elif qname == "scale":
+            raise ValueError("legacy rescale is not supported by the GPU garbler")
+
+    for layer in spec["layers"]:
+        kind = layer[0]
+        if kind == "flatten":
+            flat = w * h * ch
+        elif kind == "dense":
+            m = layer[1]
+            out.append({"type": "dense", "M": m, "K": flat, "channel_tf": 0,
+                        "weights": rng.integers(-wmax, wmax + 1, size=(m, flat), dtype=np.int64),
+                        "biases": rng.integers(-wmax, wmax + 1, size=(m,), dtype=np.int64)})
+            flat = m
+            after_linear()
+        elif kind == "conv":
+            _, filt, ksz, stride = layer
+            out.append({"type": "conv2d", "geom": (w, h, ch, filt, ksz, ksz, stride, stride),
+                        "weights": rng.integers(-wmax, wmax + 1, size=(filt * ch * ksz * ksz,), dtype=np.int64),
+                        "biases": rng.integers(-wmax, wmax + 1, size=(filt,), dtype=np.int64)})
+            w, h, ch = (w - ksz) // stride + 1, (h - ksz) // stride + 1, filt
+            after_linear()
+        elif kind in ("relu", "sign"):
+            out.append({"type": kind})
+        elif kind == "rescale":
+            out.append({"type": "rescale", "factors": tuple(layer[1])})
+        else:
+            raise ValueError("layer %r is not supported by the GPU garbler" % (kind,))
+    return out, spec["input"][0] * spec["input"][1] * spec["input"][2]
+
+
 def synthetic_inputs(spec, batch, seed=42):
     """Integer inputs U[0,255] (micro_benchmarks/non_sgx/main.cpp:57-65) of
     the circuit's input shape, one row per inference."""
