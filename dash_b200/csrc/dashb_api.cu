@@ -133,7 +133,9 @@ struct DevMem {
     cudaError_t upload(const void* src, size_t n) {
         cudaError_t e = alloc(n);
         if (e != cudaSuccess) return e;
-        if (n) e = cudaMemcpy(p, src, n, cudaMemcpyHostToDevice);
+        /* cudaMemcpyDefault: the source may also be device memory (tables
+         * that the GPU garbler left on the device) */
+        if (n) e = cudaMemcpy(p, src, n, cudaMemcpyDefault);
         return e;
     }
 };

@@ -26,6 +26,7 @@
 #include "../../include/dash_b200.h"
 #include "../../include/dash_b200_garble.h"
 #include "../../include/dash_gcm_format.h"
+#include "../../include/dash_b200_gcm.h"
 #include "kernels.h"
 
 using namespace dashb;
@@ -154,7 +155,8 @@ struct Garbler {
     std::vector<std::vector<int16_t>> cur;
     /* output */
     gcm_circuit g;
-    std::vector<std::unique_ptr<std::vector<uint8_t>>> store; /* owns every array of g */
+    std::vector<std::unique_ptr<std::vector<uint8_t>>> store; /* owns every host array of g */
+    std::vector<std::unique_ptr<DevBuf>> dev_store;           /* ciphertext tables stay on the device */
     std::vector<gcm_layer> glayers;
     dashb_garble_stats st;
     cudaEvent_t ev0{nullptr}, ev1{nullptr};
@@ -173,6 +175,19 @@ struct Garbler {
         a.data = store.back()->data();
         a.nbytes = nbytes;
         return a;
+    }
+
+    gcm_array keep_dev(std::unique_ptr<DevBuf> d) {
+        gcm_array a;
+        a.data = d->p;
+        a.nbytes = d->n;
+        dev_store.push_back(std::move(d));
+        return a;
+    }
+    bool on_device(const void* ptr) const {
+        for (const auto& d : dev_store)
+            if (d->p == ptr) return true;
+        return false;
     }
 
     /* a fresh label of modulus q from the host-side PRF stream */
@@ -249,11 +264,13 @@ int download_plane(const DevBuf& d, uint64_t n, uint32_t nc, std::vector<int16_t
  * come back in `tables`, output planes replace G.cur when replace_cur.
  */
 int run_gates(Garbler& G, std::vector<GateDesc>& descs, const std::vector<uint64_t>& table_rows,
-              std::vector<std::vector<uint8_t>>& tables, const std::vector<int>& out_q, bool replace_cur) {
+              std::vector<gcm_array>& tables, const std::vector<int>& out_q, bool replace_cur) {
     const uint64_t n = G.cur_n;
     GarbleParams P;
     memset(&P, 0, sizeof(P));
-    std::vector<DevBuf> d_in(G.k), d_out(out_q.size()), d_tab(table_rows.size());
+    std::vector<DevBuf> d_in(G.k), d_out(out_q.size());
+    std::vector<std::unique_ptr<DevBuf>> d_tab;
+    for (size_t t = 0; t < table_rows.size(); ++t) d_tab.emplace_back(new DevBuf);
     uint32_t nc_max = 1;
     for (int j = 0; j < G.k; ++j) {
         GRC(upload_plane(G.cur[j], n, G.nc(G.crt[j]), d_in[j]));
@@ -267,9 +284,9 @@ int run_gates(Garbler& G, std::vector<GateDesc>& descs, const std::vector<uint64
     }
     if (table_rows.size() > sizeof(P.tables) / sizeof(P.tables[0])) return report_error(DASHB_EINVAL, "garbler: too many tables in one launch");
     for (size_t t = 0; t < table_rows.size(); ++t) {
-        GCU(d_tab[t].alloc(table_rows[t] * 16));
-        if (table_rows[t]) GCU(cudaMemset(d_tab[t].p, 0, table_rows[t] * 16));
-        P.tables[t] = (u128*)d_tab[t].p;
+        GCU(d_tab[t]->alloc(table_rows[t] * 16));
+        if (table_rows[t]) GCU(cudaMemset(d_tab[t]->p, 0, table_rows[t] * 16));
+        P.tables[t] = (u128*)d_tab[t]->p;
     }
     for (const GateDesc& d : descs) {
         if (d.q_in) nc_max = std::max(nc_max, G.nc((int)d.q_in));
@@ -298,11 +315,10 @@ int run_gates(Garbler& G, std::vector<GateDesc>& descs, const std::vector<uint64
     float ms = 0;
     GCU(cudaEventElapsedTime(&ms, G.ev0, G.ev1));
     G.st.kernel_ms += ms;
-    tables.resize(table_rows.size());
+    tables.clear();
     for (size_t t = 0; t < table_rows.size(); ++t) {
-        tables[t].resize(table_rows[t] * 16);
-        if (table_rows[t]) GCU(cudaMemcpy(tables[t].data(), d_tab[t].p, tables[t].size(), cudaMemcpyDeviceToHost));
-        G.st.table_bytes += tables[t].size();
+        G.st.table_bytes += table_rows[t] * 16;
+        tables.push_back(G.keep_dev(std::move(d_tab[t])));
     }
     if (replace_cur) {
         std::vector<std::vector<int16_t>> next(out_q.size());
@@ -411,8 +427,6 @@ void sign_gadget_descs(const Garbler& G, std::vector<GateDesc>& D, const std::ve
     }
 }
 
-gcm_array keep_vec(Garbler& G, const std::vector<uint8_t>& v) { return G.keep(v.data(), v.size()); }
-
 /* GarbledRelu::garble (layer/garbled_relu.h:118-176) / GarbledSign::garble
  * (layer/garbled_sign.h:16-40) */
 int garble_sign_layer(Garbler& G, bool relu) {
@@ -480,7 +494,7 @@ int garble_sign_layer(Garbler& G, bool relu) {
         sign_gadget_descs(G, D, G.crt, -1, 1, true, rows);
         table_rows = {rows[0], rows[1], rows[2], rows[3]};
     }
-    std::vector<std::vector<uint8_t>> tables;
+    std::vector<gcm_array> tables;
     const uint64_t n = G.cur_n;
     GRC(run_gates(G, D, table_rows, tables, out_q, true));
     gcm_layer L;
@@ -488,7 +502,7 @@ int garble_sign_layer(Garbler& G, bool relu) {
     L.p[0] = relu ? GCM_RELU : GCM_SIGN;
     L.p[1] = (int64_t)n;
     L.n_arrays = (int)tables.size();
-    for (size_t t = 0; t < tables.size(); ++t) L.a[t] = keep_vec(G, tables[t]);
+    for (size_t t = 0; t < tables.size(); ++t) L.a[t] = tables[t];
     G.glayers.push_back(L);
     return DASHB_OK;
 }
@@ -646,7 +660,7 @@ int garble_rescale(Garbler& G, const int64_t* factors_in, int nf) {
         d.out_plane = j;
         D.push_back(d);
     }
-    std::vector<std::vector<uint8_t>> tables;
+    std::vector<gcm_array> tables;
     GRC(run_gates(G, D, std::vector<uint64_t>{tm_rows, be_rows}, tables, out_q, true));
     gcm_layer L;
     memset(&L, 0, sizeof(L));
@@ -656,8 +670,8 @@ int garble_rescale(Garbler& G, const int64_t* factors_in, int nf) {
     for (int i = 0; i < nf; ++i) L.p[3 + i] = factors[i];
     L.n_arrays = k + 2;
     for (int j = 0; j < k; ++j) L.a[j] = G.keep(down[j].data(), down[j].size() * 2);
-    L.a[k] = keep_vec(G, tables[0]);
-    L.a[k + 1] = keep_vec(G, tables[1]);
+    L.a[k] = tables[0];
+    L.a[k + 1] = tables[1];
     G.glayers.push_back(L);
     return DASHB_OK;
 }
@@ -749,23 +763,43 @@ int garble_decoding_info(Garbler& G) {
         D.push_back(d);
         rows[j] = (uint64_t)G.crt[j] * G.cur_n;
     }
-    std::vector<std::vector<uint8_t>> tables;
+    std::vector<gcm_array> tables;
     GRC(run_gates(G, D, rows, tables, std::vector<int>(), false));
     G.g.has_dec = 1;
-    for (int j = 0; j < k; ++j) G.g.dec[j] = keep_vec(G, tables[j]);
+    for (int j = 0; j < k; ++j) G.g.dec[j] = tables[j];
     return DASHB_OK;
 }
 
 }  // namespace
 
-extern "C" int dashb_garble_to_file(const int32_t* crt_base, int k, const int32_t* mrs_base, int n_mrs, int max_modulus,
-                                    uint64_t input_size, const dashb_plain_layer* layers, int n_layers, const uint8_t seed[16],
-                                    const char* path, dashb_garble_stats* stats) {
+/* downloads every device-resident array of the circuit and writes the file */
+static int save_material(Garbler& G, const char* path) {
+    gcm_circuit g = G.g;
+    std::vector<gcm_layer> layers = G.glayers;
+    std::vector<std::unique_ptr<std::vector<uint8_t>>> host;
+    auto to_host = [&](gcm_array& a) -> int {
+        if (!G.on_device(a.data)) return DASHB_OK;
+        host.emplace_back(new std::vector<uint8_t>(a.nbytes));
+        if (a.nbytes) GCU(cudaMemcpy(host.back()->data(), a.data, a.nbytes, cudaMemcpyDeviceToHost));
+        a.data = host.back()->data();
+        return DASHB_OK;
+    };
+    for (gcm_layer& L : layers)
+        for (int a = 0; a < L.n_arrays; ++a) GRC(to_host(L.a[a]));
+    for (int j = 0; j < g.k; ++j) GRC(to_host(g.dec[j]));
+    g.layers = layers.data();
+    if (gcm_save(&g, path) != 0) return report_error(DASHB_EIO, "garbler: cannot write %s", path);
+    return DASHB_OK;
+}
+
+static int garble_impl(const int32_t* crt_base, int k, const int32_t* mrs_base, int n_mrs, int max_modulus,
+                       uint64_t input_size, const dashb_plain_layer* layers, int n_layers, const uint8_t seed[16],
+                       const char* path, dashb_circuit** circuit, dashb_garble_stats* stats) {
     const auto t_start = std::chrono::steady_clock::now();
     if (!crt_base || k < 1 || k > MAXK || n_mrs < 0 || n_mrs > MAXM || (n_mrs && !mrs_base) || !layers || n_layers < 1 || !seed ||
-        !path || input_size == 0)
-        return report_error(DASHB_EINVAL, "dashb_garble_to_file: bad arguments");
-    if (initialised_device() < 0) return report_error(DASHB_ENODEV, "dashb_garble_to_file: call dashb_init() first");
+        (!path && !circuit) || input_size == 0)
+        return report_error(DASHB_EINVAL, "dashb_garble: bad arguments");
+    if (initialised_device() < 0) return report_error(DASHB_ENODEV, "dashb_garble: call dashb_init() first");
     Garbler G;
     memset(&G.g, 0, sizeof(G.g));
     memset(&G.st, 0, sizeof(G.st));
@@ -869,10 +903,29 @@ extern "C" int dashb_garble_to_file(const int32_t* crt_base, int k, const int32_
     G.g.zero = G.keep(zero_all.data(), zero_all.size() * 2);
     G.g.upshift = G.keep(up_all.data(), up_all.size() * 2);
     G.g.n_layers = (int)G.glayers.size();
-    G.g.layers = G.glayers.data();
-    if (gcm_save(&G.g, path) != 0) return report_error(DASHB_EIO, "garbler: cannot write %s", path);
-    G.g.layers = nullptr;
+    if (path) GRC(save_material(G, path));
+    if (circuit) {
+        /* straight into an evaluator circuit: the tables are copied device to device */
+        G.g.layers = G.glayers.data();
+        const int rc = dashb_circuit_from_gcm(&G.g, circuit);
+        G.g.layers = nullptr;
+        if (rc != DASHB_OK) return rc;
+    }
     G.st.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count();
     if (stats) *stats = G.st;
     return DASHB_OK;
+}
+
+extern "C" int dashb_garble_to_file(const int32_t* crt_base, int k, const int32_t* mrs_base, int n_mrs, int max_modulus,
+                                    uint64_t input_size, const dashb_plain_layer* layers, int n_layers, const uint8_t seed[16],
+                                    const char* path, dashb_garble_stats* stats) {
+    if (!path) return report_error(DASHB_EINVAL, "dashb_garble_to_file: no path");
+    return garble_impl(crt_base, k, mrs_base, n_mrs, max_modulus, input_size, layers, n_layers, seed, path, nullptr, stats);
+}
+
+extern "C" int dashb_garble_to_circuit(const int32_t* crt_base, int k, const int32_t* mrs_base, int n_mrs, int max_modulus,
+                                       uint64_t input_size, const dashb_plain_layer* layers, int n_layers,
+                                       const uint8_t seed[16], dashb_circuit** circuit, dashb_garble_stats* stats) {
+    if (!circuit) return report_error(DASHB_EINVAL, "dashb_garble_to_circuit: no circuit pointer");
+    return garble_impl(crt_base, k, mrs_base, n_mrs, max_modulus, input_size, layers, n_layers, seed, nullptr, circuit, stats);
 }

@@ -25,12 +25,7 @@ class GarbleStats(C.Structure):
                 ("table_bytes", C.c_uint64)]
 
 
-def garble_to_file(crt, mrs, input_size, layers, path, seed=b"dash-b200-garble", max_modulus=0):
-    """Garbles `layers` on the current device and writes the DGCM material to
-    `path`.  Returns the statistics as a dict."""
-    L = api.lib()
-    L.dashb_garble_to_file.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_int,
-                                       C.c_char_p, C.c_char_p, C.c_void_p]
+def _marshal(layers):
     arr = (PlainLayer * len(layers))()
     keep = []
     for i, l in enumerate(layers):
@@ -51,10 +46,44 @@ def garble_to_file(crt, mrs, input_size, layers, path, seed=b"dash-b200-garble",
             keep += [w, b]
             arr[i].weights = w.ctypes.data
             arr[i].biases = b.ctypes.data
+    return arr, keep
+
+
+def _stats(st):
+    return {f: getattr(st, f) for f, _ in GarbleStats._fields_}
+
+
+def garble_to_file(crt, mrs, input_size, layers, path, seed=b"dash-b200-garble", max_modulus=0):
+    """Garbles `layers` on the current device and writes the DGCM material to
+    `path`.  Returns the statistics as a dict."""
+    L = api.lib()
+    L.dashb_garble_to_file.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_int,
+                                       C.c_char_p, C.c_char_p, C.c_void_p]
+    arr, keep = _marshal(layers)
     crt_a = np.ascontiguousarray(crt, dtype=np.int32)
     mrs_a = np.ascontiguousarray(mrs if len(mrs) else [0], dtype=np.int32)
     seed = (bytes(seed) + b"\0" * 16)[:16]
     st = GarbleStats()
     api._check(L.dashb_garble_to_file(crt_a.ctypes.data, len(crt), mrs_a.ctypes.data, len(mrs), int(max_modulus),
                                       int(input_size), C.byref(arr), len(layers), seed, os.fsencode(path), C.byref(st)))
-    return {f: getattr(st, f) for f, _ in GarbleStats._fields_}
+    del keep
+    return _stats(st)
+
+
+def garble_to_circuit(crt, mrs, input_size, layers, max_batch, seed=b"dash-b200-garble", max_modulus=0):
+    """Garbles `layers` straight into an evaluator circuit on the current
+    device (the tables never leave the GPU).  Returns (api.Circuit, stats)."""
+    L = api.lib()
+    L.dashb_garble_to_circuit.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_int,
+                                          C.c_char_p, C.POINTER(C.c_void_p), C.c_void_p]
+    arr, keep = _marshal(layers)
+    crt_a = np.ascontiguousarray(crt, dtype=np.int32)
+    mrs_a = np.ascontiguousarray(mrs if len(mrs) else [0], dtype=np.int32)
+    seed = (bytes(seed) + b"\0" * 16)[:16]
+    st = GarbleStats()
+    h = C.c_void_p()
+    api._check(L.dashb_garble_to_circuit(crt_a.ctypes.data, len(crt), mrs_a.ctypes.data, len(mrs), int(max_modulus),
+                                         int(input_size), C.byref(arr), len(layers), seed, C.byref(h), C.byref(st)))
+    del keep
+    api._check(L.dashb_finalize(h, int(max_batch)))
+    return api.Circuit(h, max_batch), _stats(st)

@@ -69,6 +69,18 @@ int dashb_garble_to_file(const int32_t* crt_base, int k, const int32_t* mrs_base
                          uint64_t input_size, const dashb_plain_layer* layers, int n_layers, const uint8_t seed[16],
                          const char* path, dashb_garble_stats* stats);
 
+/*
+ * Same, straight into an evaluator circuit on the current device: the
+ * ciphertext tables never leave the GPU (device-to-device copies into the
+ * circuit).  The circuit comes back un-finalized, with decoding information
+ * and input encoding set: call dashb_finalize(*circuit, max_batch), then
+ * dashb_garble_inputs / dashb_evaluate_device / dashb_decode_outputs.
+ */
+struct dashb_circuit;
+int dashb_garble_to_circuit(const int32_t* crt_base, int k, const int32_t* mrs_base, int n_mrs, int max_modulus,
+                            uint64_t input_size, const dashb_plain_layer* layers, int n_layers, const uint8_t seed[16],
+                            struct dashb_circuit** circuit, dashb_garble_stats* stats);
+
 #ifdef __cplusplus
 }
 #endif

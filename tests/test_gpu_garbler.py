@@ -86,3 +86,31 @@ def test_same_seed_same_circuit_other_seed_other_labels(gpu, tmp_path):
         paths.append(open(p, "rb").read())
     assert paths[0] == paths[1]
     assert paths[0] != paths[2] and len(paths[0]) == len(paths[2])
+
+
+def test_garble_straight_into_an_evaluator_circuit(gpu, tmp_path):
+    """dashb_garble_to_circuit: same seed as the file path -> the same labels,
+    without the tables ever leaving the device."""
+    import workloads as W
+    from dash_b200 import garble
+
+    spec = W.MODELS["CIFAR_TINY_SCALE"]
+    plain, n_in = W.plain_layers(spec, weight_seed=3)
+    path = str(tmp_path / "g.gcm")
+    garble.garble_to_file(spec["crt"], spec["mrs"], n_in, plain, path, seed=b"abc")
+    X = W.synthetic_inputs(spec, 12, seed=2)
+    a = gpu.Circuit.load(path, max_batch=12)
+    a.garble_inputs(X)
+    a.evaluate_device()
+    want = a.move_outputs()
+    want_vals, ok = a.decode_outputs()
+    assert ok.all()
+    b, stats = garble.garble_to_circuit(spec["crt"], spec["mrs"], n_in, plain, 12, seed=b"abc")
+    b.garble_inputs(X)
+    b.evaluate_device()
+    assert_labels_equal(b.move_outputs(), want, "file path vs in-memory path")
+    vals, ok = b.decode_outputs()
+    assert ok.all() and np.array_equal(vals, want_vals)
+    assert stats["rows"] > 0
+    a.close()
+    b.close()
