@@ -114,3 +114,64 @@ def test_garble_straight_into_an_evaluator_circuit(gpu, tmp_path):
     assert stats["rows"] > 0
     a.close()
     b.close()
+
+
+def _plain_eval(layers, x, P):
+    """Integer semantics of the plaintext circuit (circuit/layer/*.h
+    plain_eval): values are residues mod P read as signed numbers."""
+    def signed(v):
+        v = np.mod(v, P)
+        return np.where(v >= P // 2, v - P, v)
+
+    v = np.asarray(x, dtype=object)
+    for l in layers:
+        if l["type"] == "dense":
+            w = np.asarray(l["weights"], dtype=object).reshape(l["M"], l["K"])
+            v = signed(w.dot(v) + np.asarray(l["biases"], dtype=object))
+        elif l["type"] == "conv2d":
+            in_w, in_h, ch, filt, fw, fh, sw, sh = l["geom"]
+            ow, oh = (in_w - fw) // sw + 1, (in_h - fh) // sh + 1
+            w = np.asarray(l["weights"], dtype=object)
+            out = np.zeros(filt * ow * oh, dtype=object)
+            fs = fw * fh
+            for f in range(filt):
+                for y in range(oh):
+                    for xx in range(ow):
+                        acc = int(l["biases"][f])
+                        for c in range(ch):
+                            for i in range(fh):
+                                for j in range(fw):
+                                    # weight index as the reference reads it (label_tensor.h:967-969)
+                                    acc += int(w[f * fs * ch + c * fs + i * fh + j]) * int(v[c * in_w * in_h + (y * sh + i) * in_w + xx * sw + j])
+                        out[f * ow * oh + y * ow + xx] = acc
+            v = signed(out)
+        elif l["type"] == "relu":
+            v = np.where(v > 0, v, 0)
+        else:
+            raise ValueError(l["type"])
+    return np.array([int(t) for t in v], dtype=np.int64)
+
+
+@pytest.mark.parametrize("name", ["MLP_TINY", "MNIST_TINY_CNN"])
+def test_gpu_garbled_circuit_decodes_to_the_plain_evaluation(gpu, name):
+    """Independent of the reference: with an exact sign base (accuracy 100 %)
+    decode(evaluate(garble(C), encode(x))) must equal C(x) computed with plain
+    integers, for circuits whose values stay inside (-P/2, P/2)."""
+    import workloads as W
+    from dash_b200 import garble
+
+    spec = W.MODELS[name]
+    plain, n_in = W.plain_layers(spec, weight_seed=11, wmax=2)
+    P = 1
+    for p in spec["crt"]:
+        P *= p
+    batch = 6
+    X = W.synthetic_inputs(spec, batch, seed=4) % 8  # small inputs keep every intermediate value far from P/2
+    c, _ = garble.garble_to_circuit(spec["crt"], spec["mrs"], n_in, plain, batch, seed=b"plain")
+    c.garble_inputs(X)
+    c.evaluate_device()
+    vals, ok = c.decode_outputs()
+    assert ok.all()
+    for b in range(batch):
+        assert np.array_equal(vals[b], _plain_eval(plain, X[b], P)), "inference %d" % b
+    c.close()
