@@ -676,6 +676,100 @@ int garble_rescale(Garbler& G, const int64_t* factors_in, int nf) {
     return DASHB_OK;
 }
 
+/* Legacy rescale (layer/garbled_rescale.h:27-35,52-75; RescaleGadget with
+ * use_sign_base_extension, rescale_gadget.h:114-243): l iterations of
+ * "divide by 2, regenerate the mod-2 residue with a full sign gadget".  Each
+ * iteration is two launches: the trans-modulus gates (their outputs become the
+ * current tensor), then the sign gadget on that tensor. */
+int garble_rescale_legacy(Garbler& G, int l_iter) {
+    const int k = G.k;
+    if (l_iter < 1 || l_iter > 16) return report_error(DASHB_EINVAL, "garbler: bad number of legacy rescale iterations");
+    if (G.crt[0] != 2) return report_error(DASHB_EINVAL, "garbler: legacy rescale needs modulus 2 first in the CRT base (the reference writes the regenerated residue to index 0, rescale_gadget.h:219-222)");
+    if (G.n_mrs < 1) return report_error(DASHB_EINVAL, "garbler: legacy rescale needs an MRS base");
+    const uint64_t n = G.cur_n;
+    std::vector<uint32_t> d_off(k);
+    std::vector<Label> down(k);
+    for (int j = 0; j < k; ++j) {
+        const int q = G.crt[j];
+        const Label base = G.random_label(q);
+        d_off[j] = G.add_const_label(base);
+        down[j] = G.lin(G.R[q], pmod(G.P / 4, q), base, 1, q);
+    }
+    GRC(G.upload_labels());
+    gcm_layer L;
+    memset(&L, 0, sizeof(L));
+    L.p[0] = GCM_RESCALE_LEGACY;
+    L.p[1] = (int64_t)n;
+    L.p[2] = l_iter;
+    L.n_arrays = k + 5 * l_iter;
+    for (int j = 0; j < k; ++j) L.a[j] = G.keep(down[j].data(), down[j].size() * 2);
+    std::vector<int> out_q(k);
+    for (int j = 0; j < k; ++j) out_q[j] = G.crt[j];
+    const uint64_t tag0 = G.layer_tag;
+    for (int it = 0; it < l_iter; ++it) {
+        /* steps 1-2.3: upshift, project residue mod 2 into every other modulus, subtract, halve */
+        G.layer_tag = tag0 | ((uint64_t)(2 * it + 1) << 16);
+        std::vector<GateDesc> D;
+        uint64_t tm_rows = 0;
+        for (int j = 1; j < k; ++j) {
+            const int q = G.crt[j];
+            GateDesc d = blank_desc();
+            d.q_in = 2;
+            d.in[d.n_in++] = term_plane(0, 1);
+            d.in[d.n_in++] = term_const(G.u_off[0], 1);
+            d.q_out = (uint32_t)q;
+            d.out[d.n_out++] = term_prf(tag(TAG_T, 0, j), 1);
+            d.f = GB_F_ID;
+            d.table = 0;
+            d.table_off = tm_rows;
+            d.table_stride = 2;
+            tm_rows += n * 2;
+            D.push_back(d);
+            const int64_t inv2 = mul_inv_ll(2, q);
+            GateDesc o = blank_desc();
+            o.q_out = (uint32_t)q;
+            o.out[o.n_out++] = term_plane((uint32_t)j, inv2);
+            o.out[o.n_out++] = term_const(G.u_off[j], inv2);
+            o.out[o.n_out++] = term_prf(tag(TAG_T, 0, j), pmod(-inv2, q));
+            o.out_plane = j;
+            D.push_back(o);
+        }
+        GateDesc z = blank_desc(); /* step 2.3 */
+        z.q_out = 2;
+        z.out[z.n_out++] = term_const(G.z_off[2], 1);
+        z.out_plane = 0;
+        D.push_back(z);
+        std::vector<gcm_array> t1;
+        GRC(run_gates(G, D, std::vector<uint64_t>{tm_rows}, t1, out_q, true));
+        L.a[k + 5 * it] = t1[0];
+        /* step 3: sign gadget with bounds (1, 0) regenerates residue 2; step 4: downshift */
+        G.layer_tag = tag0 | ((uint64_t)(2 * it + 2) << 16);
+        D.clear();
+        uint64_t rows[4];
+        sign_gadget_descs(G, D, std::vector<int>{2}, 1, 0, false, rows);
+        GateDesc s0 = blank_desc();
+        s0.q_out = 2;
+        s0.out[s0.n_out++] = term_prf(tag(TAG_S, 0, 0), 1);
+        s0.out[s0.n_out++] = term_const(d_off[0], 1); /* minus the downshift base, mod 2 */
+        s0.out_plane = 0;
+        D.push_back(s0);
+        for (int j = 1; j < k; ++j) {
+            GateDesc o = blank_desc();
+            o.q_out = (uint32_t)G.crt[j];
+            o.out[o.n_out++] = term_plane((uint32_t)j, 1);
+            o.out[o.n_out++] = term_const(d_off[j], G.crt[j] - 1);
+            o.out_plane = j;
+            D.push_back(o);
+        }
+        std::vector<gcm_array> t2;
+        GRC(run_gates(G, D, std::vector<uint64_t>{rows[0], rows[1], rows[2], rows[3]}, t2, out_q, true));
+        for (int a = 0; a < 4; ++a) L.a[k + 5 * it + 1 + a] = t2[a];
+    }
+    G.layer_tag = tag0;
+    G.glayers.push_back(L);
+    return DASHB_OK;
+}
+
 /* Dense / conv2d: the output base labels are the layer evaluated on the
  * input base labels with the zero label as bias (layer/garbled_dense.h:
  * 89-118, garbled_conv2d.h:86-112); done by the evaluator itself, batch 1. */
@@ -889,6 +983,7 @@ static int garble_impl(const int32_t* crt_base, int k, const int32_t* mrs_base, 
             case DASHB_LAYER_RELU: GRC(garble_sign_layer(G, true)); break;
             case DASHB_LAYER_SIGN: GRC(garble_sign_layer(G, false)); break;
             case DASHB_LAYER_RESCALE: GRC(garble_rescale(G, &pl.p[3], (int)pl.p[2])); break;
+            case DASHB_LAYER_RESCALE_LEGACY: GRC(garble_rescale_legacy(G, (int)pl.p[2])); break;
             default: return report_error(DASHB_EINVAL, "garbler: layer type %d is not supported", (int)pl.p[0]);
         }
     }

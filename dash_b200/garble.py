@@ -4,7 +4,7 @@ offline phase on the GPU.  A plaintext circuit is a list of layer dicts:
     {"type": "dense", "M": m, "K": k, "channel_tf": 0, "weights": int64 [M][K], "biases": int64 [M]}
     {"type": "conv2d", "geom": (in_w, in_h, channels, filters, f_w, f_h, s_w, s_h),
      "weights": int64 (reference order), "biases": int64 [filters]}
-    {"type": "relu"} | {"type": "sign"} | {"type": "rescale", "factors": (32,)}
+    {"type": "relu"} | {"type": "sign"} | {"type": "rescale", "factors": (32,)} | {"type": "rescale_legacy", "l": 2}
 """
 import ctypes as C
 import os
@@ -13,7 +13,7 @@ import numpy as np
 
 from . import api
 
-TYPES = {"dense": 1, "conv2d": 2, "relu": 3, "sign": 4, "rescale": 5}
+TYPES = {"dense": 1, "conv2d": 2, "relu": 3, "sign": 4, "rescale": 5, "rescale_legacy": 6}
 
 
 class PlainLayer(C.Structure):
@@ -36,6 +36,8 @@ def _marshal(layers):
         elif t == 2:
             for x, v in enumerate(l["geom"]):
                 arr[i].p[1 + x] = int(v)
+        elif t == 6:
+            arr[i].p[2] = int(l["l"])
         elif t == 5:
             arr[i].p[2] = len(l["factors"])
             for x, v in enumerate(l["factors"]):

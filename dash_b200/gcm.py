@@ -91,6 +91,8 @@ def plain_circuit(g):
             out.append({"type": "sign"})
         elif t == 5:
             out.append({"type": "rescale", "factors": tuple(int(x) for x in p[3:3 + int(p[2])])})
+        elif t == 6:
+            out.append({"type": "rescale_legacy", "l": int(p[2])})
         else:
             raise ValueError("layer type %d has no plaintext form here" % t)
     return out

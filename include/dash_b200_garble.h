@@ -18,8 +18,8 @@
  * decoded outputs (tests/test_gpu_garbler.py).
  *
  * Supported layers: dense, conv2d, ReLU (approximate sign gadget + mixed-
- * modulus half gates), sign, rescale with base extension.  Not supported:
- * legacy rescale, standalone projection layers.
+ * modulus half gates), sign, rescale with base extension, legacy rescale.
+ * Not supported: standalone projection layers.
  */
 #ifndef DASH_B200_GARBLE_H
 #define DASH_B200_GARBLE_H
@@ -39,6 +39,7 @@ extern "C" {
  *   RELU     (n is the previous layer's output size)
  *   SIGN
  *   RESCALE  p[2]=nf p[3..3+nf)=factors (each a CRT modulus)
+ *   RESCALE_LEGACY  p[2]=l (iterations of "halve + sign gadget"; needs crt_base[0] == 2)
  * Weights and biases are the quantised integers of Dense::get_q_weights /
  * get_q_biases (garbling/layer/garbled_dense.h:91-96); any representative
  * modulo the CRT modulus is accepted.

@@ -10,7 +10,7 @@ from helpers import assert_labels_equal
 pytestmark = pytest.mark.gpu
 
 CASES = [("MLP_TINY", 9), ("MNIST_TINY_CNN", 7), ("CIFAR_TINY_SCALE", 6), ("SIGN_TINY", 11), ("RESCALE_2_3", 5),
-         ("RESCALE_OPT", 4), ("RELU_99", 8), ("RESCALE_2", 3)]
+         ("RESCALE_OPT", 4), ("RELU_99", 8), ("RESCALE_2", 3), ("RESCALE_LEGACY", 10)]
 
 
 @pytest.mark.parametrize("name,batch", CASES)
