@@ -22,9 +22,12 @@ def api():
 
 
 def declared_symbols():
-    text = open(os.path.join(ROOT, "include", "dash_b200.h")).read()
-    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"\b(dashb_[a-z0-9_]+)\s*\(", text)))
+    syms = set()
+    for header in ("dash_b200.h", "dash_b200_garble.h"):
+        text = open(os.path.join(ROOT, "include", header)).read()
+        text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+        syms |= set(re.findall(r"\b(dashb_[a-z0-9_]+)\s*\(", text))
+    return sorted(syms)
 
 
 def test_library_exports_every_declared_symbol(api):
@@ -33,6 +36,20 @@ def test_library_exports_every_declared_symbol(api):
     assert len(syms) >= 25
     for s in syms:
         assert hasattr(L, s), "libdash_b200.so does not export " + s
+
+
+def test_garbler_fails_loudly_without_a_device(api):
+    """The offline phase has no CPU path either."""
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from dash_b200 import garble
+
+    layers = [{"type": "dense", "M": 2, "K": 3, "weights": [[1, 2, 3], [4, 5, 6]], "biases": [0, 1]}]
+    with pytest.raises(api.DashB200Error):
+        garble.garble_to_file([2, 3, 5], [], 3, layers, "/tmp/never.gcm")
+    assert not os.path.exists("/tmp/never.gcm")
 
 
 def test_no_gpu_fails_loudly(api):
