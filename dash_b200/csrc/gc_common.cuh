@@ -65,15 +65,19 @@ GC_HD uint32_t mulhi32(uint32_t a, uint32_t b) {
 #endif
 }
 
-/* x * m + a (mod 2^128), m < 2^32 */
+/* x * m + a (mod 2^128), m < 2^32: four 32x32->64 multiply-adds on 32-bit
+ * limbs (one IMAD.WIDE each) instead of 64-bit products */
 GC_HD u128 muladd_small(u128 x, uint32_t m, uint32_t a) {
+    uint64_t t = (uint64_t)(uint32_t)x.lo * m + a;
+    const uint32_t r0 = (uint32_t)t;
+    t = (uint64_t)(uint32_t)(x.lo >> 32) * m + (t >> 32);
+    const uint32_t r1 = (uint32_t)t;
+    t = (uint64_t)(uint32_t)x.hi * m + (t >> 32);
+    const uint32_t r2 = (uint32_t)t;
+    const uint32_t r3 = (uint32_t)(x.hi >> 32) * m + (uint32_t)(t >> 32);
     u128 r;
-    uint64_t carry = mulhi64(x.lo, m);
-    r.lo = x.lo * m;
-    r.hi = x.hi * m + carry;
-    uint64_t lo2 = r.lo + a;
-    r.hi += (lo2 < r.lo) ? 1u : 0u;
-    r.lo = lo2;
+    r.lo = (uint64_t)r0 | ((uint64_t)r1 << 32);
+    r.hi = (uint64_t)r2 | ((uint64_t)r3 << 32);
     return r;
 }
 
