@@ -44,10 +44,17 @@ using gc::ModInfo;
 
 constexpr int TC_BM = 128, TC_BN = 128, TC_BK = 128; /* u8: bytes == elements */
 constexpr int TC_STAGES_DENSE = 4; /* long K loops: deep ring, one CTA per SM */
-constexpr int TC_STAGES_CONV = 2;  /* few K blocks per tile: three CTAs per SM overlap MMA and epilogue */
+constexpr int TC_STAGES_CONV = 2;  /* few K blocks per tile: several CTAs per SM overlap MMA and epilogue */
+/* column sub-tiles of 128 per CTA: the weight tile staged once feeds NB MMAs.
+ * The kernel is bound by L2 -> shared-memory operand traffic (profiles/
+ * r1_dense_tc_vs_dp4a.md), NB = 2 moves 48 KB instead of 64 KB per two tiles. */
+#ifndef DASHB_TC_NB
+#define DASHB_TC_NB 2
+#endif
+constexpr int TC_NB = DASHB_TC_NB;
 constexpr int TC_THREADS = 192;
-constexpr uint32_t TC_STAGE_BYTES = TC_BM * TC_BK + TC_BK * TC_BN;
-constexpr uint32_t tc_smem_bytes(int stages) { return (uint32_t)stages * TC_STAGE_BYTES + 1024; }
+__host__ __device__ constexpr uint32_t tc_stage_bytes(int nb) { return TC_BM * TC_BK + (uint32_t)nb * TC_BK * TC_BN; }
+__host__ __device__ constexpr uint32_t tc_smem_bytes(int stages, int nb) { return (uint32_t)stages * tc_stage_bytes(nb) + 1024; }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -97,7 +104,7 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes
     return d;
 }
 
-template <bool CONV, int TC_STAGES>
+template <bool CONV, int TC_STAGES, int NB>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ DenseTcParams P) {
     extern __shared__ uint8_t smem_raw[];
@@ -108,8 +115,11 @@ k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ Den
     const ModInfo m = P.mod[j];
     const uint32_t nc4 = (m.nc + 3) >> 2;
     const uint32_t Nj = nc4 * 4 * P.Bp;
-    const uint32_t n0 = blockIdx.x * TC_BN;
+    constexpr uint32_t TC_STAGE_BYTES = tc_stage_bytes(NB);
+    const uint32_t n0 = blockIdx.x * (TC_BN * NB);
     if (n0 >= Nj) return; /* uniform per CTA: planes of small moduli have fewer columns */
+    /* column sub-tiles that start inside the plane */
+    const uint32_t nb_act = min((uint32_t)NB, (Nj - n0 + TC_BN - 1) / TC_BN);
     /* conv: blockIdx.y = filter block * npix + output pixel */
     const uint32_t pix = CONV ? blockIdx.y % P.npix : 0u;
     const uint32_t m0 = P.v0 + (CONV ? blockIdx.y / P.npix : blockIdx.y) * TC_BM;
@@ -117,7 +127,7 @@ k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ Den
     const uint32_t nkb = P.nkb;
 
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(TC_BN));
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(TC_BN * NB));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     if (threadIdx.x == 0) {
@@ -142,13 +152,17 @@ k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ Den
                 if (round > 0) mbar_wait(&bar_empty[s], (round - 1) & 1);
                 uint8_t* sA = smem + s * TC_STAGE_BYTES;
                 uint8_t* sB = sA + TC_BM * TC_BK;
-                mbar_expect_tx(&bar_full[s], TC_BM * TC_BK + P.b_box_bytes);
+                mbar_expect_tx(&bar_full[s], TC_BM * TC_BK + nb_act * P.b_box_bytes);
                 tma_load_2d(sA, reinterpret_cast<const CUtensorMap*>(&maps.a[j]), &bar_full[s], (int)(kb * TC_BK), (int)m0);  /* {k, m} */
-                if (CONV)
-                    tma_load_4d(sB, reinterpret_cast<const CUtensorMap*>(&maps.b[j]), &bar_full[s], (int)n0,
-                                (int)((pix % P.ow) * P.sx), (int)((pix / P.ow) * P.sy), (int)(kb * P.cb)); /* {n, x, y, c} */
-                else
-                    tma_load_2d(sB, reinterpret_cast<const CUtensorMap*>(&maps.b[j]), &bar_full[s], (int)n0, (int)(kb * TC_BK));  /* {n, k} */
+                for (uint32_t h = 0; h < nb_act; ++h) {
+                    uint8_t* sBh = sB + h * (TC_BK * TC_BN);
+                    const int nh = (int)(n0 + h * TC_BN);
+                    if (CONV)
+                        tma_load_4d(sBh, reinterpret_cast<const CUtensorMap*>(&maps.b[j]), &bar_full[s], nh,
+                                    (int)((pix % P.ow) * P.sx), (int)((pix / P.ow) * P.sy), (int)(kb * P.cb)); /* {n, x, y, c} */
+                    else
+                        tma_load_2d(sBh, reinterpret_cast<const CUtensorMap*>(&maps.b[j]), &bar_full[s], nh, (int)(kb * TC_BK));  /* {n, k} */
+                }
             }
         }
     } else if (warp == 1) {
@@ -162,16 +176,18 @@ k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ Den
                 asm volatile("tcgen05.fence::after_thread_sync;");
                 const uint32_t aA = smem_u32(smem + s * TC_STAGE_BYTES);
                 const uint32_t aB = aA + TC_BM * TC_BK;
+                for (uint32_t h = 0; h < nb_act; ++h) {
 #pragma unroll
-                for (int k4 = 0; k4 < TC_BK / 32; ++k4) {
-                    const uint64_t da = umma_desc(aA + k4 * 32, 16, 1024);         /* +32 B inside the swizzled row */
-                    const uint64_t db = umma_desc(aB + k4 * 32 * TC_BN, 16, 1024); /* +32 k-rows of 128 B */
-                    const uint32_t acc = (kb | (uint32_t)k4) ? 1u : 0u;
-                    asm volatile(
-                        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}" ::"r"(tmem_base),
-                        "l"(da), "l"(db), "r"(idesc), "r"(acc), "r"(0), "r"(0), "r"(0), "r"(0)
-                        : "memory");
+                    for (int k4 = 0; k4 < TC_BK / 32; ++k4) {
+                        const uint64_t da = umma_desc(aA + k4 * 32, 16, 1024);                                  /* +32 B inside the swizzled row */
+                        const uint64_t db = umma_desc(aB + h * (TC_BK * TC_BN) + k4 * 32 * TC_BN, 16, 1024);    /* +32 k-rows of 128 B */
+                        const uint32_t acc = (kb | (uint32_t)k4) ? 1u : 0u;
+                        asm volatile(
+                            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                            "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}" ::"r"(tmem_base + h * TC_BN),
+                            "l"(da), "l"(db), "r"(idesc), "r"(acc), "r"(0), "r"(0), "r"(0), "r"(0)
+                            : "memory");
+                    }
                 }
                 /* frees the stage when the MMAs that read it are done */
                 asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
@@ -190,7 +206,7 @@ k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ Den
         const bool row_ok = row < P.v1;
         const uint32_t* cst = reinterpret_cast<const uint32_t*>(P.cst[j]) + (uint64_t)(row_ok ? row : 0) * nc4;
         uint8_t* orow = P.out[j] + ((uint64_t)(row_ok ? row : 0) * (CONV ? P.npix : 1u) + pix) * Nj + n0;
-        for (int c0 = 0; c0 < TC_BN; c0 += 32) {
+        for (int c0 = 0; c0 < TC_BN * (int)nb_act; c0 += 32) {
             uint32_t v[32];
             const uint32_t taddr = tmem_base + ((sub * 32u) << 16) + (uint32_t)c0;
             asm volatile(
@@ -228,7 +244,7 @@ k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ Den
     }
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
-    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_BN));
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_BN * NB));
 }
 
 /* ---- host side: tensor maps ---- */
@@ -282,11 +298,11 @@ cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p, cud
     if (p.v1 <= p.v0) return cudaSuccess;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(k_dense_tc<false, TC_STAGES_DENSE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)tc_smem_bytes(TC_STAGES_DENSE));
+        cudaError_t e = cudaFuncSetAttribute(k_dense_tc<false, TC_STAGES_DENSE, TC_NB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)tc_smem_bytes(TC_STAGES_DENSE, TC_NB));
         if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(k_dense_tc<true, TC_STAGES_CONV>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)tc_smem_bytes(TC_STAGES_CONV));
+        e = cudaFuncSetAttribute(k_dense_tc<true, TC_STAGES_CONV, TC_NB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)tc_smem_bytes(TC_STAGES_CONV, TC_NB));
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
@@ -294,11 +310,11 @@ cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p, cud
     for (int j = 0; j < p.k; ++j) max_cols = max(max_cols, ((p.mod[j].nc + 3) & ~3u) * p.Bp);
     const uint32_t mblocks = (p.v1 - p.v0 + TC_BM - 1) / TC_BM;
     if (p.npix > 1 || p.conv) {
-        dim3 grid((max_cols + TC_BN - 1) / TC_BN, mblocks * p.npix, p.k);
-        k_dense_tc<true, TC_STAGES_CONV><<<grid, TC_THREADS, tc_smem_bytes(TC_STAGES_CONV), s>>>(maps, p);
+        dim3 grid((max_cols + TC_BN * TC_NB - 1) / (TC_BN * TC_NB), mblocks * p.npix, p.k);
+        k_dense_tc<true, TC_STAGES_CONV, TC_NB><<<grid, TC_THREADS, tc_smem_bytes(TC_STAGES_CONV, TC_NB), s>>>(maps, p);
     } else {
-        dim3 grid((max_cols + TC_BN - 1) / TC_BN, mblocks, p.k);
-        k_dense_tc<false, TC_STAGES_DENSE><<<grid, TC_THREADS, tc_smem_bytes(TC_STAGES_DENSE), s>>>(maps, p);
+        dim3 grid((max_cols + TC_BN * TC_NB - 1) / (TC_BN * TC_NB), mblocks, p.k);
+        k_dense_tc<false, TC_STAGES_DENSE, TC_NB><<<grid, TC_THREADS, tc_smem_bytes(TC_STAGES_DENSE, TC_NB), s>>>(maps, p);
     }
     return cudaGetLastError();
 }
