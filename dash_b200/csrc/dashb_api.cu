@@ -342,6 +342,7 @@ void fill_sign_params(dashb_circuit* c, SignParams& p, uint64_t n, int n_out) {
     p.k = c->k;
     p.n_mrs = c->n_mrs;
     p.n_out = n_out;
+    p.lanes = c->lanes_used;
     p.n = n;
     uint32_t S = 0, Mp = 0;
     for (int j = 0; j < c->k; ++j) {

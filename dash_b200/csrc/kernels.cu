@@ -697,6 +697,156 @@ __global__ void __launch_bounds__(SIGN_THREADS) k_sign(const __grid_constant__ S
     }
 }
 
+/* ------------------------------------------ sign gadget, latency mode */
+/*
+ * Same gadget, one WARP per (element, inference): for small launches (a
+ * single inference, the small layers of a small batch) k_sign leaves most of
+ * the GPU idle while every thread walks its ~88 hashes one after the other.
+ * Here the k input hashes, the k*(n-1) cast-1 projections and the k top-digit
+ * projections are spread over the lanes (they do not depend on the carry);
+ * only the carry chain itself -- two hashes per mixed-radix digit -- stays
+ * sequential on lane 0, and the half gates again run one modulus per lane.
+ * Critical path: ~2n+4 hashes instead of k*n + 2n.  It issues ~7x the
+ * instructions per element, so launch_sign only picks it when the launch
+ * could not fill the machine anyway.  Results identical to k_sign.
+ */
+constexpr int WIDE_WARPS = 4;
+
+/* acc[d] += digit_d(x), shared-memory atomics (several lanes add into the same digits) */
+__device__ __noinline__ void accumulate_atomic(u128 x, const ModInfo m, uint32_t* acc) {
+    gc::for_each_digit(x, m, [&](uint32_t d, uint32_t v) { atomicAdd(acc + d, v); });
+}
+
+__device__ __forceinline__ u128 compress_acc32(const uint32_t* acc, const ModInfo& m, uint32_t& colour) {
+    gc::Compressor c(m);
+    uint32_t dg = 0;
+    for (int d = (int)m.nc - 1; d >= 0; --d) {
+        dg = gc::mod_q(acc[d], m);
+        c.push(dg);
+    }
+    colour = dg;
+    return c.value();
+}
+
+__device__ __forceinline__ u128 shfl128(u128 v, int src) {
+    u128 r;
+    r.lo = __shfl_sync(0xffffffffu, v.lo, src);
+    r.hi = __shfl_sync(0xffffffffu, v.hi, src);
+    return r;
+}
+
+template <bool RELU>
+__global__ void __launch_bounds__(WIDE_WARPS * 32) k_sign_wide(const __grid_constant__ SignParams P, uint32_t acc_digits) {
+    __shared__ AesSmem aes;
+    __shared__ u128 s_h[WIDE_WARPS][MAXK];
+    __shared__ uint32_t s_col[WIDE_WARPS][MAXK];
+    extern __shared__ uint32_t s_wacc[]; /* [warp][n_mrs][acc_digits] */
+    aes_smem_load(aes);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint64_t idx = (uint64_t)blockIdx.x * WIDE_WARPS + warp;
+    if (idx >= P.n * P.batch) return; /* whole warps leave together */
+    const uint32_t b = (uint32_t)(idx % P.batch);
+    const uint64_t e = P.e0 + idx / P.batch;
+    const int k = P.k, nm = P.n_mrs;
+    u128* h = s_h[warp];
+    uint32_t* col = s_col[warp];
+    uint32_t* acc = s_wacc + (size_t)warp * nm * acc_digits;
+
+    for (uint32_t t = lane; t < (uint32_t)nm * acc_digits; t += 32) acc[t] = 0;
+    /* step 1a: hash every CRT residue label, one per lane */
+    if (lane < k) {
+        const ModInfo Pm = P.crt[lane];
+        uint32_t c;
+        const u128 key = load_compress(P.in[lane], Pm, e, b, P.Bp, c);
+        h[lane] = hash(aes, key);
+        col[lane] = c;
+    }
+    __syncwarp();
+    const u128* approx_e = P.approx + e * (uint64_t)nm * P.S;
+    const uint64_t cast_e = e * (uint64_t)(k + 1) * P.Mp;
+    /* steps 1b + 2.2 for every (digit i >= 1, residue j): independent of the carry */
+    for (int t = lane; t < k * (nm - 1); t += 32) {
+        const int j = t % k, i = 1 + t / k;
+        const ModInfo M = P.mrs[i];
+        const ModInfo C = P.cast[i];
+        uint64_t cnt1 = cast_e;
+        for (int i2 = nm - 1; i2 > i; --i2) cnt1 += (uint64_t)(k + 1) * P.mrs[i2].q;
+        const u128 lab = gc::sub128(ldg128(approx_e + (uint64_t)nm * P.prefix[j] + (uint64_t)i * P.crt[j].q + col[j]), h[j]);
+        const u128 hl = hash(aes, lab);
+        const uint32_t c0 = gc::colour_of(lab, M);
+        accumulate_atomic(gc::sub128(ldg128(P.cast1 + cnt1 + (uint64_t)j * M.q + c0), hl), C, acc + (size_t)i * acc_digits);
+    }
+    /* most significant digit: the k approximate digits themselves */
+    if (lane < k) {
+        const u128 lab = gc::sub128(ldg128(approx_e + (uint64_t)nm * P.prefix[lane] + col[lane]), h[lane]);
+        accumulate_atomic(lab, P.mrs[0], acc);
+    }
+    __syncwarp();
+    /* the carry chain, least significant digit first (lane 0) */
+    u128 htop = gc::make_u128(0, 0);
+    uint32_t ctop = 0;
+    if (lane == 0) {
+        u128 carry = P.carry0;
+        uint64_t cnt1 = cast_e, cnt2 = cast_e;
+        for (int i = nm - 1; i >= 1; --i) {
+            const ModInfo M = P.mrs[i];
+            const ModInfo C = P.cast[i];
+            uint32_t* a = acc + (size_t)i * acc_digits;
+            const u128 hl = hash(aes, carry);
+            const uint32_t c0 = gc::colour_of(carry, M);
+            accumulate_atomic(gc::sub128(ldg128(P.cast1 + cnt1 + (uint64_t)k * M.q + c0), hl), C, a);
+            cnt1 += (uint64_t)(k + 1) * M.q;
+            uint32_t c2;
+            const u128 sum2 = compress_acc32(a, C, c2);
+            carry = gc::sub128(ldg128(P.cast2 + cnt2 + c2), hash(aes, sum2));
+            cnt2 += C.q;
+        }
+        accumulate_atomic(carry, P.mrs[0], acc);
+        const u128 top = compress_acc32(acc, P.mrs[0], ctop);
+        htop = hash(aes, top);
+    }
+    htop = shfl128(htop, 0);
+    ctop = __shfl_sync(0xffffffffu, ctop, 0);
+    const uint32_t m0 = P.mrs[0].q;
+    const u128* sign_e = P.sign + e * (uint64_t)P.n_out * m0;
+    if (!RELU) {
+        if (lane < P.n_out) store_digits(P.out[lane], P.outm[lane], e, b, P.Bp, gc::sub128(ldg128(sign_e + (uint64_t)lane * m0 + ctop), htop));
+        return;
+    }
+    /* step 4 (ReLU): hash of the sign label on lane 0, then one modulus per lane */
+    const u128 s = gc::sub128(ldg128(sign_e + ctop), htop);
+    u128 hs = gc::make_u128(0, 0);
+    if (lane == 0) hs = hash(aes, s);
+    hs = shfl128(hs, 0);
+    const uint32_t cs = (uint32_t)s.lo & 1u;
+    if (lane < k) {
+        const int j = lane;
+        const ModInfo Pm = P.crt[j];
+        const u128 G = gc::sub128(ldg128(P.garbler + e * (uint64_t)P.S + P.prefix[j] + col[j]), h[j]);
+        const u128* ev = P.evaluator + (e * (uint64_t)k + j) * 3;
+        const u128 E = gc::sub128(ldg128(ev + cs), hs);
+        const u128 mini = ldg128(ev + 2);
+        const int16_t row16 = (int16_t)((mini.lo >> (16 * cs)) & 0xffff);
+        const int16_t t16 = (int16_t)(row16 - (int16_t)(hs.lo & 0xffff));
+        int tt = (int)t16 % (int)Pm.q;
+        if (tt < 0) tt += (int)Pm.q;
+        const uint64_t off = plane_off(Pm, e, b, P.Bp);
+        const uint8_t* xin = P.in[j] + off;
+        uint8_t* xout = P.out[j] + off;
+        uint32_t xw = 0, ow = 0;
+        const uint32_t last = Pm.nc - 1;
+        gc::for_each_digit2(E, G, Pm, [&](uint32_t d, uint32_t de, uint32_t dg) {
+            if ((d & 3) == 0) xw = *reinterpret_cast<const uint32_t*>(xin + (uint64_t)(d >> 2) * 4 * P.Bp);
+            const uint32_t x = (xw >> (8 * (d & 3))) & 0xff;
+            ow |= gc::mod_q(de + (uint32_t)tt * x + Pm.q - dg, Pm) << (8 * (d & 3));
+            if ((d & 3) == 3 || d == last) {
+                *reinterpret_cast<uint32_t*>(xout + (uint64_t)(d >> 2) * 4 * P.Bp) = ow;
+                ow = 0;
+            }
+        });
+    }
+}
+
 cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s) {
     if (p.n == 0) return cudaSuccess;
     const uint64_t total = p.n * p.batch;
@@ -704,6 +854,20 @@ cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s) {
     uint32_t acc_digits = p.mrs[0].nc;
     for (int i = 1; i < p.n_mrs; ++i) acc_digits = max(acc_digits, p.cast[i].nc);
     const size_t smem = (size_t)acc_digits * SIGN_THREADS * sizeof(uint16_t);
+    /* latency mode: one warp per (element, inference) while that still leaves SMs idle otherwise */
+    static const long wide_max = getenv("DASHB_WIDE_MAX") ? atol(getenv("DASHB_WIDE_MAX")) : 8192;
+    /* with other lanes in flight the GPU is busy anyway: only tiny launches go wide */
+    if ((long)total <= (p.lanes > 1 ? wide_max / 4 : wide_max) && p.k <= 32 && p.n_out <= 32) {
+        const unsigned wgrid = (unsigned)((total + WIDE_WARPS - 1) / WIDE_WARPS);
+        const size_t wsmem = (size_t)WIDE_WARPS * p.n_mrs * acc_digits * sizeof(uint32_t);
+        if (wsmem <= 40 * 1024) {
+            if (relu)
+                k_sign_wide<true><<<wgrid, WIDE_WARPS * 32, wsmem, s>>>(p, acc_digits);
+            else
+                k_sign_wide<false><<<wgrid, WIDE_WARPS * 32, wsmem, s>>>(p, acc_digits);
+            return cudaGetLastError();
+        }
+    }
     if (relu)
         k_sign<true><<<grid, SIGN_THREADS, smem, s>>>(p);
     else

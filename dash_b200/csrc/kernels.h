@@ -76,6 +76,7 @@ struct SignParams {
     uint32_t S, Mp;
     uint32_t batch, Bp;
     int k, n_mrs, n_out;
+    int lanes;               /* sub-batch lanes evaluating concurrently (picks latency vs throughput kernel) */
 };
 
 struct ProjParams {
