@@ -1126,6 +1126,12 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
                 tp.sy = L.cv_sh;
                 tp.cb = L.cv_cb;
                 tp.b_box_bytes = conv ? 128u * L.cv_fw * L.cv_fh * L.cv_cb : 128u * 128u;
+                /* narrow convolutions: filters on the N dimension of the MMA (dense_tc.cu: k_conv_tc_n) */
+                static const bool conv_n_off = getenv("DASHB_CONV_N") != nullptr && atoi(getenv("DASHB_CONV_N")) == 0;
+                /* measured equal or better up to 32 filters, slower above (both are L2->SM bound); the
+                 * kernel itself handles 32 | filters <= 128 (DASHB_CONV_N_MAX for experiments and tests) */
+                static const int conv_n_max = getenv("DASHB_CONV_N_MAX") ? atoi(getenv("DASHB_CONV_N_MAX")) : 32;
+                if (conv && !conv_n_off && L.M % 32 == 0 && L.M <= (uint64_t)conv_n_max) tp.npad = (uint32_t)L.M;
                 for (int j = 0; j < c->k; ++j) {
                     maps.a[j] = L.map_a[j];
                     const uint64_t Nj = (uint64_t)((c->crt_mi[j].nc + 3) & ~3u) * Bp;

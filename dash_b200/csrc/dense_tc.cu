@@ -247,6 +247,156 @@ k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ Den
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TC_BN * NB));
 }
 
+/*
+ * Convolution with the FILTERS on the N dimension of the MMA: D[plane byte]
+ * [filter] = sum_k plane[k][byte] * W[filter][k].  The A operand (M = 128) is
+ * the im2col'd plane tile exactly as the kernel above stages it (now an
+ * MN-major A), the B operand the weight rows (K-major).  An MMA then costs
+ * N/2 = filters/2 cycles instead of 64, every TMEM lane holds a result (a
+ * lane is a plane byte), so all four epilogue warps work whatever the filter
+ * count -- with the filters on M, 32 filters fill a quarter of the tile and
+ * keep one epilogue warp busy.  For 32 | filters <= 128.
+ */
+template <int TC_STAGES>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+k_conv_tc_n(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ DenseTcParams P) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t bar_full[TC_STAGES], bar_empty[TC_STAGES], bar_acc;
+    __shared__ uint32_t tmem_base_s;
+    constexpr uint32_t STAGE = TC_BK * TC_BN + TC_BM * TC_BK; /* plane tile, then weight tile */
+    const int j = blockIdx.z;
+    const ModInfo m = P.mod[j];
+    const uint32_t nc4 = (m.nc + 3) >> 2;
+    const uint32_t Nj = nc4 * 4 * P.Bp;
+    const uint32_t n0 = blockIdx.x * TC_BN;
+    if (n0 >= Nj) return;
+    const uint32_t pix = blockIdx.y;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t nkb = P.nkb, npad = P.npad;
+    const uint32_t tmem_cols = npad <= 32 ? 32u : npad <= 64 ? 64u : 128u; /* a power of two >= 32 */
+
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(tmem_cols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < TC_STAGES; ++s) {
+            mbar_init(&bar_full[s], 1);
+            mbar_init(&bar_empty[s], 1);
+        }
+        mbar_init(&bar_acc, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;");
+        asm volatile("fence.proxy.async.shared::cta;");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const uint32_t tmem_base = tmem_base_s;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (uint32_t kb = 0; kb < nkb; ++kb) {
+                const uint32_t s = kb % TC_STAGES, round = kb / TC_STAGES;
+                if (round > 0) mbar_wait(&bar_empty[s], (round - 1) & 1);
+                uint8_t* sP = smem + s * STAGE;
+                uint8_t* sW = sP + TC_BK * TC_BN;
+                mbar_expect_tx(&bar_full[s], TC_BM * TC_BK + P.b_box_bytes);
+                tma_load_4d(sP, reinterpret_cast<const CUtensorMap*>(&maps.b[j]), &bar_full[s], (int)n0, (int)((pix % P.ow) * P.sx),
+                            (int)((pix / P.ow) * P.sy), (int)(kb * P.cb));
+                tma_load_2d(sW, reinterpret_cast<const CUtensorMap*>(&maps.a[j]), &bar_full[s], (int)(kb * TC_BK), 0); /* all filter rows */
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            /* S32 accumulator, U8 x U8, A MN-major (bit 15), B K-major, M = 128, N = npad */
+            const uint32_t idesc = (2u << 4) | (1u << 15) | ((npad >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+            for (uint32_t kb = 0; kb < nkb; ++kb) {
+                const uint32_t s = kb % TC_STAGES, round = kb / TC_STAGES;
+                mbar_wait(&bar_full[s], round & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;");
+                const uint32_t aP = smem_u32(smem + s * STAGE);
+                const uint32_t aW = aP + TC_BK * TC_BN;
+#pragma unroll
+                for (int k4 = 0; k4 < TC_BK / 32; ++k4) {
+                    const uint64_t da = umma_desc(aP + k4 * 32 * TC_BN, 16, 1024); /* +32 k-rows of 128 plane bytes */
+                    const uint64_t db = umma_desc(aW + k4 * 32, 16, 1024);         /* +32 B inside the swizzled weight row */
+                    const uint32_t acc = (kb | (uint32_t)k4) ? 1u : 0u;
+                    asm volatile(
+                        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}" ::"r"(tmem_base),
+                        "l"(da), "l"(db), "r"(idesc), "r"(acc), "r"(0), "r"(0), "r"(0), "r"(0)
+                        : "memory");
+                }
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                                 smem_u32(&bar_empty[s]))
+                             : "memory");
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar_acc))
+                         : "memory");
+        }
+    } else {
+        /* epilogue: TMEM lane = plane byte, column = filter.  The reduced
+         * bytes are transposed through shared memory (the operand stages are
+         * free once the accumulator is complete) so that the global stores
+         * are 16 bytes per thread along a filter's row, and the constant
+         * label bytes come from a small shared copy instead of one global
+         * load per output. */
+        mbar_wait(&bar_acc, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        const uint32_t sub = (uint32_t)warp & 3u;
+        const uint32_t te = threadIdx.x - 64; /* 0..127 among the epilogue threads */
+        const uint32_t l128 = sub * 32 + lane;
+        const uint32_t n = n0 + l128;
+        const uint32_t ncp = nc4 * 4;
+        const uint32_t d4_first = n0 / (4 * P.Bp);
+        uint8_t* s_out = smem;                                        /* [npad][128] */
+        uint32_t* s_cst = reinterpret_cast<uint32_t*>(smem + 128 * 128); /* [npad][4] words of 4 digits */
+        for (uint32_t i = te; i < npad * 4; i += 128) {
+            const uint32_t f = i >> 2, d4 = d4_first + (i & 3u);
+            s_cst[i] = d4 < nc4 ? __ldg(reinterpret_cast<const uint32_t*>(P.cst[j] + (uint64_t)f * ncp) + d4) : 0u;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const uint32_t q = (n < Nj ? n / (4 * P.Bp) : d4_first) - d4_first; /* < 4: a 128-byte chunk spans at most 3 digit words */
+        const uint32_t sh = 8 * (n & 3u);
+        for (uint32_t c0 = 0; c0 < npad; c0 += 32) {
+            uint32_t v[32];
+            const uint32_t taddr = tmem_base + ((sub * 32u) << 16) + c0;
+            asm volatile(
+                "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                  "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                  "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                  "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const uint32_t f = c0 + i; /* filter */
+                uint32_t x = v[i] + ((s_cst[f * 4 + q] >> sh) & 0xffu);
+                x -= gc::mulhi32(x, m.mq) * m.q;
+                if ((int32_t)x < 0) x += m.q;
+                s_out[f * 128 + l128] = (uint8_t)x;
+            }
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        /* 8 threads x 16 bytes per filter row, 16 rows per pass */
+        const uint32_t col16 = (te & 7u) * 16;
+        if (n0 + col16 < Nj) { /* Nj is a multiple of 64 */
+            for (uint32_t f = te >> 3; f < npad; f += 16) {
+                if (f < P.v0 || f >= P.v1) continue;
+                const uint4 w = *reinterpret_cast<const uint4*>(s_out + f * 128 + col16);
+                *reinterpret_cast<uint4*>(P.out[j] + ((uint64_t)f * P.npix + pix) * Nj + n0 + col16) = w;
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols));
+}
+
 /* ---- host side: tensor maps ---- */
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -309,6 +459,18 @@ cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p, cud
     uint32_t max_cols = 0;
     for (int j = 0; j < p.k; ++j) max_cols = max(max_cols, ((p.mod[j].nc + 3) & ~3u) * p.Bp);
     const uint32_t mblocks = (p.v1 - p.v0 + TC_BM - 1) / TC_BM;
+    if (p.conv && p.npad) {
+        static bool attr_n = false;
+        constexpr uint32_t smem_n = TC_STAGES_CONV * (TC_BK * TC_BN + TC_BM * TC_BK) + 1024;
+        if (!attr_n) {
+            cudaError_t e = cudaFuncSetAttribute(k_conv_tc_n<TC_STAGES_CONV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_n);
+            if (e != cudaSuccess) return e;
+            attr_n = true;
+        }
+        dim3 grid((max_cols + TC_BN - 1) / TC_BN, p.npix, p.k);
+        k_conv_tc_n<TC_STAGES_CONV><<<grid, TC_THREADS, smem_n, s>>>(maps, p);
+        return cudaGetLastError();
+    }
     if (p.npix > 1 || p.conv) {
         dim3 grid((max_cols + TC_BN * TC_NB - 1) / (TC_BN * TC_NB), mblocks * p.npix, p.k);
         k_dense_tc<true, TC_STAGES_CONV, TC_NB><<<grid, TC_THREADS, tc_smem_bytes(TC_STAGES_CONV, TC_NB), s>>>(maps, p);

@@ -58,6 +58,7 @@ struct DenseTcParams {
     uint32_t b_box_bytes;  /* bytes one B box brings in (dense: 128*128) */
     /* convolution: per output pixel one GEMM; box {128, f_w, f_h, cb} at {n, x*sx, y*sy, kb*cb} */
     uint32_t conv, npix, ow, sx, sy, cb;
+    uint32_t npad;         /* != 0: filters on the N dimension (k_conv_tc_n), N = npad */
     int k;
 };
 

@@ -201,9 +201,12 @@ def test_dense_tensor_core_path(gpu, tmp_path, M, K, batch):
     (12, 12, 16, 32, 2, 2),  # 2x2/2 "pool replacement", K = 64
     (9, 9, 33, 130, 2, 1),   # two filter blocks (130 > 128), 33 channels = 32 + 1
     (7, 7, 3, 16, 5, 2),     # 5x5 filter: 5 channels per block, only 3 present
+    (9, 9, 20, 64, 3, 1),    # 64 filters: filters-on-N kernel, two K blocks
+    (6, 6, 40, 128, 3, 1),   # 128 filters on N, three K blocks
+    (8, 8, 8, 96, 2, 2),     # 96 filters on N (TMEM allocation rounds up to 128 columns)
 ])
 @pytest.mark.parametrize("batch", [1, 19])
-def test_conv_tensor_core_path(gpu, tmp_path, geom, batch):
+def test_conv_tensor_core_path(gpu, tmp_path, geom, batch, monkeypatch):
     """Convolutions wide enough for the tcgen05 kernel (im2col by a 4-D TMA
     box, dense_tc.cu), followed by a ReLU; bit-exact against the reference
     and against the dp4a kernel's result for the same circuit."""
@@ -213,6 +216,7 @@ def test_conv_tensor_core_path(gpu, tmp_path, geom, batch):
     if not R.available():
         pytest.skip("oracle/_ref not present on this box")
     w, h, ch, filters, f, stride = geom
+    monkeypatch.setenv("DASHB_CONV_N_MAX", "128")  # read once per process: also exercises the filters-on-N kernel at 64..128 filters
     spec = dict(input=(w, h, ch), layers=[("conv", filters, f, stride), ("relu",)], quant=("simple", 0.02), **W.cpm(8, 99.0))
     ref = W.build_reference_circuit(spec, seed=w * h, weight_seed=filters)
     path = str(tmp_path / "conv.gcm")
