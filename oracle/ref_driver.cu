@@ -38,6 +38,7 @@ static inline int dash_ref_seeded_rdrand16(unsigned short* p) {
 #include "circuit/layer/conv2d.h"
 #include "circuit/layer/dense.h"
 #include "circuit/layer/flatten.h"
+#include "circuit/layer/max_pool2d.h"
 #include "circuit/layer/projection.h"
 #include "circuit/layer/relu.h"
 #include "circuit/layer/rescale.h"
@@ -47,6 +48,8 @@ static inline int dash_ref_seeded_rdrand16(unsigned short* p) {
 #include "misc/datatypes.h"
 
 #include "../integration/dash_adapter.h"
+#define ONNX_LITE_BUILD_CIRCUIT
+#include "../integration/dash_onnx_lite.h"
 
 namespace {
 
@@ -96,6 +99,23 @@ extern "C" {
 void* ref_new(void) { return new RefHandle(); }
 void ref_free(void* h) { delete static_cast<RefHandle*>(h); }
 const char* ref_error(void* h) { return static_cast<RefHandle*>(h)->err.c_str(); }
+
+/* layers of an ONNX model (integration/dash_onnx_lite.h), appended like the ref_add_* calls */
+int ref_load_onnx(void* hv, const char* path, int q_method, float q_const, int q_param) {
+    auto* h = static_cast<RefHandle*>(hv);
+    dash_onnx::Model m;
+    if (!dash_onnx::read_model(path, m)) {
+        h->err = "cannot parse ONNX model";
+        return -1;
+    }
+    std::vector<Layer*> layers = dash_onnx::build_layers(m, qm(q_method), q_const, q_param);
+    if (layers.empty()) {
+        h->err = "ONNX model has no supported layers or is malformed";
+        return -1;
+    }
+    for (auto* l : layers) h->layers.push_back(l);
+    return (int)layers.size();
+}
 
 int ref_add_flatten(void* hv, uint64_t d0, uint64_t d1, uint64_t d2) {
     auto* h = static_cast<RefHandle*>(hv);

@@ -31,6 +31,7 @@ def lib():
         L.ref_error.restype = C.c_char_p
         L.ref_error.argtypes = [C.c_void_p]
         L.ref_add_flatten.argtypes = [C.c_void_p] + [C.c_uint64] * 3
+        L.ref_load_onnx.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_float, C.c_int]
         L.ref_add_dense.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_int]
         L.ref_add_conv2d.argtypes = [C.c_void_p] + [C.c_uint64] * 8 + [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int]
         for f in (L.ref_add_relu, L.ref_add_sign):
@@ -94,6 +95,14 @@ class RefCircuit:
     def _d3(dims):
         d = list(dims) + [0, 0]
         return d[0], d[1], d[2]
+
+    def load_onnx(self, path, q_method=0, q_const=0.02, q_param=-1):
+        """Appends the layers of an ONNX model through integration/dash_onnx_lite.h
+        (the protobuf-free restatement of circuit/onnx_modelloader.h)."""
+        n = self.L.ref_load_onnx(self.h, os.fsencode(path), q_method, q_const, q_param)
+        if n < 0:
+            raise RuntimeError("ref_load_onnx: " + self.L.ref_error(self.h).decode())
+        return n
 
     def add_flatten(self, dims):
         self._chk(self.L.ref_add_flatten(self.h, *self._d3(dims)))

@@ -175,3 +175,43 @@ def test_gpu_garbled_circuit_decodes_to_the_plain_evaluation(gpu, name):
     for b in range(batch):
         assert np.array_equal(vals[b], _plain_eval(plain, X[b], P)), "inference %d" % b
     c.close()
+
+
+def test_onnx_model_to_gpu_garbled_inference(gpu, tmp_path):
+    """The whole pipeline without protobuf and without the reference's
+    garbler: ONNX file -> integration/dash_onnx_lite.h (reference layer
+    classes quantise) -> plaintext circuit -> GPU garbler -> GPU evaluator;
+    decoded values equal the reference's own garble + evaluate + decode of the
+    same model."""
+    import sys
+
+    from helpers import ROOT
+    sys.path.insert(0, ROOT + "/tests")
+    from onnx_writer import cnn
+
+    from dash_b200 import garble, gcm
+    from oracle import refbind as R
+
+    if not R.available():
+        pytest.skip("oracle/_ref not present on this box")
+    layers = [("conv", 4, 3, 1), ("relu",), ("conv", 4, 2, 2), ("relu",), ("flatten",), ("dense", 8), ("relu",), ("dense", 4)]
+    blob, _ = cnn("pytorch", 10, 10, 1, layers, seed=12)
+    path = str(tmp_path / "m.onnx")
+    open(path, "wb").write(blob)
+    ref = R.RefCircuit()
+    ref.load_onnx(path, 2, 0.02, 32)  # ScaleQuantPlus, s = 32: a Rescale after every linear layer
+    crt, mrs = [32, 3, 5, 7, 11, 13, 17], [10, 9, 9, 8, 7, 7, 6]
+    ref.garble(crt, mrs, 32, 3)
+    ref.export(str(tmp_path / "ref.gcm"))
+    g = gcm.read_gcm(str(tmp_path / "ref.gcm"))
+    plain = gcm.plain_circuit(g)
+    assert [l["type"] for l in plain].count("rescale") == 4
+    batch = 5
+    X = np.random.default_rng(1).integers(0, 256, size=(batch, 100), dtype=np.int64)
+    want = np.array([ref.decode_outputs(ref.cpu_evaluate(ref.garble_inputs(x), 2)[0]) for x in X])
+    c, _ = garble.garble_to_circuit(crt, mrs, 100, plain, batch, seed=b"onnx", max_modulus=g["max_modulus"])
+    c.garble_inputs(X)
+    c.evaluate_device()
+    vals, ok = c.decode_outputs()
+    assert ok.all() and np.array_equal(vals, want.reshape(vals.shape))
+    c.close()
