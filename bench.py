@@ -259,6 +259,22 @@ def main():
         api._check(L.dashb_evaluate_device(circ.h))
         api._check(L.dashb_decode_outputs(circ.h, vals_t.data_ptr(), ok_t.data_ptr()))
 
+    # the same call with compressed 128-bit labels on the host side
+    # (LabelTensor::compress form, dashb_evaluate_compressed)
+    from dash_b200 import gcm as gcm_io
+
+    crt_list = gcm_io.read_gcm(gcm)["crt"]
+    import ctypes as C
+
+    comp_in = [torch.from_numpy(gcm_io.compress_labels(q, l)).pin_memory() for q, l in zip(crt_list, in_np)]
+    comp_out = [torch.empty((B, circ.output_size, 2), dtype=torch.uint64).pin_memory() for _ in range(circ.k)]
+    comp_in_ptrs = (C.c_void_p * circ.k)(*[t.data_ptr() for t in comp_in])
+    comp_out_ptrs = (C.c_void_p * circ.k)(*[t.data_ptr() for t in comp_out])
+    L.dashb_evaluate_compressed.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+
+    def step_compressed():
+        api._check(L.dashb_evaluate_compressed(circ.h, comp_in_ptrs, B, comp_out_ptrs))
+
     sampler = ClockSampler(local_rank)
     sampler.start()
     time.sleep(0.2)
@@ -266,6 +282,7 @@ def main():
     launches = circ.launch_count()
     ms_e2e = timed(step_e2e, args.steps, args.warmup)
     ms_val = timed(step_values, args.steps, args.warmup)
+    ms_comp = timed(step_compressed, args.steps, args.warmup)
     values_ok = bool(ok_t.numpy().all())
     circ.move_inputs(in_np)  # restore the label inputs for the profiling pass
     # per-kernel durations for the roofline: same steps with the sub-batch
@@ -343,6 +360,10 @@ def main():
                        "h2d_bytes_per_step": int(xs.numel() * 8), "d2h_bytes_per_step": int(vals_t.numel() * 8 + B),
                        "all_outputs_decoded": values_ok,
                        "api": "dashb_garble_inputs + dashb_evaluate_device + dashb_decode_outputs (int64 values in, int64 values out)"},
+        "e2e_compressed": {"value": total_inf / (ms_comp / 1e3), "unit": "inferences/s", "ms_per_step": ms_comp / args.steps,
+                           "h2d_bytes_per_step": int(sum(t.numel() * 8 for t in comp_in)),
+                           "d2h_bytes_per_step": int(sum(t.numel() * 8 for t in comp_out)),
+                           "api": "dashb_evaluate_compressed (labels as 16-byte LabelTensor::compress values in pinned host memory)"},
         "gpu_launches": int(launches * args.steps),
         "clocks": sampler.summary(),
         "roofline": roofline,
@@ -373,8 +394,6 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             from dash_b200 import garble as gb
-            from dash_b200 import gcm as gcm_io
-
             gref = gcm_io.read_gcm(gcm)
             plain = gcm_io.plain_circuit(gref)
             torch.cuda.synchronize()

@@ -48,6 +48,9 @@ def lib():
         L.dashb_move_outputs.argtypes = [C.c_void_p, C.c_void_p]
         L.dashb_evaluate.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.dashb_layer_outputs.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.dashb_move_inputs_compressed.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+        L.dashb_move_outputs_compressed.argtypes = [C.c_void_p, C.c_void_p]
+        L.dashb_evaluate_compressed.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
         L.dashb_decode_outputs.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         for f in (L.dashb_input_size, L.dashb_output_size, L.dashb_last_launch_count):
             f.restype = C.c_uint64
@@ -202,6 +205,35 @@ class Circuit:
         self.batch = batch
         out = self._out_arrays(self.output_size, self.out_moduli)
         _check(self.L.dashb_evaluate(self.h, _ptr_array(labels), batch, _ptr_array(out)))
+        return out
+
+    # ---- compressed 128-bit labels on the host side (uint64 [batch][label][2]) ----
+    def _in_compressed(self, labels):
+        labels = [np.ascontiguousarray(l, dtype=np.uint64) for l in labels]
+        if len(labels) != self.k:
+            raise ValueError("expected %d label tensors" % self.k)
+        batch = labels[0].shape[0]
+        for l in labels:
+            if l.shape != (batch, self.input_size, 2):
+                raise ValueError("compressed labels must be uint64 [batch][input_size][2]")
+        return labels, batch
+
+    def move_inputs_compressed(self, labels):
+        labels, batch = self._in_compressed(labels)
+        _check(self.L.dashb_move_inputs_compressed(self.h, _ptr_array(labels), batch))
+        self.batch = batch
+        self._keep = labels
+
+    def move_outputs_compressed(self):
+        out = [np.zeros((self.batch, self.output_size, 2), dtype=np.uint64) for _ in range(self.k)]
+        _check(self.L.dashb_move_outputs_compressed(self.h, _ptr_array(out)))
+        return out
+
+    def evaluate_compressed(self, labels):
+        labels, batch = self._in_compressed(labels)
+        self.batch = batch
+        out = [np.zeros((batch, self.output_size, 2), dtype=np.uint64) for _ in range(self.k)]
+        _check(self.L.dashb_evaluate_compressed(self.h, _ptr_array(labels), batch, _ptr_array(out)))
         return out
 
     def layer_outputs(self, layer, n, moduli):

@@ -1021,12 +1021,18 @@ static int split_batch(dashb_circuit* c, uint64_t batch) {
  * layout-changing ingest kernels (stream s).  With cs != s the copies of
  * all lanes run back to back on the copy engine while earlier lanes compute;
  * s waits for the lane's last copy. */
-static int enqueue_inputs(dashb_circuit* c, Lane& ln, const int16_t* const* in, cudaStream_t cs, cudaStream_t s) {
+/* bytes one label of modulus index j takes on the host side of the boundary */
+static size_t wire_label_bytes(const dashb_circuit* c, int j, bool compressed) {
+    return compressed ? 16 : (size_t)c->crt_mi[j].nc * 2;
+}
+
+/* `in`: per CRT modulus int16 [batch][label][nc], or (compressed) dashb_u128 [batch][label] */
+static int enqueue_inputs(dashb_circuit* c, Lane& ln, const void* const* in, bool compressed, cudaStream_t cs, cudaStream_t s) {
     size_t off = 0;
     for (int j = 0; j < c->k; ++j) {
-        const uint64_t rows = c->input_size * c->crt_mi[j].nc;
-        const size_t bytes = (size_t)ln.batch * rows * 2;
-        CU(cudaMemcpyAsync((char*)ln.stage_in.p + off, in[j] + (size_t)ln.b0 * rows, bytes, cudaMemcpyHostToDevice, cs));
+        const size_t per = c->input_size * wire_label_bytes(c, j, compressed);
+        const size_t bytes = (size_t)ln.batch * per;
+        CU(cudaMemcpyAsync((char*)ln.stage_in.p + off, (const char*)in[j] + (size_t)ln.b0 * per, bytes, cudaMemcpyHostToDevice, cs));
         off += bytes;
     }
     /* the ingest kernels are short; in the pipelined path they run on a
@@ -1039,10 +1045,12 @@ static int enqueue_inputs(dashb_circuit* c, Lane& ln, const int16_t* const* in, 
     }
     off = 0;
     for (int j = 0; j < c->k; ++j) {
-        const uint64_t rows = c->input_size * c->crt_mi[j].nc;
-        CU(launch_ingest((const int16_t*)((char*)ln.stage_in.p + off), ln.t_in.plane[j], c->input_size, c->crt_mi[j].nc,
-                         ln.batch, ln.Bp, is));
-        off += (size_t)ln.batch * rows * 2;
+        const void* st = (const char*)ln.stage_in.p + off;
+        if (compressed)
+            CU(launch_ingest_compressed(st, ln.t_in.plane[j], c->input_size, c->crt_mi[j], ln.batch, ln.Bp, is));
+        else
+            CU(launch_ingest((const int16_t*)st, ln.t_in.plane[j], c->input_size, c->crt_mi[j].nc, ln.batch, ln.Bp, is));
+        off += (size_t)ln.batch * c->input_size * wire_label_bytes(c, j, compressed);
     }
     if (is != s) {
         CU(cudaEventRecord(ln.ing_done, is));
@@ -1053,7 +1061,7 @@ static int enqueue_inputs(dashb_circuit* c, Lane& ln, const int16_t* const* in, 
     return DASHB_OK;
 }
 
-int dashb_move_inputs(dashb_circuit* c, const int16_t* const* in, uint64_t batch) {
+static int move_inputs_any(dashb_circuit* c, const void* const* in, uint64_t batch, bool compressed) {
     if (!c || !in) return fail(DASHB_EINVAL, "null argument");
     if (!c->finalized) return fail(DASHB_ESTATE, "circuit not finalized");
     for (int j = 0; j < c->k; ++j)
@@ -1062,8 +1070,16 @@ int dashb_move_inputs(dashb_circuit* c, const int16_t* const* in, uint64_t batch
     if (rc) return rc;
     if ((rc = fork_lanes(c))) return rc;
     for (int i = 0; i < c->lanes_used; ++i)
-        if ((rc = enqueue_inputs(c, *c->lanes[i], in, c->lanes[i]->s, c->lanes[i]->s))) return rc;
+        if ((rc = enqueue_inputs(c, *c->lanes[i], in, compressed, c->lanes[i]->s, c->lanes[i]->s))) return rc;
     return join_lanes(c);
+}
+
+int dashb_move_inputs(dashb_circuit* c, const int16_t* const* in, uint64_t batch) {
+    return move_inputs_any(c, reinterpret_cast<const void* const*>(in), batch, false);
+}
+
+int dashb_move_inputs_compressed(dashb_circuit* c, const dashb_u128* const* in, uint64_t batch) {
+    return move_inputs_any(c, reinterpret_cast<const void* const*>(in), batch, true);
 }
 
 int dashb_garble_inputs(dashb_circuit* c, const int64_t* values, uint64_t batch) {
@@ -1362,49 +1378,58 @@ int dashb_evaluate_device(dashb_circuit* c) {
     return DASHB_OK;
 }
 
-static int enqueue_outputs(dashb_circuit* c, Lane& ln, int16_t* const* out, cudaStream_t s) {
+static int enqueue_outputs(dashb_circuit* c, Lane& ln, void* const* out, bool compressed, cudaStream_t s) {
     size_t off = 0;
     for (int j = 0; j < c->k; ++j) {
-        const uint32_t nc = (uint32_t)nr_comps(ln.t_cur.q[j]);
-        const uint64_t rows = ln.t_cur.n * (uint64_t)nc;
-        const size_t bytes = (size_t)ln.batch * rows * 2;
-        int16_t* st = (int16_t*)((char*)ln.stage_out.p + off);
-        CU(launch_egress(ln.t_cur.plane[j], st, ln.t_cur.n, nc, ln.batch, ln.Bp, s));
-        CU(cudaMemcpyAsync(out[j] + (size_t)ln.b0 * rows, st, bytes, cudaMemcpyDeviceToHost, s));
+        const ModInfo m = make_modinfo((uint32_t)ln.t_cur.q[j]);
+        const size_t per = ln.t_cur.n * (compressed ? 16 : (size_t)m.nc * 2);
+        const size_t bytes = (size_t)ln.batch * per;
+        void* st = (char*)ln.stage_out.p + off;
+        if (compressed)
+            CU(launch_egress_compressed(ln.t_cur.plane[j], st, ln.t_cur.n, m, ln.batch, ln.Bp, s));
+        else
+            CU(launch_egress(ln.t_cur.plane[j], (int16_t*)st, ln.t_cur.n, m.nc, ln.batch, ln.Bp, s));
+        CU(cudaMemcpyAsync((char*)out[j] + (size_t)ln.b0 * per, st, bytes, cudaMemcpyDeviceToHost, s));
         off += bytes;
     }
     return DASHB_OK;
 }
 
-static int copy_out(dashb_circuit* c, int16_t* const* out) {
+static int copy_out(dashb_circuit* c, void* const* out, bool compressed) {
     for (int j = 0; j < c->k; ++j)
         if (!out[j]) return fail(DASHB_EINVAL, "output buffer %d missing", j);
     int rc = fork_lanes(c);
     if (rc) return rc;
     for (int i = 0; i < c->lanes_used; ++i)
-        if ((rc = enqueue_outputs(c, *c->lanes[i], out, c->lanes[i]->s))) return rc;
+        if ((rc = enqueue_outputs(c, *c->lanes[i], out, compressed, c->lanes[i]->s))) return rc;
     if ((rc = join_lanes(c))) return rc;
     CU(cudaStreamSynchronize(g_stream));
     return DASHB_OK;
 }
 
+int dashb_move_outputs_compressed(dashb_circuit* c, dashb_u128* const* out) {
+    if (!c || !out) return fail(DASHB_EINVAL, "null argument");
+    if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "nothing evaluated");
+    return copy_out(c, reinterpret_cast<void* const*>(out), true);
+}
+
 int dashb_move_outputs(dashb_circuit* c, int16_t* const* out) {
     if (!c || !out) return fail(DASHB_EINVAL, "null argument");
     if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "nothing evaluated");
-    return copy_out(c, out);
+    return copy_out(c, reinterpret_cast<void* const*>(out), false);
 }
 
 /* cuda_move_inputs + cuda_evaluate + cuda_move_outputs as one pipelined
  * pass: every lane copies its slice in, runs all layers and copies its
  * outputs back on its own stream. */
-int dashb_evaluate(dashb_circuit* c, const int16_t* const* in, uint64_t batch, int16_t* const* out) {
+static int evaluate_any(dashb_circuit* c, const void* const* in, uint64_t batch, void* const* out, bool compressed) {
     if (!c || !in || !out) return fail(DASHB_EINVAL, "null argument");
     if (!c->finalized) return fail(DASHB_ESTATE, "circuit not finalized");
     if (c->timing) { /* serialised, per-layer events */
-        int rc = dashb_move_inputs(c, in, batch);
+        int rc = move_inputs_any(c, in, batch, compressed);
         if (rc) return rc;
         if ((rc = dashb_evaluate_device(c))) return rc;
-        return dashb_move_outputs(c, out);
+        return copy_out(c, out, compressed);
     }
     for (int j = 0; j < c->k; ++j)
         if (!in[j] || !out[j]) return fail(DASHB_EINVAL, "label buffer %d missing", j);
@@ -1421,7 +1446,7 @@ int dashb_evaluate(dashb_circuit* c, const int16_t* const* in, uint64_t batch, i
     for (int i = 0; i < c->lanes_used; ++i) {
         /* all H2D copies go through one copy stream, lane after lane, so that
          * lane i-1 computes while lane i still transfers */
-        if ((rc = enqueue_inputs(c, *c->lanes[i], in, c->copy_s, c->lanes[i]->s))) return rc;
+        if ((rc = enqueue_inputs(c, *c->lanes[i], in, compressed, c->copy_s, c->lanes[i]->s))) return rc;
         if (trace) cudaEventRecord(tr[1 + 3 * i], c->lanes[i]->s);
     }
     const int nl = (int)c->layers.size();
@@ -1435,7 +1460,7 @@ int dashb_evaluate(dashb_circuit* c, const int16_t* const* in, uint64_t batch, i
         for (int j = 0; j < c->k; ++j) c->out_q[j] = c->layers[nl - 1]->out_q[j];
     }
     for (int i = 0; i < c->lanes_used; ++i) {
-        if ((rc = enqueue_outputs(c, *c->lanes[i], out, c->lanes[i]->s))) return rc;
+        if ((rc = enqueue_outputs(c, *c->lanes[i], out, compressed, c->lanes[i]->s))) return rc;
         if (trace) cudaEventRecord(tr[3 + 3 * i], c->lanes[i]->s);
     }
     if ((rc = join_lanes(c))) return rc;
@@ -1453,6 +1478,14 @@ int dashb_evaluate(dashb_circuit* c, const int16_t* const* in, uint64_t batch, i
     return DASHB_OK;
 }
 
+int dashb_evaluate(dashb_circuit* c, const int16_t* const* in, uint64_t batch, int16_t* const* out) {
+    return evaluate_any(c, reinterpret_cast<const void* const*>(in), batch, reinterpret_cast<void* const*>(out), false);
+}
+
+int dashb_evaluate_compressed(dashb_circuit* c, const dashb_u128* const* in, uint64_t batch, dashb_u128* const* out) {
+    return evaluate_any(c, reinterpret_cast<const void* const*>(in), batch, reinterpret_cast<void* const*>(out), true);
+}
+
 int dashb_layer_outputs(dashb_circuit* c, int layer, int16_t* const* out) {
     if (!c || !out) return fail(DASHB_EINVAL, "null argument");
     if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "no inputs moved");
@@ -1462,7 +1495,7 @@ int dashb_layer_outputs(dashb_circuit* c, int layer, int16_t* const* out) {
     int rc = run_layers(c, layer);
     c->timing = t;
     if (rc) return rc;
-    return copy_out(c, out);
+    return copy_out(c, reinterpret_cast<void* const*>(out), false);
 }
 
 int dashb_decode_outputs(dashb_circuit* c, int64_t* values, uint8_t* ok) {

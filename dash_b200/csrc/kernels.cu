@@ -412,6 +412,42 @@ cudaError_t launch_linear(const LinearParams& p, cudaStream_t s) {
     return cudaGetLastError();
 }
 
+/* Compressed wire form: a label crosses PCIe as the 16
+ * bytes LabelTensor::compress produces (garbling/label_tensor.h:715-727)
+ * instead of 2*nc bytes of int16 digits; host layout [batch][label]. */
+__global__ void __launch_bounds__(128) k_ingest_compressed(const u128* __restrict__ src, uint8_t* __restrict__ plane, uint64_t n,
+                                                            const ModInfo m, uint32_t batch, uint32_t Bp) {
+    const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n * batch) return;
+    const uint32_t b = (uint32_t)(idx % batch);
+    const uint64_t e = idx / batch;
+    store_digits(plane, m, e, b, Bp, ldg128(src + (uint64_t)b * n + e));
+}
+
+__global__ void __launch_bounds__(128) k_egress_compressed(const uint8_t* __restrict__ plane, u128* __restrict__ dst, uint64_t n,
+                                                            const ModInfo m, uint32_t batch, uint32_t Bp) {
+    const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n * batch) return;
+    const uint32_t b = (uint32_t)(idx % batch);
+    const uint64_t e = idx / batch;
+    uint32_t colour;
+    dst[(uint64_t)b * n + e] = load_compress(plane, m, e, b, Bp, colour);
+}
+
+cudaError_t launch_ingest_compressed(const void* src, uint8_t* plane, uint64_t n, const ModInfo& m, uint32_t batch, uint32_t Bp,
+                                     cudaStream_t s) {
+    if (n * batch == 0) return cudaSuccess;
+    k_ingest_compressed<<<(unsigned)((n * batch + 127) / 128), 128, 0, s>>>((const u128*)src, plane, n, m, batch, Bp);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_egress_compressed(const uint8_t* plane, void* dst, uint64_t n, const ModInfo& m, uint32_t batch, uint32_t Bp,
+                                     cudaStream_t s) {
+    if (n * batch == 0) return cudaSuccess;
+    k_egress_compressed<<<(unsigned)((n * batch + 127) / 128), 128, 0, s>>>(plane, (u128*)dst, n, m, batch, Bp);
+    return cudaGetLastError();
+}
+
 /* -------------------------------------------------------- projection */
 /* GarbledProjection::cuda_evaluate / eval_proj (layer/garbled_projection.h:
  * 168-194, misc/cuda_util.h:297-317): out = digits(ciphers[e][colour] -

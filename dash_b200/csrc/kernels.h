@@ -230,6 +230,10 @@ cudaError_t launch_ingest(const int16_t* src, uint8_t* plane, uint64_t n, uint32
                           cudaStream_t s);
 cudaError_t launch_egress(const uint8_t* plane, int16_t* dst, uint64_t n, uint32_t nc, uint32_t batch, uint32_t Bp,
                           cudaStream_t s);
+cudaError_t launch_ingest_compressed(const void* src, uint8_t* plane, uint64_t n, const gc::ModInfo& m, uint32_t batch, uint32_t Bp,
+                                     cudaStream_t s);
+cudaError_t launch_egress_compressed(const uint8_t* plane, void* dst, uint64_t n, const gc::ModInfo& m, uint32_t batch, uint32_t Bp,
+                                     cudaStream_t s);
 cudaError_t launch_linear(const LinearParams& p, cudaStream_t s);
 cudaError_t dense_tc_make_map(void* map_out, const void* ptr, uint64_t inner, uint64_t outer);
 cudaError_t conv_tc_make_map(void* map_out, const void* ptr, uint64_t row_bytes, uint64_t in_w, uint64_t in_h,

@@ -109,3 +109,43 @@ def encode_inputs(g, x):
         off = g["in_offset"][j].astype(np.int64)
         labels.append(((base + (x % q)[:, None] * off[None, :]) % q).astype(np.int16))
     return labels
+
+
+def compress_labels(q, labels):
+    """LabelTensor::compress (garbling/label_tensor.h:715-727) for a whole
+    array: int16 digits [..., nc] -> uint64 [..., 2] (low, high half of the
+    128-bit value sum_i d_i q^i), vectorised on 32-bit limbs."""
+    labels = np.asarray(labels)
+    nc = labels.shape[-1]
+    lab = labels.reshape(-1, nc).astype(np.uint64)
+    x = [np.zeros(lab.shape[0], dtype=np.uint64) for _ in range(4)]
+    qq = np.uint64(q)
+    mask, s32 = np.uint64(0xFFFFFFFF), np.uint64(32)
+    for d in range(nc - 1, -1, -1):
+        carry = lab[:, d]
+        for i in range(4):
+            t = x[i] * qq + carry
+            x[i] = t & mask
+            carry = t >> s32
+    out = np.stack([x[0] | (x[1] << s32), x[2] | (x[3] << s32)], axis=-1)
+    return np.ascontiguousarray(out.reshape(labels.shape[:-1] + (2,)))
+
+
+def decompress_labels(q, values):
+    """LabelTensor::decompress: uint64 [..., 2] -> int16 digits [..., nc(q)]
+    (exact base-q digits; valid labels are below q^nc)."""
+    values = np.asarray(values, dtype=np.uint64)
+    nc = nr_comps(q)
+    v = values.reshape(-1, 2)
+    mask, s32 = np.uint64(0xFFFFFFFF), np.uint64(32)
+    x = [v[:, 0] & mask, v[:, 0] >> s32, v[:, 1] & mask, v[:, 1] >> s32]
+    qq = np.uint64(q)
+    out = np.zeros((v.shape[0], nc), dtype=np.int16)
+    for d in range(nc):
+        r = np.zeros(v.shape[0], dtype=np.uint64)
+        for i in range(3, -1, -1):
+            cur = (r << s32) | x[i]
+            x[i] = cur // qq
+            r = cur % qq
+        out[:, d] = r.astype(np.int16)
+    return out.reshape(values.shape[:-1] + (nc,))

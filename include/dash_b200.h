@@ -236,6 +236,19 @@ int dashb_move_outputs(dashb_circuit* c, int16_t* const* out);
 /* The three calls above in sequence. */
 int dashb_evaluate(dashb_circuit* c, const int16_t* const* in, uint64_t batch,
                    int16_t* const* out);
+/*
+ * The same three calls with labels in their compressed 128-bit form on the
+ * host side (what LabelTensor::compress() leaves in get_compressed(),
+ * garbling/label_tensor.h:715-727; SURVEY.md row f2: "compressed 128-bit
+ * labels are the natural wire form"): per CRT modulus dashb_u128
+ * [batch][label].  16 bytes per label cross PCIe instead of 2*nc (6.5x less
+ * for the k = 9 base); the digits are extracted / recombined on the device.
+ * No counterpart in the reference, whose GPU path always copies digit arrays.
+ */
+int dashb_move_inputs_compressed(dashb_circuit* c, const dashb_u128* const* in, uint64_t batch);
+int dashb_move_outputs_compressed(dashb_circuit* c, dashb_u128* const* out);
+int dashb_evaluate_compressed(dashb_circuit* c, const dashb_u128* const* in, uint64_t batch, dashb_u128* const* out);
+
 /* Debug/parity hook: copies the output labels of layer `layer` (index into
  * the layers added, flatten not counted) of the last evaluation. */
 int dashb_layer_outputs(dashb_circuit* c, int layer, int16_t* const* out);

@@ -230,3 +230,30 @@ def test_conv_tensor_core_path(gpu, tmp_path, geom, batch, monkeypatch):
         want, _ = ref.cpu_evaluate([l[b] for l in labels], 4)
         assert_labels_equal([g[b] for g in got], want, "conv %s inference %d" % (geom, b))
     c.close()
+
+
+@pytest.mark.parametrize("name", ["MLP_TINY", "CONV_UNIT", "RESCALE_2_3"])
+@pytest.mark.parametrize("batch", [1, 37, 130])
+def test_compressed_wire_labels(gpu, name, batch):
+    """dashb_evaluate_compressed / move_*_compressed: labels cross the
+    boundary as LabelTensor::compress leaves them (16 bytes each); the result,
+    decompressed, is the int16-path result bit for bit."""
+    from dash_b200 import gcm
+
+    g = Golden(name)
+    c = gpu.Circuit.load(g.gcm, max_batch=batch)
+    labels = tile_batch(g.inputs, batch)
+    want = c.evaluate(labels)
+    info = gcm.read_gcm(g.gcm)
+    comp = [gcm.compress_labels(q, l) for q, l in zip(info["crt"], labels)]
+    got = c.evaluate_compressed(comp)
+    for j, q in enumerate(c.out_moduli):
+        assert np.array_equal(gcm.decompress_labels(q, got[j]), want[j]), "modulus %d" % q
+    # the separate calls
+    c.move_inputs_compressed(comp)
+    c.evaluate_device()
+    again = c.move_outputs_compressed()
+    for a, b in zip(again, got):
+        assert np.array_equal(a, b)
+    assert_labels_equal(c.move_outputs(), want, "int16 outputs after compressed inputs")
+    c.close()
