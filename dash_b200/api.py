@@ -65,6 +65,8 @@ def lib():
         L.dashb_set_shard.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.dashb_evaluate_layers.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.dashb_current_plane.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.dashb_current_slice_compress.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, C.c_void_p]
+        L.dashb_current_slice_decompress.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, C.c_void_p]
         L.dashb_layer_slice.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.dashb_set_layer_timing.argtypes = [C.c_void_p, C.c_int]
         L.dashb_layer_time_ms.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float)]
@@ -140,6 +142,12 @@ class Circuit:
         ptr, bpe, n = C.c_void_p(), C.c_uint64(), C.c_uint64()
         _check(self.L.dashb_current_plane(self.h, j, C.byref(ptr), C.byref(bpe), C.byref(n)))
         return ptr.value, bpe.value, n.value
+
+    def slice_compress(self, j, e0, e1, dev_ptr):
+        _check(self.L.dashb_current_slice_compress(self.h, j, e0, e1, dev_ptr))
+
+    def slice_decompress(self, j, e0, e1, dev_ptr):
+        _check(self.L.dashb_current_slice_decompress(self.h, j, e0, e1, dev_ptr))
 
     def layer_slice(self, layer, rank):
         e0, e1 = C.c_uint64(), C.c_uint64()

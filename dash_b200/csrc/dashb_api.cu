@@ -1356,6 +1356,37 @@ int dashb_current_plane(dashb_circuit* c, int j, void** dev_ptr, uint64_t* bytes
     return DASHB_OK;
 }
 
+/* Elements [e0, e1) of plane j of the current tensor <-> compressed labels
+ * in device memory, dashb_u128 [batch][e1 - e0]; enqueued on the library
+ * stream.  The exchange of output-channel sharding sends these 16 bytes per
+ * label instead of the digit planes. */
+static int slice_args(dashb_circuit* c, int j, uint64_t e0, uint64_t e1, const void* dev) {
+    if (!c || !dev) return fail(DASHB_EINVAL, "null argument");
+    if (!c->finalized || c->batch == 0 || c->lanes_used != 1) return fail(DASHB_ESTATE, "no single-lane evaluation in flight");
+    if (j < 0 || j >= c->k || e1 < e0 || e1 > c->lanes[0]->t_cur.n) return fail(DASHB_EINVAL, "bad modulus index or element range");
+    return DASHB_OK;
+}
+
+int dashb_current_slice_compress(dashb_circuit* c, int j, uint64_t e0, uint64_t e1, void* dev_dst) {
+    int rc = slice_args(c, j, e0, e1, dev_dst);
+    if (rc) return rc;
+    Lane& ln = *c->lanes[0];
+    const ModInfo m = make_modinfo((uint32_t)ln.t_cur.q[j]);
+    const uint64_t row = (uint64_t)((m.nc + 3) & ~3u) * ln.Bp;
+    CU(launch_egress_compressed(ln.t_cur.plane[j] + e0 * row, dev_dst, e1 - e0, m, ln.batch, ln.Bp, g_stream));
+    return DASHB_OK;
+}
+
+int dashb_current_slice_decompress(dashb_circuit* c, int j, uint64_t e0, uint64_t e1, const void* dev_src) {
+    int rc = slice_args(c, j, e0, e1, dev_src);
+    if (rc) return rc;
+    Lane& ln = *c->lanes[0];
+    const ModInfo m = make_modinfo((uint32_t)ln.t_cur.q[j]);
+    const uint64_t row = (uint64_t)((m.nc + 3) & ~3u) * ln.Bp;
+    CU(launch_ingest_compressed(dev_src, ln.t_cur.plane[j] + e0 * row, e1 - e0, m, ln.batch, ln.Bp, g_stream));
+    return DASHB_OK;
+}
+
 int dashb_layer_slice(const dashb_circuit* c, int layer, int rank, uint64_t* e0, uint64_t* e1) {
     if (!c || !e0 || !e1 || layer < 0 || layer >= (int)c->layers.size() || rank < 0 || rank >= c->shard_world)
         return fail(DASHB_EINVAL, "bad argument");

@@ -278,6 +278,13 @@ int dashb_set_shard(dashb_circuit* c, int rank, int world);
 int dashb_evaluate_layers(dashb_circuit* c, int first, int last);
 int dashb_current_plane(dashb_circuit* c, int j, void** dev_ptr, uint64_t* bytes_per_element,
                         uint64_t* n_elements);
+
+/* Elements [e0, e1) of plane j of the current tensor as compressed labels in
+ * DEVICE memory (dashb_u128 [batch][e1 - e0]) and back, enqueued on the
+ * library stream: the sharded exchange then moves 16 bytes per label over
+ * NVLink instead of 4*ceil(nc/4)*Bp/batch bytes of digits. */
+int dashb_current_slice_compress(dashb_circuit* c, int j, uint64_t e0, uint64_t e1, void* dev_dst);
+int dashb_current_slice_decompress(dashb_circuit* c, int j, uint64_t e0, uint64_t e1, const void* dev_src);
 int dashb_layer_slice(const dashb_circuit* c, int layer, int rank, uint64_t* e0, uint64_t* e1);
 
 /* ---- introspection ---------------------------------------------------- */

@@ -66,7 +66,7 @@ def main():
         nbytes = 0
     else:
         c = api.Circuit.load(path, max_batch=B, shard=(rank, world))
-        ev = ChannelShardedEvaluator(c, rank, world, dist=dist if world > 1 else None)
+        ev = ChannelShardedEvaluator(c, rank, world, dist=dist if world > 1 else None, compressed="--compressed" in sys.argv)
         labels = [np.stack([gcm.encode_inputs(g, x)[j] for x in X]) for j in range(len(spec["crt"]))]
         out = ev.evaluate(labels)
         ev.bytes_exchanged = 0
@@ -96,7 +96,8 @@ def main():
                           "ms_per_step": ms, "inferences_per_s": total / (ms / 1e3), "garble_s_per_rank": garble_s,
                           "garble_kernel_ms": st["kernel_ms"], "table_GB": st["table_bytes"] / 1e9,
                           "nvlink_bytes_received_per_step_per_rank": nbytes, "bit_exact_vs_oracle": bool(exact),
-                          "scaling": "weak" if mode == "batch" else "strong"}), flush=True)
+                          "scaling": "weak" if mode == "batch" else "strong",
+                          "exchange": None if mode == "batch" else ("compressed labels" if "--compressed" in sys.argv else "digit planes")}), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
