@@ -136,6 +136,10 @@ struct DevMem {
         /* cudaMemcpyDefault: the source may also be device memory (tables
          * that the GPU garbler left on the device) */
         if (n) e = cudaMemcpy(p, src, n, cudaMemcpyDefault);
+        /* The library's streams are non-blocking: nothing orders them behind
+         * the NULL stream this copy ran on, and cudaMemcpy may return while a
+         * pageable staging DMA or a device-to-device copy is still in flight. */
+        if (e == cudaSuccess && n) e = cudaStreamSynchronize(cudaStreamLegacy);
         return e;
     }
 };
@@ -412,6 +416,7 @@ int dashb_init(int device) {
         CU(cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking));
     }
     CU(upload_aes_tables());
+    CU(cudaDeviceSynchronize()); /* the tables went up on the NULL stream; the library's streams are non-blocking */
     g_device = device;
     return DASHB_OK;
 }
@@ -961,6 +966,7 @@ int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
         CU(cudaMemset(ln->buf_in.p, 0, in_bytes));
         CU(cudaMemset(ln->buf_a.p, 0, act_bytes));
         CU(cudaMemset(ln->buf_b.p, 0, act_bytes));
+        /* (asynchronous on the NULL stream: dashb_finalize ends with a device synchronisation) */
         c->lanes.push_back(std::move(ln));
     }
     CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
@@ -974,6 +980,10 @@ int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
     CU(c->d_ok.alloc(max_batch));
     c->ev.resize(c->layers.size() + 1);
     for (auto& e : c->ev) CU(cudaEventCreate(&e));
+    /* the buffer clears above and every upload made while building ran on
+     * the NULL stream; the evaluation streams are non-blocking, so wait here
+     * once instead of racing the first evaluation */
+    CU(cudaDeviceSynchronize());
     c->finalized = true;
     return DASHB_OK;
 }

@@ -308,6 +308,10 @@ int run_gates(Garbler& G, std::vector<GateDesc>& descs, const std::vector<uint64
     P.r_off = (const uint32_t*)G.d_r_off.p;
     P.layer_tag = G.layer_tag;
     cudaStream_t s = library_stream();
+    /* every upload and table clear above ran on the NULL stream (and a
+     * pageable cudaMemcpy may return before its DMA lands); the library
+     * stream is non-blocking, so nothing orders the kernel behind them */
+    GCU(cudaDeviceSynchronize());
     GCU(cudaEventRecord(G.ev0, s));
     GCU(launch_garble_gates(P, s));
     GCU(cudaEventRecord(G.ev1, s));

@@ -215,3 +215,26 @@ def test_onnx_model_to_gpu_garbled_inference(gpu, tmp_path):
     vals, ok = c.decode_outputs()
     assert ok.all() and np.array_equal(vals, want.reshape(vals.shape))
     c.close()
+
+
+def test_garbling_is_deterministic_under_repetition(gpu, tmp_path):
+    """Regression: uploads and table clears on the NULL stream used to race
+    the gate kernel on the library's non-blocking stream (about one run in
+    twenty produced different, wrong material).  Thirty garblings of the same
+    circuit with the same seed must give one file."""
+    import hashlib
+
+    import workloads as W
+    from dash_b200 import garble
+
+    spec = dict(input=(12, 12, 2),
+                layers=[("conv", 16, 3, 1), ("relu",), ("conv", 32, 2, 2), ("relu",), ("flatten",), ("dense", 64), ("relu",),
+                        ("dense", 10)],
+                quant=("scaleplus", 32), crt=W.SCALE_CRT, mrs=W.SCALE_MRS, max_modulus=32)
+    plain, n_in = W.plain_layers(spec, weight_seed=1)
+    digests = set()
+    for r in range(30):
+        path = str(tmp_path / ("g%d.gcm" % (r % 2)))
+        garble.garble_to_file(spec["crt"], spec["mrs"], n_in, plain, path, seed=b"smoke")
+        digests.add(hashlib.sha256(open(path, "rb").read()).hexdigest())
+    assert len(digests) == 1
