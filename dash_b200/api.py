@@ -74,6 +74,7 @@ def lib():
         L.dashb_hostcheck_compress.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
         L.dashb_hostcheck_digits.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
         L.dashb_hostcheck_colour.argtypes = [C.c_int, C.c_void_p]
+        L.dashb_hostcheck_digits_frac.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
         L.dashb_hostcheck_hash.argtypes = [C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
@@ -296,6 +297,16 @@ def hostcheck_digits(q, x):
     c = np.array([x & (2**64 - 1), x >> 64], dtype=np.uint64)
     d = np.zeros(nr_comps(q), dtype=np.int16)
     lib().dashb_hostcheck_digits(int(q), c.ctypes.data, d.ctypes.data)
+    return d
+
+
+def hostcheck_digits_frac(q, x):
+    """Digits of a valid payload (x < q^nc) through the multiplicative
+    extraction of the gadget kernels; None if the modulus has no plan."""
+    c = np.array([x & (2**64 - 1), x >> 64], dtype=np.uint64)
+    d = np.zeros(nr_comps(q), dtype=np.int16)
+    if not lib().dashb_hostcheck_digits_frac(int(q), c.ctypes.data, d.ctypes.data):
+        return None
     return d
 
 

@@ -100,6 +100,143 @@ ModInfo make_modinfo(uint32_t q) {
     return m;
 }
 
+/* ---- plan of the multiplicative digit extraction (gc::FracInfo) ---- */
+namespace {
+/* little-endian 32-bit limbs, enough for 2^288 */
+struct Big {
+    uint32_t w[10];
+    Big() { memset(w, 0, sizeof(w)); }
+    void mul_small(uint32_t m) {
+        uint64_t c = 0;
+        for (int i = 0; i < 10; ++i) {
+            c += (uint64_t)w[i] * m;
+            w[i] = (uint32_t)c;
+            c >>= 32;
+        }
+    }
+    void shl1(uint32_t bit) {
+        for (int i = 9; i > 0; --i) w[i] = (w[i] << 1) | (w[i - 1] >> 31);
+        w[0] = (w[0] << 1) | bit;
+    }
+    void set_bit(int b) { w[b >> 5] |= 1u << (b & 31); }
+    bool is_zero() const {
+        for (int i = 0; i < 10; ++i)
+            if (w[i]) return false;
+        return true;
+    }
+    static int cmp(const Big& a, const Big& b) {
+        for (int i = 9; i >= 0; --i)
+            if (a.w[i] != b.w[i]) return a.w[i] < b.w[i] ? -1 : 1;
+        return 0;
+    }
+    void sub(const Big& b) {
+        uint64_t br = 0;
+        for (int i = 0; i < 10; ++i) {
+            const uint64_t d = (uint64_t)w[i] - b.w[i] - br;
+            w[i] = (uint32_t)d;
+            br = (d >> 32) & 1u;
+        }
+    }
+};
+}  // namespace
+
+gc::FracInfo make_fracinfo(const ModInfo& m) {
+    gc::FracInfo fi;
+    memset(&fi, 0, sizeof(fi));
+    const uint32_t q = m.q, nc = m.nc, t = m.t;
+    if (q < 2 || nc < 2) return fi;
+    uint32_t sh = 0;
+    while ((q >> sh) != 0) ++sh; /* bit length: q < 2^sh */
+    const int F = 160 - (int)sh;
+    Big D;
+    D.w[0] = 1;
+    for (uint32_t i = 0; i < nc; ++i) D.mul_small(q);
+    /* mu = ceil(2^(288-sh) / D), bit by bit */
+    Big rem, mu;
+    const int E = 288 - (int)sh;
+    for (int b = E; b >= 0; --b) {
+        rem.shl1(b == E ? 1u : 0u);
+        if (Big::cmp(rem, D) >= 0) {
+            rem.sub(D);
+            mu.set_bit(b);
+        }
+    }
+    if (!rem.is_zero()) {
+        /* mu += 1 */
+        uint64_t c = 1;
+        for (int i = 0; i < 10 && c; ++i) {
+            c += mu.w[i];
+            mu.w[i] = (uint32_t)c;
+            c >>= 32;
+        }
+    }
+    for (int i = 5; i < 10; ++i)
+        if (mu.w[i]) return fi; /* cannot happen: mu < q * 2^(160-sh) + 1 <= 2^160 */
+    /* first chunk: as many digits as fit next to the 2^sh alignment factor */
+    uint32_t a = 0;
+    uint64_t pa = 1;
+    while (a < t && a < nc && ((pa * q) << sh) <= 0xffffffffull) {
+        pa *= q;
+        ++a;
+    }
+    if (a == 0 || a >= nc) return fi;
+    const uint32_t rest = nc - a;
+    const uint32_t nmid = rest / t, rl = rest % t;
+    const uint32_t nst = 1 + nmid + (rl ? 1 : 0);
+    if (nst < 2 || nst > 10) return fi;
+    uint64_t plast = 1;
+    for (uint32_t i = 0; i < (rl ? rl : t); ++i) plast *= q;
+    uint32_t lens[10];
+    long double mults[10];
+    lens[0] = a;
+    mults[0] = (long double)(pa << sh);
+    for (uint32_t s = 1; s < nst; ++s) {
+        lens[s] = t;
+        mults[s] = (long double)m.Q;
+    }
+    lens[nst - 1] = rl ? rl : t;
+    mults[nst - 1] = (long double)plast;
+    const long double lq = log2l((long double)q);
+    for (int guard = 6; guard < 40; ++guard) {
+        uint32_t W[10];
+        uint32_t remd = nc;
+        for (uint32_t s = 0; s < nst; ++s) {
+            const long double need = lq * remd + guard;
+            uint32_t w = (uint32_t)ceill(need / 32);
+            if (w < 1) w = 1;
+            if (w > 5) w = 5;
+            if (s > 0 && w > W[s - 1]) w = W[s - 1];
+            W[s] = w;
+            remd -= lens[s];
+        }
+        /* what the dropped limbs can take away, in units of the stage-0 fraction */
+        long double tot = 0, amp = 1;
+        for (uint32_t s = 0; s < nst; ++s) {
+            if (W[s] < 5) tot += ldexpl(1.0L, 32 * (5 - (int)W[s])) / amp;
+            amp *= mults[s];
+        }
+        const long double addc_ld = 5 + ceill(tot * (1 + 1e-12L)) + 2;
+        if (addc_ld >= 2147483648.0L) continue;
+        const uint32_t addc = (uint32_t)addc_ld;
+        /* excess bound: (addc + 1) * D <= 2^F, exactly */
+        Big lhs = D, rhs;
+        lhs.mul_small(addc + 1);
+        rhs.set_bit(F);
+        if (Big::cmp(lhs, rhs) > 0) continue;
+        for (int i = 0; i < 5; ++i) fi.mu[i] = mu.w[i];
+        fi.addc = addc;
+        fi.nst = nst;
+        fi.m_first = (uint32_t)(pa << sh);
+        fi.m_last = (uint32_t)plast;
+        fi.len_first = a;
+        fi.len_last = lens[nst - 1];
+        fi.wl = 0;
+        for (uint32_t s = 0; s < nst; ++s) fi.wl |= W[s] << (3 * s);
+        return fi;
+    }
+    return fi;
+}
+
 /* util::mul_inv (misc/util.h:92-103) */
 uint64_t mul_inv(unsigned __int128 a, uint16_t b) {
     long long b0 = b, t, q;
@@ -233,6 +370,7 @@ struct dashb_circuit {
     int crt[MAXK];
     int mrs[MAXM];
     ModInfo crt_mi[MAXK], mrs_mi[MAXM], cast_mi[MAXM];
+    gc::FracInfo crt_fi[MAXK], cast_fi[MAXM]; /* multiplicative digit extraction plans */
     uint64_t input_size{0};
     std::vector<std::vector<int16_t>> zero; /* by modulus-2 */
     DevMem d_zero[MAXK], d_up[MAXK];
@@ -351,12 +489,14 @@ void fill_sign_params(dashb_circuit* c, SignParams& p, uint64_t n, int n_out) {
     uint32_t S = 0, Mp = 0;
     for (int j = 0; j < c->k; ++j) {
         p.crt[j] = c->crt_mi[j];
+        p.crtf[j] = c->crt_fi[j];
         p.prefix[j] = S;
         S += (uint32_t)c->crt[j];
     }
     for (int i = 0; i < c->n_mrs; ++i) {
         p.mrs[i] = c->mrs_mi[i];
         p.cast[i] = c->cast_mi[i];
+        p.castf[i] = c->cast_fi[i];
         if (i) Mp += (uint32_t)c->mrs[i];
     }
     p.S = S;
@@ -442,6 +582,7 @@ int dashb_circuit_create(dashb_circuit** out, const int32_t* crt_base, int k, co
         if (crt_base[j] > max_modulus) return fail(DASHB_EINVAL, "no zero label for CRT modulus %d", crt_base[j]);
         c->crt[j] = crt_base[j];
         c->crt_mi[j] = make_modinfo((uint32_t)crt_base[j]);
+        c->crt_fi[j] = make_fracinfo(c->crt_mi[j]);
         c->cur_q[j] = crt_base[j];
     }
     c->cur_size = input_size;
@@ -456,7 +597,11 @@ int dashb_circuit_create(dashb_circuit** out, const int32_t* crt_base, int k, co
         c->mrs_mi[i] = make_modinfo((uint32_t)mrs_base[i]);
         const int64_t cm = (int64_t)(k + 1) * mrs_base[i];
         if (i > 0 && cm > 32767) return fail(DASHB_EINVAL, "cast modulus %lld too large", (long long)cm);
+        /* the sign kernels sum k+1 digits of this modulus in 16-bit fields */
+        if ((int64_t)(k + 1) * ((i > 0 ? cm : (int64_t)mrs_base[i]) - 1) > 65535)
+            return fail(DASHB_EINVAL, "MRS modulus %d: the sum of %d digits does not fit 16 bits", mrs_base[i], k + 1);
         c->cast_mi[i] = make_modinfo((uint32_t)(i > 0 ? cm : mrs_base[i]));
+        c->cast_fi[i] = make_fracinfo(c->cast_mi[i]);
     }
     if (n_mrs) {
         const int ql = mrs_base[n_mrs - 1];
@@ -667,6 +812,7 @@ static int fill_rescale_static(dashb_circuit* c, Layer& L, uint64_t n, const int
     uint32_t off = 0;
     for (int j = 0; j < k; ++j) {
         p.crt[j] = c->crt_mi[j];
+        p.crtf[j] = c->crt_fi[j];
         p.loff[j] = off;
         off += (c->crt_mi[j].nc + 3) & ~3u;
     }
@@ -1644,6 +1790,20 @@ void dashb_hostcheck_compress(int q, const int16_t* digits, uint64_t out2[2]) {
 void dashb_hostcheck_digits(int q, const uint64_t in2[2], int16_t* digits) {
     ModInfo m = make_modinfo((uint32_t)q);
     gc::for_each_digit(gc::make_u128(in2[0], in2[1]), m, [&](uint32_t d, uint32_t v) { digits[d] = (int16_t)v; });
+}
+/* same digits through the multiplicative extraction (valid payloads only);
+ * returns 0 if the modulus has no plan */
+int dashb_hostcheck_digits_frac(int q, const uint64_t in2[2], int16_t* digits) {
+    ModInfo m = make_modinfo((uint32_t)q);
+    gc::FracInfo fi = make_fracinfo(m);
+    if (fi.nst == 0) return 0;
+    gc::for_each_chunk_msb(gc::make_u128(in2[0], in2[1]), m, fi, [&](uint32_t d0, uint32_t len, uint32_t r) {
+        for (uint32_t i = 0; i < len; ++i) {
+            digits[d0 + i] = (int16_t)(r % m.q);
+            r /= m.q;
+        }
+    });
+    return 1;
 }
 int dashb_hostcheck_colour(int q, const uint64_t in2[2]) {
     ModInfo m = make_modinfo((uint32_t)q);

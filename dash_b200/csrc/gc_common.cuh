@@ -217,6 +217,265 @@ GC_HD void for_each_digit2(u128 x, u128 y, const ModInfo& m, F&& f) {
     }
 }
 
+/*
+ * Digit extraction by multiplication, most significant chunk first, for
+ * VALID payloads (x < q^nc, which every label of a correct evaluation is).
+ * x / q^nc is held as a fixed-point fraction N / 2^160 (five 32-bit limbs,
+ * n[4] the most significant); multiplying the fraction by q^len pushes the
+ * next `len` digits out of the top as one chunk value.  With D = q^nc,
+ * sh = bit length of q and mu = ceil(2^(288-sh) / D) < 2^160,
+ *     N0 = floor(x * mu / 2^128) + addc       (fraction N0 / 2^(160-sh)),
+ * the first multiplier carries the extra 2^sh that aligns the fraction to
+ * 2^160.  The result is exact as long as the fraction over-estimates x/D by
+ * less than 1/D: every later value x / q^r has a fractional part that is a
+ * multiple of 1/q^r, so an excess below 1/q^r cannot reach the next integer.
+ * Sources of error, all accounted for by the host when it builds the plan
+ * (make_fracinfo, dashb_api.cu): mu is rounded up (< 1 unit), the columns
+ * 0..2 of the product x * mu are not formed (< 4 units), the product is
+ * truncated (< 1 unit) and the limbs a stage no longer needs are dropped
+ * before its multiplication (stage i keeps the top W_i limbs).  addc makes up
+ * for every truncation, so the fraction never under-estimates, and
+ * (addc + 1) * D <= 2^(160-sh) bounds the excess.  A long division by Q costs
+ * ~13 Moeller-Granlund steps of ~16 instructions per label; this costs 14
+ * wide multiplies up front and W_i per stage (15 in total for q = 70), on the
+ * FMA pipe instead of the ALU pipe.  tests/test_cabi.py pins it against
+ * for_each_digit on the host.
+ */
+struct FracInfo {
+    uint32_t mu[5];      /* ceil(2^(288-sh) / q^nc), little-endian limbs */
+    uint32_t addc;       /* added to N0 (see above) */
+    uint32_t nst;        /* stages (chunks); 0 = no plan, use for_each_digit */
+    uint32_t m_first;    /* q^len_first << sh */
+    uint32_t m_last;     /* q^len_last */
+    uint32_t len_first;  /* digits of the first (most significant) chunk */
+    uint32_t len_last;   /* digits of the last chunk; the ones between have ModInfo::t, multiplier ModInfo::Q */
+    uint32_t wl;         /* 3 bits per stage: limbs of the fraction the stage keeps (1..5) */
+};
+
+GC_HD void frac_init(u128 x, const FracInfo& fi, uint32_t (&n)[5]) {
+    const uint32_t x0 = (uint32_t)x.lo, x1 = (uint32_t)(x.lo >> 32), x2 = (uint32_t)x.hi, x3 = (uint32_t)(x.hi >> 32);
+#if defined(__CUDA_ARCH__)
+    /* Columns 3..8 of x * mu, products of even and odd columns kept in two
+     * sets of 64-bit accumulators (e4:e5, e6:e7, e8 and o3:o4, o5:o6, o7:o8)
+     * so that every product is one wide multiply-add with the carry chained
+     * into the next pair; the sets are added once at the end.  addc rides in
+     * on the first product of column 4. */
+    const uint32_t m0 = fi.mu[0], m1 = fi.mu[1], m2 = fi.mu[2], m3 = fi.mu[3], m4 = fi.mu[4];
+    uint32_t e4, e5, e6, e7, e8;
+    asm("{\n\t"
+        ".reg .u64 t;\n\t"
+        ".reg .u32 o3, o4, o5, o6, o7, o8;\n\t"
+        "mul.wide.u32 t, %5, %9;\n\t" /* x3*m0 -> o3:o4 */
+        "mov.b64 {o3, o4}, t;\n\t"
+        "mul.wide.u32 t, %5, %11;\n\t" /* x3*m2 -> o5:o6 */
+        "mov.b64 {o5, o6}, t;\n\t"
+        "mul.wide.u32 t, %5, %13;\n\t" /* x3*m4 -> o7:o8 */
+        "mov.b64 {o7, o8}, t;\n\t"
+        "mul.wide.u32 t, %5, %10;\n\t" /* x3*m1 (+ addc) -> e4:e5 */
+        "mov.b64 {%0, %1}, t;\n\t"
+        "add.cc.u32 %0, %0, %14;\n\t"
+        "addc.u32 %1, %1, 0;\n\t"
+        "mul.wide.u32 t, %5, %12;\n\t" /* x3*m3 -> e6:e7 */
+        "mov.b64 {%2, %3}, t;\n\t"
+        "mov.u32 %4, 0;\n\t"
+        /* row x2: m1 (col 3), m3 (col 5) odd; m2 (col 4), m4 (col 6) even */
+        "mad.lo.cc.u32 o3, %6, %10, o3;\n\t"
+        "madc.hi.cc.u32 o4, %6, %10, o4;\n\t"
+        "madc.lo.cc.u32 o5, %6, %12, o5;\n\t"
+        "madc.hi.cc.u32 o6, %6, %12, o6;\n\t"
+        "addc.cc.u32 o7, o7, 0;\n\t"
+        "addc.u32 o8, o8, 0;\n\t"
+        "mad.lo.cc.u32 %0, %6, %11, %0;\n\t"
+        "madc.hi.cc.u32 %1, %6, %11, %1;\n\t"
+        "madc.lo.cc.u32 %2, %6, %13, %2;\n\t"
+        "madc.hi.cc.u32 %3, %6, %13, %3;\n\t"
+        "addc.u32 %4, %4, 0;\n\t"
+        /* row x1: m2 (col 3), m4 (col 5) odd; m3 (col 4) even */
+        "mad.lo.cc.u32 o3, %7, %11, o3;\n\t"
+        "madc.hi.cc.u32 o4, %7, %11, o4;\n\t"
+        "madc.lo.cc.u32 o5, %7, %13, o5;\n\t"
+        "madc.hi.cc.u32 o6, %7, %13, o6;\n\t"
+        "addc.cc.u32 o7, o7, 0;\n\t"
+        "addc.u32 o8, o8, 0;\n\t"
+        "mad.lo.cc.u32 %0, %7, %12, %0;\n\t"
+        "madc.hi.cc.u32 %1, %7, %12, %1;\n\t"
+        "addc.cc.u32 %2, %2, 0;\n\t"
+        "addc.cc.u32 %3, %3, 0;\n\t"
+        "addc.u32 %4, %4, 0;\n\t"
+        /* row x0: m3 (col 3) odd; m4 (col 4) even */
+        "mad.lo.cc.u32 o3, %8, %12, o3;\n\t"
+        "madc.hi.cc.u32 o4, %8, %12, o4;\n\t"
+        "addc.cc.u32 o5, o5, 0;\n\t"
+        "addc.cc.u32 o6, o6, 0;\n\t"
+        "addc.cc.u32 o7, o7, 0;\n\t"
+        "addc.u32 o8, o8, 0;\n\t"
+        "mad.lo.cc.u32 %0, %8, %13, %0;\n\t"
+        "madc.hi.cc.u32 %1, %8, %13, %1;\n\t"
+        "addc.cc.u32 %2, %2, 0;\n\t"
+        "addc.cc.u32 %3, %3, 0;\n\t"
+        "addc.u32 %4, %4, 0;\n\t"
+        /* columns 4..8: even + odd */
+        "add.cc.u32 %0, %0, o4;\n\t"
+        "addc.cc.u32 %1, %1, o5;\n\t"
+        "addc.cc.u32 %2, %2, o6;\n\t"
+        "addc.cc.u32 %3, %3, o7;\n\t"
+        "addc.u32 %4, %4, o8;\n\t"
+        "}"
+        : "=&r"(e4), "=&r"(e5), "=&r"(e6), "=&r"(e7), "=&r"(e8)
+        : "r"(x3), "r"(x2), "r"(x1), "r"(x0), "r"(m0), "r"(m1), "r"(m2), "r"(m3), "r"(m4), "r"(fi.addc));
+    n[0] = e4, n[1] = e5, n[2] = e6, n[3] = e7, n[4] = e8;
+#else
+    const uint32_t xl[4] = {x0, x1, x2, x3};
+    uint32_t r[6] = {0, 0, 0, 0, 0, 0}; /* columns 3..8 of x * mu */
+    for (int i = 0; i < 4; ++i) {
+        uint32_t carry = 0;
+        for (int j = 0; j < 5; ++j) {
+            if (i + j < 3) continue;
+            const uint64_t t = (uint64_t)xl[i] * fi.mu[j] + r[i + j - 3] + carry;
+            r[i + j - 3] = (uint32_t)t;
+            carry = (uint32_t)(t >> 32);
+        }
+        r[i + 2] = carry;
+    }
+    uint64_t t = (uint64_t)r[1] + fi.addc;
+    n[0] = (uint32_t)t;
+    t = (uint64_t)r[2] + (t >> 32);
+    n[1] = (uint32_t)t;
+    t = (uint64_t)r[3] + (t >> 32);
+    n[2] = (uint32_t)t;
+    t = (uint64_t)r[4] + (t >> 32);
+    n[3] = (uint32_t)t;
+    n[4] = r[5] + (uint32_t)(t >> 32);
+#endif
+}
+
+/* fraction *= mult, keeping the top W limbs; returns the integer part */
+GC_HD uint32_t frac_stage(uint32_t (&n)[5], uint32_t mult, uint32_t W) {
+#if defined(__CUDA_ARCH__)
+    /* n'[i] = lo(n[i]*mult) + hi(n[i-1]*mult) + carry: one wide multiply and
+     * one add per limb */
+    uint32_t chunk;
+    if (W > 4) {
+        asm("{\n\t"
+            ".reg .u32 h0, h1, h2, h3;\n\t"
+            "mul.hi.u32 h0, %1, %6;\n\t"
+            "mul.lo.u32 %1, %1, %6;\n\t"
+            "mul.hi.u32 h1, %2, %6;\n\t"
+            "mul.lo.u32 %2, %2, %6;\n\t"
+            "mul.hi.u32 h2, %3, %6;\n\t"
+            "mul.lo.u32 %3, %3, %6;\n\t"
+            "mul.hi.u32 h3, %4, %6;\n\t"
+            "mul.lo.u32 %4, %4, %6;\n\t"
+            "mul.hi.u32 %0, %5, %6;\n\t"
+            "mul.lo.u32 %5, %5, %6;\n\t"
+            "add.cc.u32 %2, %2, h0;\n\t"
+            "addc.cc.u32 %3, %3, h1;\n\t"
+            "addc.cc.u32 %4, %4, h2;\n\t"
+            "addc.cc.u32 %5, %5, h3;\n\t"
+            "addc.u32 %0, %0, 0;\n\t"
+            "}"
+            : "=&r"(chunk), "+r"(n[0]), "+r"(n[1]), "+r"(n[2]), "+r"(n[3]), "+r"(n[4])
+            : "r"(mult));
+    } else if (W > 3) {
+        asm("{\n\t"
+            ".reg .u32 h1, h2, h3;\n\t"
+            "mul.hi.u32 h1, %1, %5;\n\t"
+            "mul.lo.u32 %1, %1, %5;\n\t"
+            "mul.hi.u32 h2, %2, %5;\n\t"
+            "mul.lo.u32 %2, %2, %5;\n\t"
+            "mul.hi.u32 h3, %3, %5;\n\t"
+            "mul.lo.u32 %3, %3, %5;\n\t"
+            "mul.hi.u32 %0, %4, %5;\n\t"
+            "mul.lo.u32 %4, %4, %5;\n\t"
+            "add.cc.u32 %2, %2, h1;\n\t"
+            "addc.cc.u32 %3, %3, h2;\n\t"
+            "addc.cc.u32 %4, %4, h3;\n\t"
+            "addc.u32 %0, %0, 0;\n\t"
+            "}"
+            : "=&r"(chunk), "+r"(n[1]), "+r"(n[2]), "+r"(n[3]), "+r"(n[4])
+            : "r"(mult));
+    } else if (W > 2) {
+        asm("{\n\t"
+            ".reg .u32 h2, h3;\n\t"
+            "mul.hi.u32 h2, %1, %4;\n\t"
+            "mul.lo.u32 %1, %1, %4;\n\t"
+            "mul.hi.u32 h3, %2, %4;\n\t"
+            "mul.lo.u32 %2, %2, %4;\n\t"
+            "mul.hi.u32 %0, %3, %4;\n\t"
+            "mul.lo.u32 %3, %3, %4;\n\t"
+            "add.cc.u32 %2, %2, h2;\n\t"
+            "addc.cc.u32 %3, %3, h3;\n\t"
+            "addc.u32 %0, %0, 0;\n\t"
+            "}"
+            : "=&r"(chunk), "+r"(n[2]), "+r"(n[3]), "+r"(n[4])
+            : "r"(mult));
+    } else if (W > 1) {
+        asm("{\n\t"
+            ".reg .u32 h3;\n\t"
+            "mul.hi.u32 h3, %1, %3;\n\t"
+            "mul.lo.u32 %1, %1, %3;\n\t"
+            "mul.hi.u32 %0, %2, %3;\n\t"
+            "mul.lo.u32 %2, %2, %3;\n\t"
+            "add.cc.u32 %2, %2, h3;\n\t"
+            "addc.u32 %0, %0, 0;\n\t"
+            "}"
+            : "=&r"(chunk), "+r"(n[3]), "+r"(n[4])
+            : "r"(mult));
+    } else {
+        chunk = __umulhi(n[4], mult);
+        n[4] *= mult;
+    }
+    return chunk;
+#else
+    uint64_t t = 0;
+    if (W > 4) {
+        t = (uint64_t)n[0] * mult;
+        n[0] = (uint32_t)t;
+        t >>= 32;
+    }
+    if (W > 3) {
+        t += (uint64_t)n[1] * mult;
+        n[1] = (uint32_t)t;
+        t >>= 32;
+    }
+    if (W > 2) {
+        t += (uint64_t)n[2] * mult;
+        n[2] = (uint32_t)t;
+        t >>= 32;
+    }
+    if (W > 1) {
+        t += (uint64_t)n[3] * mult;
+        n[3] = (uint32_t)t;
+        t >>= 32;
+    }
+    t += (uint64_t)n[4] * mult;
+    n[4] = (uint32_t)t;
+    return (uint32_t)(t >> 32);
+#endif
+}
+
+/* Calls f(d0, len, r) once per chunk, most significant chunk first: r holds
+ * the digits d0 .. d0+len-1 of x, r = sum_i digit_{d0+i} q^i.  x < q^nc. */
+template <typename F>
+GC_HD void for_each_chunk_msb(u128 x, const ModInfo& m, const FracInfo& fi, F&& f) {
+    uint32_t n[5];
+    frac_init(x, fi, n);
+    uint32_t wl = fi.wl;
+    uint32_t d0 = m.nc;
+    const uint32_t last = fi.nst - 1;
+    /* one loop, one copy of f: multiplier and length picked per stage */
+#if defined(__CUDA_ARCH__)
+#pragma unroll 1
+#endif
+    for (uint32_t s = 0; s <= last; ++s) {
+        const uint32_t mult = s == 0 ? fi.m_first : s == last ? fi.m_last : m.Q;
+        const uint32_t len = s == 0 ? fi.len_first : s == last ? fi.len_last : m.t;
+        d0 -= len;
+        f(d0, len, frac_stage(n, mult, wl & 7u));
+        wl >>= 3;
+    }
+}
+
 /* Colour digit of a compressed label: x mod q, from the residues of the
  * limb weights 2^32, 2^64, 2^96 mod q (a dozen multiply-adds instead of a
  * four-limb long division).  The constants depend on the modulus only. */

@@ -153,13 +153,17 @@ __device__ __forceinline__ uint32_t sbox_at(const AesSmem& a, uint32_t s) {
  * kernel (not inlined at its ~8 call sites) with rolled rounds: the gadget
  * kernels then fit the instruction cache (ncu: 24 % stall_no_inst when
  * inlined and unrolled). */
+#ifndef DASHB_AES_UNROLL
+#define DASHB_AES_UNROLL 1
+#endif
+constexpr int AES_UNROLL = DASHB_AES_UNROLL; /* rounds per trip of the middle-round loop (1, 3 or 9) */
 __device__ __noinline__ u128 hash(const AesSmem& a, u128 x) {
     const uint32_t four = c_four;
     uint32_t s0 = gc::bswap32((uint32_t)x.lo) ^ c_rk[0];
     uint32_t s1 = gc::bswap32((uint32_t)(x.lo >> 32)) ^ c_rk[1];
     uint32_t s2 = gc::bswap32((uint32_t)x.hi) ^ c_rk[2];
     uint32_t s3 = gc::bswap32((uint32_t)(x.hi >> 32)) ^ c_rk[3];
-#pragma unroll 1
+#pragma unroll(AES_UNROLL)
     for (int r = 1; r < 10; ++r) {
         const uint4 k4 = reinterpret_cast<const uint4*>(c_rk)[r];
         const uint32_t t0 = te_at<0, 3>(a, s0, four) ^ te_at<1, 2>(a, s1, four) ^ te_at<2, 1>(a, s2, four) ^ te_at<3, 0>(a, s3, four) ^ k4.x;
@@ -567,39 +571,63 @@ namespace dashb {
 #define DASHB_SIGN_THREADS 128
 #endif
 constexpr int SIGN_THREADS = DASHB_SIGN_THREADS;
+#ifndef DASHB_SIGN_MINB
+#define DASHB_SIGN_MINB 10 /* CTAs per SM the register allocation aims at */
+#endif
 
-/* digit-wise accumulation of a compressed label (no reduction: at most k+1
- * digits below 2^11 are summed).  One copy per kernel, digit loop unrolled
- * by two, accumulator pointer stepped (see rs_accumulate). */
-__device__ __noinline__ void accumulate(u128 x, const ModInfo m, uint16_t* acc) {
-    uint32_t w[4] = {(uint32_t)x.lo, (uint32_t)(x.lo >> 32), (uint32_t)x.hi, (uint32_t)(x.hi >> 32)};
-    auto digits = [&](uint32_t r, uint32_t n, bool exact) {
+/* Digit accumulators of one thread: 32-bit words holding two digits' sums
+ * (digit 2w in the low half, 2w+1 in the high half), word-major in shared
+ * memory (acc[w * SIGN_THREADS]).  A sum of k+1 digits stays below 2^16
+ * (checked when the circuit is created), so the halves never meet. */
+
+/* Digit-wise accumulation of a compressed label by long division, least
+ * significant digit first: the fallback for a modulus without a
+ * multiplicative plan.  One copy per kernel. */
+__device__ __noinline__ void accumulate(u128 x, const ModInfo m, uint32_t* acc) {
+    gc::for_each_digit(x, m, [&](uint32_t d, uint32_t v) { acc[(d >> 1) * SIGN_THREADS] += v << (16 * (d & 1)); });
+}
+
+/* The same accumulation with the digits taken by multiplication, most
+ * significant chunk first (gc::for_each_chunk_msb; labels of a correct
+ * evaluation are always below q^nc).  Two digits cost two reciprocal
+ * multiplies, two multiply-adds that also pack them (d0 + 2^16 d1 =
+ * r + q1 (2^16 - q) - q2 (q 2^16)) and one shared-memory read-modify-write.
+ * Inlined at its two call sites: the plan is read straight from the
+ * kernel-parameter bank. */
+#ifndef DASHB_FRAC
+#define DASHB_FRAC 1
+#endif
+__device__ __forceinline__ void accumulate_frac(u128 x, const ModInfo& m, const gc::FracInfo& fi, uint32_t* acc) {
+    const uint32_t c1 = 65536u - m.q, c2 = m.q << 16;
+    gc::for_each_chunk_msb(x, m, fi, [&](uint32_t d0, uint32_t len, uint32_t r) {
+        uint32_t* a = acc + (d0 >> 1) * SIGN_THREADS;
         uint32_t i = 0;
-        for (; i + 1 < n; i += 2) {
-            const uint32_t q1 = exact ? gc::div_q(r, m) : gc::div_q_any(r, m);
+        if (d0 & 1u) { /* the chunk starts in the high half of a word */
+            const uint32_t q1 = gc::div_q(r, m);
+            a[0] += (r - q1 * m.q) << 16;
+            a += SIGN_THREADS;
+            r = q1;
+            i = 1;
+        }
+#pragma unroll 1
+        for (; i + 1 < len; i += 2) {
+            const uint32_t q1 = gc::div_q(r, m);
             const uint32_t q2 = gc::div_q(q1, m);
-            acc[0] = (uint16_t)(acc[0] + (r - q1 * m.q));
-            acc[SIGN_THREADS] = (uint16_t)(acc[SIGN_THREADS] + (q1 - q2 * m.q));
-            acc += 2 * SIGN_THREADS;
+            a[0] += r + q1 * c1 - q2 * c2;
+            a += SIGN_THREADS;
             r = q2;
         }
-        if (i < n) {
-            const uint32_t q1 = exact ? gc::div_q(r, m) : gc::div_q_any(r, m);
-            acc[0] = (uint16_t)(acc[0] + (r - q1 * m.q));
-            acc += SIGN_THREADS;
-        }
-    };
-#pragma unroll 1
-    for (uint32_t c = 0; c + 1 < m.nchunks; ++c) digits(gc::divmod_Q(w, m, gc::limbs_before(m, c)), m.t, true);
-    digits(w[0], m.top_len, false);
+        if (i < len) a[0] += r; /* the chunk's last digit is what is left */
+    });
 }
 
 /* compress(acc mod q) and the colour of the sum */
-__device__ __forceinline__ u128 compress_acc(const uint16_t* acc, const ModInfo& m, uint32_t& colour) {
+__device__ __forceinline__ u128 compress_acc(const uint32_t* acc, const ModInfo& m, uint32_t& colour) {
     gc::Compressor c(m);
     uint32_t dg = 0;
     for (int d = (int)m.nc - 1; d >= 0; --d) {
-        dg = gc::mod_q(acc[d * SIGN_THREADS], m);
+        const uint32_t w = acc[(d >> 1) * SIGN_THREADS];
+        dg = gc::mod_q((d & 1) ? (w >> 16) : (w & 0xffffu), m);
         c.push(dg);
     }
     colour = dg;
@@ -623,9 +651,9 @@ __device__ __forceinline__ u128 compress_acc(const uint16_t* acc, const ModInfo&
  * are never read by the reference and are not formed.
  */
 template <bool RELU>
-__global__ void __launch_bounds__(SIGN_THREADS) k_sign(const __grid_constant__ SignParams P) {
+__global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __grid_constant__ SignParams P) {
     __shared__ AesSmem aes;
-    extern __shared__ uint16_t s_acc[]; /* [acc_digits][SIGN_THREADS] */
+    extern __shared__ uint32_t s_acc[]; /* [ceil(acc_digits / 2)][SIGN_THREADS] */
     aes_smem_load(aes);
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P.n * P.batch) return;
@@ -645,7 +673,7 @@ __global__ void __launch_bounds__(SIGN_THREADS) k_sign(const __grid_constant__ S
     }
 
     /* Step 2: mixed-radix addition from the least significant digit */
-    uint16_t* acc = s_acc + threadIdx.x;
+    uint32_t* acc = s_acc + threadIdx.x;
     u128 carry = P.carry0;
     const u128* approx_e = P.approx + e * (uint64_t)nm * P.S;
     uint64_t cnt1 = e * (uint64_t)(k + 1) * P.Mp, cnt2 = cnt1;
@@ -656,7 +684,7 @@ __global__ void __launch_bounds__(SIGN_THREADS) k_sign(const __grid_constant__ S
         const ModInfo M = pin(P.mrs[i]);
         const ModInfo C = pin(P.cast[i]);
         const gc::ColourConsts cc = gc::colour_consts(M);
-        for (uint32_t d = 0; d < C.nc; ++d) acc[d * SIGN_THREADS] = 0;
+        for (uint32_t w = 0; w < (C.nc + 1) / 2; ++w) acc[w * SIGN_THREADS] = 0;
 #pragma unroll 1
         for (int j = 0; j <= k; ++j) {
             /* Step 1b: approx. MRS digit i of residue j (j == k: the carry) */
@@ -667,7 +695,11 @@ __global__ void __launch_bounds__(SIGN_THREADS) k_sign(const __grid_constant__ S
             /* Step 2.2: cast to modulus (k+1)*m_i */
             const u128 hl = hash(aes, lab);
             const uint32_t c0 = gc::colour_of(lab, M, cc);
-            accumulate(gc::sub128(ldg128(P.cast1 + cnt1 + (uint64_t)j * M.q + c0), hl), C, acc);
+            const u128 c1 = gc::sub128(ldg128(P.cast1 + cnt1 + (uint64_t)j * M.q + c0), hl);
+            if (DASHB_FRAC && P.castf[i].nst)
+                accumulate_frac(c1, C, P.castf[i], acc);
+            else
+                accumulate(c1, C, acc);
         }
         cnt1 += (uint64_t)(k + 1) * M.q;
         /* Step 2.3 / 2.4: sum of the casts -> carry into digit i-1 */
@@ -678,12 +710,15 @@ __global__ void __launch_bounds__(SIGN_THREADS) k_sign(const __grid_constant__ S
     }
     /* most significant digit: sum = carry + sum_j digit_{j,0} */
     const ModInfo M0 = pin(P.mrs[0]);
-    for (uint32_t d = 0; d < M0.nc; ++d) acc[d * SIGN_THREADS] = 0;
+    for (uint32_t w = 0; w < (M0.nc + 1) / 2; ++w) acc[w * SIGN_THREADS] = 0;
 #pragma unroll 1
     for (int j = 0; j <= k; ++j) {
         u128 lab = carry;
         if (j < k) lab = gc::sub128(ldg128(approx_e + (uint64_t)nm * P.prefix[j] + col[j]), h[j]);
-        accumulate(lab, M0, acc);
+        if (DASHB_FRAC && P.castf[0].nst)
+            accumulate_frac(lab, M0, P.castf[0], acc);
+        else
+            accumulate(lab, M0, acc);
     }
     uint32_t ctop;
     const u128 top = compress_acc(acc, M0, ctop);
@@ -889,7 +924,7 @@ cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s) {
     const unsigned grid = (unsigned)((total + SIGN_THREADS - 1) / SIGN_THREADS);
     uint32_t acc_digits = p.mrs[0].nc;
     for (int i = 1; i < p.n_mrs; ++i) acc_digits = max(acc_digits, p.cast[i].nc);
-    const size_t smem = (size_t)acc_digits * SIGN_THREADS * sizeof(uint16_t);
+    const size_t smem = (size_t)((acc_digits + 1) / 2) * SIGN_THREADS * sizeof(uint32_t);
     /* latency mode: one warp per (element, inference) while that still leaves SMs idle otherwise */
     static const long wide_max = getenv("DASHB_WIDE_MAX") ? atol(getenv("DASHB_WIDE_MAX")) : 8192;
     /* with other lanes in flight the GPU is busy anyway: only tiny launches go wide */
@@ -939,71 +974,125 @@ cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s) {
  *     update.  16-bit accumulators where (k+1)(q-1)^2 < 2^16, else 32-bit.
  */
 constexpr int RS_THREADS = 128;
+#ifndef DASHB_RS_MINB
+#define DASHB_RS_MINB 9 /* CTAs per SM the register allocation aims at */
+#endif
+
+/* Accumulators of one thread, 32-bit words in shared memory, word-major
+ * (acc[w * RS_THREADS]).  PACKED (the usual case, (k+1)(q-1)^2 < 2^16): two
+ * digits per word, digit 2w in the low half and 2w+1 in the high half -- the
+ * halves never meet, so one multiply-add updates both.  Otherwise one digit
+ * per word. */
 
 /* acc[d] = ((x_j[d] + upshift_j[d]) mod q) * a   (step 1, pre-multiplied) */
-template <typename A>
-__device__ __forceinline__ void rs_init(A* acc, const uint8_t* plane, const uint8_t* up, const ModInfo& m, uint64_t e,
+template <bool PACKED>
+__device__ __forceinline__ void rs_init(uint32_t* acc, const uint8_t* plane, const uint8_t* up, const ModInfo& m, uint64_t e,
                                         uint32_t b, uint32_t Bp, uint32_t a) {
     const uint8_t* p = plane + plane_off(m, e, b, Bp);
     for (uint32_t d4 = 0; d4 < nc4_of(m); ++d4) {
         const uint32_t xw = *reinterpret_cast<const uint32_t*>(p + (uint64_t)d4 * 4 * Bp);
         const uint32_t uw = __ldg(reinterpret_cast<const uint32_t*>(up) + d4);
+        uint32_t v[4];
 #pragma unroll
         for (uint32_t t = 0; t < 4; ++t) {
-            if (4 * d4 + t >= m.nc) break;
-            uint32_t v = ((xw >> (8 * t)) & 0xff) + ((uw >> (8 * t)) & 0xff);
-            v = v >= m.q ? v - m.q : v;
-            acc[(4 * d4 + t) * RS_THREADS] = (A)(v * a);
+            v[t] = ((xw >> (8 * t)) & 0xff) + ((uw >> (8 * t)) & 0xff);
+            v[t] = (v[t] >= m.q ? v[t] - m.q : v[t]) * a;
+        }
+        if (PACKED) { /* the padding digits of the last word are zero in both labels */
+            acc[(2 * d4) * RS_THREADS] = v[0] | (v[1] << 16);
+            acc[(2 * d4 + 1) * RS_THREADS] = v[2] | (v[3] << 16);
+        } else {
+#pragma unroll
+            for (uint32_t t = 0; t < 4; ++t)
+                if (4 * d4 + t < m.nc) acc[(4 * d4 + t) * RS_THREADS] = v[t];
         }
     }
 }
 
 /* acc[d] = label[d] * a for a broadcast label (zero padded u8[4*nc4]) */
-template <typename A>
-__device__ __forceinline__ void rs_set(A* acc, const uint8_t* label, const ModInfo& m, uint32_t a) {
-    for (uint32_t d = 0; d < m.nc; ++d) acc[d * RS_THREADS] = (A)(__ldg(label + d) * a);
+template <bool PACKED>
+__device__ __forceinline__ void rs_set(uint32_t* acc, const uint8_t* label, const ModInfo& m, uint32_t a) {
+    if (PACKED) {
+        for (uint32_t w = 0; w < 2 * nc4_of(m); ++w)
+            acc[w * RS_THREADS] = __ldg(label + 2 * w) * a | (__ldg(label + 2 * w + 1) * a) << 16;
+    } else {
+        for (uint32_t d = 0; d < m.nc; ++d) acc[d * RS_THREADS] = __ldg(label + d) * a;
+    }
 }
 
-/* acc[d] += digit_d(pr) * bcoef.  Not inlined (and the modulus by value, in
- * registers): its three call sites share one copy of the long division, the
- * kernel's hot loop then stays in the instruction cache (ncu showed
- * stall_no_instruction 4.5 per issue with the inlined copies). */
-template <typename A>
-__device__ __noinline__ void rs_accumulate(A* acc, u128 pr, const ModInfo m, uint32_t bcoef) {
-    /* gc::for_each_digit with the digit loop unrolled by two and the
-     * accumulator pointer stepped instead of indexed */
-    uint32_t w[4] = {(uint32_t)pr.lo, (uint32_t)(pr.lo >> 32), (uint32_t)pr.hi, (uint32_t)(pr.hi >> 32)};
-    auto digits = [&](uint32_t r, uint32_t n, bool exact) {
+/* acc[d] += digit_d(pr) * bcoef by long division, least significant digit
+ * first: the fallback for a modulus without a multiplicative plan.  Not
+ * inlined, the modulus by value (in registers): one copy per kernel. */
+template <bool PACKED>
+__device__ __noinline__ void rs_accumulate(uint32_t* acc, u128 pr, const ModInfo m, uint32_t bcoef) {
+    gc::for_each_digit(pr, m, [&](uint32_t d, uint32_t v) {
+        if (PACKED)
+            acc[(d >> 1) * RS_THREADS] += (v * bcoef) << (16 * (d & 1));
+        else
+            acc[d * RS_THREADS] += v * bcoef;
+    });
+}
+
+/* The same with the digits taken by multiplication, most significant chunk
+ * first (gc::for_each_chunk_msb; valid payloads).  Inlined: the plan is read
+ * from the kernel-parameter bank, and the body is a fraction of the long
+ * division's size.  PACKED: two digits cost two reciprocal multiplies, two
+ * multiply-adds that also pack them (see accumulate_frac) and one
+ * multiply-add into the shared-memory word. */
+template <bool PACKED>
+__device__ __forceinline__ void rs_accumulate_frac(uint32_t* acc, u128 pr, const ModInfo& m, const gc::FracInfo& fi,
+                                                   uint32_t bcoef) {
+    const uint32_t c1 = 65536u - m.q, c2 = m.q << 16;
+    gc::for_each_chunk_msb(pr, m, fi, [&](uint32_t d0, uint32_t len, uint32_t r) {
         uint32_t i = 0;
-        for (; i + 1 < n; i += 2) {
-            const uint32_t q1 = exact ? gc::div_q(r, m) : gc::div_q_any(r, m);
-            const uint32_t q2 = gc::div_q(q1, m);
-            acc[0] = (A)(acc[0] + (r - q1 * m.q) * bcoef);
-            acc[RS_THREADS] = (A)(acc[RS_THREADS] + (q1 - q2 * m.q) * bcoef);
-            acc += 2 * RS_THREADS;
-            r = q2;
-        }
-        if (i < n) {
-            const uint32_t q1 = exact ? gc::div_q(r, m) : gc::div_q_any(r, m);
-            acc[0] = (A)(acc[0] + (r - q1 * m.q) * bcoef);
-            acc += RS_THREADS;
-        }
-    };
+        if (PACKED) {
+            uint32_t* a = acc + (d0 >> 1) * RS_THREADS;
+            if (d0 & 1u) { /* the chunk starts in the high half of a word */
+                const uint32_t q1 = gc::div_q(r, m);
+                a[0] += ((r - q1 * m.q) * bcoef) << 16;
+                a += RS_THREADS;
+                r = q1;
+                i = 1;
+            }
 #pragma unroll 1
-    for (uint32_t c = 0; c + 1 < m.nchunks; ++c) digits(gc::divmod_Q(w, m, gc::limbs_before(m, c)), m.t, true);
-    /* most significant chunk: what is left of the value; an out-of-range
-     * payload can push it past the reciprocal's exact range on its first
-     * division (see gc::for_each_digit) */
-    digits(w[0], m.top_len, false);
+            for (; i + 1 < len; i += 2) {
+                const uint32_t q1 = gc::div_q(r, m);
+                const uint32_t q2 = gc::div_q(q1, m);
+                a[0] += (r + q1 * c1 - q2 * c2) * bcoef;
+                a += RS_THREADS;
+                r = q2;
+            }
+            if (i < len) a[0] += r * bcoef; /* the chunk's last digit is what is left */
+        } else {
+            uint32_t* a = acc + d0 * RS_THREADS;
+#pragma unroll 1
+            for (; i + 1 < len; i += 2) {
+                const uint32_t q1 = gc::div_q(r, m);
+                const uint32_t q2 = gc::div_q(q1, m);
+                a[0] += (r - q1 * m.q) * bcoef;
+                a[RS_THREADS] += (q1 - q2 * m.q) * bcoef;
+                a += 2 * RS_THREADS;
+                r = q2;
+            }
+            if (i < len) a[0] += r * bcoef;
+        }
+    });
+}
+
+template <bool PACKED>
+__device__ __forceinline__ uint32_t rs_field(const uint32_t* acc, uint32_t d) {
+    if (!PACKED) return acc[d * RS_THREADS];
+    const uint32_t w = acc[(d >> 1) * RS_THREADS];
+    return (d & 1u) ? (w >> 16) : (w & 0xffffu);
 }
 
 /* reduce, compress and return the colour digit */
-template <typename A>
-__device__ __forceinline__ u128 rs_finish_compress(const A* acc, const ModInfo& m, uint32_t& colour) {
+template <bool PACKED>
+__device__ __forceinline__ u128 rs_finish_compress(const uint32_t* acc, const ModInfo& m, uint32_t& colour) {
     gc::Compressor c(m);
     uint32_t dg = 0;
     for (int d = (int)m.nc - 1; d >= 0; --d) {
-        dg = gc::mod_q(acc[d * RS_THREADS], m);
+        dg = gc::mod_q(rs_field<PACKED>(acc, (uint32_t)d), m);
         c.push(dg);
     }
     colour = dg;
@@ -1013,19 +1102,21 @@ __device__ __forceinline__ u128 rs_finish_compress(const A* acc, const ModInfo& 
 /* plane <- ((acc mod q) * mul - down) mod q; mul == 1 / down == nullptr skip
  * that step.  With next_a != 0 the accumulator restarts at (acc mod q) *
  * next_a for the next chain. */
-template <typename A>
-__device__ __forceinline__ void rs_finish_store(A* acc, uint8_t* plane, const uint8_t* down, uint32_t mul, uint32_t next_a,
+template <bool PACKED>
+__device__ __forceinline__ void rs_finish_store(uint32_t* acc, uint8_t* plane, const uint8_t* down, uint32_t mul, uint32_t next_a,
                                                 const ModInfo& m, uint64_t e, uint32_t b, uint32_t Bp) {
     uint8_t* p = plane + plane_off(m, e, b, Bp);
     for (uint32_t d4 = 0; d4 < nc4_of(m); ++d4) {
         const uint32_t dw = down ? __ldg(reinterpret_cast<const uint32_t*>(down) + d4) : 0u;
         uint32_t ow = 0;
+        uint32_t nv[4] = {0, 0, 0, 0};
 #pragma unroll
         for (uint32_t t = 0; t < 4; ++t) {
             const uint32_t d = 4 * d4 + t;
             if (d >= m.nc) break;
-            uint32_t v = gc::mod_q(acc[d * RS_THREADS], m);
-            if (next_a) acc[d * RS_THREADS] = (A)(v * next_a);
+            uint32_t v = gc::mod_q(rs_field<PACKED>(acc, d), m);
+            nv[t] = v * next_a;
+            if (!PACKED && next_a) acc[d * RS_THREADS] = nv[t];
             if (mul != 1) v = gc::mod_q(v * mul, m);
             if (down) {
                 v = v + m.q - ((dw >> (8 * t)) & 0xff);
@@ -1033,12 +1124,16 @@ __device__ __forceinline__ void rs_finish_store(A* acc, uint8_t* plane, const ui
             }
             ow |= v << (8 * t);
         }
+        if (PACKED && next_a) {
+            acc[(2 * d4) * RS_THREADS] = nv[0] | (nv[1] << 16);
+            acc[(2 * d4 + 1) * RS_THREADS] = nv[2] | (nv[3] << 16);
+        }
         *reinterpret_cast<uint32_t*>(p + (uint64_t)d4 * 4 * Bp) = ow;
     }
 }
 
-template <typename A>
-__device__ __forceinline__ void rescale_body(const RescaleParams& P, const AesSmem& aes, A* acc, uint64_t e, uint32_t b) {
+template <bool PACKED>
+__device__ __forceinline__ void rescale_body(const RescaleParams& P, const AesSmem& aes, uint32_t* acc, uint64_t e, uint32_t b) {
     const int k = P.k;
     /* Steps 1-2 for the factors' own residues: the hash each factor's
      * trans-modulus projections key on (rescale_gadget.h:271-300).  A later
@@ -1049,15 +1144,18 @@ __device__ __forceinline__ void rescale_body(const RescaleParams& P, const AesSm
     for (int i = 0; i < P.nf; ++i) {
         const int j = P.fidx[i];
         const ModInfo m = pin(P.crt[j]);
-        rs_init(acc, P.in[j], P.up[j], m, e, b, P.Bp, P.a1f[i]);
+        rs_init<PACKED>(acc, P.in[j], P.up[j], m, e, b, P.Bp, P.a1f[i]);
 #pragma unroll 1
         for (int i2 = 0; i2 < i; ++i2) {
             if (P.tm_off[i2][j] == ~0ull) continue;
             const u128 pr = gc::sub128(ldg128(P.tm + P.tm_off[i2][j] + e * (uint64_t)P.factor[i2] + fcol[i2]), hf[i2]);
-            rs_accumulate(acc, pr, m, P.b1f[i][i2]);
+            if (DASHB_FRAC && P.crtf[j].nst)
+                rs_accumulate_frac<PACKED>(acc, pr, m, P.crtf[j], P.b1f[i][i2]);
+            else
+                rs_accumulate<PACKED>(acc, pr, m, P.b1f[i][i2]);
         }
         uint32_t colour;
-        const u128 key = rs_finish_compress(acc, m, colour);
+        const u128 key = rs_finish_compress<PACKED>(acc, m, colour);
         hf[i] = hash(aes, key);
         fcol[i] = colour;
     }
@@ -1075,23 +1173,26 @@ __device__ __forceinline__ void rescale_body(const RescaleParams& P, const AesSm
             if (P.fidx[i] == jt) x = i;
         if (x < 0) {
             /* steps 1-2: upshift, then divide by every factor */
-            rs_init(acc, P.in[jt], P.up[jt], m, e, b, P.Bp, P.a1[jt]);
+            rs_init<PACKED>(acc, P.in[jt], P.up[jt], m, e, b, P.Bp, P.a1[jt]);
 #pragma unroll 1
             for (int i = 0; i < P.nf; ++i) {
                 if (P.tm_off[i][jt] == ~0ull) continue;
                 const u128 pr = gc::sub128(ldg128(P.tm + P.tm_off[i][jt] + e * (uint64_t)P.factor[i] + fcol[i]), hf[i]);
-                rs_accumulate(acc, pr, m, P.b1[i][jt]);
+                if (DASHB_FRAC && P.crtf[jt].nst)
+                    rs_accumulate_frac<PACKED>(acc, pr, m, P.crtf[jt], P.b1[i][jt]);
+                else
+                    rs_accumulate<PACKED>(acc, pr, m, P.b1[i][jt]);
             }
             /* step 4 for this residue (the base extension below only changes
              * the factors' residues, base_extension_gadget.h:253-294); the
              * accumulator restarts as the elimination's target */
-            rs_finish_store(acc, P.out[jt], P.legacy ? nullptr : P.down[jt], 1, P.legacy ? 0u : (uint32_t)P.a2[t], m, e, b, P.Bp);
+            rs_finish_store<PACKED>(acc, P.out[jt], P.legacy ? nullptr : P.down[jt], 1, P.legacy ? 0u : (uint32_t)P.a2[t], m, e, b, P.Bp);
         } else if (P.legacy) {
             /* step 2.3: the factor's residue is the zero label */
-            rs_set(acc, P.zero[jt], m, 1);
-            rs_finish_store(acc, P.out[jt], nullptr, 1, 0, m, e, b, P.Bp);
+            rs_set<PACKED>(acc, P.zero[jt], m, 1);
+            rs_finish_store<PACKED>(acc, P.out[jt], nullptr, 1, 0, m, e, b, P.Bp);
         } else {
-            rs_set(acc, P.zero[jt], m, P.a2[t]);
+            rs_set<PACKED>(acc, P.zero[jt], m, P.a2[t]);
         }
         if (P.legacy) continue;
         /* step 3: garbled mixed-radix conversion, all eliminations of this target */
@@ -1099,28 +1200,31 @@ __device__ __forceinline__ void rescale_body(const RescaleParams& P, const AesSm
 #pragma unroll 1
         for (int i = 0; i < ni; ++i) {
             const u128 pr = gc::sub128(ldg128(P.be + P.be_off[i][t] + e * (uint64_t)P.crt[P.perm[i]].q + col[i]), h[i]);
-            rs_accumulate(acc, pr, m, P.b2[i][t]);
+            if (DASHB_FRAC && P.crtf[jt].nst)
+                rs_accumulate_frac<PACKED>(acc, pr, m, P.crtf[jt], P.b2[i][t]);
+            else
+                rs_accumulate<PACKED>(acc, pr, m, P.b2[i][t]);
         }
         if (x < 0) {
             uint32_t colour;
-            const u128 key = rs_finish_compress(acc, m, colour);
+            const u128 key = rs_finish_compress<PACKED>(acc, m, colour);
             h[t] = hash(aes, key);
             col[t] = colour;
         } else {
             /* the extended residue is the last mixed-radix digit times -invv, then the downshift */
-            rs_finish_store(acc, P.out[jt], P.down[jt], P.neg_invv[x], 0, m, e, b, P.Bp);
+            rs_finish_store<PACKED>(acc, P.out[jt], P.down[jt], P.neg_invv[x], 0, m, e, b, P.Bp);
         }
     }
 }
 
-template <typename A>
-__global__ void __launch_bounds__(RS_THREADS) k_rescale(const __grid_constant__ RescaleParams P) {
+template <bool PACKED>
+__global__ void __launch_bounds__(RS_THREADS, DASHB_RS_MINB) k_rescale(const __grid_constant__ RescaleParams P) {
     __shared__ AesSmem aes;
-    extern __shared__ uint32_t s_rs[]; /* A [max nc][RS_THREADS] */
+    extern __shared__ uint32_t s_rs[]; /* [2 * max nc4 (PACKED) or max nc][RS_THREADS] */
     aes_smem_load(aes);
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P.n * P.batch) return;
-    rescale_body<A>(P, aes, reinterpret_cast<A*>(s_rs) + threadIdx.x, P.e0 + idx / P.batch, (uint32_t)(idx % P.batch));
+    rescale_body<PACKED>(P, aes, s_rs + threadIdx.x, P.e0 + idx / P.batch, (uint32_t)(idx % P.batch));
 }
 
 cudaError_t launch_rescale(const RescaleParams& p, cudaStream_t s) {
@@ -1133,13 +1237,13 @@ cudaError_t launch_rescale(const RescaleParams& p, cudaStream_t s) {
         static bool opted_in[MAX_DEVICES];
         const int dev = initialised_device();
         if (dev >= 0 && dev < MAX_DEVICES && !opted_in[dev]) { /* 128 digits x 128 threads x 4 B */
-            cudaError_t e = cudaFuncSetAttribute(k_rescale<uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * RS_THREADS * 4);
+            cudaError_t e = cudaFuncSetAttribute(k_rescale<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * RS_THREADS * 4);
             if (e != cudaSuccess) return e;
             opted_in[dev] = true;
         }
-        k_rescale<uint32_t><<<grid, RS_THREADS, (size_t)nc * RS_THREADS * 4, s>>>(p);
+        k_rescale<false><<<grid, RS_THREADS, (size_t)nc * RS_THREADS * 4, s>>>(p);
     } else {
-        k_rescale<uint16_t><<<grid, RS_THREADS, (size_t)nc * RS_THREADS * 2, s>>>(p);
+        k_rescale<true><<<grid, RS_THREADS, (size_t)((nc + 3) / 4 * 2) * RS_THREADS * 4, s>>>(p);
     }
     return cudaGetLastError();
 }

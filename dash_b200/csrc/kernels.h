@@ -69,6 +69,8 @@ struct SignParams {
     gc::ModInfo mrs[MAXM];
     gc::ModInfo cast[MAXM];  /* modulus (k+1)*m_i, i >= 1 */
     gc::ModInfo outm[MAXK];  /* sign layer: out moduli */
+    gc::FracInfo castf[MAXM]; /* digit extraction plans of cast[] (gc_common.cuh) */
+    gc::FracInfo crtf[MAXK];  /* ... of crt[] */
     const gc::u128 *approx, *cast1, *cast2, *sign, *garbler, *evaluator;
     gc::u128 carry0;         /* compressed zero label of m_{n_mrs-1} */
     uint64_t n;   /* elements this launch processes ... */
@@ -95,6 +97,7 @@ struct RescaleParams {
     const uint8_t* in[MAXK];
     uint8_t* out[MAXK];
     gc::ModInfo crt[MAXK];
+    gc::FracInfo crtf[MAXK];    /* digit extraction plans of crt[] (gc_common.cuh) */
     const uint8_t* up[MAXK];    /* upshift label digits (u8[4*nc4_j], zero padded) */
     const uint8_t* down[MAXK];  /* downshift label digits */
     const uint8_t* zero[MAXK];  /* zero label digits */

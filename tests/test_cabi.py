@@ -93,3 +93,30 @@ def test_device_primitives_on_host_match_oracle(api):
             assert api.hostcheck_colour(q, x) == x % q
             if q <= 181:  # out-of-range payloads: identical digits as long as the top quotient fits int16
                 assert list(api.hostcheck_digits(q, x)) == list(O.decompress(q, x))
+
+
+def test_multiplicative_digit_extraction_matches_division(api):
+    """gc::for_each_chunk_msb (the gadget kernels' digit extraction for valid
+    payloads, x < q^nc) against the oracle's decompress (LabelTensor::
+    decompress, garbling/label_tensor.h:726-742) and the long-division
+    extraction, for every modulus a circuit can use: CRT moduli 2..256, MRS
+    digits and cast moduli (k+1)*m_i; edge payloads included."""
+    rng = random.Random(5)
+    planned = 0
+    for q in list(range(2, 257)) + [9 * 98, 10 * 76, 9 * 9, 10 * 7, 8 * 10, 9 * 126, 13 * 126, 1000, 4096, 1638, 32767]:
+        nc = O.nr_comps(q)
+        D = q**nc
+        xs = [0, 1, D - 1, D - 2, D // 2, D // 3] + [q**i for i in range(nc)] + [q**i - 1 for i in range(1, nc + 1)]
+        xs += [rng.randrange(D) for _ in range(40)]
+        for x in xs:
+            got = api.hostcheck_digits_frac(q, x)
+            if got is None:  # no plan: the kernels fall back to the division
+                break
+            want = [(x // q**i) % q for i in range(nc)]
+            assert list(got) == want, (q, x)
+            if q <= 256:
+                assert list(O.decompress(q, x)) == want
+            assert list(api.hostcheck_digits(q, x)) == want
+        else:
+            planned += 1
+    assert planned >= 260
