@@ -183,7 +183,7 @@ gc::FracInfo make_fracinfo(const ModInfo& m) {
     const uint32_t rest = nc - a;
     const uint32_t nmid = rest / t, rl = rest % t;
     const uint32_t nst = 1 + nmid + (rl ? 1 : 0);
-    if (nst < 2 || nst > 10) return fi;
+    if (nst < 2 || nst > (uint32_t)gc::FRAC_MAXST) return fi;
     uint64_t plast = 1;
     for (uint32_t i = 0; i < (rl ? rl : t); ++i) plast *= q;
     uint32_t lens[10];
@@ -226,12 +226,10 @@ gc::FracInfo make_fracinfo(const ModInfo& m) {
         for (int i = 0; i < 5; ++i) fi.mu[i] = mu.w[i];
         fi.addc = addc;
         fi.nst = nst;
-        fi.m_first = (uint32_t)(pa << sh);
-        fi.m_last = (uint32_t)plast;
-        fi.len_first = a;
-        fi.len_last = lens[nst - 1];
-        fi.wl = 0;
-        for (uint32_t s = 0; s < nst; ++s) fi.wl |= W[s] << (3 * s);
+        for (uint32_t s = 0; s < nst; ++s) {
+            fi.mult[s] = s == 0 ? (uint32_t)(pa << sh) : s == nst - 1 ? (uint32_t)plast : m.Q;
+            fi.desc[s] = lens[s] | W[s] << 8;
+        }
         return fi;
     }
     return fi;

@@ -241,15 +241,14 @@ GC_HD void for_each_digit2(u128 x, u128 y, const ModInfo& m, F&& f) {
  * FMA pipe instead of the ALU pipe.  tests/test_cabi.py pins it against
  * for_each_digit on the host.
  */
+constexpr int FRAC_MAXST = 10;
 struct FracInfo {
-    uint32_t mu[5];      /* ceil(2^(288-sh) / q^nc), little-endian limbs */
-    uint32_t addc;       /* added to N0 (see above) */
-    uint32_t nst;        /* stages (chunks); 0 = no plan, use for_each_digit */
-    uint32_t m_first;    /* q^len_first << sh */
-    uint32_t m_last;     /* q^len_last */
-    uint32_t len_first;  /* digits of the first (most significant) chunk */
-    uint32_t len_last;   /* digits of the last chunk; the ones between have ModInfo::t, multiplier ModInfo::Q */
-    uint32_t wl;         /* 3 bits per stage: limbs of the fraction the stage keeps (1..5) */
+    uint32_t mu[5];             /* ceil(2^(288-sh) / q^nc), little-endian limbs */
+    uint32_t addc;              /* added to N0 (see above) */
+    uint32_t nst;               /* stages (chunks); 0 = no plan, use for_each_digit */
+    uint32_t mult[FRAC_MAXST];  /* stage s multiplies by q^len_s (stage 0: << sh) */
+    uint32_t desc[FRAC_MAXST];  /* len_s | W_s << 8: digits of the chunk, limbs of the fraction the stage keeps (1..5) */
+    uint32_t pad[5];            /* 128 bytes: indexing an array of plans is a shift */
 };
 
 GC_HD void frac_init(u128 x, const FracInfo& fi, uint32_t (&n)[5]) {
@@ -460,19 +459,17 @@ template <typename F>
 GC_HD void for_each_chunk_msb(u128 x, const ModInfo& m, const FracInfo& fi, F&& f) {
     uint32_t n[5];
     frac_init(x, fi, n);
-    uint32_t wl = fi.wl;
     uint32_t d0 = m.nc;
-    const uint32_t last = fi.nst - 1;
-    /* one loop, one copy of f: multiplier and length picked per stage */
+    /* one loop, one copy of f; multiplier, length and width come from the
+     * plan's per-stage tables (two loads from the parameter bank) */
 #if defined(__CUDA_ARCH__)
 #pragma unroll 1
 #endif
-    for (uint32_t s = 0; s <= last; ++s) {
-        const uint32_t mult = s == 0 ? fi.m_first : s == last ? fi.m_last : m.Q;
-        const uint32_t len = s == 0 ? fi.len_first : s == last ? fi.len_last : m.t;
+    for (uint32_t s = 0; s < fi.nst; ++s) {
+        const uint32_t desc = fi.desc[s];
+        const uint32_t len = desc & 0xffu;
         d0 -= len;
-        f(d0, len, frac_stage(n, mult, wl & 7u));
-        wl >>= 3;
+        f(d0, len, frac_stage(n, fi.mult[s], desc >> 8));
     }
 }
 

@@ -198,15 +198,24 @@ __device__ __forceinline__ uint64_t plane_off(const ModInfo& m, uint64_t e, uint
     return (e * nc4_of(m) * (uint64_t)Bp + b) * 4;
 }
 
-/* compress the label (element e, inference b) of a digit plane */
+/* compress the label (element e, inference b) of a digit plane.  The words
+ * are read two ahead of the Horner steps that consume them: a rolled loop
+ * that used each word right after its load exposed the full memory latency
+ * once per word (ncu: the largest long-scoreboard stall after the half gates'
+ * re-reads). */
 __device__ __forceinline__ u128 load_compress(const uint8_t* plane, const ModInfo& m, uint64_t e, uint32_t b,
                                                uint32_t Bp, uint32_t& colour) {
     const uint8_t* p = plane + plane_off(m, e, b, Bp);
     gc::Compressor c(m);
-    uint32_t w = 0;
-    uint32_t valid = m.nc - 4 * (nc4_of(m) - 1); /* digits in the top word */
-    for (int d4 = (int)nc4_of(m) - 1; d4 >= 0; --d4) {
-        w = *reinterpret_cast<const uint32_t*>(p + (uint64_t)d4 * 4 * Bp);
+    const int top = (int)nc4_of(m) - 1;
+    auto word = [&](int d4) { return d4 >= 0 ? *reinterpret_cast<const uint32_t*>(p + (uint64_t)d4 * 4 * Bp) : 0u; };
+    uint32_t w = 0, n0 = word(top), n1 = word(top - 1);
+    uint32_t valid = m.nc - 4 * (uint32_t)top; /* digits in the top word */
+#pragma unroll 1
+    for (int d4 = top; d4 >= 0; --d4) {
+        w = n0;
+        n0 = n1;
+        n1 = word(d4 - 2);
         if (valid > 3) c.push(w >> 24);
         if (valid > 2) c.push((w >> 16) & 0xff);
         if (valid > 1) c.push((w >> 8) & 0xff);
@@ -610,12 +619,23 @@ __device__ __forceinline__ void accumulate_frac(u128 x, const ModInfo& m, const 
             i = 1;
         }
 #pragma unroll 1
-        for (; i + 1 < len; i += 2) {
+        for (; i + 3 < len; i += 4) { /* two words per trip */
+            const uint32_t q1 = gc::div_q(r, m);
+            const uint32_t q2 = gc::div_q(q1, m);
+            const uint32_t q3 = gc::div_q(q2, m);
+            const uint32_t q4 = gc::div_q(q3, m);
+            a[0] += r + q1 * c1 - q2 * c2;
+            a[SIGN_THREADS] += q2 + q3 * c1 - q4 * c2;
+            a += 2 * SIGN_THREADS;
+            r = q4;
+        }
+        if (i + 1 < len) {
             const uint32_t q1 = gc::div_q(r, m);
             const uint32_t q2 = gc::div_q(q1, m);
             a[0] += r + q1 * c1 - q2 * c2;
             a += SIGN_THREADS;
             r = q2;
+            i += 2;
         }
         if (i < len) a[0] += r; /* the chunk's last digit is what is left */
     });
@@ -673,7 +693,12 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
     }
 
     /* Step 2: mixed-radix addition from the least significant digit */
-    uint32_t* acc = s_acc + threadIdx.x;
+    /* hide the thread index's origin: under register pressure the compiler
+     * otherwise re-reads %tid.x (S2R) inside the digit loops to rebuild the
+     * accumulator address */
+    uint32_t tid = threadIdx.x;
+    asm volatile("" : "+r"(tid));
+    uint32_t* acc = s_acc + tid;
     u128 carry = P.carry0;
     const u128* approx_e = P.approx + e * (uint64_t)nm * P.S;
     uint64_t cnt1 = e * (uint64_t)(k + 1) * P.Mp, cnt2 = cnt1;
@@ -685,17 +710,23 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
         const ModInfo C = pin(P.cast[i]);
         const gc::ColourConsts cc = gc::colour_consts(M);
         for (uint32_t w = 0; w < (C.nc + 1) / 2; ++w) acc[w * SIGN_THREADS] = 0;
+        /* Ciphertext rows are requested ahead of the hashes that separate
+         * them from their use: residue j+1's approximate-digit row before
+         * label j is hashed, the cast-1 row (its index is the label's colour,
+         * known before the hash) before the hash as well. */
+        auto approx_row = [&](int j) { return ldg128(approx_e + (uint64_t)nm * P.prefix[j] + (uint64_t)i * P.crt[j].q + col[j]); };
+        u128 row = approx_row(0);
 #pragma unroll 1
         for (int j = 0; j <= k; ++j) {
             /* Step 1b: approx. MRS digit i of residue j (j == k: the carry) */
             u128 lab = carry;
-            if (j < k)
-                lab = gc::sub128(ldg128(approx_e + (uint64_t)nm * P.prefix[j] + (uint64_t)i * P.crt[j].q + col[j]),
-                                 h[j]);
+            if (j < k) lab = gc::sub128(row, h[j]);
+            if (j + 1 < k) row = approx_row(j + 1);
             /* Step 2.2: cast to modulus (k+1)*m_i */
-            const u128 hl = hash(aes, lab);
             const uint32_t c0 = gc::colour_of(lab, M, cc);
-            const u128 c1 = gc::sub128(ldg128(P.cast1 + cnt1 + (uint64_t)j * M.q + c0), hl);
+            const u128 crow = ldg128(P.cast1 + cnt1 + (uint64_t)j * M.q + c0);
+            const u128 hl = hash(aes, lab);
+            const u128 c1 = gc::sub128(crow, hl);
             if (DASHB_FRAC && P.castf[i].nst)
                 accumulate_frac(c1, C, P.castf[i], acc);
             else
@@ -711,10 +742,12 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
     /* most significant digit: sum = carry + sum_j digit_{j,0} */
     const ModInfo M0 = pin(P.mrs[0]);
     for (uint32_t w = 0; w < (M0.nc + 1) / 2; ++w) acc[w * SIGN_THREADS] = 0;
+    u128 row0 = ldg128(approx_e + (uint64_t)nm * P.prefix[0] + col[0]);
 #pragma unroll 1
     for (int j = 0; j <= k; ++j) {
         u128 lab = carry;
-        if (j < k) lab = gc::sub128(ldg128(approx_e + (uint64_t)nm * P.prefix[j] + col[j]), h[j]);
+        if (j < k) lab = gc::sub128(row0, h[j]);
+        if (j + 1 < k) row0 = ldg128(approx_e + (uint64_t)nm * P.prefix[j + 1] + col[j + 1]);
         if (DASHB_FRAC && P.castf[0].nst)
             accumulate_frac(lab, M0, P.castf[0], acc);
         else
@@ -756,8 +789,17 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
         uint8_t* xout = P.out[j] + off;
         uint32_t xw = 0, ow = 0;
         const uint32_t last = Pm.nc - 1;
+        /* the input label's words again (they were read for the key in step
+         * 1a), two ahead of their use */
+        const uint32_t nw = nc4_of(Pm);
+        auto xword = [&](uint32_t d4) { return d4 < nw ? *reinterpret_cast<const uint32_t*>(xin + (uint64_t)d4 * 4 * P.Bp) : 0u; };
+        uint32_t xn0 = xword(0), xn1 = xword(1);
         gc::for_each_digit2(E, G, Pm, [&](uint32_t d, uint32_t de, uint32_t dg) {
-            if ((d & 3) == 0) xw = *reinterpret_cast<const uint32_t*>(xin + (uint64_t)(d >> 2) * 4 * P.Bp);
+            if ((d & 3) == 0) {
+                xw = xn0;
+                xn0 = xn1;
+                xn1 = xword((d >> 2) + 2);
+            }
             const uint32_t x = (xw >> (8 * (d & 3))) & 0xff;
             ow |= gc::mod_q(de + (uint32_t)tt * x + Pm.q - dg, Pm) << (8 * (d & 3));
             if ((d & 3) == 3 || d == last) {
@@ -906,8 +948,17 @@ __global__ void __launch_bounds__(WIDE_WARPS * 32) k_sign_wide(const __grid_cons
         uint8_t* xout = P.out[j] + off;
         uint32_t xw = 0, ow = 0;
         const uint32_t last = Pm.nc - 1;
+        /* the input label's words again (they were read for the key in step
+         * 1a), two ahead of their use */
+        const uint32_t nw = nc4_of(Pm);
+        auto xword = [&](uint32_t d4) { return d4 < nw ? *reinterpret_cast<const uint32_t*>(xin + (uint64_t)d4 * 4 * P.Bp) : 0u; };
+        uint32_t xn0 = xword(0), xn1 = xword(1);
         gc::for_each_digit2(E, G, Pm, [&](uint32_t d, uint32_t de, uint32_t dg) {
-            if ((d & 3) == 0) xw = *reinterpret_cast<const uint32_t*>(xin + (uint64_t)(d >> 2) * 4 * P.Bp);
+            if ((d & 3) == 0) {
+                xw = xn0;
+                xn0 = xn1;
+                xn1 = xword((d >> 2) + 2);
+            }
             const uint32_t x = (xw >> (8 * (d & 3))) & 0xff;
             ow |= gc::mod_q(de + (uint32_t)tt * x + Pm.q - dg, Pm) << (8 * (d & 3));
             if ((d & 3) == 3 || d == last) {
@@ -1055,12 +1106,23 @@ __device__ __forceinline__ void rs_accumulate_frac(uint32_t* acc, u128 pr, const
                 i = 1;
             }
 #pragma unroll 1
-            for (; i + 1 < len; i += 2) {
+            for (; i + 3 < len; i += 4) { /* two words per trip */
+                const uint32_t q1 = gc::div_q(r, m);
+                const uint32_t q2 = gc::div_q(q1, m);
+                const uint32_t q3 = gc::div_q(q2, m);
+                const uint32_t q4 = gc::div_q(q3, m);
+                a[0] += (r + q1 * c1 - q2 * c2) * bcoef;
+                a[RS_THREADS] += (q2 + q3 * c1 - q4 * c2) * bcoef;
+                a += 2 * RS_THREADS;
+                r = q4;
+            }
+            if (i + 1 < len) {
                 const uint32_t q1 = gc::div_q(r, m);
                 const uint32_t q2 = gc::div_q(q1, m);
                 a[0] += (r + q1 * c1 - q2 * c2) * bcoef;
                 a += RS_THREADS;
                 r = q2;
+                i += 2;
             }
             if (i < len) a[0] += r * bcoef; /* the chunk's last digit is what is left */
         } else {
