@@ -581,7 +581,7 @@ namespace dashb {
 #endif
 constexpr int SIGN_THREADS = DASHB_SIGN_THREADS;
 #ifndef DASHB_SIGN_MINB
-#define DASHB_SIGN_MINB 10 /* CTAs per SM the register allocation aims at */
+#define DASHB_SIGN_MINB 8 /* CTAs per SM the register allocation aims at */
 #endif
 
 /* Digit accumulators of one thread: 32-bit words holding two digits' sums
@@ -1026,7 +1026,7 @@ cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s) {
  */
 constexpr int RS_THREADS = 128;
 #ifndef DASHB_RS_MINB
-#define DASHB_RS_MINB 9 /* CTAs per SM the register allocation aims at */
+#define DASHB_RS_MINB 8 /* CTAs per SM the register allocation aims at */
 #endif
 
 /* Accumulators of one thread, 32-bit words in shared memory, word-major
@@ -1040,8 +1040,14 @@ template <bool PACKED>
 __device__ __forceinline__ void rs_init(uint32_t* acc, const uint8_t* plane, const uint8_t* up, const ModInfo& m, uint64_t e,
                                         uint32_t b, uint32_t Bp, uint32_t a) {
     const uint8_t* p = plane + plane_off(m, e, b, Bp);
-    for (uint32_t d4 = 0; d4 < nc4_of(m); ++d4) {
-        const uint32_t xw = *reinterpret_cast<const uint32_t*>(p + (uint64_t)d4 * 4 * Bp);
+    /* the label's words are requested two ahead of their use (see load_compress) */
+    const uint32_t nw = nc4_of(m);
+    auto word = [&](uint32_t d4) { return d4 < nw ? *reinterpret_cast<const uint32_t*>(p + (uint64_t)d4 * 4 * Bp) : 0u; };
+    uint32_t n0 = word(0), n1 = word(1);
+    for (uint32_t d4 = 0; d4 < nw; ++d4) {
+        const uint32_t xw = n0;
+        n0 = n1;
+        n1 = word(d4 + 2);
         const uint32_t uw = __ldg(reinterpret_cast<const uint32_t*>(up) + d4);
         uint32_t v[4];
 #pragma unroll
@@ -1234,12 +1240,22 @@ __device__ __forceinline__ void rescale_body(const RescaleParams& P, const AesSm
         for (int i = 0; i < P.nf; ++i)
             if (P.fidx[i] == jt) x = i;
         if (x < 0) {
-            /* steps 1-2: upshift, then divide by every factor */
+            /* steps 1-2: upshift, then divide by every factor.  The first
+             * factor's ciphertext row is requested before the accumulator is
+             * set up, the next one before the current one is consumed. */
+            auto tm_row = [&](int i) {
+                return i < P.nf && P.tm_off[i][jt] != ~0ull
+                           ? ldg128(P.tm + P.tm_off[i][jt] + e * (uint64_t)P.factor[i] + fcol[i])
+                           : gc::make_u128(0, 0);
+            };
+            u128 trow = tm_row(0);
             rs_init<PACKED>(acc, P.in[jt], P.up[jt], m, e, b, P.Bp, P.a1[jt]);
 #pragma unroll 1
             for (int i = 0; i < P.nf; ++i) {
+                const u128 cur = trow;
+                trow = tm_row(i + 1);
                 if (P.tm_off[i][jt] == ~0ull) continue;
-                const u128 pr = gc::sub128(ldg128(P.tm + P.tm_off[i][jt] + e * (uint64_t)P.factor[i] + fcol[i]), hf[i]);
+                const u128 pr = gc::sub128(cur, hf[i]);
                 if (DASHB_FRAC && P.crtf[jt].nst)
                     rs_accumulate_frac<PACKED>(acc, pr, m, P.crtf[jt], P.b1[i][jt]);
                 else
@@ -1259,9 +1275,14 @@ __device__ __forceinline__ void rescale_body(const RescaleParams& P, const AesSm
         if (P.legacy) continue;
         /* step 3: garbled mixed-radix conversion, all eliminations of this target */
         const int ni = t < P.non_ext ? t : P.non_ext;
+        auto be_row = [&](int i) {
+            return i < ni ? ldg128(P.be + P.be_off[i][t] + e * (uint64_t)P.crt[P.perm[i]].q + col[i]) : gc::make_u128(0, 0);
+        };
+        u128 brow = be_row(0);
 #pragma unroll 1
         for (int i = 0; i < ni; ++i) {
-            const u128 pr = gc::sub128(ldg128(P.be + P.be_off[i][t] + e * (uint64_t)P.crt[P.perm[i]].q + col[i]), h[i]);
+            const u128 pr = gc::sub128(brow, h[i]);
+            brow = be_row(i + 1); /* the next row travels while this one is accumulated */
             if (DASHB_FRAC && P.crtf[jt].nst)
                 rs_accumulate_frac<PACKED>(acc, pr, m, P.crtf[jt], P.b2[i][t]);
             else
