@@ -331,6 +331,10 @@ __global__ void __launch_bounds__(LIN_THREADS, 8) k_linear(const __grid_constant
     const ModInfo m = pin(P.mod[j]);
     const uint32_t ncols = ((m.nc + 3) & ~3u) * P.Bp; /* nc4 words of 4 digits per inference */
     const uint32_t col = (blockIdx.x * LIN_THREADS + threadIdx.x) * 4;
+    /* the grid's x extent is sized for the modulus with the most digits: CTAs
+     * past this modulus' columns leave before staging anything (58 % of the
+     * CTAs of a k = 9 launch) */
+    if (blockIdx.x * LIN_THREADS * 4 >= ncols) return;
     /* groups of 8 rows that overlap [v0, v1) */
     const uint32_t vg_first = P.v0 / LIN_ROWS;
     const uint32_t nvg = (P.v1 + LIN_ROWS - 1) / LIN_ROWS - vg_first;

@@ -17,8 +17,8 @@ VARIANTS = {
     "base": "",
     "nofrac": "-DDASHB_FRAC=0",
     "aes3": "-DDASHB_AES_UNROLL=3",
-    "minb9": "-DDASHB_SIGN_MINB=9 -DDASHB_RS_MINB=8",
-    "minb8": "-DDASHB_SIGN_MINB=8 -DDASHB_RS_MINB=8",
+    "minb9": "-DDASHB_SIGN_MINB=9",
+    "minb10": "-DDASHB_SIGN_MINB=10",
     "minb12": "-DDASHB_SIGN_MINB=12 -DDASHB_RS_MINB=10",
 }
 
