@@ -145,6 +145,10 @@ gc::FracInfo make_fracinfo(const ModInfo& m) {
     memset(&fi, 0, sizeof(fi));
     const uint32_t q = m.q, nc = m.nc, t = m.t;
     if (q < 2 || nc < 2) return fi;
+    /* DASHB_NO_FRAC: no plans, every kernel takes its long-division path
+     * (the one moduli with more than FRAC_MAXST chunks take; tests/
+     * test_gpu_parity.py::test_division_fallback keeps it covered) */
+    if (getenv("DASHB_NO_FRAC")) return fi;
     uint32_t sh = 0;
     while ((q >> sh) != 0) ++sh; /* bit length: q < 2^sh */
     const int F = 160 - (int)sh;

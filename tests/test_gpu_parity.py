@@ -38,6 +38,23 @@ def test_golden_every_layer(gpu, name):
     c.close()
 
 
+@pytest.mark.parametrize("name", ["MLP_TINY", "RELU_EDGE", "SIGN_TINY", "RESCALE_2_3", "RESCALE_LEGACY", "RESCALE_OPT"])
+def test_division_fallback(gpu, name, monkeypatch):
+    """The gadget kernels take a label's digits by multiplication where the
+    modulus has a plan and by long division otherwise (a modulus cut into more
+    than 10 chunks); no circuit of the configurations has such a modulus, so
+    DASHB_NO_FRAC switches the plans off when the circuit is created."""
+    if name not in GOLDEN:
+        pytest.skip("no such golden circuit")
+    monkeypatch.setenv("DASHB_NO_FRAC", "1")
+    g = Golden(name)
+    batch = 19
+    c = gpu.Circuit.load(g.gcm, max_batch=batch)
+    got = c.evaluate(tile_batch(g.inputs, batch))
+    assert_labels_equal(got, tile_batch(g.layers[-1], batch), "%s final, division path" % name)
+    c.close()
+
+
 # ---- circuits garbled on the box by the reference build (oracle/_ref) -----
 def _live(name, gpu, tmp_path, batch, seed=77):
     import workloads as W
