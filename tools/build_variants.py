@@ -17,9 +17,10 @@ VARIANTS = {
     "base": "",
     "nofrac": "-DDASHB_FRAC=0",
     "aes3": "-DDASHB_AES_UNROLL=3",
-    "minb9": "-DDASHB_SIGN_MINB=9",
-    "minb10": "-DDASHB_SIGN_MINB=10",
-    "minb12": "-DDASHB_SIGN_MINB=12 -DDASHB_RS_MINB=10",
+    "sign9": "-DDASHB_SIGN_MINB=9",
+    "sign10": "-DDASHB_SIGN_MINB=10",
+    "rs10": "-DDASHB_RS_MINB=10",
+    "rs12": "-DDASHB_RS_MINB=12",
 }
 
 if __name__ == "__main__":
