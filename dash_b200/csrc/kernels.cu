@@ -324,6 +324,37 @@ constexpr int LIN_KC = 1024; /* taps staged in shared memory per chunk */
 
 constexpr int LIN_PIXC = 4; /* output pixels a CTA walks through with one staging of the weights */
 
+/* The multiply-accumulate loop over one staged chunk of taps, for a row
+ * group of which only the first NR rows exist (5 filters: 20 dot products per
+ * tap group instead of 32). */
+template <int NR>
+__device__ __forceinline__ void lin_taps(const uint8_t* in, uint64_t rowlen, const int32_t* s_koff, const uint4 (*s_w)[2],
+                                         uint32_t k4_n, uint32_t (&acc)[LIN_ROWS][4]) {
+#pragma unroll 1
+    for (uint32_t kk = 0; kk < k4_n; ++kk) {
+        const uint32_t x0 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 0] * rowlen));
+        const uint32_t x1 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 1] * rowlen));
+        const uint32_t x2 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 2] * rowlen));
+        const uint32_t x3 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 3] * rowlen));
+        /* 4x4 byte transpose: y_c = (x0.c, x1.c, x2.c, x3.c) */
+        const uint32_t t0 = __byte_perm(x0, x1, 0x5140), t1 = __byte_perm(x0, x1, 0x7362);
+        const uint32_t u0 = __byte_perm(x2, x3, 0x5140), u1 = __byte_perm(x2, x3, 0x7362);
+        const uint32_t y0 = __byte_perm(t0, u0, 0x5410), y1 = __byte_perm(t0, u0, 0x7632);
+        const uint32_t y2 = __byte_perm(t1, u1, 0x5410), y3 = __byte_perm(t1, u1, 0x7632);
+        const uint4 wa = s_w[kk][0];
+        uint4 wb = make_uint4(0, 0, 0, 0);
+        if (NR > 4) wb = s_w[kk][1];
+        const uint32_t w[LIN_ROWS] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+            acc[r][0] = __dp4a(y0, w[r], acc[r][0]);
+            acc[r][1] = __dp4a(y1, w[r], acc[r][1]);
+            acc[r][2] = __dp4a(y2, w[r], acc[r][2]);
+            acc[r][3] = __dp4a(y3, w[r], acc[r][3]);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(LIN_THREADS, 8) k_linear(const __grid_constant__ LinearParams P) {
     __shared__ uint4 s_w[LIN_KC / 4][2];  /* [k/4][8 rows] packed weights */
     __shared__ int32_t s_koff[LIN_KC];
@@ -339,6 +370,7 @@ __global__ void __launch_bounds__(LIN_THREADS, 8) k_linear(const __grid_constant
     const uint32_t vg_first = P.v0 / LIN_ROWS;
     const uint32_t nvg = (P.v1 + LIN_ROWS - 1) / LIN_ROWS - vg_first;
     const uint32_t vg = vg_first + blockIdx.y % nvg;
+    const uint32_t nr = min((uint32_t)LIN_ROWS, P.v1 - vg * LIN_ROWS); /* rows of this group that exist */
     const uint32_t pix0 = (blockIdx.y / nvg) * LIN_PIXC;
     const uint32_t pix1 = min(pix0 + LIN_PIXC, P.npix);
     const uint64_t rowlen = ncols;
@@ -375,46 +407,37 @@ __global__ void __launch_bounds__(LIN_THREADS, 8) k_linear(const __grid_constant
                 __syncthreads();
             }
             if (!active) continue;
-#pragma unroll 1
-            for (uint32_t kk = 0; kk < k4_n; ++kk) {
-                const uint32_t x0 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 0] * rowlen));
-                const uint32_t x1 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 1] * rowlen));
-                const uint32_t x2 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 2] * rowlen));
-                const uint32_t x3 = __ldg(reinterpret_cast<const uint32_t*>(in + (int64_t)s_koff[4 * kk + 3] * rowlen));
-                /* 4x4 byte transpose: y_c = (x0.c, x1.c, x2.c, x3.c) */
-                const uint32_t t0 = __byte_perm(x0, x1, 0x5140), t1 = __byte_perm(x0, x1, 0x7362);
-                const uint32_t u0 = __byte_perm(x2, x3, 0x5140), u1 = __byte_perm(x2, x3, 0x7362);
-                const uint32_t y0 = __byte_perm(t0, u0, 0x5410), y1 = __byte_perm(t0, u0, 0x7632);
-                const uint32_t y2 = __byte_perm(t1, u1, 0x5410), y3 = __byte_perm(t1, u1, 0x7632);
-                const uint4 wa = s_w[kk][0], wb = s_w[kk][1];
-                const uint32_t w[LIN_ROWS] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
-#pragma unroll
-                for (int r = 0; r < LIN_ROWS; ++r) {
-                    acc[r][0] = __dp4a(y0, w[r], acc[r][0]);
-                    acc[r][1] = __dp4a(y1, w[r], acc[r][1]);
-                    acc[r][2] = __dp4a(y2, w[r], acc[r][2]);
-                    acc[r][3] = __dp4a(y3, w[r], acc[r][3]);
-                }
-            }
+            if (nr > 5)
+                lin_taps<8>(in, rowlen, s_koff, s_w, k4_n, acc);
+            else if (nr > 2)
+                lin_taps<5>(in, rowlen, s_koff, s_w, k4_n, acc);
+            else
+                lin_taps<2>(in, rowlen, s_koff, s_w, k4_n, acc);
         }
         if (!active) continue;
+        /* row v of this pixel: output word and constant word step by a fixed
+         * stride from row to row */
+        const uint64_t ostep = (uint64_t)P.npix * rowlen;
+        uint8_t* op = P.out[j] + ((uint64_t)(vg * LIN_ROWS) * P.npix + pix) * rowlen + col;
+        const uint32_t* cp = reinterpret_cast<const uint32_t*>(P.cst[j]) + (uint64_t)(vg * LIN_ROWS) * nc4 + d4;
 #pragma unroll
-        for (int r = 0; r < LIN_ROWS; ++r) {
+        for (int r = 0; r < LIN_ROWS; ++r, op += ostep, cp += nc4) {
             const uint32_t v = vg * LIN_ROWS + r;
             if (v >= P.v1) break;
             if (v < P.v0) continue;
-            const uint32_t cst = __ldg(reinterpret_cast<const uint32_t*>(P.cst[j]) + (uint64_t)v * nc4 + d4);
+            const uint32_t cst = __ldg(cp);
             uint32_t o = 0;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-                /* x mod q for any 32-bit x: the reciprocal over-estimates the
-                 * quotient by at most one */
                 uint32_t x = acc[r][c] + ((cst >> (8 * c)) & 0xff);
                 x -= gc::mulhi32(x, m.mq) * m.q;
-                if ((int32_t)x < 0) x += m.q;
+                /* x mod q for any 32-bit x: the reciprocal over-estimates the
+                 * quotient by at most one; never when the launch's largest
+                 * possible sum is within the reciprocal's exact range */
+                if (!P.exact_mod && (int32_t)x < 0) x += m.q;
                 o |= x << (8 * c);
             }
-            *reinterpret_cast<uint32_t*>(P.out[j] + ((uint64_t)v * P.npix + pix) * rowlen + col) = o;
+            *reinterpret_cast<uint32_t*>(op) = o;
         }
     }
 }
@@ -424,8 +447,14 @@ cudaError_t launch_linear(const LinearParams& p, cudaStream_t s) {
     for (int j = 0; j < p.k; ++j) max_cols = max(max_cols, ((p.mod[j].nc + 3) & ~3u) * p.Bp);
     if (p.v1 <= p.v0) return cudaSuccess; /* this rank owns no row of the layer */
     const uint32_t nvg = (p.v1 + LIN_ROWS - 1) / LIN_ROWS - p.v0 / LIN_ROWS;
+    LinearParams q = p;
+    q.exact_mod = 1; /* K (q-1)^2 + (q-1) <= lim for every modulus: no fix-up after the reciprocal */
+    for (int j = 0; j < p.k; ++j) {
+        const uint64_t qm = p.mod[j].q - 1;
+        if ((uint64_t)p.K * qm * qm + qm > p.mod[j].lim) q.exact_mod = 0;
+    }
     dim3 grid((max_cols / 4 + LIN_THREADS - 1) / LIN_THREADS, ((p.npix + LIN_PIXC - 1) / LIN_PIXC) * nvg, p.k);
-    k_linear<<<grid, LIN_THREADS, 0, s>>>(p);
+    k_linear<<<grid, LIN_THREADS, 0, s>>>(q);
     return cudaGetLastError();
 }
 

@@ -37,6 +37,7 @@ struct LinearParams {
     uint32_t step_x, step_y;   /* element offset per output x / y step */
     uint32_t Bp;
     int k;
+    int exact_mod;             /* set by launch_linear: sums stay within the reciprocal's exact range */
 };
 
 /* tcgen05 dense path (dense_tc.cu).  A tensor map is CUtensorMap's 128 opaque
