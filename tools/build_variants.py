@@ -21,6 +21,8 @@ VARIANTS = {
     "sign10": "-DDASHB_SIGN_MINB=10",
     "rs10": "-DDASHB_RS_MINB=10",
     "rs12": "-DDASHB_RS_MINB=12",
+    "sign64": "-DDASHB_SIGN_THREADS=64 -DDASHB_SIGN_MINB=16",
+    "sign256": "-DDASHB_SIGN_THREADS=256 -DDASHB_SIGN_MINB=4",
 }
 
 if __name__ == "__main__":
