@@ -75,6 +75,7 @@ def lib():
         L.dashb_hostcheck_digits.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
         L.dashb_hostcheck_colour.argtypes = [C.c_int, C.c_void_p]
         L.dashb_hostcheck_digits_frac.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+        L.dashb_hostcheck_frac_sweep.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_void_p]
         L.dashb_hostcheck_hash.argtypes = [C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
@@ -308,6 +309,14 @@ def hostcheck_digits_frac(q, x):
     if not lib().dashb_hostcheck_digits_frac(int(q), c.ctypes.data, d.ctypes.data):
         return None
     return d
+
+
+def hostcheck_frac_sweep(q_lo, q_hi, samples, seed=1):
+    """(moduli on which the two digit extractions differ, moduli with a plan)
+    over [q_lo, q_hi], `samples` random valid payloads + edge payloads each."""
+    n = C.c_int(0)
+    bad = lib().dashb_hostcheck_frac_sweep(int(q_lo), int(q_hi), int(samples), int(seed), C.byref(n))
+    return bad, n.value
 
 
 def hostcheck_colour(q, x):

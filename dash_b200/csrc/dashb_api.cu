@@ -1807,6 +1807,69 @@ int dashb_hostcheck_digits_frac(int q, const uint64_t in2[2], int16_t* digits) {
     });
     return 1;
 }
+/* For every modulus in [q_lo, q_hi] that has a plan: `samples` random valid
+ * payloads plus the edge payloads 0, 1, q^nc - 1, q^i and q^i - 1 through both
+ * extractions; returns the number of moduli on which they differ (0 = all
+ * agree) and, in *planned, how many moduli had a plan. */
+int dashb_hostcheck_frac_sweep(int q_lo, int q_hi, int samples, uint64_t seed, int* planned) {
+    int bad = 0, np = 0;
+    uint64_t st = seed * 0x9e3779b97f4a7c15ull + 1;
+    auto next = [&]() { /* splitmix64 */
+        uint64_t z = (st += 0x9e3779b97f4a7c15ull);
+        z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+        z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+        return z ^ (z >> 31);
+    };
+    for (int q = q_lo; q <= q_hi; ++q) {
+        if (q < 2) continue;
+        const ModInfo m = make_modinfo((uint32_t)q);
+        const gc::FracInfo fi = make_fracinfo(m);
+        if (fi.nst == 0) continue;
+        ++np;
+        /* D = q^nc as 128 bits (2^128 itself for the powers of two that reach it: then every payload is valid) */
+        unsigned __int128 D = 1;
+        bool full = false;
+        for (uint32_t i = 0; i < m.nc; ++i) {
+            const unsigned __int128 nd = D * (unsigned)q;
+            if (nd / (unsigned)q != D) full = true;
+            D = nd;
+        }
+        bool differs = false;
+        auto check = [&](unsigned __int128 x) {
+            if (!full && x >= D) return;
+            uint32_t a[128] = {0}, b[128] = {0};
+            const gc::u128 v = gc::make_u128((uint64_t)x, (uint64_t)(x >> 64));
+            gc::for_each_digit(v, m, [&](uint32_t d, uint32_t dg) { a[d] = dg; });
+            gc::for_each_chunk_msb(v, m, fi, [&](uint32_t d0, uint32_t len, uint32_t r) {
+                for (uint32_t i = 0; i < len; ++i) {
+                    b[d0 + i] = r % m.q;
+                    r /= m.q;
+                }
+                if (r) differs = true; /* a chunk must hold exactly len digits */
+            });
+            for (uint32_t d = 0; d < m.nc; ++d)
+                if (a[d] != b[d]) differs = true;
+        };
+        check(0);
+        check(1);
+        check(full ? ~(unsigned __int128)0 : D - 1);
+        check(full ? ~(unsigned __int128)0 - 1 : D - 2);
+        unsigned __int128 pw = 1;
+        for (uint32_t i = 0; i < m.nc; ++i) {
+            check(pw);
+            check(pw - 1);
+            pw *= (unsigned)q;
+        }
+        for (int t = 0; t < samples; ++t) {
+            unsigned __int128 x = ((unsigned __int128)next() << 64) | next();
+            if (!full) x %= D;
+            check(x);
+        }
+        if (differs) ++bad;
+    }
+    if (planned) *planned = np;
+    return bad;
+}
 int dashb_hostcheck_colour(int q, const uint64_t in2[2]) {
     ModInfo m = make_modinfo((uint32_t)q);
     return (int)gc::colour_of(gc::make_u128(in2[0], in2[1]), m);

@@ -120,3 +120,13 @@ def test_multiplicative_digit_extraction_matches_division(api):
         else:
             planned += 1
     assert planned >= 260
+
+
+def test_multiplicative_digit_extraction_every_modulus(api):
+    """Every modulus a circuit can name (CRT moduli, MRS digits, cast moduli
+    (k+1)*m_i: 2..32767): the plan's extraction against the long division on
+    random valid payloads and the edge payloads, in C++ (the Python loop above
+    covers 2..256 against the oracle)."""
+    bad, planned = api.hostcheck_frac_sweep(2, 32767, 200, seed=3)
+    assert bad == 0
+    assert planned > 1500  # every modulus cut into at most 10 chunks has a plan
