@@ -359,6 +359,7 @@ struct Layer {
 struct Lane {
     cudaStream_t s{nullptr};
     cudaEvent_t done{nullptr}, in_done{nullptr}, ing_done{nullptr};
+    cudaEvent_t in_done_x[3] = {nullptr, nullptr, nullptr}; /* the lane's copies on the further copy streams */
     DevMem buf_in, buf_a, buf_b, stage_in, stage_out, xvals;
     Tensor t_in, t_cur;
     int which{0};
@@ -390,6 +391,9 @@ struct dashb_circuit {
     uint32_t lane_cap{0};
     cudaEvent_t ev_fork{nullptr};
     cudaStream_t copy_s{nullptr};   /* H2D copies of the pipelined dashb_evaluate */
+    static constexpr int MAX_COPY = 4;
+    cudaStream_t copy_x[MAX_COPY - 1] = {nullptr, nullptr, nullptr}; /* further copy streams (DASHB_COPY_STREAMS) */
+    int n_copy{1};
     cudaStream_t ingest_s{nullptr}; /* its ingest kernels (highest priority) */
     DevMem dec[MAXK];
     bool has_dec{false};
@@ -405,10 +409,14 @@ struct dashb_circuit {
         for (auto e : ev) cudaEventDestroy(e);
         if (ev_fork) cudaEventDestroy(ev_fork);
         if (copy_s) cudaStreamDestroy(copy_s);
+        for (auto x : copy_x)
+            if (x) cudaStreamDestroy(x);
         if (ingest_s) cudaStreamDestroy(ingest_s);
         for (auto& l : lanes) {
             if (l->done) cudaEventDestroy(l->done);
             if (l->in_done) cudaEventDestroy(l->in_done);
+            for (auto x : l->in_done_x)
+                if (x) cudaEventDestroy(x);
             if (l->ing_done) cudaEventDestroy(l->ing_done);
             if (l->s) cudaStreamDestroy(l->s);
         }
@@ -1104,6 +1112,7 @@ int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
         CU(cudaStreamCreateWithFlags(&ln->s, cudaStreamNonBlocking));
         CU(cudaEventCreateWithFlags(&ln->done, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&ln->in_done, cudaEventDisableTiming));
+        for (auto& x : ln->in_done_x) CU(cudaEventCreateWithFlags(&x, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&ln->ing_done, cudaEventDisableTiming));
         CU(ln->buf_in.alloc(in_bytes));
         CU(ln->buf_a.alloc(act_bytes));
@@ -1119,6 +1128,19 @@ int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
     }
     CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     CU(cudaStreamCreateWithFlags(&c->copy_s, cudaStreamNonBlocking));
+    /* A host-to-device copy of a few MB (one modulus of one lane) runs well
+     * below the link rate on its own (tools/h2d_bandwidth.py: 22 GB/s at
+     * 5 MiB, 55 GB/s from 188 MiB).  Spreading the copies over several
+     * streams does not recover that: measured 7.38 / 8.83 / 8.91 / 9.34 ms per
+     * end-to-end step with 1 / 2 / 3 / 4 copy streams
+     * (tools/probe_copy_streams.py), so one stream stays the default;
+     * DASHB_COPY_STREAMS keeps the experiment reproducible. */
+    c->n_copy = 1;
+    if (const char* env = getenv("DASHB_COPY_STREAMS")) {
+        const int v = atoi(env);
+        if (v >= 1 && v <= dashb_circuit::MAX_COPY) c->n_copy = v;
+    }
+    for (int i = 0; i + 1 < c->n_copy; ++i) CU(cudaStreamCreateWithFlags(&c->copy_x[i], cudaStreamNonBlocking));
     {
         int lo = 0, hi = 0;
         CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
@@ -1141,6 +1163,7 @@ static int fork_lanes(dashb_circuit* c) {
     CU(cudaEventRecord(c->ev_fork, g_stream));
     for (int i = 0; i < c->lanes_used; ++i) CU(cudaStreamWaitEvent(c->lanes[i]->s, c->ev_fork, 0));
     CU(cudaStreamWaitEvent(c->copy_s, c->ev_fork, 0));
+    for (int i = 0; i + 1 < c->n_copy; ++i) CU(cudaStreamWaitEvent(c->copy_x[i], c->ev_fork, 0));
     CU(cudaStreamWaitEvent(c->ingest_s, c->ev_fork, 0));
     return DASHB_OK;
 }
@@ -1190,7 +1213,10 @@ static int enqueue_inputs(dashb_circuit* c, Lane& ln, const void* const* in, boo
     for (int j = 0; j < c->k; ++j) {
         const size_t per = c->input_size * wire_label_bytes(c, j, compressed);
         const size_t bytes = (size_t)ln.batch * per;
-        CU(cudaMemcpyAsync((char*)ln.stage_in.p + off, (const char*)in[j] + (size_t)ln.b0 * per, bytes, cudaMemcpyHostToDevice, cs));
+        /* pipelined path: the moduli's copies alternate between the copy streams */
+        const int which = (cs == c->copy_s) ? j % c->n_copy : 0;
+        cudaStream_t cj = which ? c->copy_x[which - 1] : cs;
+        CU(cudaMemcpyAsync((char*)ln.stage_in.p + off, (const char*)in[j] + (size_t)ln.b0 * per, bytes, cudaMemcpyHostToDevice, cj));
         off += bytes;
     }
     /* the ingest kernels are short; in the pipelined path they run on a
@@ -1200,6 +1226,11 @@ static int enqueue_inputs(dashb_circuit* c, Lane& ln, const void* const* in, boo
     if (cs != s) {
         CU(cudaEventRecord(ln.in_done, cs));
         CU(cudaStreamWaitEvent(is, ln.in_done, 0));
+        if (cs == c->copy_s)
+            for (int i = 0; i + 1 < c->n_copy; ++i) {
+                CU(cudaEventRecord(ln.in_done_x[i], c->copy_x[i]));
+                CU(cudaStreamWaitEvent(is, ln.in_done_x[i], 0));
+            }
     }
     off = 0;
     for (int j = 0; j < c->k; ++j) {
