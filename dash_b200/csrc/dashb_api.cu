@@ -13,7 +13,6 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
-#include <dlfcn.h>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -1208,43 +1207,17 @@ static size_t wire_label_bytes(const dashb_circuit* c, int j, bool compressed) {
     return compressed ? 16 : (size_t)c->crt_mi[j].nc * 2;
 }
 
-/* cudaMemcpyBatchAsync (CUDA 12.8+), looked up at run time so that the
- * library still loads against an older runtime.  Experiment, off by default
- * (DASHB_COPY_BATCH=1): one submission for a lane's k copies instead of k. */
-typedef cudaError_t (*memcpy_batch_fn)(void**, void**, size_t*, size_t, cudaMemcpyAttributes*, size_t*, size_t, size_t*, cudaStream_t);
-static memcpy_batch_fn memcpy_batch() {
-    static const memcpy_batch_fn fn =
-        getenv("DASHB_COPY_BATCH") && atoi(getenv("DASHB_COPY_BATCH")) ? (memcpy_batch_fn)dlsym(RTLD_DEFAULT, "cudaMemcpyBatchAsync") : nullptr;
-    return fn;
-}
-
 /* `in`: per CRT modulus int16 [batch][label][nc], or (compressed) dashb_u128 [batch][label] */
 static int enqueue_inputs(dashb_circuit* c, Lane& ln, const void* const* in, bool compressed, cudaStream_t cs, cudaStream_t s) {
     size_t off = 0;
-    if (memcpy_batch_fn batch = (cs == c->copy_s && c->n_copy == 1) ? memcpy_batch() : nullptr) {
-        void *dsts[MAXK], *srcs[MAXK];
-        size_t sizes[MAXK], idx0 = 0, fail_idx = 0;
-        for (int j = 0; j < c->k; ++j) {
-            const size_t per = c->input_size * wire_label_bytes(c, j, compressed);
-            sizes[j] = (size_t)ln.batch * per;
-            dsts[j] = (char*)ln.stage_in.p + off;
-            srcs[j] = const_cast<char*>((const char*)in[j] + (size_t)ln.b0 * per);
-            off += sizes[j];
-        }
-        cudaMemcpyAttributes attr;
-        memset(&attr, 0, sizeof(attr));
-        attr.srcAccessOrder = cudaMemcpySrcAccessOrderStream;
-        CU(batch(dsts, srcs, sizes, (size_t)c->k, &attr, &idx0, 1, &fail_idx, cs));
-    } else {
-        for (int j = 0; j < c->k; ++j) {
-            const size_t per = c->input_size * wire_label_bytes(c, j, compressed);
-            const size_t bytes = (size_t)ln.batch * per;
-            /* pipelined path: the moduli's copies alternate between the copy streams */
-            const int which = (cs == c->copy_s) ? j % c->n_copy : 0;
-            cudaStream_t cj = which ? c->copy_x[which - 1] : cs;
-            CU(cudaMemcpyAsync((char*)ln.stage_in.p + off, (const char*)in[j] + (size_t)ln.b0 * per, bytes, cudaMemcpyHostToDevice, cj));
-            off += bytes;
-        }
+    for (int j = 0; j < c->k; ++j) {
+        const size_t per = c->input_size * wire_label_bytes(c, j, compressed);
+        const size_t bytes = (size_t)ln.batch * per;
+        /* pipelined path: the moduli's copies alternate between the copy streams */
+        const int which = (cs == c->copy_s) ? j % c->n_copy : 0;
+        cudaStream_t cj = which ? c->copy_x[which - 1] : cs;
+        CU(cudaMemcpyAsync((char*)ln.stage_in.p + off, (const char*)in[j] + (size_t)ln.b0 * per, bytes, cudaMemcpyHostToDevice, cj));
+        off += bytes;
     }
     /* the ingest kernels are short; in the pipelined path they run on a
      * high-priority stream so that they are not queued behind the thousands
