@@ -58,6 +58,7 @@ def lib():
         for f in (L.dashb_num_layers, L.dashb_crt_base_size):
             f.argtypes = [C.c_void_p]
         L.dashb_output_modulus.argtypes = [C.c_void_p, C.c_int]
+        L.dashb_crt_modulus.argtypes = [C.c_void_p, C.c_int]
         L.dashb_layer_type.argtypes = [C.c_void_p, C.c_int]
         for f in (L.dashb_algorithmic_bytes, L.dashb_aes_blocks, L.dashb_reference_aes_blocks):
             f.restype = C.c_double
@@ -119,7 +120,7 @@ class Circuit:
         self.n_layers = self.L.dashb_num_layers(self.h)
         self.out_moduli = [self.L.dashb_output_modulus(self.h, j) for j in range(self.k)]
         self.batch = 0
-        self.in_moduli = None
+        self.in_moduli = [self.L.dashb_crt_modulus(self.h, j) for j in range(self.k)]
 
     @classmethod
     def load(cls, path, max_batch=1, shard=None):
@@ -177,9 +178,11 @@ class Circuit:
         if len(labels) != self.k:
             raise ValueError("expected %d label tensors" % self.k)
         batch = labels[0].shape[0]
-        for l in labels:
-            if l.ndim != 3 or l.shape[0] != batch or l.shape[1] != self.input_size:
-                raise ValueError("labels must be [batch][input_size][nc]")
+        for q, l in zip(self.in_moduli, labels):
+            # the library reads batch * input_size * nc(q) digits from each buffer: a wrong last dimension
+            # would make it read past the array
+            if l.ndim != 3 or l.shape[0] != batch or l.shape[1] != self.input_size or l.shape[2] != nr_comps(q):
+                raise ValueError("labels of modulus %d must be [batch][input_size][%d], got %s" % (q, nr_comps(q), l.shape))
         return labels, batch
 
     def move_inputs(self, labels):

@@ -713,7 +713,8 @@ int dashb_add_conv2d(dashb_circuit* c, uint64_t in_w, uint64_t in_h, uint64_t ch
     L->ow = (uint32_t)ow;
     L->step_x = (uint32_t)s_w;
     L->step_y = (uint32_t)(s_h * in_w);
-    if ((uint64_t)L->npix * ((filters + 7) / 8) > 65535) return fail(DASHB_EINVAL, "conv2d: output grid too large");
+    if (ow * oh > 0x7fffffffull || ((ow * oh + 3) / 4) * ((filters + 7) / 8) > 0xffffffffull)
+        return fail(DASHB_EINVAL, "conv2d: output grid too large");
     CU(L->koff.upload(koff.data(), koff.size() * 4));
     /* tcgen05 path (dense_tc.cu): one GEMM per output pixel, im2col by a 4-D
      * TMA box of cb channels; weights regrouped into 128-column K blocks of
@@ -1662,17 +1663,29 @@ static int evaluate_any(dashb_circuit* c, const void* const* in, uint64_t batch,
         for (auto& e : tr) cudaEventCreate(&e);
         cudaEventRecord(tr[0], g_stream);
     }
-    if ((rc = fork_lanes(c))) return rc;
+    /* a failure part-way leaves the lane streams forked: join them again and
+     * drop the trace events before reporting it (the message survives: the
+     * clean-up calls do not touch the error text unless they fail themselves) */
+    auto bail = [&](int code) {
+        const std::string msg = g_err;
+        join_lanes(c);
+        cudaStreamSynchronize(g_stream);
+        if (trace)
+            for (auto& e : tr) cudaEventDestroy(e);
+        g_err = msg;
+        return code;
+    };
+    if ((rc = fork_lanes(c))) return bail(rc);
     for (int i = 0; i < c->lanes_used; ++i) {
         /* all H2D copies go through one copy stream, lane after lane, so that
          * lane i-1 computes while lane i still transfers */
-        if ((rc = enqueue_inputs(c, *c->lanes[i], in, compressed, c->copy_s, c->lanes[i]->s))) return rc;
+        if ((rc = enqueue_inputs(c, *c->lanes[i], in, compressed, c->copy_s, c->lanes[i]->s))) return bail(rc);
         if (trace) cudaEventRecord(tr[1 + 3 * i], c->lanes[i]->s);
     }
     const int nl = (int)c->layers.size();
     for (int li = 0; li < nl; ++li)
         for (int i = 0; i < c->lanes_used; ++i) {
-            if ((rc = run_layer(c, *c->lanes[i], li, c->lanes[i]->s))) return rc;
+            if ((rc = run_layer(c, *c->lanes[i], li, c->lanes[i]->s))) return bail(rc);
             if (trace && li == nl - 1) cudaEventRecord(tr[2 + 3 * i], c->lanes[i]->s);
         }
     if (nl > 0) {
@@ -1680,10 +1693,10 @@ static int evaluate_any(dashb_circuit* c, const void* const* in, uint64_t batch,
         for (int j = 0; j < c->k; ++j) c->out_q[j] = c->layers[nl - 1]->out_q[j];
     }
     for (int i = 0; i < c->lanes_used; ++i) {
-        if ((rc = enqueue_outputs(c, *c->lanes[i], out, compressed, c->lanes[i]->s))) return rc;
+        if ((rc = enqueue_outputs(c, *c->lanes[i], out, compressed, c->lanes[i]->s))) return bail(rc);
         if (trace) cudaEventRecord(tr[3 + 3 * i], c->lanes[i]->s);
     }
-    if ((rc = join_lanes(c))) return rc;
+    if ((rc = join_lanes(c))) return bail(rc);
     CU(cudaStreamSynchronize(g_stream));
     if (trace) {
         for (int i = 0; i < c->lanes_used; ++i) {
@@ -1764,6 +1777,7 @@ uint64_t dashb_input_size(const dashb_circuit* c) { return c ? c->input_size : 0
 uint64_t dashb_output_size(const dashb_circuit* c) { return c ? c->cur_size : 0; }
 int dashb_num_layers(const dashb_circuit* c) { return c ? (int)c->layers.size() : 0; }
 int dashb_crt_base_size(const dashb_circuit* c) { return c ? c->k : 0; }
+int dashb_crt_modulus(const dashb_circuit* c, int j) { return (c && j >= 0 && j < c->k) ? c->crt[j] : 0; }
 int dashb_output_modulus(const dashb_circuit* c, int j) { return (c && j >= 0 && j < c->k) ? c->cur_q[j] : 0; }
 uint64_t dashb_last_launch_count(const dashb_circuit* c) { return c ? c->launches : 0; }
 int dashb_layer_type(const dashb_circuit* c, int layer) {
@@ -1802,10 +1816,24 @@ int dashb_circuit_load(dashb_circuit** out, const char* path) {
     *out = nullptr;
     if (g_device < 0) return fail(DASHB_ENODEV, "dashb_init() has not succeeded; no device, no evaluation");
     gcm_circuit g;
-    if (gcm_load(&g, path) != 0) return fail(DASHB_EIO, "cannot read DGCM file %s", path);
+    if (gcm_load(&g, path) != 0) return fail(DASHB_EIO, "cannot read DGCM file %s (missing, truncated or malformed)", path);
+    if (!gcm_sizes_ok(&g)) {
+        gcm_free(&g);
+        return fail(DASHB_EINVAL, "DGCM file %s: an array's size does not match its layer's parameters", path);
+    }
     int rc = dashb_circuit_from_gcm(&g, out);
     gcm_free(&g);
     return rc;
+}
+
+int dashb_material_check(const char* path) {
+    if (!path) return fail(DASHB_EINVAL, "null argument");
+    gcm_circuit g;
+    if (gcm_load(&g, path) != 0) return fail(DASHB_EIO, "cannot read DGCM file %s (missing, truncated or malformed)", path);
+    const int ok = gcm_sizes_ok(&g);
+    gcm_free(&g);
+    if (!ok) return fail(DASHB_EINVAL, "DGCM file %s: an array's size does not match its layer's parameters", path);
+    return DASHB_OK;
 }
 
 void dashb_circuit_destroy(dashb_circuit* c) { delete c; }

@@ -871,7 +871,12 @@ int garble_decoding_info(Garbler& G) {
 }  // namespace
 
 /* downloads every device-resident array of the circuit and writes the file */
-static int save_material(Garbler& G, const char* path) {
+/* Writes the material.  With `secrets_path` the file at `path` is what the
+ * evaluating party may hold (tables, weights, bias / zero / shift labels)
+ * and everything that opens inputs or outputs -- the input base labels, the
+ * offset labels R_q and the decoding information -- goes to `secrets_path`
+ * alone (a DGCM file without layers). */
+static int save_material(Garbler& G, const char* path, const char* secrets_path) {
     gcm_circuit g = G.g;
     std::vector<gcm_layer> layers = G.glayers;
     std::vector<std::unique_ptr<std::vector<uint8_t>>> host;
@@ -886,13 +891,24 @@ static int save_material(Garbler& G, const char* path) {
         for (int a = 0; a < L.n_arrays; ++a) GRC(to_host(L.a[a]));
     for (int j = 0; j < g.k; ++j) GRC(to_host(g.dec[j]));
     g.layers = layers.data();
+    if (secrets_path) {
+        gcm_circuit pub = g;
+        pub.has_dec = 0;
+        pub.has_ginp = 0;
+        if (gcm_save(&pub, path) != 0) return report_error(DASHB_EIO, "garbler: cannot write %s", path);
+        gcm_circuit sec = g;
+        sec.n_layers = 0;
+        sec.layers = nullptr;
+        if (gcm_save(&sec, secrets_path) != 0) return report_error(DASHB_EIO, "garbler: cannot write %s", secrets_path);
+        return DASHB_OK;
+    }
     if (gcm_save(&g, path) != 0) return report_error(DASHB_EIO, "garbler: cannot write %s", path);
     return DASHB_OK;
 }
 
 static int garble_impl(const int32_t* crt_base, int k, const int32_t* mrs_base, int n_mrs, int max_modulus,
                        uint64_t input_size, const dashb_plain_layer* layers, int n_layers, const uint8_t seed[16],
-                       const char* path, dashb_circuit** circuit, dashb_garble_stats* stats) {
+                       const char* path, const char* secrets_path, dashb_circuit** circuit, dashb_garble_stats* stats) {
     const auto t_start = std::chrono::steady_clock::now();
     if (!crt_base || k < 1 || k > MAXK || n_mrs < 0 || n_mrs > MAXM || (n_mrs && !mrs_base) || !layers || n_layers < 1 || !seed ||
         (!path && !circuit) || input_size == 0)
@@ -1002,7 +1018,7 @@ static int garble_impl(const int32_t* crt_base, int k, const int32_t* mrs_base, 
     G.g.zero = G.keep(zero_all.data(), zero_all.size() * 2);
     G.g.upshift = G.keep(up_all.data(), up_all.size() * 2);
     G.g.n_layers = (int)G.glayers.size();
-    if (path) GRC(save_material(G, path));
+    if (path) GRC(save_material(G, path, secrets_path));
     if (circuit) {
         /* straight into an evaluator circuit: the tables are copied device to device */
         G.g.layers = G.glayers.data();
@@ -1019,12 +1035,20 @@ extern "C" int dashb_garble_to_file(const int32_t* crt_base, int k, const int32_
                                     uint64_t input_size, const dashb_plain_layer* layers, int n_layers, const uint8_t seed[16],
                                     const char* path, dashb_garble_stats* stats) {
     if (!path) return report_error(DASHB_EINVAL, "dashb_garble_to_file: no path");
-    return garble_impl(crt_base, k, mrs_base, n_mrs, max_modulus, input_size, layers, n_layers, seed, path, nullptr, stats);
+    return garble_impl(crt_base, k, mrs_base, n_mrs, max_modulus, input_size, layers, n_layers, seed, path, nullptr, nullptr, stats);
+}
+
+extern "C" int dashb_garble_to_files(const int32_t* crt_base, int k, const int32_t* mrs_base, int n_mrs, int max_modulus,
+                                     uint64_t input_size, const dashb_plain_layer* layers, int n_layers, const uint8_t seed[16],
+                                     const char* evaluator_path, const char* garbler_path, dashb_garble_stats* stats) {
+    if (!evaluator_path || !garbler_path) return report_error(DASHB_EINVAL, "dashb_garble_to_files: two paths are needed");
+    return garble_impl(crt_base, k, mrs_base, n_mrs, max_modulus, input_size, layers, n_layers, seed, evaluator_path, garbler_path,
+                       nullptr, stats);
 }
 
 extern "C" int dashb_garble_to_circuit(const int32_t* crt_base, int k, const int32_t* mrs_base, int n_mrs, int max_modulus,
                                        uint64_t input_size, const dashb_plain_layer* layers, int n_layers,
                                        const uint8_t seed[16], dashb_circuit** circuit, dashb_garble_stats* stats) {
     if (!circuit) return report_error(DASHB_EINVAL, "dashb_garble_to_circuit: no circuit pointer");
-    return garble_impl(crt_base, k, mrs_base, n_mrs, max_modulus, input_size, layers, n_layers, seed, nullptr, circuit, stats);
+    return garble_impl(crt_base, k, mrs_base, n_mrs, max_modulus, input_size, layers, n_layers, seed, nullptr, nullptr, circuit, stats);
 }

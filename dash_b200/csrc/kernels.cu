@@ -10,6 +10,7 @@
  */
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstring>
 
 #include "../../include/dash_b200.h"
@@ -369,9 +370,10 @@ __global__ void __launch_bounds__(LIN_THREADS, 8) k_linear(const __grid_constant
     /* groups of 8 rows that overlap [v0, v1) */
     const uint32_t vg_first = P.v0 / LIN_ROWS;
     const uint32_t nvg = (P.v1 + LIN_ROWS - 1) / LIN_ROWS - vg_first;
-    const uint32_t vg = vg_first + blockIdx.y % nvg;
+    const uint32_t by = P.y0 + blockIdx.y;
+    const uint32_t vg = vg_first + by % nvg;
     const uint32_t nr = min((uint32_t)LIN_ROWS, P.v1 - vg * LIN_ROWS); /* rows of this group that exist */
-    const uint32_t pix0 = (blockIdx.y / nvg) * LIN_PIXC;
+    const uint32_t pix0 = (by / nvg) * LIN_PIXC;
     const uint32_t pix1 = min(pix0 + LIN_PIXC, P.npix);
     const uint64_t rowlen = ncols;
     const bool active = col < ncols;
@@ -453,9 +455,17 @@ cudaError_t launch_linear(const LinearParams& p, cudaStream_t s) {
         const uint64_t qm = p.mod[j].q - 1;
         if ((uint64_t)p.K * qm * qm + qm > p.mod[j].lim) q.exact_mod = 0;
     }
-    dim3 grid((max_cols / 4 + LIN_THREADS - 1) / LIN_THREADS, ((p.npix + LIN_PIXC - 1) / LIN_PIXC) * nvg, p.k);
-    k_linear<<<grid, LIN_THREADS, 0, s>>>(q);
-    return cudaGetLastError();
+    /* (pixel group, row group) pairs sit on grid.y, which ends at 65535: a large
+     * convolution (222x222 outputs, 64 filters: 98 568 pairs) goes out as several launches */
+    const uint64_t ny = (uint64_t)((p.npix + LIN_PIXC - 1) / LIN_PIXC) * nvg;
+    for (uint64_t y0 = 0; y0 < ny; y0 += 65535) {
+        q.y0 = (uint32_t)y0;
+        dim3 grid((max_cols / 4 + LIN_THREADS - 1) / LIN_THREADS, (unsigned)std::min<uint64_t>(65535, ny - y0), p.k);
+        k_linear<<<grid, LIN_THREADS, 0, s>>>(q);
+        const cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
 }
 
 /* Compressed wire form: a label crosses PCIe as the 16

@@ -38,6 +38,7 @@ struct LinearParams {
     uint32_t Bp;
     int k;
     int exact_mod;             /* set by launch_linear: sums stay within the reciprocal's exact range */
+    uint32_t y0;               /* set by launch_linear: first (pixel group, row group) index of this launch */
 };
 
 /* tcgen05 dense path (dense_tc.cu).  A tensor map is CUtensorMap's 128 opaque

@@ -55,24 +55,45 @@ def _stats(st):
     return {f: getattr(st, f) for f, _ in GarbleStats._fields_}
 
 
-def garble_to_file(crt, mrs, input_size, layers, path, seed=b"dash-b200-garble", max_modulus=0):
+def _seed16(seed):
+    """The PRF key of a garbling.  None = 16 fresh random bytes from the OS
+    (every label, the offsets R_q included, derives from it, so a deployment
+    must never reuse or publish it); tests and benchmarks that need
+    reproducible material pass their own constant."""
+    if seed is None:
+        return os.urandom(16)
+    return (bytes(seed) + b"\0" * 16)[:16]
+
+
+def garble_to_file(crt, mrs, input_size, layers, path, seed=None, max_modulus=0, secrets_path=None):
     """Garbles `layers` on the current device and writes the DGCM material to
-    `path`.  Returns the statistics as a dict."""
+    `path`.  With `secrets_path` the input encoding (base labels, offsets R_q)
+    and the decoding information go to that second, garbler-only file and
+    `path` holds only what the evaluating party may see; without it one file
+    holds everything (single-party tests and benchmarks).  Returns the
+    statistics as a dict."""
     L = api.lib()
-    L.dashb_garble_to_file.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_int,
-                                       C.c_char_p, C.c_char_p, C.c_void_p]
     arr, keep = _marshal(layers)
     crt_a = np.ascontiguousarray(crt, dtype=np.int32)
     mrs_a = np.ascontiguousarray(mrs if len(mrs) else [0], dtype=np.int32)
-    seed = (bytes(seed) + b"\0" * 16)[:16]
+    seed = _seed16(seed)
     st = GarbleStats()
-    api._check(L.dashb_garble_to_file(crt_a.ctypes.data, len(crt), mrs_a.ctypes.data, len(mrs), int(max_modulus),
-                                      int(input_size), C.byref(arr), len(layers), seed, os.fsencode(path), C.byref(st)))
+    if secrets_path is None:
+        L.dashb_garble_to_file.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_int,
+                                           C.c_char_p, C.c_char_p, C.c_void_p]
+        api._check(L.dashb_garble_to_file(crt_a.ctypes.data, len(crt), mrs_a.ctypes.data, len(mrs), int(max_modulus),
+                                          int(input_size), C.byref(arr), len(layers), seed, os.fsencode(path), C.byref(st)))
+    else:
+        L.dashb_garble_to_files.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_int,
+                                            C.c_char_p, C.c_char_p, C.c_char_p, C.c_void_p]
+        api._check(L.dashb_garble_to_files(crt_a.ctypes.data, len(crt), mrs_a.ctypes.data, len(mrs), int(max_modulus),
+                                           int(input_size), C.byref(arr), len(layers), seed, os.fsencode(path),
+                                           os.fsencode(secrets_path), C.byref(st)))
     del keep
     return _stats(st)
 
 
-def garble_to_circuit(crt, mrs, input_size, layers, max_batch, seed=b"dash-b200-garble", max_modulus=0):
+def garble_to_circuit(crt, mrs, input_size, layers, max_batch, seed=None, max_modulus=0):
     """Garbles `layers` straight into an evaluator circuit on the current
     device (the tables never leave the GPU).  Returns (api.Circuit, stats)."""
     L = api.lib()
@@ -81,7 +102,7 @@ def garble_to_circuit(crt, mrs, input_size, layers, max_batch, seed=b"dash-b200-
     arr, keep = _marshal(layers)
     crt_a = np.ascontiguousarray(crt, dtype=np.int32)
     mrs_a = np.ascontiguousarray(mrs if len(mrs) else [0], dtype=np.int32)
-    seed = (bytes(seed) + b"\0" * 16)[:16]
+    seed = _seed16(seed)
     st = GarbleStats()
     h = C.c_void_p()
     api._check(L.dashb_garble_to_circuit(crt_a.ctypes.data, len(crt), mrs_a.ctypes.data, len(mrs), int(max_modulus),

@@ -19,6 +19,19 @@
  * garbling/label_tensor.h:238-246): for CRT modulus j a host buffer of
  * int16 `[batch][label][nc(p_j)]`, digit 0 = colour, digits in [0, p_j).
  * nc(q) = floor(128 / log2 q) (label_tensor.h:1353-1357).
+ * The batch dimension and security.  A batch evaluates ONE garbled circuit
+ * (one set of tables, one set of wire labels) on several inputs.  The
+ * reference has no batch: one garbling serves one inference, and that is
+ * what the scheme's security needs -- an evaluator who sees two labels of the
+ * same wire learns (x - x') * R_q and from it the global offset labels.
+ * Batching several inputs through one circuit is therefore only sound for
+ * testing and benchmarking, or when all inputs of the batch come from one
+ * party that accepts them being linked; independent private inferences each
+ * need their own garbling (dashb_garble_to_circuit makes one in milliseconds)
+ * and their own circuit object.  Throughput numbers quoted for a shared-table
+ * batch are an upper bound for that deployment: the kernels do the same work
+ * per inference, but the tables then stream from HBM instead of staying in L2.
+ *
  * Ciphertext tables are arrays of 16-byte little-endian unsigned integers
  * (`__uint128_t` in the reference) in exactly the order the reference's
  * garbler fills them; the per-operator comments give that order.
@@ -292,6 +305,8 @@ uint64_t dashb_input_size(const dashb_circuit* c);
 uint64_t dashb_output_size(const dashb_circuit* c);
 int dashb_num_layers(const dashb_circuit* c);
 int dashb_crt_base_size(const dashb_circuit* c);
+/* CRT modulus j (= modulus j of the circuit's input labels). */
+int dashb_crt_modulus(const dashb_circuit* c, int j);
 /* Modulus j of the circuit's output labels. */
 int dashb_output_modulus(const dashb_circuit* c, int j);
 /* Kernel launches issued by the last dashb_evaluate_device. */
@@ -320,6 +335,12 @@ int dashb_layer_type(const dashb_circuit* c, int layer);
  *      a garbled circuit only in process memory; format in
  *      include/dash_gcm_format.h) ---------------------------------------- */
 int dashb_circuit_load(dashb_circuit** out, const char* path);
+/* Parses a DGCM file on the host and checks every array's byte count against
+ * what its layer's parameters imply (what dashb_circuit_load does before it
+ * touches the device): DASHB_OK, DASHB_EIO (unreadable, truncated, a record
+ * twice, a length that leaves the file) or DASHB_EINVAL (size mismatch).
+ * Needs no device. */
+int dashb_material_check(const char* path);
 
 void dashb_circuit_destroy(dashb_circuit* c);
 

@@ -60,7 +60,10 @@ typedef struct dashb_garble_stats {
 
 /*
  * Garbles the circuit and writes the material, the decoding information and
- * the input encoding (GINB/GINO sections) to `path`.  max_modulus is raised
+ * the input encoding (GINB/GINO sections) to `path`.  `seed` is the AES key of
+ * the PRF every label (the offsets R_q included) is drawn from: it must be
+ * secret, fresh randomness in a deployment; a constant is for reproducible
+ * tests only.  max_modulus is raised
  * to the smallest value that covers every modulus the gadgets use (as the
  * reference's constructors do, garbled_circuit_interface.h:128-135).  Needs
  * dashb_init() on the current device.  Returns DASHB_OK or a DASHB_E* code
@@ -69,6 +72,20 @@ typedef struct dashb_garble_stats {
 int dashb_garble_to_file(const int32_t* crt_base, int k, const int32_t* mrs_base, int n_mrs, int max_modulus,
                          uint64_t input_size, const dashb_plain_layer* layers, int n_layers, const uint8_t seed[16],
                          const char* path, dashb_garble_stats* stats);
+
+/*
+ * Same garbling, written as two files: `evaluator_path` holds what the
+ * evaluating party needs and nothing else (tables, weights, the bias / zero /
+ * shift labels); `garbler_path` holds what must stay with the garbler -- the
+ * input base labels, the offset labels R_q (GINB/GINO sections) and the
+ * decoding information -- as a DGCM file without layers.  Whoever holds the
+ * second file can open every input and output label; the single-file form
+ * above is for tests, benchmarks and single-party use only.  No counterpart
+ * in the reference (it never serialises a circuit).
+ */
+int dashb_garble_to_files(const int32_t* crt_base, int k, const int32_t* mrs_base, int n_mrs, int max_modulus,
+                          uint64_t input_size, const dashb_plain_layer* layers, int n_layers, const uint8_t seed[16],
+                          const char* evaluator_path, const char* garbler_path, dashb_garble_stats* stats);
 
 /*
  * Same, straight into an evaluator circuit on the current device: the

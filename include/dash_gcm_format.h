@@ -152,10 +152,17 @@ static inline int gcm_save(const gcm_circuit* c, const char* path) {
     return rc;
 }
 
-static inline int gcm__rd(FILE* f, uint32_t* tag, uint32_t* aux, void** p, uint64_t* n) {
-    if (fread(tag, 4, 1, f) != 1 || fread(aux, 4, 1, f) != 1 || fread(n, 8, 1, f) != 1) return -1;
-    uint64_t padded = (*n + 15) & ~(uint64_t)15;
+/* Reads one record.  `left` = bytes of the file after the record header that
+ * is about to be read; a length that does not fit (or whose padded size
+ * wraps) is rejected before anything is allocated. */
+static inline int gcm__rd(FILE* f, uint64_t* left, uint32_t* tag, uint32_t* aux, void** p, uint64_t* n) {
     *p = NULL;
+    if (*left < 16) return -1;
+    if (fread(tag, 4, 1, f) != 1 || fread(aux, 4, 1, f) != 1 || fread(n, 8, 1, f) != 1) return -1;
+    *left -= 16;
+    if (*n > ((uint64_t)1 << 40) || *n > *left) return -1;
+    const uint64_t padded = (*n + 15) & ~(uint64_t)15;
+    if (padded < *n || padded > *left) return -1;
     if (padded) {
         *p = malloc(padded);
         if (!*p) return -1;
@@ -164,6 +171,7 @@ static inline int gcm__rd(FILE* f, uint32_t* tag, uint32_t* aux, void** p, uint6
             *p = NULL;
             return -1;
         }
+        *left -= padded;
     }
     return 0;
 }
@@ -196,16 +204,28 @@ static inline int gcm_load(gcm_circuit* c, const char* path) {
         return -1;
     }
     c->owns_data = 1;
-    int cur = -1, rc = 0, done = 0;
+    uint64_t left = 0;
+    if (fseek(f, 0, SEEK_END) == 0) {
+        const long end = ftell(f);
+        if (end >= 8 && fseek(f, 8, SEEK_SET) == 0) left = (uint64_t)end - 8;
+    }
+    int cur = -1, rc = 0, done = 0, seen_head = 0;
     while (!rc && !done) {
         uint32_t tag, aux;
         uint64_t n;
         void* p;
-        if (gcm__rd(f, &tag, &aux, &p, &n)) {
+        if (gcm__rd(f, &left, &tag, &aux, &p, &n)) {
+            rc = -1;
+            break;
+        }
+        /* every record but the header needs the header first; nothing may come twice */
+        if ((tag != GCM_TAG_HEAD) != (seen_head != 0)) {
+            free(p);
             rc = -1;
             break;
         }
         if (tag == GCM_TAG_HEAD) {
+            seen_head = 1;
             if (n < (8 + 64) * 8) {
                 rc = -1;
                 free(p);
@@ -226,12 +246,15 @@ static inline int gcm_load(gcm_circuit* c, const char* path) {
                 if (!c->layers) rc = -1;
             }
             free(p);
-        } else if (tag == GCM_TAG_ZERO) {
-            c->zero.data = p;
-            c->zero.nbytes = n;
-        } else if (tag == GCM_TAG_UPSH) {
-            c->upshift.data = p;
-            c->upshift.nbytes = n;
+        } else if (tag == GCM_TAG_ZERO || tag == GCM_TAG_UPSH) {
+            gcm_array* a = tag == GCM_TAG_ZERO ? &c->zero : &c->upshift;
+            if (a->data) {
+                rc = -1;
+                free(p);
+            } else {
+                a->data = p;
+                a->nbytes = n;
+            }
         } else if (tag == GCM_TAG_LAYR) {
             ++cur;
             if (!c->layers || cur >= c->n_layers || n != sizeof(c->layers[0].p) || aux > GCM_MAX_ARRAYS) rc = -1;
@@ -241,7 +264,8 @@ static inline int gcm_load(gcm_circuit* c, const char* path) {
             }
             free(p);
         } else if (tag == GCM_TAG_ARRY) {
-            if (cur < 0 || cur >= c->n_layers || (int)aux >= c->layers[cur].n_arrays) {
+            if (cur < 0 || cur >= c->n_layers || (int)aux >= c->layers[cur].n_arrays || c->layers[cur].a[aux].data ||
+                c->layers[cur].a[aux].nbytes) {
                 rc = -1;
                 free(p);
             } else {
@@ -249,7 +273,7 @@ static inline int gcm_load(gcm_circuit* c, const char* path) {
                 c->layers[cur].a[aux].nbytes = n;
             }
         } else if (tag == GCM_TAG_DECI) {
-            if (aux >= 32) {
+            if (aux >= 32 || c->dec[aux].data) {
                 rc = -1;
                 free(p);
             } else {
@@ -257,11 +281,11 @@ static inline int gcm_load(gcm_circuit* c, const char* path) {
                 c->dec[aux].nbytes = n;
             }
         } else if (tag == GCM_TAG_GINB || tag == GCM_TAG_GINO) {
-            if (aux >= 32) {
+            gcm_array* a = aux < 32 ? (tag == GCM_TAG_GINB ? &c->in_base[aux] : &c->in_offset[aux]) : NULL;
+            if (!a || a->data) {
                 rc = -1;
                 free(p);
             } else {
-                gcm_array* a = tag == GCM_TAG_GINB ? &c->in_base[aux] : &c->in_offset[aux];
                 a->data = p;
                 a->nbytes = n;
                 c->has_ginp = 1;

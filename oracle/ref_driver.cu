@@ -57,6 +57,8 @@ crt_val_t proj_identity(crt_val_t x, void*) { return x; }
 crt_val_t proj_plus_one(crt_val_t x, void*) { return x + 1; }
 crt_val_t proj_times_two(crt_val_t x, void*) { return 2 * x; }
 crt_val_t proj_half(crt_val_t x, void*) { return x / 2; }
+crt_val_t proj_half_minus_ten(crt_val_t x, void*) { return x / 2 - 10; } /* test_projection.h:15 */
+crt_val_t proj_quarter(crt_val_t x, void*) { return x / 4; }             /* test_projection.h:16 */
 
 struct RefHandle {
     std::vector<Layer*> layers;  // owned by circuit once built
@@ -117,6 +119,28 @@ int ref_load_onnx(void* hv, const char* path, int q_method, float q_const, int q
     return (int)layers.size();
 }
 
+/* Plaintext layer introspection for the ONNX-reader test (what
+ * dash/test/test_onnx_modelloader.h:10-43 asserts on): kind of plaintext
+ * layer `layer` (Layer::LayerType as int), dims of the circuit input, and the
+ * float weights / biases of a Dense layer as the loader stored them. */
+int ref_plain_num_layers(void* hv) { return (int)static_cast<RefHandle*>(hv)->layers.size(); }
+int ref_plain_layer_type(void* hv, int layer) { return (int)static_cast<RefHandle*>(hv)->layers.at(layer)->get_type(); }
+int ref_plain_layer_dims(void* hv, int layer, int output, uint64_t* dims, int cap) {
+    auto* l = static_cast<RefHandle*>(hv)->layers.at(layer);
+    dim_t d = output ? l->get_output_dims() : l->get_input_dims();
+    for (int i = 0; i < cap && i < (int)d.size(); ++i) dims[i] = d[i];
+    return (int)d.size();
+}
+/* which: 0 weights, 1 biases; returns the element count (copies at most cap floats) */
+long ref_plain_dense_floats(void* hv, int layer, int which, float* out, long cap) {
+    auto* d = dynamic_cast<Dense*>(static_cast<RefHandle*>(hv)->layers.at(layer));
+    if (!d) return -1;
+    auto& t = which ? d->get_biases() : d->get_weights();
+    const long n = (long)t.size();
+    for (long i = 0; i < n && i < cap; ++i) out[i] = (float)t.data()[i];
+    return n;
+}
+
 int ref_add_flatten(void* hv, uint64_t d0, uint64_t d1, uint64_t d2) {
     auto* h = static_cast<RefHandle*>(hv);
     h->layers.push_back(new Flatten(dim_t{d0, d1, d2}));
@@ -169,11 +193,16 @@ int ref_add_rescale(void* hv, const int* factors, int nf, uint64_t d0, uint64_t 
     static_cast<RefHandle*>(hv)->layers.push_back(new Rescale(s, dims3(d0, d1, d2)));
     return 0;
 }
-/* func: 0 identity, 1 x+1, 2 2x, 3 x/2 (cf. dash/test/test_projection.h) */
+/* func: 0 identity, 1 x+1, 2 2x, 3 x/2, 4 x/2-10, 5 x/4 (cf. dash/test/test_projection.h:14-16) */
 int ref_add_projection(void* hv, uint64_t n, const int* in_mod, const int* out_mod, int k, int func) {
     std::vector<crt_val_t> im(in_mod, in_mod + k), om(out_mod, out_mod + k);
     crt_val_t (*f)(crt_val_t, void*) =
-        func == 0 ? proj_identity : (func == 1 ? proj_plus_one : (func == 2 ? proj_times_two : proj_half));
+        func == 0   ? proj_identity
+        : func == 1 ? proj_plus_one
+        : func == 2 ? proj_times_two
+        : func == 3 ? proj_half
+        : func == 4 ? proj_half_minus_ten
+                    : proj_quarter;
     static_cast<RefHandle*>(hv)->layers.push_back(new Projection(dim_t{n}, im, om, f));
     return 0;
 }

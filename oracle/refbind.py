@@ -56,6 +56,11 @@ def lib():
         L.ref_plain_q_eval.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.ref_compress_hash.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ref_decompress.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+        L.ref_plain_num_layers.argtypes = [C.c_void_p]
+        L.ref_plain_layer_type.argtypes = [C.c_void_p, C.c_int]
+        L.ref_plain_layer_dims.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        L.ref_plain_dense_floats.restype = C.c_long
+        L.ref_plain_dense_floats.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_long]
         _lib = L
     return _lib
 
@@ -103,6 +108,20 @@ class RefCircuit:
         if n < 0:
             raise RuntimeError("ref_load_onnx: " + self.L.ref_error(self.h).decode())
         return n
+
+    def plain_layer_dims(self, layer, output=False):
+        d = np.zeros(8, dtype=np.uint64)
+        n = self.L.ref_plain_layer_dims(self.h, layer, int(output), d.ctypes.data, 8)
+        return [int(x) for x in d[:n]]
+
+    def plain_dense_floats(self, layer, biases=False):
+        """float32 weights (or biases) of plaintext Dense layer `layer`, as stored by the loader."""
+        n = self.L.ref_plain_dense_floats(self.h, layer, int(biases), None, 0)
+        if n < 0:
+            raise RuntimeError("plaintext layer %d is not a Dense layer" % layer)
+        out = np.zeros(n, dtype=np.float32)
+        self.L.ref_plain_dense_floats(self.h, layer, int(biases), out.ctypes.data, n)
+        return out
 
     def add_flatten(self, dims):
         self._chk(self.L.ref_add_flatten(self.h, *self._d3(dims)))

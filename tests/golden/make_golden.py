@@ -21,7 +21,7 @@ import workloads as W  # noqa: E402
 from oracle import refbind as R  # noqa: E402
 
 GOLDEN = ["SIGN_TINY", "RELU_99", "RESCALE_LEGACY", "RESCALE_2", "RESCALE_2_3", "RESCALE_OPT", "PROJECTION",
-          "MLP_TINY", "CONV_UNIT", "RELU_EDGE"]
+          "MLP_TINY", "CONV_UNIT", "RELU_EDGE", "PROJ_UP_BACK", "PROJ_DOWN_BACK", "PROJ_2X2"]
 
 # extra unit circuits only used as fixtures
 W.MODELS["CONV_UNIT"] = dict(  # stride 2, two channels, three filters (cf. test_conv2d.h:133-261)
@@ -31,6 +31,17 @@ W.MODELS["RELU_EDGE"] = dict(  # test_relu.h:144-225: crt {2,3,5}, mrs {26,6,3,2
     input=(14, 1, 1), layers=[("flatten",), ("relu",)], quant=("simple", 1.0), crt=[2, 3, 5], mrs=[26, 6, 3, 2],
     max_modulus=0)
 
+# dash/test/test_projection.h:18-188, the three circuits with the test's own functions
+W.MODELS["PROJ_UP_BACK"] = dict(   # :18-50  19 -x*2-> 91 -x/2-10-> 19, max_modulus 100; 15 -> 5
+    input=(1, 1, 1), layers=[("flatten",), ("projection", [19], [91], 2), ("projection", [91], [19], 4)],
+    quant=("simple", 1.0), crt=[19], mrs=[], max_modulus=100)
+W.MODELS["PROJ_DOWN_BACK"] = dict(  # :52-83  19 -x/4-> 10 -x*2-> 19; 12 -> 6
+    input=(1, 1, 1), layers=[("flatten",), ("projection", [19], [10], 5), ("projection", [10], [19], 2)],
+    quant=("simple", 1.0), crt=[19], mrs=[], max_modulus=0)
+W.MODELS["PROJ_2X2"] = dict(        # :85-120 one projection x*2 over a 2x2 tensor; {3,2,1,-1} -> {6,4,2,-2}
+    input=(2, 2, 1), layers=[("flatten",), ("projection", [19], [19], 2)],
+    quant=("simple", 1.0), crt=[19], mrs=[], max_modulus=100)
+
 BATCH = 3
 
 
@@ -39,6 +50,12 @@ def inputs_for(name, spec, n):
         P = 30  # 0, +-1, +-mid, +-extremes of the signed range (-P/2, P/2)
         row = np.array([0, 1, -1, 7, -7, 14, -14, 2, -2, 13, -13, 5, -5, 3], dtype=np.int64)
         return np.stack([row, -row, np.roll(row, 3)])[:, :n]
+    if name == "PROJ_UP_BACK":   # first row = the reference test's input
+        return np.array([[15], [4], [9]], dtype=np.int64)
+    if name == "PROJ_DOWN_BACK":
+        return np.array([[12], [8], [17]], dtype=np.int64)
+    if name == "PROJ_2X2":
+        return np.array([[3, 2, 1, -1], [0, 4, -4, 9], [-9, 7, -2, 5]], dtype=np.int64)
     if name in ("RESCALE_LEGACY", "RESCALE_2", "RESCALE_2_3"):
         rng = np.random.default_rng(3)
         return rng.integers(-1000, 1000, size=(BATCH, n), dtype=np.int64)
@@ -46,7 +63,10 @@ def inputs_for(name, spec, n):
 
 
 def main():
+    regenerate_all = "--all" in sys.argv
     for name in GOLDEN:
+        if not regenerate_all and os.path.exists(os.path.join(HERE, name + ".npz")):
+            continue  # existing fixtures stay byte-identical; pass --all to regenerate everything
         spec = W.MODELS[name]
         c = W.build_reference_circuit(spec, seed=1234, weight_seed=7)
         c.export(os.path.join(HERE, name + ".gcm"))

@@ -54,3 +54,70 @@ def test_plain_circuit_recovers_layers_and_bias_residues(tmp_path):
             lab = np.frombuffer(L["arrays"][1 + j], dtype=np.int16).reshape(-1, nc)
             z0 = int(gcm.zero_label(g, q)[0])
             assert np.array_equal((l["biases"] % q + z0) % q, lab[:, 0])
+
+
+def test_malformed_material_files_are_rejected(tmp_path):
+    """A truncated, inconsistent or hostile DGCM file must be refused by the
+    loader before any pointer reaches dashb_add_* (dashb_material_check is the
+    host half of dashb_circuit_load)."""
+    import ctypes as C
+    import struct
+
+    from dash_b200 import api
+    from helpers import GOLDEN_DIR
+
+    L = api.lib()
+    L.dashb_material_check.argtypes = [C.c_char_p]
+    import os
+
+    for name in ("MLP_TINY", "RESCALE_2_3", "RESCALE_LEGACY", "PROJECTION", "SIGN_TINY", "CONV_UNIT"):
+        assert L.dashb_material_check(os.path.join(GOLDEN_DIR, name + ".gcm").encode()) == 0, name
+    good = open(os.path.join(GOLDEN_DIR, "MLP_TINY.gcm"), "rb").read()
+
+    def check(blob):
+        p = str(tmp_path / "bad.gcm")
+        open(p, "wb").write(blob)
+        return L.dashb_material_check(p.encode())
+
+    assert check(good) == 0
+    assert check(good[: len(good) // 2]) == -5           # truncated
+    assert check(good[:8] + good[8:8 + 16 + 72 * 8] * 2 + good[8 + 16 + 72 * 8:]) == -5   # HEAD twice
+    # records: tag(4) aux(4) n(8) payload padded to 16
+    recs, pos = [], 8
+    while pos < len(good):
+        tag, aux, n = struct.unpack_from("<4sIQ", good, pos)
+        size = 16 + ((n + 15) & ~15)
+        recs.append((tag, pos, n, size))
+        pos += size
+    arr = [r for r in recs if r[0] == b"ARRY"]
+    tag, pos, n, size = arr[1]                            # first bias array of the first dense layer
+    # length near 2^64: padded size wraps to 0
+    assert check(good[:pos + 8] + struct.pack("<Q", 2**64 - 3) + good[pos + 16:]) == -5
+    # an array 16 bytes shorter than its layer implies
+    short = good[:pos + 8] + struct.pack("<Q", n - 16) + good[pos + 16:pos + size - 16] + good[pos + size:]
+    assert check(short) == -1
+    # the same array twice
+    assert check(good[:pos + size] + good[pos:pos + size] + good[pos + size:]) == -5
+    # a dense layer whose K does not match the labels arriving
+    lay = [r for r in recs if r[0] == b"LAYR"][0]
+    p2 = bytearray(good)
+    struct.pack_into("<q", p2, lay[1] + 16 + 2 * 8, 17)  # p[2] = K
+    assert check(bytes(p2)) == -1
+
+
+def test_wrong_digit_count_is_rejected_before_the_library_reads():
+    """Circuit._in_arrays checks the last dimension against nc(q): a wrong nc
+    would make the library read past the host buffer."""
+    from dash_b200 import api
+
+    class Fake(api.Circuit):
+        def __init__(self):
+            self.k, self.input_size, self.in_moduli = 2, 3, [3, 5]
+
+    f = Fake()
+    f.h = None
+    ok = [np.zeros((4, 3, api.nr_comps(3)), dtype=np.int16), np.zeros((4, 3, api.nr_comps(5)), dtype=np.int16)]
+    assert f._in_arrays(ok)[1] == 4
+    bad = [ok[0], np.zeros((4, 3, api.nr_comps(5) - 1), dtype=np.int16)]
+    with pytest.raises(ValueError):
+        f._in_arrays(bad)

@@ -108,3 +108,33 @@ def test_malformed_model_is_rejected(tmp_path):
     open(path, "wb").write(blob[: len(blob) // 2])
     with pytest.raises(RuntimeError):
         R.RefCircuit().load_onnx(path)
+
+
+def test_reference_fixture_model_dense():
+    """dash/test/test_onnx_modelloader.h:10-43 restated: the reference's own
+    fixture (dash/test/fixtures/model_dense.onnx, committed unchanged as test
+    data under tests/golden/) read through integration/dash_onnx_lite.h gives
+    the input/output dims and the six float values the reference's
+    protobuf-based loader is tested for."""
+    import os
+
+    from helpers import GOLDEN_DIR
+    from oracle import refbind as R
+
+    if not R.available():
+        pytest.skip("oracle/_ref not built")
+    c = R.RefCircuit()
+    n = c.load_onnx(os.path.join(GOLDEN_DIR, "model_dense.onnx"), 0, 10.0, -1)  # SimpleQuant, q_const 10
+    assert n == 2                                    # Flatten + Dense
+    assert c.plain_layer_dims(0) == [28, 28, 1]
+    assert c.plain_layer_dims(1, output=True)[0] == 10
+    w = c.plain_dense_floats(1)
+    b = c.plain_dense_floats(1, biases=True)
+    assert w.shape == (7840,) and b.shape == (10,)
+    f32 = np.float32
+    assert w[0] == f32(-0.02056167833507061004638671875)
+    assert w[9] == f32(0.00375685538165271282196044921875)
+    assert w[-1] == f32(0.018187098205089569091796875)
+    assert b[0] == f32(-0.02799860946834087371826171875)
+    assert b[4] == f32(-0.0069468836300075054168701171875)
+    assert b[-1] == f32(-0.02649968676269054412841796875)

@@ -13,7 +13,8 @@ between in a fixed 8 MiB array inside its own image.
 Checked here, through the C ABI, on two calls in a row (the second one reuses
 the array the first one dirtied, with another batch size): the output labels
 equal, digit for digit, those of the allocating path (Circuit.load +
-dashb_layer_outputs) on the same inputs and tables.
+dashb_layer_outputs) on the same inputs and tables, and the labels the
+reference itself computed for that layer (the golden fixture).
 """
 import ctypes as C
 
@@ -62,6 +63,11 @@ def test_projection_static_matches_allocating_path_twice(gpu):
         got = _static_call(api, torch, labels[0], arrays[0], n, q_in, q_out)
         assert got.shape == want.shape
         assert np.array_equal(got, want), "static-scratch projection differs from the allocating path (batch %d)" % batch
+        # and directly against the reference's own labels for this layer
+        ref_want = tile_batch(g.layers[0], batch)[0]
+        if batch == 37:
+            ref_want = ref_want[::-1]
+        assert np.array_equal(got, ref_want), "static-scratch projection differs from the reference's labels (batch %d)" % batch
     circ.close()
 
 

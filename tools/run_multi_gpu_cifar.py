@@ -40,7 +40,7 @@ def main():
     plain, input_size = W.plain_layers(spec)
     path = "/tmp/mg_%s_%d.gcm" % (model, rank)
     t0 = time.time()
-    st = garble.garble_to_file(spec["crt"], spec.get("mrs", []), input_size, plain, path)
+    st = garble.garble_to_file(spec["crt"], spec.get("mrs", []), input_size, plain, path, seed=b"multi-gpu-cifar")  # every rank: same seed, same circuit
     garble_s = time.time() - t0
     g = gcm.read_gcm(path) if (rank == 0 or mode == "channel") else None
     X = W.synthetic_inputs(spec, B, seed=100 + (rank if mode == "batch" else 0))

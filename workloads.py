@@ -138,11 +138,14 @@ def build_reference_circuit(spec, seed=42, weight_seed=42):
         if kind == "flatten":
             c.add_flatten([w, h, ch])
             flat = w * h * ch
-        elif kind == "dense":
+        elif kind in ("dense", "dense_tf"):
             out = layer[1]
             assert flat is not None, "dense needs a flatten first"
             bound = np.sqrt(1.0 / flat)
-            c.add_dense(_uniform(rng, bound, (out, flat)), _uniform(rng, bound, (out,)), q_method, q_const, q_param)
+            # dense_tf: the tf2onnx channel-last input permutation (Dense::get_channel_tf, label_tensor.h:820-858),
+            # channel count = filters of the convolution in front of the flatten
+            c.add_dense(_uniform(rng, bound, (out, flat)), _uniform(rng, bound, (out,)), q_method, q_const, q_param,
+                        ch if kind == "dense_tf" else 0)
             flat = out
             if qname == "scale":
                 c.add_rescale_legacy(q_param, [flat])
