@@ -78,6 +78,8 @@ def lib():
         L.dashb_hostcheck_digits_frac.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
         L.dashb_hostcheck_frac_sweep.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_void_p]
         L.dashb_hostcheck_hash.argtypes = [C.c_void_p, C.c_void_p]
+        L.dashb_hostcheck_ladder_sweep.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_void_p]
+        L.dashb_hostcheck_compress_words.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -320,6 +322,24 @@ def hostcheck_frac_sweep(q_lo, q_hi, samples, seed=1):
     n = C.c_int(0)
     bad = lib().dashb_hostcheck_frac_sweep(int(q_lo), int(q_hi), int(samples), int(seed), C.byref(n))
     return bad, n.value
+
+
+def hostcheck_ladder_sweep(q_lo, q_hi, samples, seed=1, aligned=False):
+    """Same sweep through the width-ladder walk the sign kernel uses, for plain
+    or word-aligned plans: (moduli that differ or whose plan bookkeeping is
+    inconsistent, moduli with a plan)."""
+    n = C.c_int(0)
+    bad = lib().dashb_hostcheck_ladder_sweep(int(q_lo), int(q_hi), int(samples), int(seed), int(bool(aligned)), C.byref(n))
+    return bad, n.value
+
+
+def hostcheck_compress_words(q, digits):
+    """Word-wise compress of a u8 digit-plane label (gc::WordCompressor); None for q = 256."""
+    d = np.ascontiguousarray(digits, dtype=np.int16)
+    o = np.zeros(2, dtype=np.uint64)
+    if not lib().dashb_hostcheck_compress_words(int(q), d.ctypes.data, o.ctypes.data):
+        return None
+    return int(o[0]) | (int(o[1]) << 64)
 
 
 def hostcheck_colour(q, x):

@@ -97,6 +97,19 @@ ModInfo make_modinfo(uint32_t q) {
         m.limbs |= (l - 1) << (2 * c);
         bound /= Q;
     }
+    /* word-wise compression: whole words of four digits per chunk, q^(4 cw) < 2^32 */
+    if ((uint64_t)q * q * q * q <= 0xffffffffull) {
+        m.q4 = q * q * q * q;
+        uint64_t pw = m.q4;
+        m.cw = 1;
+        while (pw * m.q4 <= 0xffffffffull) {
+            pw *= m.q4;
+            ++m.cw;
+        }
+        m.Qw = (uint32_t)pw;
+        const uint32_t nw = (m.nc + 3) / 4;
+        m.cwf = nw - ((nw - 1) / m.cw) * m.cw;
+    }
     return m;
 }
 
@@ -140,10 +153,19 @@ struct Big {
 };
 }  // namespace
 
-gc::FracInfo make_fracinfo(const ModInfo& m) {
+/* aligned4: every stage but the first delivers a multiple of four digits and
+ * the first one nc mod 4 more than that, so that the stages' digit ranges
+ * start on the 32-bit words of a u8 digit plane (the half gates of k_sign
+ * write their output labels word by word). */
+gc::FracInfo make_fracinfo(const ModInfo& m, bool aligned4 = false) {
     gc::FracInfo fi;
     memset(&fi, 0, sizeof(fi));
-    const uint32_t q = m.q, nc = m.nc, t = m.t;
+    const uint32_t q = m.q, nc = m.nc;
+    uint32_t t = m.t;
+    if (aligned4) {
+        t &= ~3u;
+        if (t == 0) return fi;
+    }
     if (q < 2 || nc < 2) return fi;
     /* DASHB_NO_FRAC: no plans, every kernel takes its long-division path
      * (the one moduli with more than FRAC_MAXST chunks take; tests/
@@ -183,20 +205,28 @@ gc::FracInfo make_fracinfo(const ModInfo& m) {
         pa *= q;
         ++a;
     }
+    if (aligned4) { /* largest a' <= a with a' = nc (mod 4) */
+        const uint32_t want = nc & 3u;
+        while (a > 0 && (a & 3u) != want) {
+            pa /= q;
+            --a;
+        }
+    }
     if (a == 0 || a >= nc) return fi;
     const uint32_t rest = nc - a;
     const uint32_t nmid = rest / t, rl = rest % t;
     const uint32_t nst = 1 + nmid + (rl ? 1 : 0);
     if (nst < 2 || nst > (uint32_t)gc::FRAC_MAXST) return fi;
-    uint64_t plast = 1;
+    uint64_t plast = 1, qt = 1;
     for (uint32_t i = 0; i < (rl ? rl : t); ++i) plast *= q;
+    for (uint32_t i = 0; i < t; ++i) qt *= q;
     uint32_t lens[10];
     long double mults[10];
     lens[0] = a;
     mults[0] = (long double)(pa << sh);
     for (uint32_t s = 1; s < nst; ++s) {
         lens[s] = t;
-        mults[s] = (long double)m.Q;
+        mults[s] = (long double)qt;
     }
     lens[nst - 1] = rl ? rl : t;
     mults[nst - 1] = (long double)plast;
@@ -231,8 +261,10 @@ gc::FracInfo make_fracinfo(const ModInfo& m) {
         fi.addc = addc;
         fi.nst = nst;
         for (uint32_t s = 0; s < nst; ++s) {
-            fi.mult[s] = s == 0 ? (uint32_t)(pa << sh) : s == nst - 1 ? (uint32_t)plast : m.Q;
+            fi.mult[s] = (uint32_t)mults[s];
             fi.desc[s] = lens[s] | W[s] << 8;
+            fi.ladder += 1u << (4 * (W[s] - 1));
+            fi.words += (lens[s] + 1) / 2;
         }
         return fi;
     }
@@ -374,6 +406,7 @@ struct dashb_circuit {
     int mrs[MAXM];
     ModInfo crt_mi[MAXK], mrs_mi[MAXM], cast_mi[MAXM];
     gc::FracInfo crt_fi[MAXK], cast_fi[MAXM]; /* multiplicative digit extraction plans */
+    gc::FracInfo crt_fa[MAXK];                /* ... with word-aligned stages (half gates of k_sign) */
     uint64_t input_size{0};
     std::vector<std::vector<int16_t>> zero; /* by modulus-2 */
     DevMem d_zero[MAXK], d_up[MAXK];
@@ -499,7 +532,7 @@ void fill_sign_params(dashb_circuit* c, SignParams& p, uint64_t n, int n_out) {
     uint32_t S = 0, Mp = 0;
     for (int j = 0; j < c->k; ++j) {
         p.crt[j] = c->crt_mi[j];
-        p.crtf[j] = c->crt_fi[j];
+        p.crtf[j] = c->crt_fa[j];
         p.prefix[j] = S;
         S += (uint32_t)c->crt[j];
     }
@@ -593,6 +626,7 @@ int dashb_circuit_create(dashb_circuit** out, const int32_t* crt_base, int k, co
         c->crt[j] = crt_base[j];
         c->crt_mi[j] = make_modinfo((uint32_t)crt_base[j]);
         c->crt_fi[j] = make_fracinfo(c->crt_mi[j]);
+        c->crt_fa[j] = make_fracinfo(c->crt_mi[j], true);
         c->cur_q[j] = crt_base[j];
     }
     c->cur_size = input_size;
@@ -1928,6 +1962,101 @@ int dashb_hostcheck_frac_sweep(int q_lo, int q_hi, int samples, uint64_t seed, i
     }
     if (planned) *planned = np;
     return bad;
+}
+/* The ladder walk (gc::for_each_chunk_ladder) over plain (aligned = 0) or
+ * word-aligned (aligned = 1) plans against the division path, same payload
+ * set as dashb_hostcheck_frac_sweep; also checks the plan's bookkeeping
+ * (ladder counts, accumulator words, word alignment of the stages). */
+int dashb_hostcheck_ladder_sweep(int q_lo, int q_hi, int samples, uint64_t seed, int aligned, int* planned) {
+    int bad = 0, np = 0;
+    uint64_t st = seed * 0x9e3779b97f4a7c15ull + 1;
+    auto next = [&]() {
+        uint64_t z = (st += 0x9e3779b97f4a7c15ull);
+        z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+        z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+        return z ^ (z >> 31);
+    };
+    for (int q = q_lo; q <= q_hi; ++q) {
+        if (q < 2) continue;
+        const ModInfo m = make_modinfo((uint32_t)q);
+        const gc::FracInfo fi = make_fracinfo(m, aligned != 0);
+        if (fi.nst == 0) continue;
+        ++np;
+        bool differs = false;
+        /* bookkeeping */
+        uint32_t stages = 0, words = 0, digits = 0, lastW = 5;
+        for (int W = 1; W <= 5; ++W) stages += (fi.ladder >> (4 * (W - 1))) & 15u;
+        for (uint32_t s = 0; s < fi.nst; ++s) {
+            const uint32_t len = fi.desc[s] & 0xffu, W = fi.desc[s] >> 8;
+            if (W > lastW || W < 1) differs = true;
+            lastW = W;
+            words += (len + 1) / 2;
+            digits += len;
+            if (aligned && s > 0 && (len & 3u)) differs = true;
+        }
+        if (stages != fi.nst || words != fi.words || digits != m.nc) differs = true;
+        if (aligned && ((fi.desc[0] & 0xffu) & 3u) != (m.nc & 3u)) differs = true;
+        unsigned __int128 D = 1;
+        bool full = false;
+        for (uint32_t i = 0; i < m.nc; ++i) {
+            const unsigned __int128 nd = D * (unsigned)q;
+            if (nd / (unsigned)q != D) full = true;
+            D = nd;
+        }
+        auto check = [&](unsigned __int128 x) {
+            if (!full && x >= D) return;
+            uint32_t a[128] = {0}, b[128] = {0};
+            const gc::u128 v = gc::make_u128((uint64_t)x, (uint64_t)(x >> 64));
+            gc::for_each_digit(v, m, [&](uint32_t d, uint32_t dg) { a[d] = dg; });
+            uint32_t d0 = m.nc;
+            gc::for_each_chunk_ladder(v, fi, [&](uint32_t len, uint32_t r) {
+                d0 -= len;
+                for (uint32_t i = 0; i < len; ++i) {
+                    b[d0 + i] = r % m.q;
+                    r /= m.q;
+                }
+                if (r) differs = true;
+            });
+            if (d0 != 0) differs = true;
+            for (uint32_t d = 0; d < m.nc; ++d)
+                if (a[d] != b[d]) differs = true;
+        };
+        check(0);
+        check(1);
+        check(full ? ~(unsigned __int128)0 : D - 1);
+        check(full ? ~(unsigned __int128)0 - 1 : D - 2);
+        unsigned __int128 pw = 1;
+        for (uint32_t i = 0; i < m.nc; ++i) {
+            check(pw);
+            check(pw - 1);
+            pw *= (unsigned)q;
+        }
+        for (int t = 0; t < samples; ++t) {
+            unsigned __int128 x = ((unsigned __int128)next() << 64) | next();
+            if (!full) x %= D;
+            check(x);
+        }
+        if (differs) ++bad;
+    }
+    if (planned) *planned = np;
+    return bad;
+}
+/* gc::WordCompressor (word-wise compress of a u8 digit plane label) on the
+ * host: digits int16[nc] -> 128-bit value; returns 0 when the modulus has no
+ * word-wise form (q = 256). */
+int dashb_hostcheck_compress_words(int q, const int16_t* digits, uint64_t out2[2]) {
+    const ModInfo m = make_modinfo((uint32_t)q);
+    if (!m.cw) return 0;
+    const uint32_t nw = (m.nc + 3) / 4;
+    gc::WordCompressor c(m);
+    for (int w = (int)nw - 1; w >= 0; --w) {
+        uint32_t word = 0;
+        for (uint32_t i = 0; i < 4 && 4 * w + i < m.nc; ++i) word |= (uint32_t)(uint8_t)digits[4 * w + i] << (8 * i);
+        c.push(word);
+    }
+    out2[0] = c.value().lo;
+    out2[1] = c.value().hi;
+    return 1;
 }
 int dashb_hostcheck_colour(int q, const uint64_t in2[2]) {
     ModInfo m = make_modinfo((uint32_t)q);

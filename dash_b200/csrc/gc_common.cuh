@@ -103,6 +103,13 @@ struct ModInfo {
     uint32_t v;        /* floor((2^64 - 1) / dn) - 2^32 */
     uint32_t limbs;    /* 2 bits per chunk c: (significant 32-bit limbs before division c) - 1 */
     uint32_t pow2s;    /* 1 << s */
+    /* word-wise compression of u8 digit planes (four digits per 32-bit word):
+     * a chunk is cw whole words, Qw = q^(4 cw) < 2^32; cw = 0 (q^4 >= 2^32,
+     * i.e. q = 256) keeps the digit-wise Compressor */
+    uint32_t cw;       /* words per chunk */
+    uint32_t cwf;      /* words of the most significant chunk: ceil(nc/4) - (chunks - 1) cw, in 1..cw */
+    uint32_t q4;       /* q^4 */
+    uint32_t Qw;       /* q^(4 cw) */
 };
 
 /* r / q for r <= m.lim (true for every chunk value and its quotients). */
@@ -248,7 +255,9 @@ struct FracInfo {
     uint32_t nst;               /* stages (chunks); 0 = no plan, use for_each_digit */
     uint32_t mult[FRAC_MAXST];  /* stage s multiplies by q^len_s (stage 0: << sh) */
     uint32_t desc[FRAC_MAXST];  /* len_s | W_s << 8: digits of the chunk, limbs of the fraction the stage keeps (1..5) */
-    uint32_t pad[5];            /* 128 bytes: indexing an array of plans is a shift */
+    uint32_t ladder;            /* stages per width, 4 bits each: bits 4(W-1)..4(W-1)+3 = stages that keep W limbs */
+    uint32_t words;             /* sum over the stages of ceil(len_s / 2): accumulator words in stage-local pair layout */
+    uint32_t pad[3];            /* 128 bytes: indexing an array of plans is a shift */
 };
 
 GC_HD void frac_init(u128 x, const FracInfo& fi, uint32_t (&n)[5]) {
@@ -473,6 +482,33 @@ GC_HD void for_each_chunk_msb(u128 x, const ModInfo& m, const FracInfo& fi, F&& 
     }
 }
 
+/* The same walk with the stage width known at compile time: the stages of a
+ * plan keep 5, then 4, ... then 1 limbs (never more than the stage before), so
+ * five short loops -- one per width, trip counts from fi.ladder -- replace the
+ * per-stage width dispatch; every loop body is the multiply chain of its width
+ * plus one copy of f.  f(len, r): r holds the next `len` digits below those
+ * already delivered (most significant chunk first), r = sum_i digit_i q^i. */
+#if defined(__CUDA_ARCH__)
+#define GC_LADDER_STEP(W)                                                            \
+    _Pragma("unroll 1") for (uint32_t c = (cnt >> (4 * ((W)-1))) & 15u; c; --c, ++s) \
+        f(fi.desc[s] & 0xffu, frac_stage(n, fi.mult[s], (W)));
+#else
+#define GC_LADDER_STEP(W) \
+    for (uint32_t c = (cnt >> (4 * ((W)-1))) & 15u; c; --c, ++s) f(fi.desc[s] & 0xffu, frac_stage(n, fi.mult[s], (W)));
+#endif
+template <typename F>
+GC_HD void for_each_chunk_ladder(u128 x, const FracInfo& fi, F&& f) {
+    uint32_t n[5];
+    frac_init(x, fi, n);
+    const uint32_t cnt = fi.ladder;
+    uint32_t s = 0;
+    GC_LADDER_STEP(5)
+    GC_LADDER_STEP(4)
+    GC_LADDER_STEP(3)
+    GC_LADDER_STEP(2)
+    GC_LADDER_STEP(1)
+}
+
 /* Colour digit of a compressed label: x mod q, from the residues of the
  * limb weights 2^32, 2^64, 2^96 mod q (a dozen multiply-adds instead of a
  * four-limb long division).  The constants depend on the modulus only. */
@@ -513,6 +549,42 @@ struct Compressor {
             x = muladd_small(x, m.Q, chunk);
             chunk = 0;
             left = m.t;
+        }
+    }
+    GC_HD u128 value() const { return x; }
+};
+
+/*
+ * LabelTensor::compress for a label held as u8 digits, four to a 32-bit word
+ * (digit 4w+i in byte i of word w, padding digits zero): words are pushed
+ * from the most significant one down; a word's value b0 + q b1 + q^2 b2 +
+ * q^3 b3 is two byte dot products (dp4a) and one multiply-add, a chunk of cw
+ * words is folded into the 128-bit value at once.  Needs m.cw != 0.  Leading
+ * zero digits (the padding of the top word) do not change the value.
+ */
+GC_HD uint32_t dot4_u8(uint32_t a, uint32_t b) {
+#if defined(__CUDA_ARCH__)
+    return __dp4a(a, b, 0u);
+#else
+    return (a & 0xff) * (b & 0xff) + ((a >> 8) & 0xff) * ((b >> 8) & 0xff) + ((a >> 16) & 0xff) * ((b >> 16) & 0xff) +
+           (a >> 24) * (b >> 24);
+#endif
+}
+struct WordCompressor {
+    u128 x;
+    uint32_t chunk, left;
+    uint32_t pat, q2;
+    const ModInfo& m;
+    GC_HD explicit WordCompressor(const ModInfo& mi) : chunk(0), left(mi.cwf), pat(1u | (mi.q << 8)), q2(mi.q * mi.q), m(mi) {
+        x = make_u128(0, 0);
+    }
+    GC_HD void push(uint32_t word) {
+        const uint32_t v = dot4_u8(word, pat << 16) * q2 + dot4_u8(word, pat);
+        chunk = chunk * m.q4 + v;
+        if (--left == 0) {
+            x = muladd_small(x, m.Qw, chunk);
+            chunk = 0;
+            left = m.cw;
         }
     }
     GC_HD u128 value() const { return x; }

@@ -11,6 +11,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstddef>
 #include <cstring>
 
 #include "../../include/dash_b200.h"
@@ -128,6 +129,7 @@ __device__ __forceinline__ ModInfo pin(const ModInfo& src) {
     ModInfo m = src;
     asm volatile("" : "+r"(m.q), "+r"(m.nc), "+r"(m.t), "+r"(m.nchunks), "+r"(m.Q), "+r"(m.mq));
     asm volatile("" : "+r"(m.lim), "+r"(m.top_len), "+r"(m.s), "+r"(m.dn), "+r"(m.v), "+r"(m.limbs), "+r"(m.pow2s));
+    asm volatile("" : "+r"(m.cw), "+r"(m.cwf), "+r"(m.q4), "+r"(m.Qw));
     return m;
 }
 
@@ -203,14 +205,30 @@ __device__ __forceinline__ uint64_t plane_off(const ModInfo& m, uint64_t e, uint
  * are read two ahead of the Horner steps that consume them: a rolled loop
  * that used each word right after its load exposed the full memory latency
  * once per word (ncu: the largest long-scoreboard stall after the half gates'
- * re-reads). */
+ * re-reads).  A word's four digits enter the value at once
+ * (gc::WordCompressor: two dp4a + two multiply-adds per word instead of four
+ * Horner steps with their chunk bookkeeping). */
 __device__ __forceinline__ u128 load_compress(const uint8_t* plane, const ModInfo& m, uint64_t e, uint32_t b,
                                                uint32_t Bp, uint32_t& colour) {
     const uint8_t* p = plane + plane_off(m, e, b, Bp);
-    gc::Compressor c(m);
     const int top = (int)nc4_of(m) - 1;
     auto word = [&](int d4) { return d4 >= 0 ? *reinterpret_cast<const uint32_t*>(p + (uint64_t)d4 * 4 * Bp) : 0u; };
     uint32_t w = 0, n0 = word(top), n1 = word(top - 1);
+    if (m.cw) {
+        /* whatever a producer left in the padding bytes of the top word stays out */
+        n0 &= 0xffffffffu >> (8 * ((4u - (m.nc & 3u)) & 3u));
+        gc::WordCompressor c(m);
+#pragma unroll 1
+        for (int d4 = top; d4 >= 0; --d4) {
+            w = n0;
+            n0 = n1;
+            n1 = word(d4 - 2);
+            c.push(w);
+        }
+        colour = w & 0xff;
+        return c.value();
+    }
+    gc::Compressor c(m);
     uint32_t valid = m.nc - 4 * (uint32_t)top; /* digits in the top word */
 #pragma unroll 1
     for (int d4 = top; d4 >= 0; --d4) {
@@ -640,51 +658,49 @@ __device__ __noinline__ void accumulate(u128 x, const ModInfo m, uint32_t* acc) 
 }
 
 /* The same accumulation with the digits taken by multiplication, most
- * significant chunk first (gc::for_each_chunk_msb; labels of a correct
- * evaluation are always below q^nc).  Two digits cost two reciprocal
- * multiplies, two multiply-adds that also pack them (d0 + 2^16 d1 =
- * r + q1 (2^16 - q) - q2 (q 2^16)) and one shared-memory read-modify-write.
- * Inlined at its two call sites: the plan is read straight from the
- * kernel-parameter bank. */
+ * significant chunk first (gc::for_each_chunk_ladder; labels of a correct
+ * evaluation are always below q^nc).  STAGE-LOCAL PAIR LAYOUT: the chunk of
+ * stage s (len_s digits) owns ceil(len_s / 2) accumulator words of its own,
+ * digit pair (2w, 2w+1) of the chunk in word w -- chunks never share a word,
+ * whatever the parity of their lengths, so the inner loop is two reciprocal
+ * multiplies, two multiply-adds that also pack the pair (d0 + 2^16 d1 =
+ * r + q1 (2^16 - q) - q2 (q 2^16)) and one shared-memory read-modify-write
+ * per pair, nothing else.  compress_acc_ladder reads the same layout. */
 #ifndef DASHB_FRAC
 #define DASHB_FRAC 1
 #endif
-__device__ __forceinline__ void accumulate_frac(u128 x, const ModInfo& m, const gc::FracInfo& fi, uint32_t* acc) {
-    const uint32_t c1 = 65536u - m.q, c2 = m.q << 16;
-    gc::for_each_chunk_msb(x, m, fi, [&](uint32_t d0, uint32_t len, uint32_t r) {
-        uint32_t* a = acc + (d0 >> 1) * SIGN_THREADS;
-        uint32_t i = 0;
-        if (d0 & 1u) { /* the chunk starts in the high half of a word */
-            const uint32_t q1 = gc::div_q(r, m);
-            a[0] += (r - q1 * m.q) << 16;
-            a += SIGN_THREADS;
-            r = q1;
-            i = 1;
-        }
+__device__ __forceinline__ void accumulate_ladder(u128 x, const ModInfo& m, const gc::FracInfo& fi, uint32_t* acc) {
+    /* c2 = -(q << 16): the subtraction rides on the multiply-add */
+    const uint32_t c1 = 65536u - m.q, c2 = 0u - (m.q << 16), mq = m.mq;
+    uint32_t* a = acc;
+    gc::for_each_chunk_ladder(x, fi, [&](uint32_t len, uint32_t r) {
 #pragma unroll 1
-        for (; i + 3 < len; i += 4) { /* two words per trip */
-            const uint32_t q1 = gc::div_q(r, m);
-            const uint32_t q2 = gc::div_q(q1, m);
-            const uint32_t q3 = gc::div_q(q2, m);
-            const uint32_t q4 = gc::div_q(q3, m);
-            a[0] += r + q1 * c1 - q2 * c2;
-            a[SIGN_THREADS] += q2 + q3 * c1 - q4 * c2;
+        for (; len >= 4; len -= 4) { /* two words per trip */
+            const uint32_t q1 = gc::mulhi32(r, mq);
+            const uint32_t q2 = gc::mulhi32(q1, mq);
+            const uint32_t q3 = gc::mulhi32(q2, mq);
+            const uint32_t q4 = gc::mulhi32(q3, mq);
+            a[0] += r + q1 * c1 + q2 * c2;
+            a[SIGN_THREADS] += q2 + q3 * c1 + q4 * c2;
             a += 2 * SIGN_THREADS;
             r = q4;
         }
-        if (i + 1 < len) {
-            const uint32_t q1 = gc::div_q(r, m);
-            const uint32_t q2 = gc::div_q(q1, m);
-            a[0] += r + q1 * c1 - q2 * c2;
+        if (len & 2) {
+            const uint32_t q1 = gc::mulhi32(r, mq);
+            const uint32_t q2 = gc::mulhi32(q1, mq);
+            a[0] += r + q1 * c1 + q2 * c2;
             a += SIGN_THREADS;
             r = q2;
-            i += 2;
         }
-        if (i < len) a[0] += r; /* the chunk's last digit is what is left */
+        if (len & 1) { /* the chunk's last digit is what is left */
+            a[0] += r;
+            a += SIGN_THREADS;
+        }
     });
 }
 
-/* compress(acc mod q) and the colour of the sum */
+/* compress(acc mod q) and the colour of the sum; absolute digit layout
+ * (accumulate) */
 __device__ __forceinline__ u128 compress_acc(const uint32_t* acc, const ModInfo& m, uint32_t& colour) {
     gc::Compressor c(m);
     uint32_t dg = 0;
@@ -695,6 +711,104 @@ __device__ __forceinline__ u128 compress_acc(const uint32_t* acc, const ModInfo&
     }
     colour = dg;
     return c.value();
+}
+
+/* the same for the stage-local pair layout (accumulate_ladder): stage after
+ * stage from the most significant one, a stage's pairs from its top word
+ * down; a stage's digits are folded into one 32-bit value (below q^len_s =
+ * the stage's multiplier, 2^sh removed for stage 0) that enters the 128-bit
+ * value with one multiply-add.  An odd stage's top word has an empty high
+ * half: a leading zero. */
+__device__ __forceinline__ u128 compress_acc_ladder(const uint32_t* acc, const ModInfo& m, const gc::FracInfo& fi,
+                                                    uint32_t& colour) {
+    u128 x = gc::make_u128(0, 0);
+    const uint32_t q = m.q, mq = m.mq;
+    uint32_t lo = 0;
+#pragma unroll 1
+    for (uint32_t s = 0; s < fi.nst; ++s) {
+        const uint32_t nw = ((fi.desc[s] & 0xffu) + 1) >> 1;
+        uint32_t chunk = 0;
+#pragma unroll 1
+        for (int w = (int)nw - 1; w >= 0; --w) {
+            const uint32_t v = acc[w * SIGN_THREADS];
+            const uint32_t hi = v >> 16;
+            lo = v & 0xffffu;
+            chunk = (chunk * q + (hi - gc::mulhi32(hi, mq) * q)) * q;
+            lo -= gc::mulhi32(lo, mq) * q;
+            chunk += lo;
+        }
+        /* q^len_s: stage 0's multiplier carries the 2^sh alignment factor, but x is still 0 there */
+        x = gc::muladd_small(x, fi.mult[s], chunk);
+        acc += nw * SIGN_THREADS;
+    }
+    colour = lo;
+    return x;
+}
+
+/* ReLU step 4 for one CRT modulus with a word-aligned plan: out = E + t x - G
+ * digit-wise mod p (gates/mixed_mod_half_gate.h:100-102), the digits of the
+ * two payloads taken by multiplication in lockstep.  Every stage of the plan
+ * covers whole 32-bit words of the digit plane (make_fracinfo(aligned4));
+ * the first one is rounded up to a whole word: the payloads have no digits
+ * above nc and the input label's padding bytes are masked, so the padding of
+ * the output word comes out zero.  Per word: 8 reciprocal multiplies and 8
+ * multiply-adds give the packed digit pairs of E and G, two PRMT spread the
+ * four x digits, then  pair = E + t x + (q,q) - G  is reduced half by half. */
+__device__ __forceinline__ void half_gate_ladder(u128 E, u128 G, const ModInfo& m, const gc::FracInfo& fi, uint32_t tt,
+                                                 const uint8_t* xin, uint8_t* xout, uint32_t Bp) {
+    uint32_t ne[5], ng[5];
+    gc::frac_init(E, fi, ne);
+    gc::frac_init(G, fi, ng);
+    const uint32_t q = m.q, mq = m.mq, c1 = 65536u - q, c2 = 0u - (q << 16), qq = q | (q << 16);
+    const uint32_t topmask = 0xffffffffu >> (8 * ((4u - (m.nc & 3u)) & 3u));
+    const uint64_t wstride = 4ull * Bp;
+    uint32_t d = (m.nc + 3u) & ~3u; /* digits not yet delivered, rounded up to whole words */
+    uint32_t s = 0;
+    const uint32_t cnt = fi.ladder;
+    bool first = true;
+    auto stage = [&](uint32_t len, uint32_t re, uint32_t rg) {
+        const uint32_t nw = (len + 3u) >> 2;
+        d -= 4 * nw;
+        const uint8_t* xp = xin + (uint64_t)(d >> 2) * wstride;
+        uint8_t* op = xout + (uint64_t)(d >> 2) * wstride;
+        uint32_t xn = *reinterpret_cast<const uint32_t*>(xp);
+#pragma unroll 1
+        for (uint32_t w = 0; w < nw; ++w) {
+            uint32_t xw = xn;
+            if (w + 1 < nw) xn = *reinterpret_cast<const uint32_t*>(xp + wstride);
+            xp += wstride;
+            if (first && w + 1 == nw) xw &= topmask;
+            const uint32_t e1 = gc::mulhi32(re, mq), e2 = gc::mulhi32(e1, mq), e3 = gc::mulhi32(e2, mq), e4 = gc::mulhi32(e3, mq);
+            const uint32_t g1 = gc::mulhi32(rg, mq), g2 = gc::mulhi32(g1, mq), g3 = gc::mulhi32(g2, mq), g4 = gc::mulhi32(g3, mq);
+            const uint32_t pe0 = re + e1 * c1 + e2 * c2, pe1 = e2 + e3 * c1 + e4 * c2;
+            const uint32_t pg0 = rg + g1 * c1 + g2 * c2, pg1 = g2 + g3 * c1 + g4 * c2;
+            re = e4;
+            rg = g4;
+            const uint32_t v0 = tt * __byte_perm(xw, 0, 0x4140) + pe0 + qq - pg0;
+            const uint32_t v1 = tt * __byte_perm(xw, 0, 0x4342) + pe1 + qq - pg1;
+            uint32_t a0 = v0 & 0xffffu, a1 = v0 >> 16, a2 = v1 & 0xffffu, a3 = v1 >> 16;
+            a0 -= gc::mulhi32(a0, mq) * q;
+            a1 -= gc::mulhi32(a1, mq) * q;
+            a2 -= gc::mulhi32(a2, mq) * q;
+            a3 -= gc::mulhi32(a3, mq) * q;
+            *reinterpret_cast<uint32_t*>(op) = a0 | (a1 << 8) | (a2 << 16) | (a3 << 24);
+            op += wstride;
+        }
+        first = false;
+    };
+#define DASHB_HG_STEP(W)                                                        \
+    _Pragma("unroll 1") for (uint32_t c = (cnt >> (4 * ((W)-1))) & 15u; c; --c, ++s) { \
+        const uint32_t mult = fi.mult[s];                                         \
+        const uint32_t re = gc::frac_stage(ne, mult, (W));                        \
+        const uint32_t rg = gc::frac_stage(ng, mult, (W));                        \
+        stage(fi.desc[s] & 0xffu, re, rg);                                        \
+    }
+    DASHB_HG_STEP(5)
+    DASHB_HG_STEP(4)
+    DASHB_HG_STEP(3)
+    DASHB_HG_STEP(2)
+    DASHB_HG_STEP(1)
+#undef DASHB_HG_STEP
 }
 
 /*
@@ -716,7 +830,7 @@ __device__ __forceinline__ u128 compress_acc(const uint32_t* acc, const ModInfo&
 template <bool RELU>
 __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __grid_constant__ SignParams P) {
     __shared__ AesSmem aes;
-    extern __shared__ uint32_t s_acc[]; /* [ceil(acc_digits / 2)][SIGN_THREADS] */
+    extern __shared__ uint32_t s_acc[]; /* [accumulator words][SIGN_THREADS] */
     aes_smem_load(aes);
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P.n * P.batch) return;
@@ -743,21 +857,38 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
     asm volatile("" : "+r"(tid));
     uint32_t* acc = s_acc + tid;
     u128 carry = P.carry0;
+    /* rows of this element's tables, as 32-bit row indices from the element's
+     * first row (a table of one element never reaches 2^32 rows) */
     const u128* approx_e = P.approx + e * (uint64_t)nm * P.S;
-    uint64_t cnt1 = e * (uint64_t)(k + 1) * P.Mp, cnt2 = cnt1;
+    const u128* cast1_e = P.cast1 + e * (uint64_t)(k + 1) * P.Mp;
+    const u128* cast2_e = P.cast2 + e * (uint64_t)(k + 1) * P.Mp;
+    uint32_t cnt1 = 0, cnt2 = 0;
+    uint32_t ctop = 0;
+    u128 top = gc::make_u128(0, 0);
+    /* One loop over the mixed-radix digits, least significant first; digit 0
+     * (the most significant) skips the cast: its k + 1 summands are the
+     * approximate digits themselves and the carry. */
 #pragma unroll 1
-    for (int i = nm - 1; i >= 1; --i) {
+    for (int i = nm - 1; i >= 0; --i) {
         /* by value: keeps the fields in registers instead of re-reading the
          * dynamically indexed parameter bank at every use */
         const ModInfo M = pin(P.mrs[i]);
-        const ModInfo C = pin(P.cast[i]);
+        const ModInfo C = pin(P.cast[i]); /* accumulation modulus: (k+1) m_i, or m_0 for digit 0 */
         const gc::ColourConsts cc = gc::colour_consts(M);
-        for (uint32_t w = 0; w < (C.nc + 1) / 2; ++w) acc[w * SIGN_THREADS] = 0;
+        /* this digit's plan, addressed through an offset the compiler cannot
+         * rebuild from i: otherwise every stage of every label recomputes
+         * &P.castf[i] (six uniform-datapath instructions) before its loads */
+        uint32_t plan_off = (uint32_t)(offsetof(SignParams, castf) + (size_t)i * sizeof(gc::FracInfo));
+        asm volatile("" : "+r"(plan_off));
+        const gc::FracInfo& fi = *reinterpret_cast<const gc::FracInfo*>(reinterpret_cast<const char*>(&P) + plan_off);
+        const bool ladder = DASHB_FRAC && fi.nst != 0;
+        const uint32_t nwords = ladder ? fi.words : (C.nc + 1) / 2;
+        for (uint32_t w = 0; w < nwords; ++w) acc[w * SIGN_THREADS] = 0;
         /* Ciphertext rows are requested ahead of the hashes that separate
          * them from their use: residue j+1's approximate-digit row before
          * label j is hashed, the cast-1 row (its index is the label's colour,
          * known before the hash) before the hash as well. */
-        auto approx_row = [&](int j) { return ldg128(approx_e + (uint64_t)nm * P.prefix[j] + (uint64_t)i * P.crt[j].q + col[j]); };
+        auto approx_row = [&](int j) { return ldg128(approx_e + ((uint32_t)nm * P.prefix[j] + (uint32_t)i * P.crt[j].q + col[j])); };
         u128 row = approx_row(0);
 #pragma unroll 1
         for (int j = 0; j <= k; ++j) {
@@ -765,48 +896,39 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
             u128 lab = carry;
             if (j < k) lab = gc::sub128(row, h[j]);
             if (j + 1 < k) row = approx_row(j + 1);
-            /* Step 2.2: cast to modulus (k+1)*m_i */
-            const uint32_t c0 = gc::colour_of(lab, M, cc);
-            const u128 crow = ldg128(P.cast1 + cnt1 + (uint64_t)j * M.q + c0);
-            const u128 hl = hash(aes, lab);
-            const u128 c1 = gc::sub128(crow, hl);
-            if (DASHB_FRAC && P.castf[i].nst)
-                accumulate_frac(c1, C, P.castf[i], acc);
+            if (i > 0) {
+                /* Step 2.2: cast to modulus (k+1)*m_i */
+                const uint32_t c0 = gc::colour_of(lab, M, cc);
+                const u128 crow = ldg128(cast1_e + (cnt1 + (uint32_t)j * M.q + c0));
+                lab = gc::sub128(crow, hash(aes, lab));
+            }
+            if (ladder)
+                accumulate_ladder(lab, C, fi, acc);
             else
-                accumulate(c1, C, acc);
+                accumulate(lab, C, acc);
         }
-        cnt1 += (uint64_t)(k + 1) * M.q;
         /* Step 2.3 / 2.4: sum of the casts -> carry into digit i-1 */
         uint32_t c2;
-        const u128 sum2 = compress_acc(acc, C, c2);
-        carry = gc::sub128(ldg128(P.cast2 + cnt2 + c2), hash(aes, sum2));
-        cnt2 += C.q;
+        const u128 sum = ladder ? compress_acc_ladder(acc, C, fi, c2) : compress_acc(acc, C, c2);
+        if (i > 0) {
+            carry = gc::sub128(ldg128(cast2_e + (cnt2 + c2)), hash(aes, sum));
+            cnt1 += (uint32_t)(k + 1) * M.q;
+            cnt2 += C.q;
+        } else {
+            top = sum;
+            ctop = c2;
+        }
     }
-    /* most significant digit: sum = carry + sum_j digit_{j,0} */
-    const ModInfo M0 = pin(P.mrs[0]);
-    for (uint32_t w = 0; w < (M0.nc + 1) / 2; ++w) acc[w * SIGN_THREADS] = 0;
-    u128 row0 = ldg128(approx_e + (uint64_t)nm * P.prefix[0] + col[0]);
-#pragma unroll 1
-    for (int j = 0; j <= k; ++j) {
-        u128 lab = carry;
-        if (j < k) lab = gc::sub128(row0, h[j]);
-        if (j + 1 < k) row0 = ldg128(approx_e + (uint64_t)nm * P.prefix[j + 1] + col[j + 1]);
-        if (DASHB_FRAC && P.castf[0].nst)
-            accumulate_frac(lab, M0, P.castf[0], acc);
-        else
-            accumulate(lab, M0, acc);
-    }
-    uint32_t ctop;
-    const u128 top = compress_acc(acc, M0, ctop);
     const u128 htop = hash(aes, top);
+    const uint32_t m0 = P.mrs[0].q;
 
     /* Step 3: sign projection(s) */
-    const u128* sign_e = P.sign + e * (uint64_t)P.n_out * M0.q;
+    const u128* sign_e = P.sign + e * (uint64_t)P.n_out * m0;
     if (!RELU) {
 #pragma unroll 1
         for (int j = 0; j < P.n_out; ++j) {
             const ModInfo mo = pin(P.outm[j]);
-            store_digits(P.out[j], mo, e, b, P.Bp, gc::sub128(ldg128(sign_e + (uint64_t)j * M0.q + ctop), htop));
+            store_digits(P.out[j], mo, e, b, P.Bp, gc::sub128(ldg128(sign_e + (uint64_t)j * m0 + ctop), htop));
         }
         return;
     }
@@ -814,11 +936,13 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
     const u128 s = gc::sub128(ldg128(sign_e + ctop), htop); /* sign label, modulus 2 */
     const u128 hs = hash(aes, s);
     const uint32_t cs = (uint32_t)s.lo & 1u;
+    const u128* garbler_e = P.garbler + e * (uint64_t)P.S;
+    const u128* ev_e = P.evaluator + e * (uint64_t)k * 3;
 #pragma unroll 1
     for (int j = 0; j < k; ++j) {
         const ModInfo Pm = pin(P.crt[j]);
-        const u128 G = gc::sub128(ldg128(P.garbler + e * (uint64_t)P.S + P.prefix[j] + col[j]), h[j]);
-        const u128* ev = P.evaluator + (e * (uint64_t)k + j) * 3;
+        const u128 G = gc::sub128(ldg128(garbler_e + (P.prefix[j] + col[j])), h[j]);
+        const u128* ev = ev_e + 3 * j;
         const u128 E = gc::sub128(ldg128(ev + cs), hs);
         /* mini gate: int16 row `cs` of the packed slot minus the low 16 hash
          * bits (gates/projection_gate_mini.h:45-56) */
@@ -830,6 +954,10 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
         const uint64_t off = plane_off(Pm, e, b, P.Bp);
         const uint8_t* xin = P.in[j] + off;
         uint8_t* xout = P.out[j] + off;
+        if (DASHB_FRAC && P.crtf[j].nst) {
+            half_gate_ladder(E, G, Pm, P.crtf[j], (uint32_t)tt, xin, xout, P.Bp);
+            continue;
+        }
         uint32_t xw = 0, ow = 0;
         const uint32_t last = Pm.nc - 1;
         /* the input label's words again (they were read for the key in step
@@ -1018,7 +1146,11 @@ cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s) {
     const unsigned grid = (unsigned)((total + SIGN_THREADS - 1) / SIGN_THREADS);
     uint32_t acc_digits = p.mrs[0].nc;
     for (int i = 1; i < p.n_mrs; ++i) acc_digits = max(acc_digits, p.cast[i].nc);
-    const size_t smem = (size_t)((acc_digits + 1) / 2) * SIGN_THREADS * sizeof(uint32_t);
+    /* k_sign: two digit sums per word; a modulus with a plan uses the stage-local pair layout */
+    uint32_t acc_words = 0;
+    for (int i = 0; i < p.n_mrs; ++i)
+        acc_words = max(acc_words, (DASHB_FRAC && p.castf[i].nst) ? p.castf[i].words : (p.cast[i].nc + 1) / 2);
+    const size_t smem = (size_t)acc_words * SIGN_THREADS * sizeof(uint32_t);
     /* latency mode: one warp per (element, inference) while that still leaves SMs idle otherwise */
     static const long wide_max = getenv("DASHB_WIDE_MAX") ? atol(getenv("DASHB_WIDE_MAX")) : 8192;
     /* with other lanes in flight the GPU is busy anyway: only tiny launches go wide */

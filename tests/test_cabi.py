@@ -130,3 +130,34 @@ def test_multiplicative_digit_extraction_every_modulus(api):
     bad, planned = api.hostcheck_frac_sweep(2, 32767, 200, seed=3)
     assert bad == 0
     assert planned > 1500  # every modulus cut into at most 10 chunks has a plan
+
+
+def test_ladder_walk_every_modulus(api):
+    """gc::for_each_chunk_ladder (stage width known at compile time, trip
+    counts from the plan) against the long division for every modulus
+    2..32767, and the word-aligned plans the ReLU half gates use for the CRT
+    moduli: each stage after the first covers whole 32-bit words of a digit
+    plane."""
+    bad, planned = api.hostcheck_ladder_sweep(2, 32767, 100, seed=5)
+    assert bad == 0 and planned > 1500
+    bad, planned = api.hostcheck_ladder_sweep(2, 256, 300, seed=6, aligned=True)
+    assert bad == 0
+    assert planned >= 70  # every modulus whose chunks hold at least four digits (q <= 76 and a few more)
+    for q in (2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31, 32):  # the CRT moduli of every configuration
+        assert api.hostcheck_ladder_sweep(q, q, 1, seed=1, aligned=True) == (0, 1), q
+
+
+def test_word_wise_compress_matches_oracle(api):
+    """gc::WordCompressor (four digits per step, dp4a) == LabelTensor::compress
+    for every u8 modulus; q = 256 has no word-wise form and keeps the
+    digit-wise path."""
+    rng = random.Random(11)
+    for q in range(2, 257):
+        nc = O.nr_comps(q)
+        for t in range(12):
+            d = [rng.randrange(q) for _ in range(nc)] if t else [q - 1] * nc
+            got = api.hostcheck_compress_words(q, d)
+            if q == 256:
+                assert got is None
+                break
+            assert got == O.compress(q, d), (q, t)

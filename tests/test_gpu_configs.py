@@ -137,8 +137,15 @@ def test_full_size_model_b_all_256_decoded(gpu):
 
 
 # ---------------------------------------------- (d) configs[2] / configs[3]
-def _rescale_plain(v, s):
-    return -((-v) // s)  # ceil(v / s), ScalarTensor::rescale (circuit/scalar_tensor.h:477-493)
+def _rescale_plain(v, s, P):
+    """What the garbled rescaling computes on plain integers: upshift by P/2
+    (garbled_circuit_interface.h:948-954), exact division of the value minus
+    its residue mod s (rescale_gadget.h:271-307), downshift by P/(2s), both
+    shifts in integer arithmetic (:969-980).  For the reference's prime bases
+    (P/2 odd, s = 2) this is ScalarTensor::rescale's ceil(v / s)
+    (circuit/scalar_tensor.h:477-493); for the base {32,3,...,17} P/(2*32) is
+    not an integer and the result is v/32 rounded to nearest."""
+    return (v + P // 2) // s - P // (2 * s)
 
 
 @pytest.mark.parametrize("model,batch", [("MODEL_F_GNNP_POOL_REPL", 16), ("MODEL_F_MINIONN_POOL_REPL", 16)])
@@ -180,8 +187,8 @@ def test_full_size_cifar_models_vs_oracle(gpu, tmp_path, model, batch):
 def test_full_size_first_scaled_layer_decodes_to_plain_integers(gpu, model):
     """The first convolution + Rescale{32} of configs[2] / configs[3] at full
     size as a circuit of its own (no sign approximation involved): every
-    decoded output equals the plain integer semantics, conv then ceil(x / 32)
-    (Conv2d::plain_q_eval + ScalarTensor::rescale), for the whole batch."""
+    decoded output equals the plain integer semantics, convolution
+    (Conv2d::plain_q_eval) then _rescale_plain, for the whole batch."""
     import workloads as W
     from dash_b200 import garble
 
@@ -213,7 +220,8 @@ def test_full_size_first_scaled_layer_decodes_to_plain_integers(gpu, model):
             patch = x[:, :, i:i + sh * (oh - 1) + 1:sh, j:j + sw * (ow - 1) + 1:sw]
             out += np.einsum("bchw,fc->bfhw", patch, wt[:, :, i, j])
     out += np.asarray(plain[0]["biases"], dtype=np.int64)[None, :, None, None]
-    want = _rescale_plain(out, int(plain[1]["factors"][0])).reshape(batch, -1)
+    P = int(np.prod(np.asarray(spec["crt"], dtype=np.int64)))
+    want = _rescale_plain(out, int(plain[1]["factors"][0]), P).reshape(batch, -1)
     assert np.array_equal(vals, want)
     c.close()
 
