@@ -231,6 +231,43 @@ gc::FracInfo make_fracinfo(const ModInfo& m, bool aligned4 = false) {
     lens[nst - 1] = rl ? rl : t;
     mults[nst - 1] = (long double)plast;
     const long double lq = log2l((long double)q);
+    /* the dropped limbs' loss for a width ladder, the compensation addc and the exact excess bound
+     * (addc + 1) * D <= 2^F; fills the plan when the ladder passes */
+    auto try_ladder = [&](const uint32_t* W) -> bool {
+        long double tot = 0, amp = 1;
+        for (uint32_t s = 0; s < nst; ++s) {
+            if (W[s] < 5) tot += ldexpl(1.0L, 32 * (5 - (int)W[s])) / amp;
+            amp *= mults[s];
+        }
+        const long double addc_ld = 5 + ceill(tot * (1 + 1e-12L)) + 2;
+        if (addc_ld >= 2147483648.0L) return false;
+        const uint32_t addc = (uint32_t)addc_ld;
+        Big lhs = D, rhs;
+        lhs.mul_small(addc + 1);
+        rhs.set_bit(F);
+        if (Big::cmp(lhs, rhs) > 0) return false;
+        for (int i = 0; i < 5; ++i) fi.mu[i] = mu.w[i];
+        fi.addc = addc;
+        fi.nst = nst;
+        fi.ladder = fi.words = 0;
+        for (uint32_t s = 0; s < nst; ++s) {
+            fi.mult[s] = (uint32_t)mults[s];
+            fi.desc[s] = lens[s] | W[s] << 8;
+            fi.ladder += 1u << (4 * (W[s] - 1));
+            fi.words += (lens[s] + 1) / 2;
+        }
+        return true;
+    };
+    /* the straight-line shape of k_sign (FracInfo::t4): stages of four digits, widths 5,[5,]4,3,2,1 */
+    if (!aligned4 && (nst == 5 || nst == 6) && lens[nst - 1] <= 4) {
+        bool four = true;
+        for (uint32_t s = 0; s + 1 < nst; ++s) four = four && lens[s] == 4;
+        const uint32_t W5[5] = {5, 4, 3, 2, 1}, W6[6] = {5, 5, 4, 3, 2, 1};
+        if (four && try_ladder(nst == 5 ? W5 : W6)) {
+            fi.t4 = 1;
+            return fi;
+        }
+    }
     for (int guard = 6; guard < 40; ++guard) {
         uint32_t W[10];
         uint32_t remd = nc;
@@ -243,31 +280,9 @@ gc::FracInfo make_fracinfo(const ModInfo& m, bool aligned4 = false) {
             W[s] = w;
             remd -= lens[s];
         }
-        /* what the dropped limbs can take away, in units of the stage-0 fraction */
-        long double tot = 0, amp = 1;
-        for (uint32_t s = 0; s < nst; ++s) {
-            if (W[s] < 5) tot += ldexpl(1.0L, 32 * (5 - (int)W[s])) / amp;
-            amp *= mults[s];
-        }
-        const long double addc_ld = 5 + ceill(tot * (1 + 1e-12L)) + 2;
-        if (addc_ld >= 2147483648.0L) continue;
-        const uint32_t addc = (uint32_t)addc_ld;
-        /* excess bound: (addc + 1) * D <= 2^F, exactly */
-        Big lhs = D, rhs;
-        lhs.mul_small(addc + 1);
-        rhs.set_bit(F);
-        if (Big::cmp(lhs, rhs) > 0) continue;
-        for (int i = 0; i < 5; ++i) fi.mu[i] = mu.w[i];
-        fi.addc = addc;
-        fi.nst = nst;
-        for (uint32_t s = 0; s < nst; ++s) {
-            fi.mult[s] = (uint32_t)mults[s];
-            fi.desc[s] = lens[s] | W[s] << 8;
-            fi.ladder += 1u << (4 * (W[s] - 1));
-            fi.words += (lens[s] + 1) / 2;
-        }
-        return fi;
+        if (try_ladder(W)) return fi;
     }
+    memset(&fi, 0, sizeof(fi));
     return fi;
 }
 
@@ -1242,8 +1257,56 @@ static size_t wire_label_bytes(const dashb_circuit* c, int j, bool compressed) {
     return compressed ? 16 : (size_t)c->crt_mi[j].nc * 2;
 }
 
+/* Device-visible addresses of the caller's label buffers when every one of
+ * them is pinned host memory mapped into this device's address space
+ * (cudaHostAlloc / cudaHostRegister under unified addressing): k_ingest_direct
+ * then reads them over PCIe itself.  Pageable buffers (or DASHB_DIRECT_INGEST=0)
+ * take the staged path: cudaMemcpyAsync into stage_in, then k_ingest. */
+static bool mapped_host_inputs(const dashb_circuit* c, const void* const* in, const void** dev) {
+    static const bool off = getenv("DASHB_DIRECT_INGEST") != nullptr && atoi(getenv("DASHB_DIRECT_INGEST")) == 0;
+    if (off) return false;
+    for (int j = 0; j < c->k; ++j) {
+        cudaPointerAttributes a;
+        if (cudaPointerGetAttributes(&a, in[j]) != cudaSuccess) {
+            cudaGetLastError();
+            return false;
+        }
+        if (a.type != cudaMemoryTypeHost || !a.devicePointer) return false;
+        dev[j] = a.devicePointer;
+    }
+    return true;
+}
+
 /* `in`: per CRT modulus int16 [batch][label][nc], or (compressed) dashb_u128 [batch][label] */
-static int enqueue_inputs(dashb_circuit* c, Lane& ln, const void* const* in, bool compressed, cudaStream_t cs, cudaStream_t s) {
+static int enqueue_inputs(dashb_circuit* c, Lane& ln, const void* const* in, bool compressed, cudaStream_t cs, cudaStream_t s,
+                          const void* const* mapped = nullptr) {
+    if (mapped && !compressed) {
+        /* no copy, no staging: one kernel per lane reads the host buffers; in the pipelined path it runs on
+         * the high-priority stream so that its CTAs take the SM slots the computing lanes free up */
+        cudaStream_t is = (cs != s) ? c->ingest_s : s;
+        IngestParams p;
+        memset(&p, 0, sizeof(p));
+        p.k = c->k;
+        p.n = c->input_size;
+        p.batch = ln.batch;
+        p.Bp = ln.Bp;
+        for (int j = 0; j < c->k; ++j) {
+            const size_t per = c->input_size * (size_t)c->crt_mi[j].nc;
+            p.src[j] = (const int16_t*)mapped[j] + (size_t)ln.b0 * per;
+            p.end[j] = (const int16_t*)mapped[j] + (size_t)c->batch * per;
+            p.plane[j] = ln.t_in.plane[j];
+            p.nc[j] = c->crt_mi[j].nc;
+        }
+        CU(launch_ingest_direct(p, is));
+        c->launches += 1;
+        if (is != s) {
+            CU(cudaEventRecord(ln.ing_done, is));
+            CU(cudaStreamWaitEvent(s, ln.ing_done, 0));
+        }
+        ln.t_cur = ln.t_in;
+        ln.which = 0;
+        return DASHB_OK;
+    }
     size_t off = 0;
     for (int j = 0; j < c->k; ++j) {
         const size_t per = c->input_size * wire_label_bytes(c, j, compressed);
@@ -1292,9 +1355,11 @@ static int move_inputs_any(dashb_circuit* c, const void* const* in, uint64_t bat
         if (!in[j]) return fail(DASHB_EINVAL, "input labels %d missing", j);
     int rc = split_batch(c, batch);
     if (rc) return rc;
+    const void* dev[MAXK];
+    const bool direct = !compressed && mapped_host_inputs(c, in, dev);
     if ((rc = fork_lanes(c))) return rc;
     for (int i = 0; i < c->lanes_used; ++i)
-        if ((rc = enqueue_inputs(c, *c->lanes[i], in, compressed, c->lanes[i]->s, c->lanes[i]->s))) return rc;
+        if ((rc = enqueue_inputs(c, *c->lanes[i], in, compressed, c->lanes[i]->s, c->lanes[i]->s, direct ? dev : nullptr))) return rc;
     return join_lanes(c);
 }
 
@@ -1709,11 +1774,14 @@ static int evaluate_any(dashb_circuit* c, const void* const* in, uint64_t batch,
         g_err = msg;
         return code;
     };
+    const void* dev[MAXK];
+    const bool direct = !compressed && mapped_host_inputs(c, in, dev);
     if ((rc = fork_lanes(c))) return bail(rc);
     for (int i = 0; i < c->lanes_used; ++i) {
         /* all H2D copies go through one copy stream, lane after lane, so that
-         * lane i-1 computes while lane i still transfers */
-        if ((rc = enqueue_inputs(c, *c->lanes[i], in, compressed, c->copy_s, c->lanes[i]->s))) return bail(rc);
+         * lane i-1 computes while lane i still transfers (pinned, mapped
+         * buffers: no copies at all, the lane's ingest kernel reads the host) */
+        if ((rc = enqueue_inputs(c, *c->lanes[i], in, compressed, c->copy_s, c->lanes[i]->s, direct ? dev : nullptr))) return bail(rc);
         if (trace) cudaEventRecord(tr[1 + 3 * i], c->lanes[i]->s);
     }
     const int nl = (int)c->layers.size();

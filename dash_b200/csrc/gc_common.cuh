@@ -257,7 +257,10 @@ struct FracInfo {
     uint32_t desc[FRAC_MAXST];  /* len_s | W_s << 8: digits of the chunk, limbs of the fraction the stage keeps (1..5) */
     uint32_t ladder;            /* stages per width, 4 bits each: bits 4(W-1)..4(W-1)+3 = stages that keep W limbs */
     uint32_t words;             /* sum over the stages of ceil(len_s / 2): accumulator words in stage-local pair layout */
-    uint32_t pad[3];            /* 128 bytes: indexing an array of plans is a shift */
+    uint32_t t4;                /* 1: five or six stages of four digits (the last one of the six may hold fewer) with
+                                 * widths 5,[5,]4,3,2,1 -- the shape of every cast modulus (k+1) m_i in 41..76; the sign
+                                 * kernel runs it as straight-line code */
+    uint32_t pad[2];            /* 128 bytes: indexing an array of plans is a shift */
 };
 
 GC_HD void frac_init(u128 x, const FracInfo& fi, uint32_t (&n)[5]) {

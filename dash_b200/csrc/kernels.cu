@@ -310,6 +310,77 @@ __global__ void __launch_bounds__(128) k_egress(const uint8_t* __restrict__ plan
     }
 }
 
+/*
+ * The same layout change without the staging copy: the caller's pinned host
+ * buffers are mapped into the device's address space, so the kernel reads
+ * them over PCIe itself (cuda_move_inputs' cudaMemcpy and the k_ingest pass
+ * in one).  A CTA takes one inference's labels of ING_E consecutive elements
+ * of one modulus -- one contiguous span of the host buffer -- with 16-byte
+ * loads, every host byte exactly once, through shared memory; the words of
+ * four u8 digits then go to the plane (4-byte stores, one sector each: they
+ * merge in L2 with the other inferences' stores of the same rows).  PCIe is
+ * the bound: the copy engine needs ~190 MB per copy to reach the link rate
+ * (profiles/r1_v9_summary.md), loads issued from a few dozen CTAs do not.
+ */
+constexpr int ING_E = 32;
+constexpr int ING_THREADS = 256;
+__global__ void __launch_bounds__(ING_THREADS) k_ingest_direct(const __grid_constant__ IngestParams P) {
+    __shared__ uint4 buf[(ING_E * 128 * 2 + 32) / 16 + 1];
+    const int j = blockIdx.z;
+    const uint32_t b = blockIdx.y;
+    const uint64_t e0 = (uint64_t)blockIdx.x * ING_E;
+    const uint32_t ne = (uint32_t)min((uint64_t)ING_E, P.n - e0);
+    const uint32_t nc = P.nc[j], nc4 = (nc + 3) >> 2;
+    const char* src = reinterpret_cast<const char*>(P.src[j] + ((uint64_t)b * P.n + e0) * nc);
+    const char* end = reinterpret_cast<const char*>(P.end[j]);
+    const uint32_t bytes = ne * nc * 2;
+    const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
+    const char* start = src - mis; /* 16-byte aligned; at worst 14 bytes before the span, never before the allocation's page */
+    const uint32_t nvec = (bytes + mis + 15) >> 4;
+    for (uint32_t i = threadIdx.x; i < nvec; i += ING_THREADS) {
+        const char* p = start + 16ull * i;
+        uint4 v;
+        if (p + 16 <= end) {
+            v = __ldcs(reinterpret_cast<const uint4*>(p)); /* streaming: read once */
+        } else { /* the very last vector of the caller's buffer: do not read past its end */
+            uint16_t h[8];
+            for (int t = 0; t < 8; ++t) h[t] = (p + 2 * t + 2 <= end) ? *reinterpret_cast<const uint16_t*>(p + 2 * t) : (uint16_t)0;
+            v.x = h[0] | ((uint32_t)h[1] << 16);
+            v.y = h[2] | ((uint32_t)h[3] << 16);
+            v.z = h[4] | ((uint32_t)h[5] << 16);
+            v.w = h[6] | ((uint32_t)h[7] << 16);
+        }
+        buf[i] = v;
+    }
+    __syncthreads();
+    const uint16_t* dig = reinterpret_cast<const uint16_t*>(reinterpret_cast<const char*>(buf) + mis);
+    uint8_t* plane = P.plane[j];
+    /* a warp walks the words of one element at a time */
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    /* the inference columns past the batch (up to Bp) are kept zero by the CTAs of the last inference */
+    const uint32_t nb = (b + 1 == P.batch) ? P.Bp - b : 1;
+    for (uint32_t el = warp; el < ne; el += ING_THREADS / 32) {
+        const uint16_t* row = dig + el * nc;
+        for (uint32_t d4 = lane; d4 < nc4; d4 += 32) {
+            uint32_t w = 0;
+#pragma unroll
+            for (uint32_t t = 0; t < 4; ++t)
+                if (4 * d4 + t < nc) w |= (uint32_t)(uint8_t)row[4 * d4 + t] << (8 * t);
+            uint32_t* dst = reinterpret_cast<uint32_t*>(plane + (((e0 + el) * nc4 + d4) * (uint64_t)P.Bp + b) * 4);
+            dst[0] = w;
+            for (uint32_t x = 1; x < nb; ++x) dst[x] = 0;
+        }
+    }
+}
+
+cudaError_t launch_ingest_direct(const IngestParams& p, cudaStream_t s) {
+    if (p.n == 0 || p.batch == 0) return cudaSuccess;
+    if (p.batch > 65535) return cudaErrorInvalidConfiguration;
+    dim3 grid((unsigned)((p.n + ING_E - 1) / ING_E), p.batch, p.k);
+    k_ingest_direct<<<grid, ING_THREADS, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_ingest(const int16_t* src, uint8_t* plane, uint64_t n, uint32_t nc, uint32_t batch, uint32_t Bp,
                           cudaStream_t s) {
     dim3 grid((unsigned)n, (Bp + 31) / 32);
@@ -699,6 +770,37 @@ __device__ __forceinline__ void accumulate_ladder(u128 x, const ModInfo& m, cons
     });
 }
 
+/* The shape nearly every cast modulus has (FracInfo::t4: five or six stages
+ * of four digits, widths 5,[5,]4,3,2,1) as straight-line code: no stage loop,
+ * no length dispatch, accumulator words at fixed offsets.  The last of six
+ * stages may hold fewer than four digits; it is run as four all the same (its
+ * missing digits come out zero), which can touch one word past the layout:
+ * launch_sign sizes the accumulators with that word of slack. */
+__device__ __forceinline__ void accumulate_t4(u128 x, const ModInfo& m, const gc::FracInfo& fi, uint32_t* acc) {
+    uint32_t n[5];
+    gc::frac_init(x, fi, n);
+    const uint32_t c1 = 65536u - m.q, c2 = 0u - (m.q << 16), mq = m.mq;
+    const uint32_t multm = fi.mult[1];
+    auto quad = [&](uint32_t r, uint32_t* a) {
+        const uint32_t q1 = gc::mulhi32(r, mq);
+        const uint32_t q2 = gc::mulhi32(q1, mq);
+        const uint32_t q3 = gc::mulhi32(q2, mq);
+        const uint32_t q4 = gc::mulhi32(q3, mq);
+        a[0] += r + q1 * c1 + q2 * c2;
+        a[SIGN_THREADS] += q2 + q3 * c1 + q4 * c2;
+    };
+    uint32_t* a = acc;
+    quad(gc::frac_stage(n, fi.mult[0], 5), a);
+    if (fi.nst == 6) {
+        a += 2 * SIGN_THREADS;
+        quad(gc::frac_stage(n, multm, 5), a);
+    }
+    quad(gc::frac_stage(n, multm, 4), a + 2 * SIGN_THREADS);
+    quad(gc::frac_stage(n, multm, 3), a + 4 * SIGN_THREADS);
+    quad(gc::frac_stage(n, multm, 2), a + 6 * SIGN_THREADS);
+    quad(gc::frac_stage(n, fi.mult[fi.nst - 1], 1), a + 8 * SIGN_THREADS);
+}
+
 /* compress(acc mod q) and the colour of the sum; absolute digit layout
  * (accumulate) */
 __device__ __forceinline__ u128 compress_acc(const uint32_t* acc, const ModInfo& m, uint32_t& colour) {
@@ -759,14 +861,16 @@ __device__ __forceinline__ void half_gate_ladder(u128 E, u128 G, const ModInfo& 
     uint32_t ne[5], ng[5];
     gc::frac_init(E, fi, ne);
     gc::frac_init(G, fi, ng);
-    const uint32_t q = m.q, mq = m.mq, c1 = 65536u - q, c2 = 0u - (q << 16), qq = q | (q << 16);
+    const uint32_t q = m.q, mq = m.mq, c1 = 65536u - q, c2 = 0u - (q << 16), qq = q | (q << 16), nq = 0u - q;
     const uint32_t topmask = 0xffffffffu >> (8 * ((4u - (m.nc & 3u)) & 3u));
-    const uint64_t wstride = 4ull * Bp;
+    uint32_t wstride32 = 4u * Bp;
+    asm volatile("" : "+r"(wstride32)); /* keep the stride in a register (else re-read from the parameter bank per word) */
+    const uint64_t wstride = wstride32;
     uint32_t d = (m.nc + 3u) & ~3u; /* digits not yet delivered, rounded up to whole words */
     uint32_t s = 0;
     const uint32_t cnt = fi.ladder;
-    bool first = true;
-    auto stage = [&](uint32_t len, uint32_t re, uint32_t rg) {
+    bool first = true; /* only a stage of the widest loop can be the first one */
+    auto stage = [&](uint32_t len, uint32_t re, uint32_t rg, bool first) {
         const uint32_t nw = (len + 3u) >> 2;
         d -= 4 * nw;
         const uint8_t* xp = xin + (uint64_t)(d >> 2) * wstride;
@@ -787,21 +891,21 @@ __device__ __forceinline__ void half_gate_ladder(u128 E, u128 G, const ModInfo& 
             const uint32_t v0 = tt * __byte_perm(xw, 0, 0x4140) + pe0 + qq - pg0;
             const uint32_t v1 = tt * __byte_perm(xw, 0, 0x4342) + pe1 + qq - pg1;
             uint32_t a0 = v0 & 0xffffu, a1 = v0 >> 16, a2 = v1 & 0xffffu, a3 = v1 >> 16;
-            a0 -= gc::mulhi32(a0, mq) * q;
-            a1 -= gc::mulhi32(a1, mq) * q;
-            a2 -= gc::mulhi32(a2, mq) * q;
-            a3 -= gc::mulhi32(a3, mq) * q;
+            a0 += gc::mulhi32(a0, mq) * nq;
+            a1 += gc::mulhi32(a1, mq) * nq;
+            a2 += gc::mulhi32(a2, mq) * nq;
+            a3 += gc::mulhi32(a3, mq) * nq;
             *reinterpret_cast<uint32_t*>(op) = a0 | (a1 << 8) | (a2 << 16) | (a3 << 24);
             op += wstride;
         }
-        first = false;
     };
 #define DASHB_HG_STEP(W)                                                        \
     _Pragma("unroll 1") for (uint32_t c = (cnt >> (4 * ((W)-1))) & 15u; c; --c, ++s) { \
         const uint32_t mult = fi.mult[s];                                         \
         const uint32_t re = gc::frac_stage(ne, mult, (W));                        \
         const uint32_t rg = gc::frac_stage(ng, mult, (W));                        \
-        stage(fi.desc[s] & 0xffu, re, rg);                                        \
+        stage(fi.desc[s] & 0xffu, re, rg, (W) == 5 && first);                     \
+        first = false;                                                            \
     }
     DASHB_HG_STEP(5)
     DASHB_HG_STEP(4)
@@ -882,6 +986,7 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
         asm volatile("" : "+r"(plan_off));
         const gc::FracInfo& fi = *reinterpret_cast<const gc::FracInfo*>(reinterpret_cast<const char*>(&P) + plan_off);
         const bool ladder = DASHB_FRAC && fi.nst != 0;
+        const bool t4 = ladder && fi.t4 != 0;
         const uint32_t nwords = ladder ? fi.words : (C.nc + 1) / 2;
         for (uint32_t w = 0; w < nwords; ++w) acc[w * SIGN_THREADS] = 0;
         /* Ciphertext rows are requested ahead of the hashes that separate
@@ -902,7 +1007,9 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
                 const u128 crow = ldg128(cast1_e + (cnt1 + (uint32_t)j * M.q + c0));
                 lab = gc::sub128(crow, hash(aes, lab));
             }
-            if (ladder)
+            if (t4)
+                accumulate_t4(lab, C, fi, acc);
+            else if (ladder)
                 accumulate_ladder(lab, C, fi, acc);
             else
                 accumulate(lab, C, acc);
@@ -1149,7 +1256,7 @@ cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s) {
     /* k_sign: two digit sums per word; a modulus with a plan uses the stage-local pair layout */
     uint32_t acc_words = 0;
     for (int i = 0; i < p.n_mrs; ++i)
-        acc_words = max(acc_words, (DASHB_FRAC && p.castf[i].nst) ? p.castf[i].words : (p.cast[i].nc + 1) / 2);
+        acc_words = max(acc_words, (DASHB_FRAC && p.castf[i].nst) ? p.castf[i].words + 1 /* accumulate_t4 */ : (p.cast[i].nc + 1) / 2);
     const size_t smem = (size_t)acc_words * SIGN_THREADS * sizeof(uint32_t);
     /* latency mode: one warp per (element, inference) while that still leaves SMs idle otherwise */
     static const long wide_max = getenv("DASHB_WIDE_MAX") ? atol(getenv("DASHB_WIDE_MAX")) : 8192;

@@ -84,6 +84,18 @@ struct SignParams {
     int lanes;               /* sub-batch lanes evaluating concurrently (picks latency vs throughput kernel) */
 };
 
+/* k_ingest_direct: labels read straight from the caller's (pinned, mapped)
+ * host buffers into the digit planes, all moduli in one launch */
+struct IngestParams {
+    const int16_t* src[MAXK]; /* device-visible address of the lane's first inference, int16 [batch][n][nc_j] */
+    const int16_t* end[MAXK]; /* one past the last digit the lane may read */
+    uint8_t* plane[MAXK];
+    uint32_t nc[MAXK];
+    uint64_t n;
+    uint32_t batch, Bp;
+    int k;
+};
+
 struct ProjParams {
     const uint8_t* in[MAXK];
     uint8_t* out[MAXK];
@@ -233,6 +245,7 @@ void host_aes_tables(const uint32_t** te0, const uint32_t** te1, const uint32_t*
 
 cudaError_t launch_ingest(const int16_t* src, uint8_t* plane, uint64_t n, uint32_t nc, uint32_t batch, uint32_t Bp,
                           cudaStream_t s);
+cudaError_t launch_ingest_direct(const IngestParams& p, cudaStream_t s);
 cudaError_t launch_egress(const uint8_t* plane, int16_t* dst, uint64_t n, uint32_t nc, uint32_t batch, uint32_t Bp,
                           cudaStream_t s);
 cudaError_t launch_ingest_compressed(const void* src, uint8_t* plane, uint64_t n, const gc::ModInfo& m, uint32_t batch, uint32_t Bp,

@@ -274,3 +274,41 @@ def test_compressed_wire_labels(gpu, name, batch):
         assert np.array_equal(a, b)
     assert_labels_equal(c.move_outputs(), want, "int16 outputs after compressed inputs")
     c.close()
+
+
+@pytest.mark.parametrize("name", ["MLP_TINY", "CONV_UNIT", "RESCALE_2_3"])
+@pytest.mark.parametrize("batch,skew", [(1, 0), (37, 1), (130, 3), (256, 5)])
+def test_direct_ingest_from_pinned_host_memory(gpu, name, batch, skew):
+    """Pinned (mapped) host buffers are read by k_ingest_direct itself, without
+    the staging copy; the labels it lays out must be those of the staged path
+    (pageable numpy buffers).  `skew` shifts every buffer by that many int16
+    from its allocation, so the 16-byte windows of the kernel start at every
+    possible misalignment, and the buffers end exactly at the last digit."""
+    import ctypes as C
+
+    import torch
+
+    from dash_b200.api import _check, _ptr_array
+
+    g = Golden(name)
+    c = gpu.Circuit.load(g.gcm, max_batch=batch)
+    labels = tile_batch(g.inputs, batch)
+    want = c.evaluate(labels)  # pageable numpy arrays: staged path
+    pinned, views = [], []
+    for l in labels:
+        t = torch.empty(l.size + skew, dtype=torch.int16).pin_memory()
+        v = t[skew:].view(l.shape)
+        v.numpy()[...] = l
+        pinned.append(t)
+        views.append(v)
+    out = [torch.empty(w.shape, dtype=torch.int16).pin_memory() for w in want]
+    in_ptrs = (C.c_void_p * len(views))(*[v.data_ptr() for v in views])
+    out_ptrs = (C.c_void_p * len(out))(*[o.data_ptr() for o in out])
+    _check(c.L.dashb_evaluate(c.h, in_ptrs, batch, out_ptrs))
+    assert_labels_equal([o.numpy() for o in out], want, "%s pinned inputs (direct ingest)" % name)
+    # the separate calls: move_inputs from pinned memory, evaluate on the device, outputs back
+    _check(c.L.dashb_move_inputs(c.h, in_ptrs, batch))
+    c.batch = batch
+    c.evaluate_device()
+    assert_labels_equal(c.move_outputs(), want, "%s pinned inputs, separate calls" % name)
+    c.close()
