@@ -34,6 +34,14 @@ CACHE = os.environ.get("DASHB_CACHE", "/tmp/dashb_cache")
 SEED = 42
 
 
+def git_blob_hash(path):
+    """What `git hash-object` prints for the file (the .git directory does not travel to the GPU box)."""
+    import hashlib
+
+    data = open(path, "rb").read()
+    return hashlib.sha1(b"blob %d\0" % len(data) + data).hexdigest()
+
+
 def host_threads():
     try:
         return len(os.sched_getaffinity(0))
@@ -285,26 +293,51 @@ def main():
     ms_comp = timed(step_compressed, args.steps, args.warmup)
     values_ok = bool(ok_t.numpy().all())
     circ.move_inputs(in_np)  # restore the label inputs for the profiling pass
-    # per-kernel durations for the roofline: same steps with the sub-batch
-    # lanes serialised on one stream and a CUDA event pair around every layer
-    circ.set_layer_timing(True)
+    # Per-kernel durations for the roofline, taken in the step as it runs (sub-batch lanes concurrent on their own
+    # streams): an event on the lane's stream before and after every layer (dashb_set_layer_timing(2)).  A layer
+    # type's busy time is the union of its (lane, layer) intervals; it can never exceed the step it is part of.
+    circ.set_layer_timing(2)
     prof_steps = min(args.steps, 20)
-    acc = None
-    for _ in range(3 + prof_steps):
+    busy = {}       # layer type -> union of its intervals, ms summed over the profiled steps
+    launch_ms = {}  # layer type -> [duration of every (lane, layer) launch]
+    prof_step_ms = 0.0
+
+    def union_ms(iv):
+        tot, end = 0.0, None
+        for a, b in sorted(iv):
+            if end is None or a > end:
+                tot += b - a
+                end = b
+            elif b > end:
+                tot += b - end
+                end = b
+        return tot
+
+    for it in range(3 + prof_steps):
         flush.zero_()
         torch.cuda.synchronize()
         step_device()
-        lm = circ.layer_times_ms()
-        if _ >= 3:
-            acc = lm if acc is None else [(n, a + b) for (n, a), (_n, b) in zip(acc, lm)]
-    layer_ms = [(n, v / prof_steps) for n, v in acc]
-    circ.set_layer_timing(False)
+        if it < 3:
+            continue
+        by = {}
+        last = 0.0
+        for name, _li, _lane, a, b in circ.layer_intervals_ms():
+            by.setdefault(name, []).append((a, b))
+            launch_ms.setdefault(name, []).append(b - a)
+            last = max(last, b)
+        prof_step_ms += last
+        for name, iv in by.items():
+            busy[name] = busy.get(name, 0.0) + union_ms(iv)
+    circ.set_layer_timing(0)
     time.sleep(0.1)
     sampler.stop()
+    busy = {n: v / prof_steps for n, v in busy.items()}
+    prof_step_ms /= prof_steps
 
     total_inf = B * world * args.steps
     value = total_inf / (ms_dev / 1e3)
     e2e_value = total_inf / (ms_e2e / 1e3)
+    ms_step = ms_dev / args.steps
 
     # ---- roofline of the dominant kernel (the fused sign/ReLU gadget) -----
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
@@ -312,37 +345,57 @@ def main():
         peak, peak_src = json.load(open(peaks_path))["hbm_gbs"], "measured (MEASURED_PEAKS.json)"
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    relu_ms = sum(ms for (name, ms) in layer_ms if name == "approx_relu")
+    relu_ms = busy.get("approx_relu", 0.0)
+    if relu_ms > 1.05 * max(ms_step, prof_step_ms):
+        raise RuntimeError("roofline: ReLU busy time %.3f ms exceeds the step it is part of (%.3f ms)" % (relu_ms, ms_step))
     relu_layers = [i for i in range(circ.n_layers) if circ.layer_type(i) == 3]
     relu_bytes = sum(circ.algorithmic_bytes(i) for i in relu_layers) * B
     relu_aes = sum(circ.aes_blocks(i) for i in relu_layers) * B
+    relu_units = sum(circ.layer_size(i) for i in relu_layers) * B  # (element, inference) pairs per step
     achieved = relu_bytes / (relu_ms / 1e3) / 1e9 if relu_ms > 0 else 0.0
-    step_ms = sum(ms for (_, ms) in layer_ms)
-    by_type = {}
-    for name, ms in layer_ms:
-        by_type[name] = by_type.get(name, 0.0) + ms
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    n_lanes = circ.L.dashb_lanes_used(circ.h)
+    n_launch = max(1, len(relu_layers) * n_lanes)
+    relu_launch = launch_ms.get("approx_relu", [0.0])
+    # DRAM traffic / issue statistics of the same kernel: one `ncu --set full` capture, valid only for the
+    # kernels.cu it was taken from (git blob hash stored with it; tools/make_traffic.py writes the file)
+    traffic, capture = None, None
+    tpath = os.path.join(ROOT, "profiles", "r2_traffic.json")
     if os.path.exists(tpath) and args.model == "MODEL_B_POOL_REPL" and B == 256:
         tj = json.load(open(tpath))
-        traffic = tj["k_sign_relu_dram_bytes_per_step"] / tj["k_sign_relu_launches_per_step"]
-    n_lanes = 4 if B >= 128 else (2 if B >= 64 else 1)
-    n_lanes = int(os.environ.get("DASHB_LANES", n_lanes))
+        if tj.get("kernels_cu_blob") == git_blob_hash(os.path.join(ROOT, "dash_b200", "csrc", "kernels.cu")):
+            capture = tj["k_sign_relu"]
+            # per launch like `achieved`: the captured launch's DRAM bytes per (element, inference) times the
+            # average launch's (element, inference) count
+            traffic = capture["dram_bytes_per_element_inference"] * relu_units / n_launch
+        else:
+            capture = {"stale": "profiles/r2_traffic.json was captured from another kernels.cu; traffic withheld"}
+    aes_peaks = json.load(open(os.path.join(ROOT, "profiles", "aes_peaks.json")))
+    aes_rate = relu_aes / (relu_ms / 1e3) if relu_ms > 0 else 0.0
     roofline = {
         "bound": "hbm", "kernel": "k_sign<relu> (fused sign gadget + half gates)", "achieved": achieved, "peak": peak,
         "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-        "algorithmic_bytes_per_launch": relu_bytes / max(1, len(relu_layers) * n_lanes),
-        "launches_per_step": len(relu_layers) * n_lanes,
-        "avg_layer_ms": relu_ms / max(1, len(relu_layers)),
-        "timing": "CUDA events around every layer, sub-batch lanes serialised on the library stream, %d steps after the timed region" % prof_steps,
-        "share_of_step": relu_ms / step_ms if step_ms else None,
-        "aes_blocks_per_s": relu_aes / (relu_ms / 1e3) if relu_ms > 0 else 0.0,
+        "algorithmic_bytes_per_launch": relu_bytes / n_launch,
+        "launches_per_step": n_launch,
+        "element_inferences_per_launch": relu_units / n_launch,
+        "busy_ms_per_step": relu_ms,
+        "avg_launch_ms": sum(relu_launch) / len(relu_launch),
+        "min_max_launch_ms": [min(relu_launch), max(relu_launch)],
+        "timing": "CUDA events on the lane streams around every layer inside the concurrent step (4 sub-batch lanes), "
+                  "%d steps after the timed region; busy time = union of the lanes' intervals" % prof_steps,
+        "step_ms_in_timing_pass": prof_step_ms,
+        "share_of_step": relu_ms / prof_step_ms if prof_step_ms else None,
+        "aes_blocks_per_s": aes_rate,
         "aes_blocks_per_s_in_step": circ.aes_blocks(-1) * B * args.steps / (ms_dev / 1e3),
-        "aes_only_kernel_peak_blocks_per_s": 19.1e9,
-        "aes_peak_source": "tools/aes_probe.cu on a B200, same 4 KB shared-memory T-table layout (profiles/r1_aes_probe.md)",
-        "note": "compute-bound on AES + base-q digit arithmetic, not on HBM (see DESIGN.md)",
-        "whole_step_algorithmic_GBps": circ.algorithmic_bytes(-1) * B / (step_ms / 1e3) / 1e9 if step_ms else None,
-        "layer_ms": by_type,
+        "aes_peak_4kb_tables": aes_peaks["aes_peak_4kb_tables"],
+        "aes_peak_conflict_free": aes_peaks["aes_peak_conflict_free"],
+        "aes_frac_of_4kb_tables_peak": aes_rate / aes_peaks["aes_peak_4kb_tables"]["blocks_per_s"],
+        "aes_frac_of_conflict_free_peak": aes_rate / aes_peaks["aes_peak_conflict_free"]["blocks_per_s"],
+        "ncu_capture": capture,
+        "issue_slot_frac": capture.get("issue_slot_frac") if capture else None,
+        "warp_instructions_per_element": capture.get("warp_instructions_per_element") if capture else None,
+        "note": "issue-bound on AES T-table lookups + base-q digit arithmetic, not on HBM (see DESIGN.md)",
+        "whole_step_algorithmic_GBps": circ.algorithmic_bytes(-1) * B / ms_step / 1e6,
+        "busy_ms_by_layer_type": busy,
     }
 
     line = {

@@ -60,6 +60,8 @@ def lib():
         L.dashb_output_modulus.argtypes = [C.c_void_p, C.c_int]
         L.dashb_crt_modulus.argtypes = [C.c_void_p, C.c_int]
         L.dashb_layer_type.argtypes = [C.c_void_p, C.c_int]
+        L.dashb_layer_size.restype = C.c_uint64
+        L.dashb_layer_size.argtypes = [C.c_void_p, C.c_int]
         for f in (L.dashb_algorithmic_bytes, L.dashb_aes_blocks, L.dashb_reference_aes_blocks):
             f.restype = C.c_double
             f.argtypes = [C.c_void_p, C.c_int]
@@ -71,6 +73,8 @@ def lib():
         L.dashb_layer_slice.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.dashb_set_layer_timing.argtypes = [C.c_void_p, C.c_int]
         L.dashb_layer_time_ms.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float)]
+        L.dashb_lanes_used.argtypes = [C.c_void_p]
+        L.dashb_layer_interval_ms.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         L.dashb_circuit_destroy.argtypes = [C.c_void_p]
         L.dashb_hostcheck_compress.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
         L.dashb_hostcheck_digits.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
@@ -277,8 +281,23 @@ class Circuit:
     def layer_type(self, layer):
         return self.L.dashb_layer_type(self.h, layer)
 
+    def layer_size(self, layer):
+        return self.L.dashb_layer_size(self.h, layer)
+
     def set_layer_timing(self, enabled):
-        _check(self.L.dashb_set_layer_timing(self.h, int(bool(enabled))))
+        """False/0 off, True/1 per-layer events with the lanes serialised, 2 per-(lane, layer) intervals in the
+        concurrent step (layer_intervals_ms)."""
+        _check(self.L.dashb_set_layer_timing(self.h, int(enabled)))
+
+    def layer_intervals_ms(self):
+        """[(layer name, layer index, lane, begin ms, end ms)] of the last evaluation in timing mode 2."""
+        out = []
+        for lane in range(self.L.dashb_lanes_used(self.h)):
+            for i in range(self.n_layers):
+                a, b = C.c_float(0), C.c_float(0)
+                _check(self.L.dashb_layer_interval_ms(self.h, lane, i, C.byref(a), C.byref(b)))
+                out.append((LAYER_NAMES.get(self.layer_type(i), "?"), i, lane, a.value, b.value))
+        return out
 
     def layer_times_ms(self):
         """Per layer-type device time of the last timed evaluation, keyed like

@@ -451,10 +451,15 @@ struct dashb_circuit {
     uint64_t out_n{0};   /* labels per inference in the lanes' current tensors */
     int out_q[MAXK];     /* their moduli */
     uint64_t launches{0};
-    bool timing{false};
+    int timing{0}; /* 0 off, 1 per-layer events with the lanes serialised, 2 per-(lane, layer) events in the concurrent step */
     std::vector<cudaEvent_t> ev;
+    std::vector<cudaEvent_t> iv;  /* mode 2: [lane][layer][begin, end] */
+    std::vector<float> iv_ms;     /* ... as milliseconds since the step began */
+    cudaEvent_t iv_t0{nullptr};
     ~dashb_circuit() {
         for (auto e : ev) cudaEventDestroy(e);
+        for (auto e : iv) cudaEventDestroy(e);
+        if (iv_t0) cudaEventDestroy(iv_t0);
         if (ev_fork) cudaEventDestroy(ev_fork);
         if (copy_s) cudaStreamDestroy(copy_s);
         for (auto x : copy_x)
@@ -1589,7 +1594,7 @@ static int run_layers(dashb_circuit* c, int upto) {
         c->lanes[i]->t_cur = c->lanes[i]->t_in;
         c->lanes[i]->which = 0;
     }
-    if (c->timing) {
+    if (c->timing == 1) {
         CU(cudaEventRecord(c->ev[0], g_stream));
         for (int li = 0; li <= upto; ++li) {
             for (int i = 0; i < c->lanes_used; ++i)
@@ -1597,10 +1602,27 @@ static int run_layers(dashb_circuit* c, int upto) {
             CU(cudaEventRecord(c->ev[li + 1], g_stream));
         }
     } else {
+        /* mode 2: the step as it always runs (lanes concurrent), with an event
+         * on the lane's stream before and after every layer */
+        const bool trace = c->timing == 2;
+        const size_t nl = c->layers.size();
+        if (trace) {
+            const size_t need = c->lanes.size() * nl * 2;
+            while (c->iv.size() < need) {
+                cudaEvent_t e;
+                CU(cudaEventCreate(&e));
+                c->iv.push_back(e);
+            }
+            if (!c->iv_t0) CU(cudaEventCreate(&c->iv_t0));
+            CU(cudaEventRecord(c->iv_t0, g_stream));
+        }
         if ((rc = fork_lanes(c))) return rc;
         for (int li = 0; li <= upto; ++li)
-            for (int i = 0; i < c->lanes_used; ++i)
+            for (int i = 0; i < c->lanes_used; ++i) {
+                if (trace) CU(cudaEventRecord(c->iv[(i * nl + li) * 2], c->lanes[i]->s));
                 if ((rc = run_layer(c, *c->lanes[i], li, c->lanes[i]->s))) return rc;
+                if (trace) CU(cudaEventRecord(c->iv[(i * nl + li) * 2 + 1], c->lanes[i]->s));
+            }
         if ((rc = join_lanes(c))) return rc;
     }
     if (upto >= 0) {
@@ -1691,9 +1713,17 @@ int dashb_evaluate_device(dashb_circuit* c) {
         return fail(DASHB_ESTATE, "channel-sharded circuit: use dashb_evaluate_layers and gather between layer groups");
     int rc = run_layers(c, (int)c->layers.size() - 1);
     if (rc) return rc;
-    if (c->timing) {
+    if (c->timing == 1) {
         CU(cudaStreamSynchronize(g_stream));
         for (size_t i = 0; i < c->layers.size(); ++i) CU(cudaEventElapsedTime(&c->layers[i]->ms, c->ev[i], c->ev[i + 1]));
+    } else if (c->timing == 2) {
+        CU(cudaStreamSynchronize(g_stream));
+        const size_t nl = c->layers.size();
+        c->iv_ms.assign(c->lanes.size() * nl * 2, 0.f);
+        for (int i = 0; i < c->lanes_used; ++i)
+            for (size_t li = 0; li < nl; ++li)
+                for (int x = 0; x < 2; ++x)
+                    CU(cudaEventElapsedTime(&c->iv_ms[(i * nl + li) * 2 + x], c->iv_t0, c->iv[(i * nl + li) * 2 + x]));
     }
     return DASHB_OK;
 }
@@ -1745,7 +1775,7 @@ int dashb_move_outputs(dashb_circuit* c, int16_t* const* out) {
 static int evaluate_any(dashb_circuit* c, const void* const* in, uint64_t batch, void* const* out, bool compressed) {
     if (!c || !in || !out) return fail(DASHB_EINVAL, "null argument");
     if (!c->finalized) return fail(DASHB_ESTATE, "circuit not finalized");
-    if (c->timing) { /* serialised, per-layer events */
+    if (c->timing == 1) { /* serialised, per-layer events */
         int rc = move_inputs_any(c, in, batch, compressed);
         if (rc) return rc;
         if ((rc = dashb_evaluate_device(c))) return rc;
@@ -1825,8 +1855,8 @@ int dashb_layer_outputs(dashb_circuit* c, int layer, int16_t* const* out) {
     if (!c || !out) return fail(DASHB_EINVAL, "null argument");
     if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "no inputs moved");
     if (layer < 0 || layer >= (int)c->layers.size()) return fail(DASHB_EINVAL, "layer index out of range");
-    const bool t = c->timing;
-    c->timing = false;
+    const int t = c->timing;
+    c->timing = 0;
     int rc = run_layers(c, layer);
     c->timing = t;
     if (rc) return rc;
@@ -1882,6 +1912,9 @@ int dashb_crt_base_size(const dashb_circuit* c) { return c ? c->k : 0; }
 int dashb_crt_modulus(const dashb_circuit* c, int j) { return (c && j >= 0 && j < c->k) ? c->crt[j] : 0; }
 int dashb_output_modulus(const dashb_circuit* c, int j) { return (c && j >= 0 && j < c->k) ? c->cur_q[j] : 0; }
 uint64_t dashb_last_launch_count(const dashb_circuit* c) { return c ? c->launches : 0; }
+uint64_t dashb_layer_size(const dashb_circuit* c, int layer) {
+    return (c && layer >= 0 && layer < (int)c->layers.size()) ? c->layers[layer]->out_size : 0;
+}
 int dashb_layer_type(const dashb_circuit* c, int layer) {
     return (c && layer >= 0 && layer < (int)c->layers.size()) ? c->layers[layer]->type : 0;
 }
@@ -1904,7 +1937,18 @@ double dashb_reference_aes_blocks(const dashb_circuit* c, int layer) { return la
 
 int dashb_set_layer_timing(dashb_circuit* c, int enabled) {
     if (!c) return fail(DASHB_EINVAL, "null circuit");
-    c->timing = enabled != 0;
+    if (enabled < 0 || enabled > 2) return fail(DASHB_EINVAL, "timing mode %d (0 off, 1 serialised, 2 concurrent intervals)", enabled);
+    c->timing = enabled;
+    return DASHB_OK;
+}
+int dashb_lanes_used(const dashb_circuit* c) { return c ? c->lanes_used : 0; }
+int dashb_layer_interval_ms(dashb_circuit* c, int lane, int layer, float* begin_ms, float* end_ms) {
+    if (!c || !begin_ms || !end_ms || layer < 0 || layer >= (int)c->layers.size() || lane < 0 || lane >= c->lanes_used)
+        return fail(DASHB_EINVAL, "bad argument");
+    const size_t at = ((size_t)lane * c->layers.size() + (size_t)layer) * 2;
+    if (at + 1 >= c->iv_ms.size()) return fail(DASHB_ESTATE, "no evaluation in timing mode 2 yet");
+    *begin_ms = c->iv_ms[at];
+    *end_ms = c->iv_ms[at + 1];
     return DASHB_OK;
 }
 int dashb_layer_time_ms(dashb_circuit* c, int layer, float* ms) {

@@ -320,6 +320,16 @@ double dashb_reference_aes_blocks(const dashb_circuit* c, int layer);
  * last evaluation run with profiling enabled; keys are layer indices. */
 int dashb_set_layer_timing(dashb_circuit* c, int enabled);
 int dashb_layer_time_ms(dashb_circuit* c, int layer, float* ms);
+/* enabled = 2: the step runs as always (sub-batch lanes concurrent on their
+ * own streams) with an event on the lane's stream before and after every
+ * layer; after dashb_evaluate_device, dashb_layer_interval_ms gives the
+ * interval [begin, end] of (lane, layer) in milliseconds since the step
+ * began.  A layer's busy time in the step is the union of its lanes'
+ * intervals.  (enabled = 1 serialises the lanes on one stream instead.) */
+int dashb_lanes_used(const dashb_circuit* c);
+int dashb_layer_interval_ms(dashb_circuit* c, int lane, int layer, float* begin_ms, float* end_ms);
+/* Labels leaving layer `layer` per inference. */
+uint64_t dashb_layer_size(const dashb_circuit* c, int layer);
 /* Layer type of layer `layer` (DASHB_LAYER_*). */
 int dashb_layer_type(const dashb_circuit* c, int layer);
 
