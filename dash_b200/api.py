@@ -106,7 +106,8 @@ def stream_handle():
     return lib().dashb_stream()
 
 
-LAYER_NAMES = {1: "dense", 2: "conv2d", 3: "approx_relu", 4: "sign", 5: "rescale", 6: "rescale", 7: "projection"}
+LAYER_NAMES = {1: "dense", 2: "conv2d", 3: "approx_relu", 4: "sign", 5: "rescale", 6: "rescale", 7: "projection",
+               8: "max_pool"}
 
 
 def _ptr_array(arrs):

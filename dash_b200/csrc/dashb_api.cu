@@ -391,6 +391,8 @@ struct Layer {
     /* projection */
     int in_q[MAXK];
     DevMem proj[MAXK];
+    /* max pooling */
+    uint32_t pl_w{0}, pl_h{0}, pl_c{0}, pl_kw{0}, pl_kh{0}, pl_sw{0}, pl_sh{0}, pl_ow{0}, pl_oh{0};
     /* channel sharding: output elements [e0, e1) / linear rows [v0, v1) of this rank */
     uint64_t e0{0}, e1{0};
     uint32_t v0{0}, v1{0};
@@ -408,6 +410,7 @@ struct Lane {
     cudaEvent_t done{nullptr}, in_done{nullptr}, ing_done{nullptr};
     cudaEvent_t in_done_x[3] = {nullptr, nullptr, nullptr}; /* the lane's copies on the further copy streams */
     DevMem buf_in, buf_a, buf_b, stage_in, stage_out, xvals;
+    DevMem pool; /* max pooling: the ReLU gadget's input (y - x) and output, two tensors of the layer's output size */
     Tensor t_in, t_cur;
     int which{0};
     uint32_t b0{0}, batch{0}, Bp{0};
@@ -434,9 +437,17 @@ struct dashb_circuit {
     uint64_t max_batch{0};
     uint32_t batch{0};
     std::vector<std::unique_ptr<Lane>> lanes;
+    int n_lanes{0};
     int lanes_used{0};
+    /* dashb_evaluate_async: a second set of lanes so that two steps are in
+     * flight (step n+1's inputs cross PCIe while step n computes) */
+    std::vector<std::unique_ptr<Lane>> lanes_alt;
+    cudaEvent_t async_done[2] = {nullptr, nullptr};
+    bool async_busy[2] = {false, false};
+    int async_next{0};
     int shard_rank{0}, shard_world{1};
     uint32_t lane_cap{0};
+    std::vector<uint32_t> lane_weights; /* DASHB_LANE_SPLIT */
     cudaEvent_t ev_fork{nullptr};
     cudaStream_t copy_s{nullptr};   /* H2D copies of the pipelined dashb_evaluate */
     static constexpr int MAX_COPY = 4;
@@ -465,6 +476,9 @@ struct dashb_circuit {
         for (auto x : copy_x)
             if (x) cudaStreamDestroy(x);
         if (ingest_s) cudaStreamDestroy(ingest_s);
+        for (auto e : async_done)
+            if (e) cudaEventDestroy(e);
+        for (auto& l : lanes_alt) lanes.push_back(std::move(l));
         for (auto& l : lanes) {
             if (l->done) cudaEventDestroy(l->done);
             if (l->in_done) cudaEventDestroy(l->in_done);
@@ -565,6 +579,8 @@ void fill_sign_params(dashb_circuit* c, SignParams& p, uint64_t n, int n_out) {
     p.S = S;
     p.Mp = Mp;
     p.carry0 = c->carry0;
+    p.tab_mul = 1;
+    p.tab_add = 0;
 }
 
 double sign_inner_aes_ref(const dashb_circuit* c) {
@@ -829,6 +845,43 @@ int dashb_add_relu(dashb_circuit* c, uint64_t n, const dashb_u128* approx, const
     for (int j = 0; j < c->k; ++j) S += (size_t)c->crt[j];
     if ((rc = upload_tables(L->garbler, garbler, n * S))) return rc;
     if ((rc = upload_tables(L->evaluator, evaluator, n * (size_t)c->k * 3))) return rc;
+    L->ref_aes = (double)n * (sign_inner_aes_ref(c) + 1 + 3.0 * c->k);
+    L->aes = (double)n * (sign_inner_aes(c) + 1);
+    L->label_bytes = (double)n * (32.0 * c->k + 16.0 * (sign_inner_aes_ref(c) + 1 + 3.0 * c->k));
+    push_layer(c, std::move(L));
+    return DASHB_OK;
+}
+
+int dashb_add_maxpool2d(dashb_circuit* c, uint64_t in_w, uint64_t in_h, uint64_t channels, uint64_t k_w, uint64_t k_h,
+                        uint64_t s_w, uint64_t s_h, const dashb_u128* approx, const dashb_u128* cast1, const dashb_u128* cast2,
+                        const dashb_u128* sign, const dashb_u128* garbler, const dashb_u128* evaluator) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if ((rc = check_all_crt(c, "maxpool2d"))) return rc;
+    if (!in_w || !in_h || !channels || !k_w || !k_h || !s_w || !s_h || k_w > in_w || k_h > in_h || in_w > 65535 || in_h > 65535)
+        return fail(DASHB_EINVAL, "maxpool2d: bad geometry");
+    if (in_w * in_h * channels != c->cur_size) return fail(DASHB_EINVAL, "maxpool2d: input size mismatch");
+    const uint64_t ow = (in_w - k_w) / s_w + 1, oh = (in_h - k_h) / s_h + 1;
+    /* the reference sizes the output tensor as (W / k_w, H / k_h, C) (circuit/layer/max_pool2d.h:26-29) and walks
+     * ((W - k_w) / s_w + 1, ...) windows (layer/garbled_maxpool2d.h:150-153): only shapes where the two agree are defined */
+    if (ow != in_w / k_w || oh != in_h / k_h)
+        return fail(DASHB_EINVAL, "maxpool2d: %llux%llu windows do not match the reference's %llux%llu output tensor",
+                    (unsigned long long)ow, (unsigned long long)oh, (unsigned long long)(in_w / k_w), (unsigned long long)(in_h / k_h));
+    if (c->shard_world > 1) return fail(DASHB_EINVAL, "maxpool2d: not available in channel-sharded circuits");
+    const uint64_t n_out = ow * oh * channels, T = k_w * k_h, n = n_out * T;
+    auto L = std::make_unique<Layer>();
+    L->type = DASHB_LAYER_MAXPOOL2D;
+    L->in_size = c->cur_size;
+    L->out_size = n_out;
+    for (int j = 0; j < c->k; ++j) L->out_q[j] = c->crt[j];
+    if ((rc = add_sign_common(c, *L, n, 1, approx, cast1, cast2, sign))) return rc;
+    size_t S = 0;
+    for (int j = 0; j < c->k; ++j) S += (size_t)c->crt[j];
+    if ((rc = upload_tables(L->garbler, garbler, n * S))) return rc;
+    if ((rc = upload_tables(L->evaluator, evaluator, n * (size_t)c->k * 3))) return rc;
+    L->pl_w = (uint32_t)in_w, L->pl_h = (uint32_t)in_h, L->pl_c = (uint32_t)channels;
+    L->pl_kw = (uint32_t)k_w, L->pl_kh = (uint32_t)k_h, L->pl_sw = (uint32_t)s_w, L->pl_sh = (uint32_t)s_h;
+    L->pl_ow = (uint32_t)ow, L->pl_oh = (uint32_t)oh;
     L->ref_aes = (double)n * (sign_inner_aes_ref(c) + 1 + 3.0 * c->k);
     L->aes = (double)n * (sign_inner_aes(c) + 1);
     L->label_bytes = (double)n * (32.0 * c->k + 16.0 * (sign_inner_aes_ref(c) + 1 + 3.0 * c->k));
@@ -1128,8 +1181,56 @@ int dashb_set_shard(dashb_circuit* c, int rank, int world) {
     int rc = check_building(c);
     if (rc) return rc;
     if (world < 1 || rank < 0 || rank >= world) return fail(DASHB_EINVAL, "bad shard %d of %d", rank, world);
+    if (world > 1)
+        for (auto& L : c->layers)
+            if (L->type == DASHB_LAYER_MAXPOOL2D) return fail(DASHB_EINVAL, "maxpool2d: not available in channel-sharded circuits");
     c->shard_rank = rank;
     c->shard_world = world;
+    return DASHB_OK;
+}
+
+/* One set of sub-batch lanes (streams, events, input / activation / staging
+ * buffers) sized for c->lane_cap inferences per lane. */
+static int make_lanes(dashb_circuit* c, std::vector<std::unique_ptr<Lane>>& lanes) {
+    const uint32_t Bp = c->lane_cap;
+    size_t in_bytes = tensor_bytes(c->input_size, c->k, c->crt, Bp);
+    size_t act_bytes = 256;
+    size_t stage_in = 0, stage_out = 0;
+    for (int j = 0; j < c->k; ++j) stage_in += (size_t)Bp * c->input_size * c->crt_mi[j].nc * 2;
+    for (auto& L : c->layers) {
+        size_t b = tensor_bytes(L->out_size, c->k, L->out_q, Bp);
+        if (b > act_bytes) act_bytes = b;
+        size_t so = 0;
+        for (int j = 0; j < c->k; ++j) so += (size_t)Bp * L->out_size * nr_comps(L->out_q[j]) * 2;
+        if (so > stage_out) stage_out = so;
+    }
+    if (stage_in > stage_out) stage_out = stage_in; /* zero-layer circuits echo the input */
+    size_t pool_bytes = 0;
+    for (auto& L : c->layers)
+        if (L->type == DASHB_LAYER_MAXPOOL2D) pool_bytes = std::max(pool_bytes, 2 * tensor_bytes(L->out_size, c->k, L->out_q, Bp));
+    for (int i = 0; i < c->n_lanes; ++i) {
+        auto ln = std::make_unique<Lane>();
+        CU(cudaStreamCreateWithFlags(&ln->s, cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&ln->done, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&ln->in_done, cudaEventDisableTiming));
+        for (auto& x : ln->in_done_x) CU(cudaEventCreateWithFlags(&x, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&ln->ing_done, cudaEventDisableTiming));
+        CU(ln->buf_in.alloc(in_bytes));
+        CU(ln->buf_a.alloc(act_bytes));
+        CU(ln->buf_b.alloc(act_bytes));
+        CU(ln->stage_in.alloc(stage_in));
+        CU(ln->stage_out.alloc(stage_out));
+        if (c->has_ginp) CU(ln->xvals.alloc((size_t)Bp * c->input_size * 8));
+        if (pool_bytes) {
+            CU(ln->pool.alloc(pool_bytes));
+            CU(cudaMemset(ln->pool.p, 0, pool_bytes));
+        }
+        CU(cudaMemset(ln->buf_in.p, 0, in_bytes));
+        CU(cudaMemset(ln->buf_a.p, 0, act_bytes));
+        CU(cudaMemset(ln->buf_b.p, 0, act_bytes));
+        /* (asynchronous on the NULL stream: the callers end with a device synchronisation) */
+        lanes.push_back(std::move(ln));
+    }
     return DASHB_OK;
 }
 
@@ -1149,38 +1250,30 @@ int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
         if (v >= 1 && v <= 16 && c->shard_world == 1) n_lanes = v;
     }
     c->lane_cap = (uint32_t)((((max_batch + n_lanes - 1) / n_lanes) + 15) & ~15ull);
-    const uint32_t Bp = c->lane_cap;
-    size_t in_bytes = tensor_bytes(c->input_size, c->k, c->crt, Bp);
-    size_t act_bytes = 256;
-    size_t stage_in = 0, stage_out = 0;
-    for (int j = 0; j < c->k; ++j) stage_in += (size_t)Bp * c->input_size * c->crt_mi[j].nc * 2;
-    for (auto& L : c->layers) {
-        size_t b = tensor_bytes(L->out_size, c->k, L->out_q, Bp);
-        if (b > act_bytes) act_bytes = b;
-        size_t so = 0;
-        for (int j = 0; j < c->k; ++j) so += (size_t)Bp * L->out_size * nr_comps(L->out_q[j]) * 2;
-        if (so > stage_out) stage_out = so;
+    if (const char* env = getenv("DASHB_LANE_SPLIT")) {
+        if (c->shard_world == 1) {
+            uint64_t wsum = 0, wmax = 0;
+            for (const char* p = env; *p;) {
+                char* endp = nullptr;
+                const long w = strtol(p, &endp, 10);
+                if (endp == p) break;
+                if (w > 0 && c->lane_weights.size() < 16) {
+                    c->lane_weights.push_back((uint32_t)w);
+                    wsum += (uint64_t)w;
+                    wmax = std::max<uint64_t>(wmax, (uint64_t)w);
+                }
+                p = *endp ? endp + 1 : endp;
+            }
+            if (c->lane_weights.size() >= 2) {
+                n_lanes = (int)c->lane_weights.size();
+                c->lane_cap = (uint32_t)(((max_batch * wmax + wsum - 1) / wsum + 31) & ~15ull);
+            } else {
+                c->lane_weights.clear();
+            }
+        }
     }
-    if (stage_in > stage_out) stage_out = stage_in; /* zero-layer circuits echo the input */
-    for (int i = 0; i < n_lanes; ++i) {
-        auto ln = std::make_unique<Lane>();
-        CU(cudaStreamCreateWithFlags(&ln->s, cudaStreamNonBlocking));
-        CU(cudaEventCreateWithFlags(&ln->done, cudaEventDisableTiming));
-        CU(cudaEventCreateWithFlags(&ln->in_done, cudaEventDisableTiming));
-        for (auto& x : ln->in_done_x) CU(cudaEventCreateWithFlags(&x, cudaEventDisableTiming));
-        CU(cudaEventCreateWithFlags(&ln->ing_done, cudaEventDisableTiming));
-        CU(ln->buf_in.alloc(in_bytes));
-        CU(ln->buf_a.alloc(act_bytes));
-        CU(ln->buf_b.alloc(act_bytes));
-        CU(ln->stage_in.alloc(stage_in));
-        CU(ln->stage_out.alloc(stage_out));
-        if (c->has_ginp) CU(ln->xvals.alloc((size_t)Bp * c->input_size * 8));
-        CU(cudaMemset(ln->buf_in.p, 0, in_bytes));
-        CU(cudaMemset(ln->buf_a.p, 0, act_bytes));
-        CU(cudaMemset(ln->buf_b.p, 0, act_bytes));
-        /* (asynchronous on the NULL stream: dashb_finalize ends with a device synchronisation) */
-        c->lanes.push_back(std::move(ln));
-    }
+    c->n_lanes = n_lanes;
+    if ((rc = make_lanes(c, c->lanes))) return rc;
     CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     CU(cudaStreamCreateWithFlags(&c->copy_s, cudaStreamNonBlocking));
     /* A host-to-device copy of a few MB (one modulus of one lane) runs well
@@ -1231,18 +1324,40 @@ static int join_lanes(dashb_circuit* c) {
     return DASHB_OK;
 }
 
+/* Sub-batch lanes of a batch.  Equal slices by default.  DASHB_LANE_SPLIT =
+ * "w0,w1,..." cuts the batch in proportion to the weights instead (one lane
+ * per weight, at most the lanes the circuit was finalized with): a small first
+ * lane starts computing early in the pipelined dashb_evaluate, a small last
+ * one shortens the tail after the last input has arrived. */
 static int split_batch(dashb_circuit* c, uint64_t batch) {
     if (batch == 0 || batch > c->max_batch)
         return fail(DASHB_EINVAL, "batch %llu outside 1..%llu", (unsigned long long)batch, (unsigned long long)c->max_batch);
-    const int n_lanes = (int)c->lanes.size();
-    uint32_t per = (uint32_t)((((batch + n_lanes - 1) / n_lanes) + 15) & ~15ull);
-    if (per > c->lane_cap) per = c->lane_cap;
+    const int n_lanes = c->n_lanes;
     c->batch = (uint32_t)batch;
-    c->lanes_used = (int)((batch + per - 1) / per);
+    std::vector<uint32_t> sizes;
+    if (!c->lane_weights.empty() && batch >= 16ull * c->lane_weights.size()) {
+        uint64_t wsum = 0, given = 0;
+        for (uint32_t w : c->lane_weights) wsum += w;
+        for (size_t i = 0; i < c->lane_weights.size(); ++i) {
+            uint64_t sz = i + 1 == c->lane_weights.size() ? batch - given : ((batch * c->lane_weights[i] / wsum) + 15) & ~15ull;
+            sz = std::min<uint64_t>(std::min<uint64_t>(sz, batch - given), c->lane_cap);
+            if (sz) sizes.push_back((uint32_t)sz);
+            given += sz;
+        }
+        if (given != batch) sizes.clear(); /* the caps did not allow this split: equal slices */
+    }
+    if (sizes.empty()) {
+        uint32_t per = (uint32_t)((((batch + n_lanes - 1) / n_lanes) + 15) & ~15ull);
+        if (per > c->lane_cap) per = c->lane_cap;
+        for (uint64_t b0 = 0; b0 < batch; b0 += per) sizes.push_back((uint32_t)std::min<uint64_t>(per, batch - b0));
+    }
+    c->lanes_used = (int)sizes.size();
+    uint32_t b0 = 0;
     for (int i = 0; i < c->lanes_used; ++i) {
         Lane& ln = *c->lanes[i];
-        ln.b0 = (uint32_t)i * per;
-        ln.batch = (uint32_t)std::min<uint64_t>(per, batch - ln.b0);
+        ln.b0 = b0;
+        ln.batch = sizes[i];
+        b0 += sizes[i];
         ln.Bp = (ln.batch + 15) & ~15u;
         carve(ln.t_in, (uint8_t*)ln.buf_in.p, c->input_size, c->k, c->crt, ln.Bp);
         ln.t_cur = ln.t_in;
@@ -1559,6 +1674,58 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
             }
             break;
         }
+        case DASHB_LAYER_MAXPOOL2D: {
+            /* k_w k_h MaxGadget steps per output, one after the other (the running maximum feeds the next):
+             * k_pool_step forms y - x, k_sign<relu> evaluates that step's ReLU gadgets, the next
+             * k_pool_step adds the result */
+            Tensor diff, relu;
+            const size_t half = tensor_bytes(L.out_size, c->k, L.out_q, Bp);
+            carve(diff, (uint8_t*)ln.pool.p, L.out_size, c->k, L.out_q, Bp);
+            carve(relu, (uint8_t*)ln.pool.p + half, L.out_size, c->k, L.out_q, Bp);
+            PoolParams pp;
+            memset(&pp, 0, sizeof(pp));
+            pp.k = c->k;
+            pp.n_out = L.out_size;
+            pp.Bp = Bp;
+            pp.in_w = L.pl_w, pp.in_h = L.pl_h, pp.ch = L.pl_c, pp.ow = L.pl_ow, pp.oh = L.pl_oh, pp.s_w = L.pl_sw, pp.s_h = L.pl_sh;
+            for (int j = 0; j < c->k; ++j) {
+                pp.in[j] = cur.plane[j];
+                pp.cur[j] = out.plane[j];
+                pp.diff[j] = diff.plane[j];
+                pp.relu[j] = relu.plane[j];
+                pp.crt[j] = c->crt_mi[j];
+            }
+            const uint32_t T = L.pl_kw * L.pl_kh;
+            for (uint32_t t = 0; t < T; ++t) {
+                pp.l = t / L.pl_kh;
+                pp.m = t % L.pl_kh;
+                pp.mode = t == 0 ? 0 : 1;
+                CU(launch_pool_step(pp, s));
+                SignParams sp;
+                fill_sign_params(c, sp, L.out_size, 1);
+                sp.tab_mul = T;
+                sp.tab_add = t;
+                for (int j = 0; j < c->k; ++j) {
+                    sp.in[j] = diff.plane[j];
+                    sp.out[j] = relu.plane[j];
+                    sp.outm[j] = c->crt_mi[j];
+                }
+                sp.approx = (const u128*)L.approx.p;
+                sp.cast1 = (const u128*)L.cast1.p;
+                sp.cast2 = (const u128*)L.cast2.p;
+                sp.sign = (const u128*)L.sign.p;
+                sp.garbler = (const u128*)L.garbler.p;
+                sp.evaluator = (const u128*)L.evaluator.p;
+                sp.batch = B;
+                sp.Bp = Bp;
+                CU(launch_sign(sp, true, s));
+                c->launches += 2;
+            }
+            pp.mode = 2;
+            CU(launch_pool_step(pp, s));
+            c->launches += 1;
+            break;
+        }
         case DASHB_LAYER_PROJECTION: {
             ProjParams p;
             memset(&p, 0, sizeof(p));
@@ -1607,7 +1774,7 @@ static int run_layers(dashb_circuit* c, int upto) {
         const bool trace = c->timing == 2;
         const size_t nl = c->layers.size();
         if (trace) {
-            const size_t need = c->lanes.size() * nl * 2;
+            const size_t need = (size_t)c->n_lanes * nl * 2;
             while (c->iv.size() < need) {
                 cudaEvent_t e;
                 CU(cudaEventCreate(&e));
@@ -1719,7 +1886,7 @@ int dashb_evaluate_device(dashb_circuit* c) {
     } else if (c->timing == 2) {
         CU(cudaStreamSynchronize(g_stream));
         const size_t nl = c->layers.size();
-        c->iv_ms.assign(c->lanes.size() * nl * 2, 0.f);
+        c->iv_ms.assign((size_t)c->n_lanes * nl * 2, 0.f);
         for (int i = 0; i < c->lanes_used; ++i)
             for (size_t li = 0; li < nl; ++li)
                 for (int x = 0; x < 2; ++x)
@@ -1772,9 +1939,67 @@ int dashb_move_outputs(dashb_circuit* c, int16_t* const* out) {
 /* cuda_move_inputs + cuda_evaluate + cuda_move_outputs as one pipelined
  * pass: every lane copies its slice in, runs all layers and copies its
  * outputs back on its own stream. */
-static int evaluate_any(dashb_circuit* c, const void* const* in, uint64_t batch, void* const* out, bool compressed) {
+static int wait_async(dashb_circuit* c) {
+    for (int set = 0; set < 2; ++set)
+        if (c->async_busy[set]) {
+            c->async_busy[set] = false;
+            CU(cudaEventSynchronize(c->async_done[set]));
+        }
+    return DASHB_OK;
+}
+
+static int evaluate_any(dashb_circuit* c, const void* const* in, uint64_t batch, void* const* out, bool compressed,
+                        bool async = false) {
     if (!c || !in || !out) return fail(DASHB_EINVAL, "null argument");
     if (!c->finalized) return fail(DASHB_ESTATE, "circuit not finalized");
+    if (async) {
+        if (c->shard_world > 1) return fail(DASHB_ESTATE, "channel-sharded circuits evaluate synchronously");
+        for (int j = 0; j < c->k; ++j)
+            if (!in[j] || !out[j]) return fail(DASHB_EINVAL, "label buffer %d missing", j);
+        const int set = c->async_next;
+        if (!c->async_done[set]) CU(cudaEventCreateWithFlags(&c->async_done[set], cudaEventDisableTiming));
+        if (c->async_busy[set]) { /* this set's previous step: its buffers and the caller's are free once it is done */
+            c->async_busy[set] = false;
+            CU(cudaEventSynchronize(c->async_done[set]));
+        }
+        if (set == 1 && c->lanes_alt.empty()) {
+            int rc = make_lanes(c, c->lanes_alt);
+            if (rc) return rc;
+            CU(cudaStreamSynchronize(cudaStreamLegacy)); /* the clears of the new buffers */
+        }
+        if (set == 1) std::swap(c->lanes, c->lanes_alt);
+        /* nothing here is ordered behind dashb_stream(): the set's own streams
+         * carry the order (the host waited for the set's previous step above) */
+        int rc = split_batch(c, batch);
+        const void* dev[MAXK];
+        const bool direct = !rc && !compressed && mapped_host_inputs(c, in, dev);
+        c->launches = 0;
+        for (int i = 0; !rc && i < c->lanes_used; ++i)
+            rc = enqueue_inputs(c, *c->lanes[i], in, compressed, c->copy_s, c->lanes[i]->s, direct ? dev : nullptr);
+        const int nl = (int)c->layers.size();
+        for (int li = 0; !rc && li < nl; ++li)
+            for (int i = 0; !rc && i < c->lanes_used; ++i) rc = run_layer(c, *c->lanes[i], li, c->lanes[i]->s);
+        if (!rc && nl > 0) {
+            c->out_n = c->layers[nl - 1]->out_size;
+            for (int j = 0; j < c->k; ++j) c->out_q[j] = c->layers[nl - 1]->out_q[j];
+        }
+        for (int i = 0; !rc && i < c->lanes_used; ++i) rc = enqueue_outputs(c, *c->lanes[i], out, compressed, c->lanes[i]->s);
+        cudaError_t e = cudaSuccess;
+        for (int i = 1; e == cudaSuccess && i < c->lanes_used; ++i) {
+            e = cudaEventRecord(c->lanes[i]->done, c->lanes[i]->s);
+            if (e == cudaSuccess) e = cudaStreamWaitEvent(c->lanes[0]->s, c->lanes[i]->done, 0);
+        }
+        if (e == cudaSuccess) e = cudaEventRecord(c->async_done[set], c->lanes[0]->s);
+        if (set == 1) std::swap(c->lanes, c->lanes_alt);
+        if (e != cudaSuccess) return fail(DASHB_ECUDA, "dashb_evaluate_async: %s", cudaGetErrorString(e));
+        c->async_busy[set] = true;
+        c->async_next = set ^ 1;
+        return rc;
+    }
+    {
+        int rc = wait_async(c); /* a synchronous call behind asynchronous ones: drain them first */
+        if (rc) return rc;
+    }
     if (c->timing == 1) { /* serialised, per-layer events */
         int rc = move_inputs_any(c, in, batch, compressed);
         if (rc) return rc;
@@ -1849,6 +2074,15 @@ int dashb_evaluate(dashb_circuit* c, const int16_t* const* in, uint64_t batch, i
 
 int dashb_evaluate_compressed(dashb_circuit* c, const dashb_u128* const* in, uint64_t batch, dashb_u128* const* out) {
     return evaluate_any(c, reinterpret_cast<const void* const*>(in), batch, reinterpret_cast<void* const*>(out), true);
+}
+
+int dashb_evaluate_async(dashb_circuit* c, const int16_t* const* in, uint64_t batch, int16_t* const* out) {
+    return evaluate_any(c, reinterpret_cast<const void* const*>(in), batch, reinterpret_cast<void* const*>(out), false, true);
+}
+
+int dashb_evaluate_wait(dashb_circuit* c) {
+    if (!c) return fail(DASHB_EINVAL, "null circuit");
+    return wait_async(c);
 }
 
 int dashb_layer_outputs(dashb_circuit* c, int layer, int16_t* const* out) {

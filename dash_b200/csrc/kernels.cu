@@ -326,57 +326,69 @@ constexpr int ING_E = 32;
 constexpr int ING_THREADS = 256;
 __global__ void __launch_bounds__(ING_THREADS) k_ingest_direct(const __grid_constant__ IngestParams P) {
     __shared__ uint4 buf[(ING_E * 128 * 2 + 32) / 16 + 1];
-    const int j = blockIdx.z;
-    const uint32_t b = blockIdx.y;
-    const uint64_t e0 = (uint64_t)blockIdx.x * ING_E;
-    const uint32_t ne = (uint32_t)min((uint64_t)ING_E, P.n - e0);
-    const uint32_t nc = P.nc[j], nc4 = (nc + 3) >> 2;
-    const char* src = reinterpret_cast<const char*>(P.src[j] + ((uint64_t)b * P.n + e0) * nc);
-    const char* end = reinterpret_cast<const char*>(P.end[j]);
-    const uint32_t bytes = ne * nc * 2;
-    const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
-    const char* start = src - mis; /* 16-byte aligned; at worst 14 bytes before the span, never before the allocation's page */
-    const uint32_t nvec = (bytes + mis + 15) >> 4;
-    for (uint32_t i = threadIdx.x; i < nvec; i += ING_THREADS) {
-        const char* p = start + 16ull * i;
-        uint4 v;
-        if (p + 16 <= end) {
-            v = __ldcs(reinterpret_cast<const uint4*>(p)); /* streaming: read once */
-        } else { /* the very last vector of the caller's buffer: do not read past its end */
-            uint16_t h[8];
-            for (int t = 0; t < 8; ++t) h[t] = (p + 2 * t + 2 <= end) ? *reinterpret_cast<const uint16_t*>(p + 2 * t) : (uint16_t)0;
-            v.x = h[0] | ((uint32_t)h[1] << 16);
-            v.y = h[2] | ((uint32_t)h[3] << 16);
-            v.z = h[4] | ((uint32_t)h[5] << 16);
-            v.w = h[6] | ((uint32_t)h[7] << 16);
-        }
-        buf[i] = v;
-    }
-    __syncthreads();
-    const uint16_t* dig = reinterpret_cast<const uint16_t*>(reinterpret_cast<const char*>(buf) + mis);
-    uint8_t* plane = P.plane[j];
-    /* a warp walks the words of one element at a time */
+    /* A small persistent grid: the kernel shares the GPU with the lanes that
+     * already compute and only has to keep the PCIe link busy (a few hundred
+     * KB in flight), not to fill the machine -- one CTA per work item took the
+     * SM slots away from the gadget kernels (measured: step 5.6 -> 8.1 ms). */
+    const uint32_t nchunk = (uint32_t)((P.n + ING_E - 1) / ING_E);
+    const uint64_t items = (uint64_t)nchunk * P.batch * P.k;
     const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    /* the inference columns past the batch (up to Bp) are kept zero by the CTAs of the last inference */
-    const uint32_t nb = (b + 1 == P.batch) ? P.Bp - b : 1;
-    for (uint32_t el = warp; el < ne; el += ING_THREADS / 32) {
-        const uint16_t* row = dig + el * nc;
-        for (uint32_t d4 = lane; d4 < nc4; d4 += 32) {
-            uint32_t w = 0;
-#pragma unroll
-            for (uint32_t t = 0; t < 4; ++t)
-                if (4 * d4 + t < nc) w |= (uint32_t)(uint8_t)row[4 * d4 + t] << (8 * t);
-            uint32_t* dst = reinterpret_cast<uint32_t*>(plane + (((e0 + el) * nc4 + d4) * (uint64_t)P.Bp + b) * 4);
-            dst[0] = w;
-            for (uint32_t x = 1; x < nb; ++x) dst[x] = 0;
+    for (uint64_t item = blockIdx.x; item < items; item += gridDim.x) {
+        /* modulus slowest, then inference, then element chunk: a CTA's items walk the host buffer forward */
+        const int j = (int)(item / ((uint64_t)nchunk * P.batch));
+        const uint64_t rem = item - (uint64_t)j * nchunk * P.batch;
+        const uint32_t b = (uint32_t)(rem / nchunk);
+        const uint64_t e0 = (rem - (uint64_t)b * nchunk) * ING_E;
+        const uint32_t ne = (uint32_t)min((uint64_t)ING_E, P.n - e0);
+        const uint32_t nc = P.nc[j], nc4 = (nc + 3) >> 2;
+        const char* src = reinterpret_cast<const char*>(P.src[j] + ((uint64_t)b * P.n + e0) * nc);
+        const char* end = reinterpret_cast<const char*>(P.end[j]);
+        const uint32_t bytes = ne * nc * 2;
+        const uint32_t mis = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
+        const char* start = src - mis; /* 16-byte aligned; at worst 14 bytes before the span, in the same page */
+        const uint32_t nvec = (bytes + mis + 15) >> 4;
+        for (uint32_t i = threadIdx.x; i < nvec; i += ING_THREADS) {
+            const char* p = start + 16ull * i;
+            uint4 v;
+            if (p + 16 <= end) {
+                v = __ldcs(reinterpret_cast<const uint4*>(p)); /* streaming: read once */
+            } else { /* the very last vector of the caller's buffer: do not read past its end */
+                uint16_t h[8];
+                for (int t = 0; t < 8; ++t) h[t] = (p + 2 * t + 2 <= end) ? *reinterpret_cast<const uint16_t*>(p + 2 * t) : (uint16_t)0;
+                v.x = h[0] | ((uint32_t)h[1] << 16);
+                v.y = h[2] | ((uint32_t)h[3] << 16);
+                v.z = h[4] | ((uint32_t)h[5] << 16);
+                v.w = h[6] | ((uint32_t)h[7] << 16);
+            }
+            buf[i] = v;
         }
+        __syncthreads();
+        const uint16_t* dig = reinterpret_cast<const uint16_t*>(reinterpret_cast<const char*>(buf) + mis);
+        uint8_t* plane = P.plane[j];
+        /* the inference columns past the batch (up to Bp) are kept zero by the items of the last inference */
+        const uint32_t nb = (b + 1 == P.batch) ? P.Bp - b : 1;
+        /* a warp walks the words of one element at a time */
+        for (uint32_t el = warp; el < ne; el += ING_THREADS / 32) {
+            const uint16_t* row = dig + el * nc;
+            for (uint32_t d4 = lane; d4 < nc4; d4 += 32) {
+                uint32_t w = 0;
+#pragma unroll
+                for (uint32_t t = 0; t < 4; ++t)
+                    if (4 * d4 + t < nc) w |= (uint32_t)(uint8_t)row[4 * d4 + t] << (8 * t);
+                uint32_t* dst = reinterpret_cast<uint32_t*>(plane + (((e0 + el) * nc4 + d4) * (uint64_t)P.Bp + b) * 4);
+                dst[0] = w;
+                for (uint32_t x = 1; x < nb; ++x) dst[x] = 0;
+            }
+        }
+        __syncthreads(); /* the buffer is free for the next item */
     }
 }
 
 cudaError_t launch_ingest_direct(const IngestParams& p, cudaStream_t s) {
     if (p.n == 0 || p.batch == 0) return cudaSuccess;
-    if (p.batch > 65535) return cudaErrorInvalidConfiguration;
-    dim3 grid((unsigned)((p.n + ING_E - 1) / ING_E), p.batch, p.k);
+    static const int ctas = getenv("DASHB_INGEST_CTAS") ? atoi(getenv("DASHB_INGEST_CTAS")) : 96;
+    const uint64_t items = ((p.n + ING_E - 1) / ING_E) * p.batch * p.k;
+    const unsigned grid = (unsigned)std::min<uint64_t>(items, (uint64_t)std::max(1, ctas));
     k_ingest_direct<<<grid, ING_THREADS, 0, s>>>(p);
     return cudaGetLastError();
 }
@@ -705,6 +717,66 @@ extern "C" int dashb_projection_static(const int16_t* d_in, const dashb_u128* d_
 
 namespace dashb {
 
+/* --------------------------------------------------------- max pooling */
+/*
+ * GarbledMaxPool2d::cpu_evaluate (layer/garbled_maxpool2d.h:143-224): every
+ * output (i, j, channel) starts from the window's first input and takes, for
+ * every kernel position (l, m) in turn -- (0, 0) included -- the MaxGadget
+ * step  cur = cur + relu(in(i s_w + l, j s_h + m) - cur)
+ * (gadgets/max_gadget.h:116-160), each step with a ReLU gadget of its own
+ * (gadgets/relu_gadget.h).  The ReLU is k_sign<relu> with the tables of gadget
+ * instance  output * (k_w k_h) + (l k_h + m);  this kernel is the label
+ * arithmetic between two of them, one 32-bit word (four digits of one
+ * inference) per thread.  The layer addresses labels with the last index
+ * fastest on both sides: input (x, y, z) at (x H + y) C + z
+ * (LabelSlice::get_first_label_id_from_slice_dims, label_tensor.h:1574-1579),
+ * output (i, j, channel) at (i oh + j) C + channel (set_label, :1290-1301).
+ */
+__device__ __forceinline__ uint32_t bytes_addsub(uint32_t a, uint32_t b, uint32_t q, bool sub) {
+    uint32_t r = 0;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+        const uint32_t x = (a >> (8 * t)) & 0xff, y = (b >> (8 * t)) & 0xff;
+        uint32_t v = sub ? x + q - y : x + y;
+        v = v >= q ? v - q : v;
+        r |= v << (8 * t);
+    }
+    return r;
+}
+
+__global__ void __launch_bounds__(256) k_pool_step(const __grid_constant__ PoolParams P) {
+    const int j = blockIdx.y;
+    const uint32_t q = P.crt[j].q;
+    const uint64_t per = (uint64_t)((P.crt[j].nc + 3) >> 2) * P.Bp; /* words of one element */
+    const uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= P.n_out * per) return;
+    const uint64_t o = w / per, rest = w - o * per;
+    /* this layer counts the LAST index fastest on both sides (slices: label_tensor.h:1574-1579, set_label: :1290-1301) */
+    const uint32_t z = (uint32_t)(o % P.ch), jj = (uint32_t)((o / P.ch) % P.oh), i = (uint32_t)(o / ((uint64_t)P.ch * P.oh));
+    const uint32_t* in = reinterpret_cast<const uint32_t*>(P.in[j]);
+    uint32_t* cur = reinterpret_cast<uint32_t*>(P.cur[j]);
+    uint32_t c;
+    if (P.mode == 0) {
+        const uint64_t first = ((uint64_t)(i * P.s_w) * P.in_h + jj * P.s_h) * P.ch + z;
+        c = in[first * per + rest];
+    } else {
+        c = bytes_addsub(cur[w], reinterpret_cast<const uint32_t*>(P.relu[j])[w], q, false);
+    }
+    cur[w] = c;
+    if (P.mode == 2) return;
+    const uint64_t pos = ((uint64_t)(i * P.s_w + P.l) * P.in_h + (jj * P.s_h + P.m)) * P.ch + z;
+    reinterpret_cast<uint32_t*>(P.diff[j])[w] = bytes_addsub(in[pos * per + rest], c, q, true);
+}
+
+cudaError_t launch_pool_step(const PoolParams& p, cudaStream_t s) {
+    if (p.n_out == 0) return cudaSuccess;
+    uint64_t words = 0;
+    for (int j = 0; j < p.k; ++j) words = std::max<uint64_t>(words, p.n_out * ((p.crt[j].nc + 3) >> 2) * p.Bp);
+    dim3 grid((unsigned)((words + 255) / 256), p.k);
+    k_pool_step<<<grid, 256, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
 /* ------------------------------------------------- sign gadget / ReLU */
 /* Per-thread digit accumulators live in shared memory, digit-major
  * (acc[d * blockDim + tid]) so that a warp's accesses are conflict-free. */
@@ -963,9 +1035,10 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
     u128 carry = P.carry0;
     /* rows of this element's tables, as 32-bit row indices from the element's
      * first row (a table of one element never reaches 2^32 rows) */
-    const u128* approx_e = P.approx + e * (uint64_t)nm * P.S;
-    const u128* cast1_e = P.cast1 + e * (uint64_t)(k + 1) * P.Mp;
-    const u128* cast2_e = P.cast2 + e * (uint64_t)(k + 1) * P.Mp;
+    const uint64_t et = e * P.tab_mul + P.tab_add; /* the gadget instance whose tables this element uses */
+    const u128* approx_e = P.approx + et * (uint64_t)nm * P.S;
+    const u128* cast1_e = P.cast1 + et * (uint64_t)(k + 1) * P.Mp;
+    const u128* cast2_e = P.cast2 + et * (uint64_t)(k + 1) * P.Mp;
     uint32_t cnt1 = 0, cnt2 = 0;
     uint32_t ctop = 0;
     u128 top = gc::make_u128(0, 0);
@@ -1030,7 +1103,7 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
     const uint32_t m0 = P.mrs[0].q;
 
     /* Step 3: sign projection(s) */
-    const u128* sign_e = P.sign + e * (uint64_t)P.n_out * m0;
+    const u128* sign_e = P.sign + et * (uint64_t)P.n_out * m0;
     if (!RELU) {
 #pragma unroll 1
         for (int j = 0; j < P.n_out; ++j) {
@@ -1043,8 +1116,8 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
     const u128 s = gc::sub128(ldg128(sign_e + ctop), htop); /* sign label, modulus 2 */
     const u128 hs = hash(aes, s);
     const uint32_t cs = (uint32_t)s.lo & 1u;
-    const u128* garbler_e = P.garbler + e * (uint64_t)P.S;
-    const u128* ev_e = P.evaluator + e * (uint64_t)k * 3;
+    const u128* garbler_e = P.garbler + et * (uint64_t)P.S;
+    const u128* ev_e = P.evaluator + et * (uint64_t)k * 3;
 #pragma unroll 1
     for (int j = 0; j < k; ++j) {
         const ModInfo Pm = pin(P.crt[j]);
@@ -1153,8 +1226,9 @@ __global__ void __launch_bounds__(WIDE_WARPS * 32) k_sign_wide(const __grid_cons
         col[lane] = c;
     }
     __syncwarp();
-    const u128* approx_e = P.approx + e * (uint64_t)nm * P.S;
-    const uint64_t cast_e = e * (uint64_t)(k + 1) * P.Mp;
+    const uint64_t et = e * P.tab_mul + P.tab_add; /* the gadget instance whose tables this element uses */
+    const u128* approx_e = P.approx + et * (uint64_t)nm * P.S;
+    const uint64_t cast_e = et * (uint64_t)(k + 1) * P.Mp;
     /* steps 1b + 2.2 for every (digit i >= 1, residue j): independent of the carry */
     for (int t = lane; t < k * (nm - 1); t += 32) {
         const int j = t % k, i = 1 + t / k;
@@ -1199,7 +1273,7 @@ __global__ void __launch_bounds__(WIDE_WARPS * 32) k_sign_wide(const __grid_cons
     htop = shfl128(htop, 0);
     ctop = __shfl_sync(0xffffffffu, ctop, 0);
     const uint32_t m0 = P.mrs[0].q;
-    const u128* sign_e = P.sign + e * (uint64_t)P.n_out * m0;
+    const u128* sign_e = P.sign + et * (uint64_t)P.n_out * m0;
     if (!RELU) {
         if (lane < P.n_out) store_digits(P.out[lane], P.outm[lane], e, b, P.Bp, gc::sub128(ldg128(sign_e + (uint64_t)lane * m0 + ctop), htop));
         return;
@@ -1213,8 +1287,8 @@ __global__ void __launch_bounds__(WIDE_WARPS * 32) k_sign_wide(const __grid_cons
     if (lane < k) {
         const int j = lane;
         const ModInfo Pm = P.crt[j];
-        const u128 G = gc::sub128(ldg128(P.garbler + e * (uint64_t)P.S + P.prefix[j] + col[j]), h[j]);
-        const u128* ev = P.evaluator + (e * (uint64_t)k + j) * 3;
+        const u128 G = gc::sub128(ldg128(P.garbler + et * (uint64_t)P.S + P.prefix[j] + col[j]), h[j]);
+        const u128* ev = P.evaluator + (et * (uint64_t)k + j) * 3;
         const u128 E = gc::sub128(ldg128(ev + cs), hs);
         const u128 mini = ldg128(ev + 2);
         const int16_t row16 = (int16_t)((mini.lo >> (16 * cs)) & 0xffff);

@@ -82,6 +82,23 @@ struct SignParams {
     uint32_t batch, Bp;
     int k, n_mrs, n_out;
     int lanes;               /* sub-batch lanes evaluating concurrently (picks latency vs throughput kernel) */
+    uint32_t tab_mul, tab_add; /* element e uses the tables of gadget instance e * tab_mul + tab_add (1, 0 except max pooling) */
+};
+
+/* k_pool_step (max pooling, max(x, y) = x + relu(y - x)): per output element
+ * and kernel position one ReLU gadget; the label arithmetic around it */
+struct PoolParams {
+    const uint8_t* in[MAXK];  /* the layer's input planes */
+    uint8_t* cur[MAXK];       /* running maximum = the layer's output planes */
+    uint8_t* diff[MAXK];      /* y - x, input of the ReLU gadget */
+    const uint8_t* relu[MAXK];/* its output */
+    gc::ModInfo crt[MAXK];
+    uint32_t in_w, in_h, ch, ow, oh, s_w, s_h;
+    uint32_t l, m;            /* kernel position of this step */
+    uint64_t n_out;
+    uint32_t Bp;
+    int k;
+    int mode;                 /* 0: cur = in[first]; diff = in[pos] - cur   1: cur += relu; diff = in[pos] - cur   2: cur += relu */
 };
 
 /* k_ingest_direct: labels read straight from the caller's (pinned, mapped)
@@ -259,6 +276,7 @@ cudaError_t conv_tc_make_map(void* map_out, const void* ptr, uint64_t row_bytes,
 cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p, cudaStream_t s);
 cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s);
 cudaError_t launch_projection(const ProjParams& p, cudaStream_t s);
+cudaError_t launch_pool_step(const PoolParams& p, cudaStream_t s);
 cudaError_t launch_rescale(const RescaleParams& p, cudaStream_t s);
 cudaError_t launch_add_label(const AddLabelParams& p, cudaStream_t s);
 cudaError_t launch_decode(const DecodeParams& p, cudaStream_t s);

@@ -129,6 +129,29 @@ int dashb_add_relu(dashb_circuit* c, uint64_t n, const dashb_u128* approx,
                    const dashb_u128* sign, const dashb_u128* garbler,
                    const dashb_u128* evaluator);
 
+/* GarbledMaxPool2d (layer/garbled_maxpool2d.h:143-224; CPU-only in the
+ * reference, :226-244) = per output (i, j, channel) a chain of MaxGadgets
+ * (gadgets/max_gadget.h:116-160: max(x, y) = x + relu(y - x)) over the kernel
+ * positions (l, m), l outer, (0, 0) included, each with a ReluGadget of its
+ * own (gadgets/relu_gadget.h).  The six tables are those of dashb_add_relu for
+ *   n = outputs * k_w * k_h  gadget instances, instance of (output o, l, m)
+ *   = o * k_w * k_h + l * k_h + m,  o = (i * oh + j) * channels + channel
+ *   (the output label's index; this layer counts the last index fastest on
+ *   both sides -- input (x, y, z) at (x * in_h + y) * channels + z,
+ *   label_tensor.h:1574-1579 and 1290-1301 -- unlike conv2d):
+ * the concatenation of every instance's one-element SignGadget / half-gate
+ * arrays in that order.  Geometry is passed explicitly; the reference layer
+ * reads its input dims from the circuit's input labels (:66-68), so it is
+ * only defined as the first layer and for shapes where its window count
+ * ((W - k_w) / s_w + 1) equals its output tensor's W / k_w (max_pool2d.h:
+ * 26-29) -- other shapes are rejected. */
+int dashb_add_maxpool2d(dashb_circuit* c, uint64_t in_w, uint64_t in_h,
+                        uint64_t channels, uint64_t k_w, uint64_t k_h,
+                        uint64_t s_w, uint64_t s_h, const dashb_u128* approx,
+                        const dashb_u128* cast1, const dashb_u128* cast2,
+                        const dashb_u128* sign, const dashb_u128* garbler,
+                        const dashb_u128* evaluator);
+
 /* GarbledSign (layer/garbled_sign.h:16-81): SignGadget, bounds (-1,1), out
  * moduli = crt_base; sign table is [n][k][m_0]. */
 int dashb_add_sign(dashb_circuit* c, uint64_t n, const dashb_u128* approx,
@@ -250,6 +273,21 @@ int dashb_move_outputs(dashb_circuit* c, int16_t* const* out);
 int dashb_evaluate(dashb_circuit* c, const int16_t* const* in, uint64_t batch,
                    int16_t* const* out);
 /*
+ * dashb_evaluate for a caller that streams batches: returns as soon as the
+ * step is enqueued; up to two steps are in flight on two sets of lanes, so
+ * that step n+1's input labels cross PCIe while step n computes (the third
+ * call first waits for the oldest step).  `in` and `out` must stay valid and
+ * untouched until that step is done: after dashb_evaluate_wait(), or after
+ * the second-next dashb_evaluate_async returns.  Steps complete in order.
+ * The work is NOT ordered with dashb_stream(); dashb_move_outputs /
+ * dashb_decode_outputs / dashb_layer_outputs refer to synchronous
+ * evaluations only (any synchronous call first drains the asynchronous
+ * ones).  No counterpart in the reference, whose GPU calls are synchronous
+ * (garbled_circuit_interface.h:551-612,733-736).
+ */
+int dashb_evaluate_async(dashb_circuit* c, const int16_t* const* in, uint64_t batch, int16_t* const* out);
+int dashb_evaluate_wait(dashb_circuit* c);
+/*
  * The same three calls with labels in their compressed 128-bit form on the
  * host side (what LabelTensor::compress() leaves in get_compressed(),
  * garbling/label_tensor.h:715-727; SURVEY.md row f2: "compressed 128-bit
@@ -340,6 +378,7 @@ int dashb_layer_type(const dashb_circuit* c, int layer);
 #define DASHB_LAYER_RESCALE 5
 #define DASHB_LAYER_RESCALE_LEGACY 6
 #define DASHB_LAYER_PROJECTION 7
+#define DASHB_LAYER_MAXPOOL2D 8
 
 /* ---- garbled-material files (no counterpart in the reference, which keeps
  *      a garbled circuit only in process memory; format in

@@ -78,6 +78,19 @@ static inline int gcm_layer_sizes_ok(const gcm_circuit* g, const gcm_layer* L, u
             return gcm__is(&L->a[4], gcm__mul(gcm__mul(n, S, &bad), 16, &bad), bad) &&
                    gcm__is(&L->a[5], gcm__mul(gcm__mul(n, (uint64_t)k, &bad), 48, &bad), bad);
         case GCM_SIGN: return L->n_arrays == 4 && n == n_in && GCM__SIGN_OK(0, k);
+        case GCM_MAXPOOL2D: {
+            const uint64_t in_w = (uint64_t)L->p[1], in_h = (uint64_t)L->p[2], ch = (uint64_t)L->p[3], kw = (uint64_t)L->p[4],
+                           kh = (uint64_t)L->p[5], sw = (uint64_t)L->p[6], sh = (uint64_t)L->p[7];
+            if (L->n_arrays != 6 || !kw || !kh || !sw || !sh || kw > in_w || kh > in_h) return 0;
+            if (gcm__mul(gcm__mul(in_w, in_h, &bad), ch, &bad) != n_in || bad) return 0;
+            *n_out = gcm__mul(gcm__mul((in_w - kw) / sw + 1, (in_h - kh) / sh + 1, &bad), ch, &bad);
+            {
+                const uint64_t n = gcm__mul(*n_out, gcm__mul(kw, kh, &bad), &bad); /* gadget instances */
+                if (!GCM__SIGN_OK(0, 1)) return 0;
+                return gcm__is(&L->a[4], gcm__mul(gcm__mul(n, S, &bad), 16, &bad), bad) &&
+                       gcm__is(&L->a[5], gcm__mul(gcm__mul(n, (uint64_t)k, &bad), 48, &bad), bad);
+            }
+        }
         case GCM_RESCALE: {
             const int nf = (int)L->p[2];
             if (nf < 1 || nf > 16 || nf >= k || L->n_arrays != k + 2 || n != n_in) return 0;
@@ -214,6 +227,15 @@ static inline int dashb_circuit_from_gcm(const gcm_circuit* g, dashb_circuit** o
                                         (const dashb_u128*)ptr[1], (const dashb_u128*)ptr[2],
                                         (const dashb_u128*)ptr[3], (const dashb_u128*)ptr[4],
                                         (const dashb_u128*)ptr[5]);
+                break;
+            case GCM_MAXPOOL2D:
+                if (L->n_arrays != 6) rc = DASHB_EINVAL;
+                else
+                    rc = dashb_add_maxpool2d(c, (uint64_t)L->p[1], (uint64_t)L->p[2], (uint64_t)L->p[3],
+                                             (uint64_t)L->p[4], (uint64_t)L->p[5], (uint64_t)L->p[6], (uint64_t)L->p[7],
+                                             (const dashb_u128*)ptr[0], (const dashb_u128*)ptr[1],
+                                             (const dashb_u128*)ptr[2], (const dashb_u128*)ptr[3],
+                                             (const dashb_u128*)ptr[4], (const dashb_u128*)ptr[5]);
                 break;
             case GCM_SIGN:
                 if (L->n_arrays != 4) rc = DASHB_EINVAL;

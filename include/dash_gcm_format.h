@@ -50,6 +50,7 @@
 #define GCM_RESCALE 5
 #define GCM_RESCALE_LEGACY 6
 #define GCM_PROJECTION 7
+#define GCM_MAXPOOL2D 8
 
 typedef struct gcm_array {
     const void* data; /* not owned by views; owned (malloc) after gcm_load */
@@ -71,6 +72,9 @@ typedef struct gcm_array {
  *                         trans_mod approx cast1 cast2 sign
  *  PROJECTION     p[1]=n p[2..2+k)=in_moduli p[2+k..2+2k)=out_moduli
  *                 arrays: ciphers[k]
+ *  MAXPOOL2D      p[1..7] = in_w in_h channels k_w k_h s_w s_h
+ *                 arrays: approx cast1 cast2 sign garbler evaluator of the
+ *                 outputs*k_w*k_h ReLU gadget instances (see dashb_add_maxpool2d)
  */
 typedef struct gcm_layer {
     int64_t p[GCM_MAX_PARAMS];

@@ -25,6 +25,7 @@
 #ifndef DASH_ADAPTER_H
 #define DASH_ADAPTER_H
 
+#include <map>
 #include <memory>
 #include <numeric>
 #include <stdexcept>
@@ -75,6 +76,12 @@ DASH_ADAPTER_MEMBER(RG_sg, RescaleGadget, SignGadget*, m_sign_gadget)
 DASH_ADAPTER_MEMBER(RG_be, RescaleGadget, BaseExtensionGadget*, m_be_gadget)
 DASH_ADAPTER_MEMBER(BE_c, BaseExtensionGadget, __uint128_t*, m_proj_gates_base_change_loop_ciphers)
 DASH_ADAPTER_MEMBER(GP_c, GarbledProjection, std::vector<__uint128_t*>, m_ciphers)
+typedef std::map<std::vector<size_t>, MaxGadget*> MaxGadgetMap;
+DASH_ADAPTER_MEMBER(GMP_g, GarbledMaxPool2d, MaxGadgetMap, m_max_gadgets)
+DASH_ADAPTER_MEMBER(MG_r, MaxGadget, ReluGadget*, m_relu_gadget)
+DASH_ADAPTER_MEMBER(RLG_sg, ReluGadget, SignGadget*, m_sign_gadget)
+DASH_ADAPTER_MEMBER(RLG_g, ReluGadget, __uint128_t*, M_GARBLER_CIPHERS)
+DASH_ADAPTER_MEMBER(RLG_e, ReluGadget, __uint128_t*, M_EVALUATOR_CIPHERS)
 #undef DASH_ADAPTER_MEMBER
 
 inline gcm_array arr(const void* p, uint64_t nbytes) { return gcm_array{p, nbytes}; }
@@ -234,6 +241,48 @@ inline void dash_view_from_circuit(GarbledCircuit* gc, DashMaterialView& v, bool
                 }
                 break;
             }
+            case Layer::max_pool: {
+                /* one MaxGadget -> ReluGadget -> SignGadget (one element each) per (output, kernel position):
+                 * their arrays are concatenated into the six tables of a ReLU layer with outputs * k_w k_h
+                 * elements, instance (output label o, l, m) at o * k_w k_h + l * k_h + m (the only copy this adapter makes) */
+                auto* g = dynamic_cast<GarbledMaxPool2d*>(gl);
+                MaxPool2d* mp = dynamic_cast<MaxPool2d*>(pl);
+                // the garbled layer takes its geometry from the circuit's input labels (garbled_maxpool2d.h:66-68)
+                const auto dims = gc->get_base_label().at(0)->get_dims();
+                const size_t W = dims.at(0), H = dims.at(1), C = dims.at(2);
+                const size_t kw = mp->get_kernel_width(), kh = mp->get_kernel_height();
+                const size_t sw = mp->get_stride_width(), sh = mp->get_stride_height();
+                const size_t ow = (W - kw) / sw + 1, oh = (H - kh) / sh + 1, T = kw * kh;
+                const size_t S = std::accumulate(crt.begin(), crt.end(), size_t{0});
+                const size_t n_mrs = mrs.size();
+                const size_t Mp = std::accumulate(mrs.begin() + 1, mrs.end(), size_t{0});
+                const size_t per[6] = {n_mrs * S, (k + 1) * Mp, (k + 1) * Mp, (size_t)mrs.at(0), S, k * 3};
+                std::unique_ptr<std::vector<int16_t>> blk[6];
+                for (int a = 0; a < 6; ++a) blk[a] = std::make_unique<std::vector<int16_t>>(ow * oh * C * T * per[a] * 8);
+                auto& gadgets = g->*get(GMP_g());
+                for (size_t i = 0; i < ow; ++i)
+                    for (size_t j = 0; j < oh; ++j)
+                        for (size_t z = 0; z < C; ++z)
+                            for (size_t l = 0; l < kw; ++l)
+                                for (size_t m = 0; m < kh; ++m) {
+                                    // output (i, j, z) lives at label index (i * oh + j) * C + z (set_label, label_tensor.h:1290-1301)
+                                    const size_t inst = ((i * oh + j) * C + z) * T + l * kh + m;
+                                    ReluGadget* rg = gadgets.at({i, j, z, l, m})->*get(MG_r());
+                                    SignGadget* sg = rg->*get(RLG_sg());
+                                    const __uint128_t* src[6] = {sg->*get(SG_approx()), sg->*get(SG_c1()), sg->*get(SG_c2()),
+                                                                 sg->*get(SG_sign()), rg->*get(RLG_g()), rg->*get(RLG_e())};
+                                    for (int a = 0; a < 6; ++a)
+                                        memcpy(reinterpret_cast<__uint128_t*>(blk[a]->data()) + inst * per[a], src[a], per[a] * 16);
+                                }
+                L.p[0] = GCM_MAXPOOL2D;
+                L.p[1] = (int64_t)W, L.p[2] = (int64_t)H, L.p[3] = (int64_t)C;
+                L.p[4] = (int64_t)kw, L.p[5] = (int64_t)kh, L.p[6] = (int64_t)sw, L.p[7] = (int64_t)sh;
+                for (int a = 0; a < 6; ++a) {
+                    push(L, blk[a]->data(), (uint64_t)ow * oh * C * T * per[a] * 16);
+                    v.owned.push_back(std::move(blk[a]));
+                }
+                break;
+            }
             case Layer::projection: {
                 auto* g = dynamic_cast<GarbledProjection*>(gl);
                 const size_t n = pl->get_input_size();
@@ -249,7 +298,7 @@ inline void dash_view_from_circuit(GarbledCircuit* gc, DashMaterialView& v, bool
             }
             default:
                 throw std::runtime_error(
-                    "dash_adapter: layer type outside the B200 hot path (mult / max / maxpool / base_extension layer)");
+                    "dash_adapter: layer type outside the B200 hot path (mult / mixed-mod mult / max / base_extension layer)");
         }
         v.layers.push_back(L);
     }

@@ -266,6 +266,11 @@ static uint64_t layer_out_size(const gcm_layer* L) {
             uint64_t oh = ((uint64_t)L->p[2] - (uint64_t)L->p[6]) / (uint64_t)L->p[8] + 1;
             return ow * oh * (uint64_t)L->p[4];
         }
+        case GCM_MAXPOOL2D: {
+            uint64_t ow = ((uint64_t)L->p[1] - (uint64_t)L->p[4]) / (uint64_t)L->p[6] + 1;
+            uint64_t oh = ((uint64_t)L->p[2] - (uint64_t)L->p[5]) / (uint64_t)L->p[7] + 1;
+            return ow * oh * (uint64_t)L->p[3];
+        }
         default: return (uint64_t)L->p[1];
     }
 }
@@ -350,8 +355,15 @@ static void eval_conv2d(const oracle_circuit* c, const gcm_layer* L, const label
 /* SignGadget::cpu_evaluate (gadgets/sign_gadget.h:583-671) with
  * ApproxResGadget::cpu_evaluate (gadgets/approx_res_gadget.h:94-102).
  * tables: approx, cast1, cast2, sign.  out has n_out moduli. */
+static void eval_sign_gadget_at(const oracle_circuit* c, const gcm_array* t, uint64_t g0, uint64_t n, const labels* in,
+                                labels* out, int n_out, int thr);
 static void eval_sign_gadget(const oracle_circuit* c, const gcm_array* t, uint64_t n, const labels* in, labels* out,
                              int n_out, int thr) {
+    eval_sign_gadget_at(c, t, 0, n, in, out, n_out, thr);
+}
+/* element e of `in` uses the tables of gadget instance g0 + e */
+static void eval_sign_gadget_at(const oracle_circuit* c, const gcm_array* t, uint64_t g0, uint64_t n, const labels* in,
+                                labels* out, int n_out, int thr) {
     const int k = c->g.k, nm = c->g.n_mrs;
     const int32_t* crt = c->g.crt_base;
     const int32_t* mrs = c->g.mrs_base;
@@ -369,13 +381,13 @@ static void eval_sign_gadget(const oracle_circuit* c, const gcm_array* t, uint64
         /* Step 1: approximate residues in mixed radix (sign_gadget.h:594-601) */
         int prefix = 0;
         for (int j = 0; j < k; ++j) {
-            const u128* cj = approx + e * (uint64_t)nm * S + (uint64_t)nm * prefix;
+            const u128* cj = approx + (g0 + e) * (uint64_t)nm * S + (uint64_t)nm * prefix;
             for (int i = 0; i < nm; ++i)
                 proj_eval(cj + (uint64_t)i * crt[j], in->d[j] + e * in->nc[j], crt[j], mrs[i], mrs_label[j][i]);
             prefix += crt[j];
         }
         /* Step 2: mixed-radix addition, least to most significant (:603-654) */
-        uint64_t cnt1 = e * (uint64_t)(k + 1) * Mp, cnt2 = cnt1;
+        uint64_t cnt1 = (g0 + e) * (uint64_t)(k + 1) * Mp, cnt2 = cnt1;
         int q_carry = mrs[nm - 1];
         memcpy(carry, c->zero[q_carry], sizeof(int16_t) * gcm_nr_comps(q_carry));
         for (int i = nm - 1; i >= 0; --i) {
@@ -397,20 +409,27 @@ static void eval_sign_gadget(const oracle_circuit* c, const gcm_array* t, uint64
         }
         /* Step 3: sign of the most significant sum (:657-662) */
         for (int j = 0; j < n_out; ++j)
-            proj_eval(sgn + e * (uint64_t)n_out * mrs[0] + (uint64_t)j * mrs[0], sum, mrs[0], out->q[j],
+            proj_eval(sgn + (g0 + e) * (uint64_t)n_out * mrs[0] + (uint64_t)j * mrs[0], sum, mrs[0], out->q[j],
                       out->d[j] + e * out->nc[j]);
     }
 }
 
 /* GarbledRelu::cpu_evaluate (layer/garbled_relu.h:181-223) and
  * MixedModHalfGate::cpu_evaluate (gates/mixed_mod_half_gate.h:91-104). */
+static void eval_relu_at(const oracle_circuit* c, const gcm_layer* L, uint64_t g0, uint64_t n, const labels* in, labels* out,
+                         int thr);
 static void eval_relu(const oracle_circuit* c, const gcm_layer* L, const labels* in, labels* out, int thr) {
+    eval_relu_at(c, L, 0, (uint64_t)L->p[1], in, out, thr);
+}
+/* n elements of `in`; element e uses the tables of gadget instance g0 + e
+ * (ReluGadget::cpu_evaluate, gadgets/relu_gadget.h, is the same evaluation) */
+static void eval_relu_at(const oracle_circuit* c, const gcm_layer* L, uint64_t g0, uint64_t n, const labels* in, labels* out,
+                         int thr) {
     const int k = c->g.k;
-    const uint64_t n = (uint64_t)L->p[1];
     labels s;
     int two = 2;
     labels_alloc(&s, 1, &two, n);
-    eval_sign_gadget(c, &L->a[0], n, in, &s, 1, thr);
+    eval_sign_gadget_at(c, &L->a[0], g0, n, in, &s, 1, thr);
     const u128* gar = (const u128*)L->a[4].data;
     const u128* eva = (const u128*)L->a[5].data;
     int S = 0;
@@ -420,8 +439,8 @@ static void eval_relu(const oracle_circuit* c, const gcm_layer* L, const labels*
         int prefix = 0;
         for (int j = 0; j < k; ++j) {
             const int p = c->g.crt_base[j], nc = in->nc[j];
-            const u128* g_c = gar + e * (uint64_t)S + prefix;
-            const u128* e_c = eva + e * (uint64_t)k * 3 + (uint64_t)j * 3;
+            const u128* g_c = gar + (g0 + e) * (uint64_t)S + prefix;
+            const u128* e_c = eva + (g0 + e) * (uint64_t)k * 3 + (uint64_t)j * 3;
             const int16_t* x = in->d[j] + e * nc;
             const int16_t* sl = s.d[0] + e * s.nc[0];
             int16_t gl[128], el[128], xs[128];
@@ -437,6 +456,48 @@ static void eval_relu(const oracle_circuit* c, const gcm_layer* L, const labels*
         }
     }
     labels_free(&s, 1);
+}
+
+/* GarbledMaxPool2d::cpu_evaluate (layer/garbled_maxpool2d.h:143-224) with
+ * MaxGadget::cpu_evaluate (gadgets/max_gadget.h:116-160): per output
+ * (i, j, channel) the running maximum starts as the window's first input and
+ * every kernel position (l, m) -- l outer, (0, 0) included -- applies
+ * cur = cur + relu(in(x, y, z) - cur) with its own ReLU gadget, instance
+ * o * k_w k_h + l k_h + m of the layer's tables.  This layer addresses
+ * labels with the LAST index fastest on both sides: input (x, y, z) of the
+ * W x H x C tensor at (x H + y) C + z, output (i, j, channel) at
+ * o = (i oh + j) C + channel. */
+static void eval_maxpool(const oracle_circuit* c, const gcm_layer* L, const labels* in, labels* out, int thr) {
+    const int k = c->g.k;
+    const uint64_t W = (uint64_t)L->p[1], H = (uint64_t)L->p[2], C = (uint64_t)L->p[3], kw = (uint64_t)L->p[4],
+                   kh = (uint64_t)L->p[5], sw = (uint64_t)L->p[6], sh = (uint64_t)L->p[7];
+    const uint64_t ow = (W - kw) / sw + 1, oh = (H - kh) / sh + 1, T = kw * kh;
+    (void)thr;
+    for (uint64_t o = 0; o < ow * oh * C; ++o) {
+        /* both the window's slices (LabelSlice::get_first_label_id_from_slice_dims, label_tensor.h:1574-1579)
+         * and set_label(label, {i, j, channel}) (:1290-1301) count the LAST index fastest */
+        const uint64_t z = o % C, j = (o / C) % oh, i = o / (C * oh);
+        labels cur, diff, res;
+        labels_alloc(&cur, k, in->q, 1);
+        labels_alloc(&diff, k, in->q, 1);
+        labels_alloc(&res, k, in->q, 1);
+        const uint64_t first = ((i * sw) * H + j * sh) * C + z;
+        for (int m = 0; m < k; ++m) memcpy(cur.d[m], in->d[m] + first * in->nc[m], sizeof(int16_t) * in->nc[m]);
+        for (uint64_t l = 0; l < kw; ++l)
+            for (uint64_t mm = 0; mm < kh; ++mm) {
+                const uint64_t pos = ((i * sw + l) * H + (j * sh + mm)) * C + z;
+                for (int m = 0; m < k; ++m) {
+                    memcpy(diff.d[m], in->d[m] + pos * in->nc[m], sizeof(int16_t) * in->nc[m]);
+                    lab_sub(diff.d[m], cur.d[m], in->nc[m], in->q[m]);
+                }
+                eval_relu_at(c, L, o * T + l * kh + mm, 1, &diff, &res, 1);
+                for (int m = 0; m < k; ++m) lab_add(cur.d[m], res.d[m], in->nc[m], in->q[m]);
+            }
+        for (int m = 0; m < k; ++m) memcpy(out->d[m] + o * out->nc[m], cur.d[m], sizeof(int16_t) * in->nc[m]);
+        labels_free(&cur, k);
+        labels_free(&diff, k);
+        labels_free(&res, k);
+    }
 }
 
 /* BaseExtensionGadget::cpu_evaluate (gadgets/base_extension_gadget.h:
@@ -635,6 +696,7 @@ int oracle_evaluate(const oracle_circuit* c, const int16_t* const* in, int upto,
                 for (int it = 1; it < (int)L->p[2]; ++it) eval_rescale_gadget(c, L, 1, it, &nxt, &nxt, nr_threads);
                 break;
             case GCM_PROJECTION: eval_projection(c, L, &cur, &nxt, nr_threads); break;
+            case GCM_MAXPOOL2D: eval_maxpool(c, L, &cur, &nxt, nr_threads); break;
             default: rc = -1;
         }
         labels_free(&cur, k);
@@ -703,6 +765,7 @@ double oracle_aes_blocks(const oracle_circuit* c) {
         double n = (double)L->p[1];
         switch ((int)L->p[0]) {
             case GCM_RELU: total += n * (sign_in + 1 + 3.0 * k); break;
+            case GCM_MAXPOOL2D: total += (double)layer_out_size(L) * (double)(L->p[4] * L->p[5]) * (sign_in + 1 + 3.0 * k); break;
             case GCM_SIGN: total += n * (sign_in + k); break;
             case GCM_RESCALE: {
                 int nf = (int)L->p[2];

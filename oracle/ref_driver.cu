@@ -193,6 +193,12 @@ int ref_add_rescale(void* hv, const int* factors, int nf, uint64_t d0, uint64_t 
     static_cast<RefHandle*>(hv)->layers.push_back(new Rescale(s, dims3(d0, d1, d2)));
     return 0;
 }
+/* MaxPool2d(input_width, input_height, channel, kernel_width, kernel_height, stride_width, stride_height)
+ * (circuit/layer/max_pool2d.h:24-37) */
+int ref_add_maxpool2d(void* hv, uint64_t w, uint64_t h_, uint64_t c, uint64_t kw, uint64_t kh, uint64_t sw, uint64_t sh) {
+    static_cast<RefHandle*>(hv)->layers.push_back(new MaxPool2d(w, h_, c, kw, kh, sw, sh));
+    return 0;
+}
 /* func: 0 identity, 1 x+1, 2 2x, 3 x/2, 4 x/2-10, 5 x/4 (cf. dash/test/test_projection.h:14-16) */
 int ref_add_projection(void* hv, uint64_t n, const int* in_mod, const int* out_mod, int k, int func) {
     std::vector<crt_val_t> im(in_mod, in_mod + k), om(out_mod, out_mod + k);

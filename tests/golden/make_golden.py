@@ -21,7 +21,8 @@ import workloads as W  # noqa: E402
 from oracle import refbind as R  # noqa: E402
 
 GOLDEN = ["SIGN_TINY", "RELU_99", "RESCALE_LEGACY", "RESCALE_2", "RESCALE_2_3", "RESCALE_OPT", "PROJECTION",
-          "MLP_TINY", "CONV_UNIT", "RELU_EDGE", "PROJ_UP_BACK", "PROJ_DOWN_BACK", "PROJ_2X2"]
+          "MLP_TINY", "CONV_UNIT", "RELU_EDGE", "PROJ_UP_BACK", "PROJ_DOWN_BACK", "PROJ_2X2",
+          "MAXPOOL_2X2", "MAXPOOL_P9", "MAXPOOL_1X1", "MAXPOOL_4X4C2_DENSE"]
 
 # extra unit circuits only used as fixtures
 W.MODELS["CONV_UNIT"] = dict(  # stride 2, two channels, three filters (cf. test_conv2d.h:133-261)
@@ -42,6 +43,17 @@ W.MODELS["PROJ_2X2"] = dict(        # :85-120 one projection x*2 over a 2x2 tens
     input=(2, 2, 1), layers=[("flatten",), ("projection", [19], [19], 2)],
     quant=("simple", 1.0), crt=[19], mrs=[], max_modulus=100)
 
+# dash/test/test_maxpool2d.h: a 2x2 window over a 2x2x1 input (stride 1), with the test's bases and values
+W.MODELS["MAXPOOL_2X2"] = dict(    # :93-170 (crt {2,3,5}, mrs {26,6,3,2}); mixed_high {3,-11,5,10} -> 10
+    input=(2, 2, 1), layers=[("maxpool", 2, 1)], quant=("simple", 1.0), crt=[2, 3, 5], mrs=[26, 6, 3, 2], max_modulus=0)
+W.MODELS["MAXPOOL_P9"] = dict(     # :173-212 (nine primes, mrs {76,7,7,7,7,7,5,5}); mid_p9 / neg_high_p9 / low_p9
+    input=(2, 2, 1), layers=[("maxpool", 2, 1)], quant=("simple", 1.0), **W.cpm(9))
+W.MODELS["MAXPOOL_1X1"] = dict(    # :74-84 TestGarbledMaxPool2DMultKernel: 1x1 kernel, outputs = inputs
+    input=(2, 2, 1), layers=[("maxpool", 1, 1)], quant=("simple", 1.0), crt=[2, 3, 5], mrs=[26, 6, 3, 2], max_modulus=0)
+W.MODELS["MAXPOOL_4X4C2_DENSE"] = dict(  # two channels, 2x2 / stride 2 windows, then a dense layer on the pooled labels
+    input=(4, 4, 2), layers=[("maxpool", 2, 2), ("flatten",), ("dense", 3)], quant=("simple", 0.1), crt=[2, 3, 5, 7],
+    mrs=[26, 3], max_modulus=0)
+
 BATCH = 3
 
 
@@ -50,6 +62,12 @@ def inputs_for(name, spec, n):
         P = 30  # 0, +-1, +-mid, +-extremes of the signed range (-P/2, P/2)
         row = np.array([0, 1, -1, 7, -7, 14, -14, 2, -2, 13, -13, 5, -5, 3], dtype=np.int64)
         return np.stack([row, -row, np.roll(row, 3)])[:, :n]
+    if name in ("MAXPOOL_2X2", "MAXPOOL_1X1"):   # first row: mixed_high of the reference test
+        return np.array([[3, -11, 5, 10], [0, 0, 0, 0], [-14, 1, 0, 7]], dtype=np.int64)
+    if name == "MAXPOOL_P9":     # mid_p9, neg_high_p9, low_p9
+        return np.array([[55773217] * 4, [-111546435] * 4, [1, 1, 1, 1]], dtype=np.int64)
+    if name == "MAXPOOL_4X4C2_DENSE":
+        return np.random.default_rng(5).integers(-2, 3, size=(BATCH, n), dtype=np.int64)
     if name == "PROJ_UP_BACK":   # first row = the reference test's input
         return np.array([[15], [4], [9]], dtype=np.int64)
     if name == "PROJ_DOWN_BACK":

@@ -312,3 +312,45 @@ def test_direct_ingest_from_pinned_host_memory(gpu, name, batch, skew):
     c.evaluate_device()
     assert_labels_equal(c.move_outputs(), want, "%s pinned inputs, separate calls" % name)
     c.close()
+
+
+@pytest.mark.parametrize("name", ["MLP_TINY", "CONV_UNIT"])
+def test_async_evaluation_two_steps_in_flight(gpu, name):
+    """dashb_evaluate_async / dashb_evaluate_wait: a stream of batches with two
+    steps in flight gives, batch for batch, the labels of the synchronous call;
+    batches differ in size and content so that a mixed-up lane set or buffer
+    would show."""
+    import ctypes as C
+
+    import torch
+
+    from dash_b200.api import _check
+
+    g = Golden(name)
+    c = gpu.Circuit.load(g.gcm, max_batch=160)
+    L = c.L
+    L.dashb_evaluate_async.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+    L.dashb_evaluate_wait.argtypes = [C.c_void_p]
+    batches = [160, 37, 130, 1, 96, 160, 64]
+    keep, want = [], []
+    for r, b in enumerate(batches):
+        labels = [np.roll(l, r, axis=0) for l in tile_batch(g.inputs, b)]
+        want.append(c.evaluate(labels))
+        ins = []
+        for l in labels:
+            t = torch.empty(l.shape, dtype=torch.int16).pin_memory()
+            t.numpy()[...] = l
+            ins.append(t)
+        outs = [torch.full(w.shape, -7, dtype=torch.int16).pin_memory() for w in want[-1]]
+        keep.append((ins, outs))
+    for (ins, outs), b in zip(keep, batches):
+        ip = (C.c_void_p * len(ins))(*[t.data_ptr() for t in ins])
+        op = (C.c_void_p * len(outs))(*[t.data_ptr() for t in outs])
+        _check(L.dashb_evaluate_async(c.h, ip, b, op))
+    _check(L.dashb_evaluate_wait(c.h))
+    for r, ((ins, outs), w) in enumerate(zip(keep, want)):
+        assert_labels_equal([o.numpy() for o in outs], w, "%s async step %d" % (name, r))
+    # a synchronous call after the asynchronous ones still works
+    labels = tile_batch(g.inputs, 5)
+    assert_labels_equal(c.evaluate(labels), tile_batch(g.layers[-1], 5), "%s sync after async" % name)
+    c.close()

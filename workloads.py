@@ -161,6 +161,10 @@ def build_reference_circuit(spec, seed=42, weight_seed=42):
                 c.add_rescale_legacy(q_param, [w, h, ch])
             elif qname == "scaleplus":
                 c.add_rescale([q_param], [w, h, ch])
+        elif kind == "maxpool":
+            _, ksz, stride = layer
+            c.add_maxpool2d(w, h, ch, ksz, ksz, stride, stride)
+            w, h = (w - ksz) // stride + 1, (h - ksz) // stride + 1
         elif kind == "relu":
             c.add_relu(dims)
         elif kind == "sign":
