@@ -323,8 +323,10 @@ __global__ void __launch_bounds__(128) k_egress(const uint8_t* __restrict__ plan
  * (profiles/r1_v9_summary.md), loads issued from a few dozen CTAs do not.
  */
 constexpr int ING_E = 32;
-constexpr int ING_THREADS = 256;
-__global__ void __launch_bounds__(ING_THREADS) k_ingest_direct(const __grid_constant__ IngestParams P) {
+/* 128 threads at <= 32 registers: such a CTA fits on an SM next to eight
+ * k_sign CTAs (8 x 128 x 60 registers) instead of displacing one of them */
+constexpr int ING_THREADS = 128;
+__global__ void __launch_bounds__(ING_THREADS, 16) k_ingest_direct(const __grid_constant__ IngestParams P) {
     __shared__ uint4 buf[(ING_E * 128 * 2 + 32) / 16 + 1];
     /* A small persistent grid: the kernel shares the GPU with the lanes that
      * already compute and only has to keep the PCIe link busy (a few hundred
@@ -376,8 +378,8 @@ __global__ void __launch_bounds__(ING_THREADS) k_ingest_direct(const __grid_cons
                 for (uint32_t t = 0; t < 4; ++t)
                     if (4 * d4 + t < nc) w |= (uint32_t)(uint8_t)row[4 * d4 + t] << (8 * t);
                 uint32_t* dst = reinterpret_cast<uint32_t*>(plane + (((e0 + el) * nc4 + d4) * (uint64_t)P.Bp + b) * 4);
-                dst[0] = w;
-                for (uint32_t x = 1; x < nb; ++x) dst[x] = 0;
+                __stcs(dst, w); /* streaming: the planes must not push the ciphertext tables out of L2 */
+                for (uint32_t x = 1; x < nb; ++x) __stcs(dst + x, 0u);
             }
         }
         __syncthreads(); /* the buffer is free for the next item */
@@ -386,7 +388,7 @@ __global__ void __launch_bounds__(ING_THREADS) k_ingest_direct(const __grid_cons
 
 cudaError_t launch_ingest_direct(const IngestParams& p, cudaStream_t s) {
     if (p.n == 0 || p.batch == 0) return cudaSuccess;
-    static const int ctas = getenv("DASHB_INGEST_CTAS") ? atoi(getenv("DASHB_INGEST_CTAS")) : 96;
+    static const int ctas = getenv("DASHB_INGEST_CTAS") ? atoi(getenv("DASHB_INGEST_CTAS")) : 192;
     const uint64_t items = ((p.n + ING_E - 1) / ING_E) * p.batch * p.k;
     const unsigned grid = (unsigned)std::min<uint64_t>(items, (uint64_t)std::max(1, ctas));
     k_ingest_direct<<<grid, ING_THREADS, 0, s>>>(p);
