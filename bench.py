@@ -161,6 +161,138 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+def union_ms(iv):
+    """Length of the union of the intervals [(begin, end)]."""
+    tot, end = 0.0, None
+    for a, b in sorted(iv):
+        if end is None or a > end:
+            tot += b - a
+            end = b
+        elif b > end:
+            tot += b - end
+            end = b
+    return tot
+
+
+def oracle_parity(path, X, got, rows, threads):
+    """Output labels of inferences `rows` against oracle/dash_oracle.c (the pinned restatement) on the material file."""
+    from dash_b200 import gcm as gcm_io
+    from oracle import oraclebind as O
+
+    g = gcm_io.read_gcm(path)
+    oc = O.OracleCircuit(path)
+    ok = True
+    for b in rows:
+        want = oc.evaluate(gcm_io.encode_inputs(g, X[b]), threads=threads)
+        ok = ok and all(np.array_equal(o[b], w) for o, w in zip(got, want))
+    oc.close()
+    return bool(ok)
+
+
+def run_c3(torch, dist, rank, world, local_rank, barrier, steps=5, batch=64):
+    """BASELINE.json configs[2]: MODEL_F_GNNP_POOL_REPL (CIFAR-10 CNN, Rescale{32} after every linear layer),
+    material garbled on every rank's own GPU, `batch` inferences per GPU, batch-sharded (no data-path collective)."""
+    from dash_b200 import garble
+
+    model = "MODEL_F_GNNP_POOL_REPL"
+    spec = W.MODELS[model]
+    plain, n_in = W.plain_layers(spec)
+    X = W.synthetic_inputs(spec, batch, seed=100 + rank)
+    seed = b"bench-c3-gnnp"
+    c, gst = garble.garble_to_circuit(spec["crt"], spec["mrs"], n_in, plain, batch, seed=seed)
+    c.garble_inputs(X)
+    stream = torch.cuda.ExternalStream(__import__("dash_b200").api.stream_handle())
+    for _ in range(2):
+        c.evaluate_device()
+    torch.cuda.synchronize()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(steps):
+        c.evaluate_device()
+    e1.record(stream)
+    e1.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    # share of the scaling gadget in the step (events on the lane streams inside the concurrent step)
+    c.set_layer_timing(2)
+    c.evaluate_device()
+    iv = {}
+    last = 0.0
+    for name, _li, _lane, a, b in c.layer_intervals_ms():
+        iv.setdefault(name, []).append((a, b))
+        last = max(last, b)
+    c.set_layer_timing(0)
+    got = c.move_outputs()
+    vals, ok = c.decode_outputs()
+    out = {"model": model, "config": "BASELINE.json configs[2]", "batch_per_gpu": batch, "n_gpus": world, "scaling": "weak",
+           "ms_per_step": ms, "inferences_per_s": batch * world / (ms / 1e3), "all_outputs_decode": bool(ok.all()),
+           "k_rescale_share_of_step": union_ms(iv.get("rescale", [])) / last if last else None,
+           "busy_ms_by_layer_type": {n: union_ms(v) for n, v in iv.items()},
+           "material": "GPU garbler, %.0f ms of kernels, %.2f GB of tables per GPU" % (gst["kernel_ms"], gst["table_bytes"] / 1e9)}
+    c.close()
+    if rank == 0:
+        path = os.path.join(CACHE, "c3_gnnp.gcm")
+        garble.garble_to_file(spec["crt"], spec["mrs"], n_in, plain, path, seed=seed)
+        out["bit_exact_vs_oracle"] = oracle_parity(path, X, got, (0, batch - 1), host_threads())
+        out["parity_inferences_checked"] = 2
+        os.remove(path)
+    return out
+
+
+def run_c4(torch, dist, rank, world, local_rank, barrier, steps=5, batch=64):
+    """BASELINE.json configs[3]: MODEL_F_MINIONN_POOL_REPL, ONE global batch, output-channel sharding across the
+    ranks (strong scaling): every rank evaluates its block of each layer's output channels, the activation slices
+    are exchanged over NVLink after every layer group."""
+    from dash_b200 import garble, gcm as gcm_io
+    from dash_b200.scheduler import ChannelShardedEvaluator
+
+    model = "MODEL_F_MINIONN_POOL_REPL"
+    spec = W.MODELS[model]
+    plain, n_in = W.plain_layers(spec)
+    X = W.synthetic_inputs(spec, batch, seed=100)
+    seed = b"bench-c4-minionn"
+    mode = os.environ.get("DASHB_C4_EXCHANGE", "p2p")
+    if world == 1:  # the strong-scaling baseline: the same batch on one GPU, nothing to exchange
+        c, gst = garble.garble_to_circuit(spec["crt"], spec["mrs"], n_in, plain, batch, seed=seed)
+        c.evaluate_layers = lambda first, last: c.evaluate_device() if first == 0 else None
+    else:
+        c, gst = garble.garble_to_circuit(spec["crt"], spec["mrs"], n_in, plain, batch, seed=seed, shard=(rank, world),
+                                          shard_lanes=2 if mode == "p2p" else 0)
+    ev = ChannelShardedEvaluator(c, rank, world, dist=dist if world > 1 else None, p2p=(mode == "p2p"))
+    ev.load_values(X)
+    ev.run()  # warm-up (peer mappings / NCCL channels, lazy module loading)
+    ev.run()
+    torch.cuda.synchronize()
+    barrier()
+    ev.bytes_exchanged = 0
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        ev.run()
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1e3 / steps
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    got = c.move_outputs()
+    out = {"model": model, "config": "BASELINE.json configs[3]", "global_batch": batch, "n_gpus": world, "scaling": "strong",
+           "ms_per_step": ms, "inferences_per_s": batch / (ms / 1e3), "exchange": ev.describe(),
+           "nvlink_bytes_received_per_rank_per_step": ev.bytes_exchanged // steps,
+           "timing": "wall clock around %d steps between device synchronisations, max over ranks" % steps}
+    c.close()
+    if rank == 0:
+        path = os.path.join(CACHE, "c4_minionn.gcm")
+        garble.garble_to_file(spec["crt"], spec["mrs"], n_in, plain, path, seed=seed)
+        out["bit_exact_vs_oracle"] = oracle_parity(path, X, got, (0,), host_threads())
+        out["parity_inferences_checked"] = 1
+        os.remove(path)
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -172,6 +304,7 @@ def main():
     ap.add_argument("--ref-inferences", type=int, default=2, help="reference arm: inferences per step")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="cpu_baseline leg budget")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the c3_batch_sharded / c4_channel_sharded legs")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -335,17 +468,6 @@ def main():
     launch_ms = {}  # layer type -> [duration of every (lane, layer) launch]
     prof_step_ms = 0.0
 
-    def union_ms(iv):
-        tot, end = 0.0, None
-        for a, b in sorted(iv):
-            if end is None or a > end:
-                tot += b - a
-                end = b
-            elif b > end:
-                tot += b - end
-                end = b
-        return tot
-
     for it in range(3 + prof_steps):
         flush.zero_()
         torch.cuda.synchronize()
@@ -413,8 +535,8 @@ def main():
         "busy_ms_per_step": relu_ms,
         "avg_launch_ms": sum(relu_launch) / len(relu_launch),
         "min_max_launch_ms": [min(relu_launch), max(relu_launch)],
-        "timing": "CUDA events on the lane streams around every layer inside the concurrent step (4 sub-batch lanes), "
-                  "%d steps after the timed region; busy time = union of the lanes' intervals" % prof_steps,
+        "timing": "CUDA events on the lane streams around every layer inside the concurrent step (%d sub-batch lanes), "
+                  "%d steps after the timed region; busy time = union of the lanes' intervals" % (n_lanes, prof_steps),
         "step_ms_in_timing_pass": prof_step_ms,
         "share_of_step": relu_ms / prof_step_ms if prof_step_ms else None,
         "aes_blocks_per_s": aes_rate,
@@ -508,6 +630,20 @@ def main():
             }
         except Exception as ex:  # the extra key must never break the contract line
             line["offline_phase"] = {"error": str(ex)[:200]}
+    # ---- BASELINE.json configs[2] and configs[3] on the same run (extra keys; every rank takes part) ----
+    circ.close()
+    del flush
+    torch.cuda.empty_cache()
+    if not args.no_extras:
+        for key, fn in (("c3_batch_sharded", run_c3), ("c4_channel_sharded", run_c4)):
+            t0 = time.perf_counter()
+            try:
+                res = fn(torch, dist, rank, world, local_rank, barrier)
+                res["leg_seconds"] = time.perf_counter() - t0
+            except Exception as ex:  # an extra key must never break the contract line
+                res = {"error": "%s: %s" % (type(ex).__name__, str(ex)[:300])}
+            line[key] = res
+            barrier()
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -71,6 +71,15 @@ def lib():
         L.dashb_current_slice_compress.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, C.c_void_p]
         L.dashb_current_slice_decompress.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_uint64, C.c_void_p]
         L.dashb_layer_slice.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.dashb_set_shard_lanes.argtypes = [C.c_void_p, C.c_int]
+        L.dashb_shard_lanes_used.argtypes = [C.c_void_p]
+        L.dashb_shard_export.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.dashb_shard_import.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.dashb_evaluate_layers_lane.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+        L.dashb_shard_exchange.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.dashb_shard_exchange_bytes.restype = C.c_uint64
+        L.dashb_shard_exchange_bytes.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.dashb_shard_status.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint32)]
         L.dashb_set_layer_timing.argtypes = [C.c_void_p, C.c_int]
         L.dashb_layer_time_ms.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float)]
         L.dashb_lanes_used.argtypes = [C.c_void_p]
@@ -130,21 +139,51 @@ class Circuit:
         self.in_moduli = [self.L.dashb_crt_modulus(self.h, j) for j in range(self.k)]
 
     @classmethod
-    def load(cls, path, max_batch=1, shard=None):
+    def load(cls, path, max_batch=1, shard=None, shard_lanes=0):
         """Reads a DGCM material file and moves the circuit to the device.
         shard=(rank, world) makes it one rank of an output-channel-sharded
-        evaluation (see dash_b200.scheduler.ChannelShardedEvaluator)."""
+        evaluation (see dash_b200.scheduler.ChannelShardedEvaluator);
+        shard_lanes > 0 prepares the peer-memory exchange with that many
+        sub-batch lanes (otherwise the exchange goes through NCCL)."""
         L = lib()
         h = C.c_void_p()
         _check(L.dashb_circuit_load(C.byref(h), os.fsencode(path)))
         if shard is not None:
             _check(L.dashb_set_shard(h, int(shard[0]), int(shard[1])))
+            if shard_lanes:
+                _check(L.dashb_set_shard_lanes(h, int(shard_lanes)))
         _check(L.dashb_finalize(h, int(max_batch)))
         return cls(h, max_batch)
 
     # ---- channel sharding -------------------------------------------------
     def evaluate_layers(self, first, last):
         _check(self.L.dashb_evaluate_layers(self.h, int(first), int(last)))
+
+    # peer-memory exchange (one process per GPU, CUDA IPC)
+    def shard_export(self, lane):
+        buf = C.create_string_buffer(192)
+        _check(self.L.dashb_shard_export(self.h, lane, buf))
+        return bytes(buf.raw)
+
+    def shard_import(self, lane, peer_rank, handles):
+        _check(self.L.dashb_shard_import(self.h, lane, int(peer_rank), C.create_string_buffer(bytes(handles), 192)))
+
+    def evaluate_layers_lane(self, lane, first, last):
+        _check(self.L.dashb_evaluate_layers_lane(self.h, int(lane), int(first), int(last)))
+
+    def shard_exchange(self, lane, layer):
+        _check(self.L.dashb_shard_exchange(self.h, int(lane), int(layer)))
+
+    def shard_exchange_bytes(self, lane, layer):
+        return self.L.dashb_shard_exchange_bytes(self.h, int(lane), int(layer))
+
+    def shard_timed_out(self, lane):
+        v = C.c_uint32(0)
+        _check(self.L.dashb_shard_status(self.h, int(lane), C.byref(v)))
+        return v.value
+
+    def lanes_used(self):
+        return self.L.dashb_lanes_used(self.h)
 
     def current_plane(self, j):
         """(device pointer, bytes per element, elements) of plane j of the

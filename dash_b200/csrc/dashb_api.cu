@@ -411,6 +411,12 @@ struct Lane {
     cudaEvent_t in_done_x[3] = {nullptr, nullptr, nullptr}; /* the lane's copies on the further copy streams */
     DevMem buf_in, buf_a, buf_b, stage_in, stage_out, xvals;
     DevMem pool; /* max pooling: the ReLU gadget's input (y - x) and output, two tensors of the layer's output size */
+    /* output-channel sharding over peer memory: two gather buffers, the epoch flags, and every rank's copies of them */
+    DevMem gat[2], flags;
+    uint8_t* peer_gat[2][MAXR] = {};
+    uint32_t* peer_flags[MAXR] = {};
+    int gcur{0};
+    uint32_t epoch{0};
     Tensor t_in, t_cur;
     int which{0};
     uint32_t b0{0}, batch{0}, Bp{0};
@@ -446,6 +452,8 @@ struct dashb_circuit {
     bool async_busy[2] = {false, false};
     int async_next{0};
     int shard_rank{0}, shard_world{1};
+    int shard_lanes{0}; /* > 0: peer-memory exchange with that many sub-batch lanes (dashb_set_shard_lanes) */
+    std::vector<void*> ipc_opened;
     uint32_t lane_cap{0};
     std::vector<uint32_t> lane_weights; /* DASHB_LANE_SPLIT */
     cudaEvent_t ev_fork{nullptr};
@@ -478,6 +486,7 @@ struct dashb_circuit {
         if (ingest_s) cudaStreamDestroy(ingest_s);
         for (auto e : async_done)
             if (e) cudaEventDestroy(e);
+        for (void* p : ipc_opened) cudaIpcCloseMemHandle(p);
         for (auto& l : lanes_alt) lanes.push_back(std::move(l));
         for (auto& l : lanes) {
             if (l->done) cudaEventDestroy(l->done);
@@ -1225,6 +1234,17 @@ static int make_lanes(dashb_circuit* c, std::vector<std::unique_ptr<Lane>>& lane
             CU(ln->pool.alloc(pool_bytes));
             CU(cudaMemset(ln->pool.p, 0, pool_bytes));
         }
+        if (c->shard_world > 1 && c->shard_lanes > 0) {
+            for (auto& g : ln->gat) {
+                CU(g.alloc(act_bytes));
+                CU(cudaMemset(g.p, 0, act_bytes));
+            }
+            CU(ln->flags.alloc(4 * (MAXR + 1)));
+            CU(cudaMemset(ln->flags.p, 0, 4 * (MAXR + 1)));
+            ln->peer_gat[0][c->shard_rank] = (uint8_t*)ln->gat[0].p;
+            ln->peer_gat[1][c->shard_rank] = (uint8_t*)ln->gat[1].p;
+            ln->peer_flags[c->shard_rank] = (uint32_t*)ln->flags.p;
+        }
         CU(cudaMemset(ln->buf_in.p, 0, in_bytes));
         CU(cudaMemset(ln->buf_a.p, 0, act_bytes));
         CU(cudaMemset(ln->buf_b.p, 0, act_bytes));
@@ -1244,7 +1264,7 @@ int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
         layer_slice(c, li, c->shard_rank, &L.e0, &L.e1, &L.v0, &L.v1);
     }
     int n_lanes = max_batch >= 128 ? 4 : (max_batch >= 64 ? 2 : 1);
-    if (c->shard_world > 1) n_lanes = 1; /* the channel-sharded path exchanges whole planes */
+    if (c->shard_world > 1) n_lanes = c->shard_lanes > 0 ? c->shard_lanes : 1; /* NCCL path: whole planes, one lane */
     if (const char* env = getenv("DASHB_LANES")) {
         int v = atoi(env);
         if (v >= 1 && v <= 16 && c->shard_world == 1) n_lanes = v;
@@ -1827,6 +1847,130 @@ int dashb_evaluate_layers(dashb_circuit* c, int first, int last) {
     }
     c->out_n = c->layers[last]->out_size;
     for (int j = 0; j < c->k; ++j) c->out_q[j] = c->layers[last]->out_q[j];
+    return DASHB_OK;
+}
+
+int dashb_set_shard_lanes(dashb_circuit* c, int lanes) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if (lanes < 1 || lanes > 8) return fail(DASHB_EINVAL, "shard lanes %d outside 1..8", lanes);
+    if (c->shard_world > MAXR) return fail(DASHB_EINVAL, "peer exchange supports up to %d ranks", MAXR);
+    c->shard_lanes = lanes;
+    return DASHB_OK;
+}
+
+int dashb_shard_lanes_used(const dashb_circuit* c) { return c ? c->lanes_used : 0; }
+
+/* 3 x 64 bytes: the IPC handles of lane `lane`'s two gather buffers and its flag array */
+int dashb_shard_export(dashb_circuit* c, int lane, void* handles) {
+    if (!c || !handles) return fail(DASHB_EINVAL, "null argument");
+    if (!c->finalized || c->shard_lanes < 1 || lane < 0 || lane >= c->n_lanes) return fail(DASHB_ESTATE, "no such sharded lane");
+    Lane& ln = *c->lanes[lane];
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle size");
+    cudaIpcMemHandle_t* h = (cudaIpcMemHandle_t*)handles;
+    CU(cudaIpcGetMemHandle(&h[0], ln.gat[0].p));
+    CU(cudaIpcGetMemHandle(&h[1], ln.gat[1].p));
+    CU(cudaIpcGetMemHandle(&h[2], ln.flags.p));
+    return DASHB_OK;
+}
+
+int dashb_shard_import(dashb_circuit* c, int lane, int peer_rank, const void* handles) {
+    if (!c || !handles) return fail(DASHB_EINVAL, "null argument");
+    if (!c->finalized || c->shard_lanes < 1 || lane < 0 || lane >= c->n_lanes) return fail(DASHB_ESTATE, "no such sharded lane");
+    if (peer_rank < 0 || peer_rank >= c->shard_world || peer_rank == c->shard_rank) return fail(DASHB_EINVAL, "bad peer rank %d", peer_rank);
+    Lane& ln = *c->lanes[lane];
+    const cudaIpcMemHandle_t* h = (const cudaIpcMemHandle_t*)handles;
+    void* p[3] = {nullptr, nullptr, nullptr};
+    for (int i = 0; i < 3; ++i) {
+        CU(cudaIpcOpenMemHandle(&p[i], h[i], cudaIpcMemLazyEnablePeerAccess));
+        c->ipc_opened.push_back(p[i]);
+    }
+    ln.peer_gat[0][peer_rank] = (uint8_t*)p[0];
+    ln.peer_gat[1][peer_rank] = (uint8_t*)p[1];
+    ln.peer_flags[peer_rank] = (uint32_t*)p[2];
+    return DASHB_OK;
+}
+
+/* layers first..last of one lane on that lane's stream */
+int dashb_evaluate_layers_lane(dashb_circuit* c, int lane, int first, int last) {
+    if (!c) return fail(DASHB_EINVAL, "null circuit");
+    if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "no inputs moved");
+    if (first < 0 || last < first || last >= (int)c->layers.size()) return fail(DASHB_EINVAL, "bad layer range");
+    if (lane < 0 || lane >= c->lanes_used) return fail(DASHB_EINVAL, "bad lane %d", lane);
+    Lane& ln = *c->lanes[lane];
+    if (first == 0) {
+        /* behind the inputs (dashb_move_inputs / dashb_garble_inputs joined the library stream) */
+        CU(cudaEventRecord(ln.in_done, g_stream));
+        CU(cudaStreamWaitEvent(ln.s, ln.in_done, 0));
+        ln.t_cur = ln.t_in;
+        ln.which = 0;
+        if (lane == 0) c->launches = 0;
+    }
+    for (int li = first; li <= last; ++li) {
+        int rc = run_layer(c, ln, li, ln.s);
+        if (rc) return rc;
+    }
+    c->out_n = c->layers[last]->out_size;
+    for (int j = 0; j < c->k; ++j) c->out_q[j] = c->layers[last]->out_q[j];
+    return DASHB_OK;
+}
+
+/* After layer `layer`: this rank's slice of the lane's current tensor goes to
+ * every rank's gather buffer; the lane's stream continues once every rank's
+ * slice has arrived here.  The lane's current tensor is then the gathered one. */
+int dashb_shard_exchange(dashb_circuit* c, int lane, int layer) {
+    if (!c) return fail(DASHB_EINVAL, "null circuit");
+    if (!c->finalized || c->shard_lanes < 1 || c->batch == 0) return fail(DASHB_ESTATE, "no sharded evaluation in flight");
+    if (lane < 0 || lane >= c->lanes_used || layer < 0 || layer >= (int)c->layers.size()) return fail(DASHB_EINVAL, "bad lane or layer");
+    Lane& ln = *c->lanes[lane];
+    const int W = c->shard_world, x = ln.gcur;
+    for (int r = 0; r < W; ++r)
+        if (!ln.peer_gat[x][r] || !ln.peer_flags[r]) return fail(DASHB_ESTATE, "rank %d's buffers were not imported (dashb_shard_import)", r);
+    const Tensor cur = ln.t_cur;
+    Tensor dst;
+    carve(dst, (uint8_t*)ln.gat[x].p, cur.n, cur.k, cur.q, ln.Bp);
+    uint64_t e0, e1;
+    uint32_t v0, v1;
+    layer_slice(c, layer, c->shard_rank, &e0, &e1, &v0, &v1);
+    ShardPushParams p;
+    memset(&p, 0, sizeof(p));
+    p.k = cur.k;
+    p.world = W;
+    p.e0 = e0;
+    p.e1 = e1;
+    for (int j = 0; j < cur.k; ++j) {
+        p.src[j] = cur.plane[j];
+        p.dst_off[j] = (uint64_t)(dst.plane[j] - (uint8_t*)ln.gat[x].p);
+        p.row[j] = (uint64_t)((nr_comps(cur.q[j]) + 3) & ~3) * ln.Bp;
+    }
+    for (int r = 0; r < W; ++r) p.peer[r] = ln.peer_gat[x][r];
+    const uint32_t epoch = ++ln.epoch;
+    CU(launch_shard_push(p, ln.s));
+    CU(launch_shard_signal(ln.peer_flags, W, c->shard_rank, epoch, ln.s));
+    CU(launch_shard_wait((uint32_t*)ln.flags.p, W, epoch, ln.s));
+    c->launches += 3;
+    ln.t_cur = dst;
+    ln.gcur ^= 1;
+    return DASHB_OK;
+}
+
+/* bytes this rank receives from its peers in dashb_shard_exchange(lane, layer) */
+uint64_t dashb_shard_exchange_bytes(dashb_circuit* c, int lane, int layer) {
+    if (!c || !c->finalized || lane < 0 || lane >= c->lanes_used || layer < 0 || layer >= (int)c->layers.size()) return 0;
+    Lane& ln = *c->lanes[lane];
+    uint64_t e0, e1;
+    uint32_t v0, v1;
+    layer_slice(c, layer, c->shard_rank, &e0, &e1, &v0, &v1);
+    const Layer& L = *c->layers[layer];
+    uint64_t per = 0;
+    for (int j = 0; j < c->k; ++j) per += (uint64_t)((nr_comps(L.out_q[j]) + 3) & ~3) * ln.Bp;
+    return (L.out_size - (e1 - e0)) * per;
+}
+
+/* 0, or the epoch at which a lane's wait for its peers timed out */
+int dashb_shard_status(dashb_circuit* c, int lane, uint32_t* timed_out_epoch) {
+    if (!c || !timed_out_epoch || lane < 0 || lane >= c->n_lanes || !c->lanes[lane]->flags.p) return fail(DASHB_EINVAL, "bad argument");
+    CU(cudaMemcpy(timed_out_epoch, (uint32_t*)c->lanes[lane]->flags.p + MAXR, 4, cudaMemcpyDeviceToHost));
     return DASHB_OK;
 }
 

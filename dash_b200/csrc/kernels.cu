@@ -719,6 +719,80 @@ extern "C" int dashb_projection_static(const int16_t* d_in, const dashb_u128* d_
 
 namespace dashb {
 
+/* ------------------------------------ output-channel sharding exchange */
+/*
+ * The all-gather of output-channel sharding as plain stores into peer
+ * memory: after a layer group every rank owns a block of elements of the
+ * activation tensor; k_shard_push reads that block once and stores it into
+ * the gather buffer of EVERY rank (NVLink / NVSwitch posted writes for the
+ * peers, a local store for itself).  k_shard_signal then publishes the lane's
+ * epoch in every rank's flag array and k_shard_wait holds the lane's stream
+ * until all ranks have published it -- the next layer reads a complete
+ * tensor.  No NCCL, no host synchronisation; with two sub-batch lanes one
+ * lane's exchange overlaps the other lane's layer group.  Gather buffers are
+ * double-buffered per lane: a rank can only be pushing group g+2 into the
+ * buffer group g used once every rank has finished group g+1, i.e. stopped
+ * reading it.  (Plain loads and stores only: no TMA, no multicast.)
+ */
+__global__ void __launch_bounds__(256) k_shard_push(const __grid_constant__ ShardPushParams P) {
+    const int j = blockIdx.y;
+    const uint64_t nvec = (P.e1 - P.e0) * P.row[j] / 16; /* rows are multiples of 64 bytes */
+    const uint4* src = reinterpret_cast<const uint4*>(P.src[j] + P.e0 * P.row[j]);
+    const uint64_t off = P.dst_off[j] + P.e0 * P.row[j];
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint4 v = src[i];
+        for (int r = 0; r < P.world; ++r) reinterpret_cast<uint4*>(P.peer[r] + off)[i] = v;
+    }
+    __threadfence_system();
+}
+
+struct ShardFlagPtrs {
+    uint32_t* p[MAXR];
+};
+__global__ void k_shard_signal(const ShardFlagPtrs F, int world, int rank, uint32_t epoch) {
+    if ((int)threadIdx.x < world) {
+        __threadfence_system();
+        *reinterpret_cast<volatile uint32_t*>(F.p[threadIdx.x] + rank) = epoch;
+        __threadfence_system();
+    }
+}
+/* flags[r] >= epoch for every rank r; gives up after ~4 s of spinning (a
+ * peer that died must not hang this GPU) and records that in flags[MAXR] */
+__global__ void k_shard_wait(uint32_t* flags, int world, uint32_t epoch) {
+    if ((int)threadIdx.x < world) {
+        const long long t0 = clock64();
+        while ((int32_t)(*reinterpret_cast<volatile uint32_t*>(flags + threadIdx.x) - epoch) < 0) {
+            if (clock64() - t0 > 8000000000ll) {
+                *reinterpret_cast<volatile uint32_t*>(flags + MAXR) = epoch;
+                break;
+            }
+            __nanosleep(200);
+        }
+        __threadfence_system();
+    }
+}
+
+cudaError_t launch_shard_push(const ShardPushParams& p, cudaStream_t s) {
+    if (p.e1 <= p.e0) return cudaSuccess;
+    uint64_t nvec = 0;
+    for (int j = 0; j < p.k; ++j) nvec = std::max<uint64_t>(nvec, (p.e1 - p.e0) * p.row[j] / 16);
+    /* a modest grid: the exchange shares the GPU with the other lane's layer group */
+    dim3 grid((unsigned)std::min<uint64_t>((nvec + 255) / 256, 148 * 2), p.k);
+    k_shard_push<<<grid, 256, 0, s>>>(p);
+    return cudaGetLastError();
+}
+cudaError_t launch_shard_signal(uint32_t* const* peer_flags, int world, int rank, uint32_t epoch, cudaStream_t s) {
+    ShardFlagPtrs f;
+    memset(&f, 0, sizeof(f));
+    for (int r = 0; r < world; ++r) f.p[r] = peer_flags[r];
+    k_shard_signal<<<1, 32, 0, s>>>(f, world, rank, epoch);
+    return cudaGetLastError();
+}
+cudaError_t launch_shard_wait(uint32_t* flags, int world, uint32_t epoch, cudaStream_t s) {
+    k_shard_wait<<<1, 32, 0, s>>>(flags, world, epoch);
+    return cudaGetLastError();
+}
+
 /* --------------------------------------------------------- max pooling */
 /*
  * GarbledMaxPool2d::cpu_evaluate (layer/garbled_maxpool2d.h:143-224): every

@@ -113,6 +113,18 @@ struct IngestParams {
     int k;
 };
 
+/* k_shard_push: one rank's slice of an activation tensor stored into the
+ * gather buffer of every rank (its own included) over NVLink peer memory */
+constexpr int MAXR = 16; /* ranks of an output-channel-sharded evaluation */
+struct ShardPushParams {
+    const uint8_t* src[MAXK]; /* plane j of the tensor the layer group produced */
+    uint64_t dst_off[MAXK];   /* offset of plane j inside a gather buffer */
+    uint64_t row[MAXK];       /* bytes per element of plane j */
+    uint64_t e0, e1;          /* this rank's elements */
+    uint8_t* peer[MAXR];      /* every rank's gather buffer (this rank's own at [rank]) */
+    int k, world;
+};
+
 struct ProjParams {
     const uint8_t* in[MAXK];
     uint8_t* out[MAXK];
@@ -276,6 +288,9 @@ cudaError_t conv_tc_make_map(void* map_out, const void* ptr, uint64_t row_bytes,
 cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p, cudaStream_t s);
 cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s);
 cudaError_t launch_projection(const ProjParams& p, cudaStream_t s);
+cudaError_t launch_shard_push(const ShardPushParams& p, cudaStream_t s);
+cudaError_t launch_shard_signal(uint32_t* const* peer_flags, int world, int rank, uint32_t epoch, cudaStream_t s);
+cudaError_t launch_shard_wait(uint32_t* flags, int world, uint32_t epoch, cudaStream_t s);
 cudaError_t launch_pool_step(const PoolParams& p, cudaStream_t s);
 cudaError_t launch_rescale(const RescaleParams& p, cudaStream_t s);
 cudaError_t launch_add_label(const AddLabelParams& p, cudaStream_t s);

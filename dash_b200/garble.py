@@ -93,9 +93,11 @@ def garble_to_file(crt, mrs, input_size, layers, path, seed=None, max_modulus=0,
     return _stats(st)
 
 
-def garble_to_circuit(crt, mrs, input_size, layers, max_batch, seed=None, max_modulus=0):
+def garble_to_circuit(crt, mrs, input_size, layers, max_batch, seed=None, max_modulus=0, shard=None, shard_lanes=0):
     """Garbles `layers` straight into an evaluator circuit on the current
-    device (the tables never leave the GPU).  Returns (api.Circuit, stats)."""
+    device (the tables never leave the GPU).  shard=(rank, world) makes it one
+    rank of an output-channel-sharded evaluation (every rank garbles the same
+    seed).  Returns (api.Circuit, stats)."""
     L = api.lib()
     L.dashb_garble_to_circuit.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64, C.c_void_p, C.c_int,
                                           C.c_char_p, C.POINTER(C.c_void_p), C.c_void_p]
@@ -108,5 +110,9 @@ def garble_to_circuit(crt, mrs, input_size, layers, max_batch, seed=None, max_mo
     api._check(L.dashb_garble_to_circuit(crt_a.ctypes.data, len(crt), mrs_a.ctypes.data, len(mrs), int(max_modulus),
                                          int(input_size), C.byref(arr), len(layers), seed, C.byref(h), C.byref(st)))
     del keep
+    if shard is not None:
+        api._check(L.dashb_set_shard(h, int(shard[0]), int(shard[1])))
+        if shard_lanes:
+            api._check(L.dashb_set_shard_lanes(h, int(shard_lanes)))
     api._check(L.dashb_finalize(h, int(max_batch)))
     return api.Circuit(h, max_batch), _stats(st)

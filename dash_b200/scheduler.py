@@ -94,16 +94,44 @@ class ChannelShardedEvaluator:
     """Output-channel sharding of ONE batch across the GPUs of a box (config
     C4): every rank owns a block of each linear layer's output rows and the
     same elements of the gadget layers behind it; after each group of layers
-    the ranks' slices of the activation planes are exchanged in place with
-    NCCL broadcasts over NVLink (one per rank and CRT modulus, straight on
-    the device planes).  Weights and tables are replicated."""
+    the ranks' slices of the activation planes are exchanged.  Weights and
+    tables are replicated.
 
-    def __init__(self, circuit, rank, world, dist=None, as_tensor=None, compressed=False):
+    Two exchanges.  p2p=True (the circuit was prepared with shard_lanes > 0):
+    the library's own all-gather, plain stores into every peer's gather
+    buffer over NVLink (CUDA IPC mappings exchanged once through
+    torch.distributed), per sub-batch lane, so that one lane's exchange
+    overlaps the other lane's layer group -- no NCCL in the data path.
+    Otherwise: NCCL all-gathers / broadcasts straight on the device planes
+    (one per CRT modulus), one lane."""
+
+    def __init__(self, circuit, rank, world, dist=None, as_tensor=None, compressed=False, p2p=False):
         self.c = circuit
         self.rank = rank
         self.world = world
         self.dist = dist
         self.as_tensor = as_tensor
+        self.p2p = bool(p2p) and world > 1
+        if self.p2p:
+            if dist is None:
+                raise ValueError("the peer-memory exchange needs torch.distributed to hand the IPC handles round")
+            n_lanes = circuit.L.dashb_shard_lanes_used(circuit.h) or 1
+            # lanes exist from dashb_finalize on; export every lane the circuit has
+            handles = []
+            lane = 0
+            while True:
+                try:
+                    handles.append(circuit.shard_export(lane))
+                except Exception:
+                    break
+                lane += 1
+            everyone = [None] * world
+            dist.all_gather_object(everyone, handles)
+            for r in range(world):
+                if r != rank:
+                    for lane, h in enumerate(everyone[r]):
+                        circuit.shard_import(lane, r, h)
+            dist.barrier()
         self.groups = layer_groups([circuit.layer_type(i) for i in range(circuit.n_layers)])
         self.bytes_exchanged = 0
         self._ext = None
@@ -177,12 +205,45 @@ class ChannelShardedEvaluator:
             self.c.sync()
             exchange()
 
-    def evaluate(self, labels):
-        """labels: the whole batch on every rank.  Returns the output labels
-        (identical on every rank)."""
+    def describe(self):
+        if self.world == 1:
+            return "none (one rank)"
+        if self.p2p:
+            return ("stores into peer memory over NVLink (k_shard_push + epoch flags), %d sub-batch lanes, "
+                    "one exchange per layer group and lane" % self.c.lanes_used())
+        return "compressed labels over NCCL" if self.compressed else "NCCL all-gather of the digit planes, one per CRT modulus and layer group"
+
+    def load_labels(self, labels):
         self.c.move_inputs(labels)
+
+    def load_values(self, values):
+        """Plaintext inputs, encoded on the device (needs the input encoding in the material)."""
+        self.c.garble_inputs(values)
+
+    def run(self):
+        """All layer groups on the inputs loaded last, exchanges included; asynchronous."""
+        if self.p2p:
+            lanes = range(self.c.lanes_used())
+            for first, last in self.groups:
+                for lane in lanes:
+                    self.c.evaluate_layers_lane(lane, first, last)
+                for lane in lanes:
+                    self.c.shard_exchange(lane, last)
+                    self.bytes_exchanged += self.c.shard_exchange_bytes(lane, last)
+            return
         for first, last in self.groups:
             self.c.evaluate_layers(first, last)
             if self.world > 1:
                 self._gather(last)
-        return self.c.move_outputs()
+
+    def evaluate(self, labels):
+        """labels: the whole batch on every rank.  Returns the output labels
+        (identical on every rank)."""
+        self.load_labels(labels)
+        self.run()
+        out = self.c.move_outputs()
+        if self.p2p:
+            for lane in range(self.c.lanes_used()):
+                if self.c.shard_timed_out(lane):
+                    raise RuntimeError("rank %d: a peer never delivered its slice (lane %d)" % (self.rank, lane))
+        return out

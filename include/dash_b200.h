@@ -330,6 +330,28 @@ int dashb_evaluate_layers(dashb_circuit* c, int first, int last);
 int dashb_current_plane(dashb_circuit* c, int j, void** dev_ptr, uint64_t* bytes_per_element,
                         uint64_t* n_elements);
 
+/* The same exchange without NCCL: plain stores into peer memory over NVLink.
+ * dashb_set_shard_lanes(c, n) (before dashb_finalize, n sub-batch lanes, 2 is
+ * the useful number) gives every lane two gather buffers and a flag array;
+ * every rank exports their CUDA IPC handles (dashb_shard_export: 3 x 64
+ * bytes per lane), hands them to its peers by any host channel and imports
+ * theirs (dashb_shard_import).  Then, per layer group and lane:
+ * dashb_evaluate_layers_lane(lane, first, last) enqueues the layers on the
+ * lane's stream and dashb_shard_exchange(lane, last) behind them one kernel
+ * that stores this rank's slice into every rank's gather buffer, a signal and
+ * a wait for all ranks' signals -- while one lane waits for its peers the
+ * other lane computes.  Nothing synchronises with the host; a peer that never
+ * signals makes the wait give up after a few seconds (dashb_shard_status).
+ * All ranks must issue the same sequence of exchanges. */
+int dashb_set_shard_lanes(dashb_circuit* c, int lanes);
+int dashb_shard_lanes_used(const dashb_circuit* c);
+int dashb_shard_export(dashb_circuit* c, int lane, void* handles_3x64);
+int dashb_shard_import(dashb_circuit* c, int lane, int peer_rank, const void* handles_3x64);
+int dashb_evaluate_layers_lane(dashb_circuit* c, int lane, int first, int last);
+int dashb_shard_exchange(dashb_circuit* c, int lane, int layer);
+uint64_t dashb_shard_exchange_bytes(dashb_circuit* c, int lane, int layer);
+int dashb_shard_status(dashb_circuit* c, int lane, uint32_t* timed_out_epoch);
+
 /* Elements [e0, e1) of plane j of the current tensor as compressed labels in
  * DEVICE memory (dashb_u128 [batch][e1 - e0]) and back, enqueued on the
  * library stream: the sharded exchange then moves 16 bytes per label over

@@ -1,0 +1,42 @@
+"""Output-channel sharding with the library's own exchange over peer memory
+(dashb_shard_export / _import / _exchange): `world` processes, one "rank"
+each, all on GPU 0, map each other's gather buffers through CUDA IPC and run
+the real protocol.  Every rank must end with the reference's output labels."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+
+from helpers import ROOT
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+@pytest.mark.parametrize("name,world,batch,lanes", [("MLP_TINY", 2, 40, 2), ("CONV_UNIT", 3, 33, 2), ("RESCALE_OPT", 2, 5, 1),
+                                                    ("SIGN_TINY", 4, 64, 2)])
+def test_peer_memory_exchange_between_processes(gpu, name, world, batch, lanes):
+    port = str(_free_port())
+    worker = os.path.join(ROOT, "tests", "p2p_shard_worker.py")
+    procs = [subprocess.Popen([sys.executable, worker, str(r), str(world), port, name, str(batch), str(lanes)],
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for r in range(world)]
+    outs = []
+    for p in procs:
+        try:
+            out, _ = p.communicate(timeout=240)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+        outs.append(out)
+    for r, (p, out) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0 and ("rank %d ok" % r) in out, "rank %d:\n%s" % (r, out[-3000:])
