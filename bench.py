@@ -278,11 +278,16 @@ def run_c4(torch, dist, rank, world, local_rank, barrier, steps=5, batch=64):
         t = torch.tensor([ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
+    trace = None
+    if world > 1 and mode == "p2p" and os.environ.get("DASHB_C4_TRACE"):
+        trace = ev.trace()
     got = c.move_outputs()
     out = {"model": model, "config": "BASELINE.json configs[3]", "global_batch": batch, "n_gpus": world, "scaling": "strong",
            "ms_per_step": ms, "inferences_per_s": batch / (ms / 1e3), "exchange": ev.describe(),
            "nvlink_bytes_received_per_rank_per_step": ev.bytes_exchanged // steps,
            "timing": "wall clock around %d steps between device synchronisations, max over ranks" % steps}
+    if trace is not None:
+        out["trace_ms_rank0_[group][lane](layers_done, exchange_done)"] = trace
     c.close()
     if rank == 0:
         path = os.path.join(CACHE, "c4_minionn.gcm")

@@ -73,6 +73,8 @@ def lib():
         L.dashb_layer_slice.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.dashb_set_shard_lanes.argtypes = [C.c_void_p, C.c_int]
         L.dashb_shard_lanes_used.argtypes = [C.c_void_p]
+        L.dashb_lane_stream.restype = C.c_void_p
+        L.dashb_lane_stream.argtypes = [C.c_void_p, C.c_int]
         L.dashb_shard_export.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.dashb_shard_import.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.dashb_evaluate_layers_lane.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]

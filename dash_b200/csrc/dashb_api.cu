@@ -393,9 +393,14 @@ struct Layer {
     DevMem proj[MAXK];
     /* max pooling */
     uint32_t pl_w{0}, pl_h{0}, pl_c{0}, pl_kw{0}, pl_kh{0}, pl_sw{0}, pl_sh{0}, pl_ow{0}, pl_oh{0};
-    /* channel sharding: output elements [e0, e1) / linear rows [v0, v1) of this rank */
+    /* sharding: output elements [e0, e1) / linear rows [v0, v1) of this rank; or, a convolution sharded by
+     * output pixels [p0, p1) (peer-memory exchange): the elements are seg = p1 - p0 pixels of each of the
+     * nseg filters, run s starting at element e0 + s * stride (stride = pixels per filter) */
     uint64_t e0{0}, e1{0};
     uint32_t v0{0}, v1{0};
+    uint32_t p0{0}, p1{0};
+    uint64_t seg{0}, stride{0}, nseg{0};
+    uint64_t slice_count() const { return seg ? seg * nseg : e1 - e0; }
     /* accounting */
     double label_bytes{0}, weight_bytes{0}, aes{0}, ref_aes{0};
     float ms{0};
@@ -1186,6 +1191,52 @@ static void layer_slice(const dashb_circuit* c, int layer, int rank, uint64_t* e
     *v1 = r1;
 }
 
+/* pixel sharding of the convolutions: with the peer-memory exchange (which moves strided slices) and without
+ * legacy rescale layers (k_add_label works on contiguous slices) */
+static bool pixel_sharding(const dashb_circuit* c) {
+    if (c->shard_world <= 1 || c->shard_lanes < 1) return false;
+    for (auto& L : c->layers)
+        if (L->type == DASHB_LAYER_RESCALE_LEGACY) return false;
+    return true;
+}
+
+/* this rank's slice of every layer, strided form included (see Layer) */
+static void assign_slices(dashb_circuit* c) {
+    const bool by_pixel = pixel_sharding(c);
+    const int W = c->shard_world, rank = c->shard_rank;
+    uint64_t seg = 0, stride = 0, nseg = 0;
+    uint32_t p0 = 0, p1 = 0;
+    for (int li = 0; li < (int)c->layers.size(); ++li) {
+        Layer& L = *c->layers[li];
+        layer_slice(c, li, rank, &L.e0, &L.e1, &L.v0, &L.v1);
+        if (L.type == DASHB_LAYER_DENSE) {
+            seg = stride = nseg = 0;
+            p0 = 0, p1 = 1;
+        } else if (L.type == DASHB_LAYER_CONV2D) {
+            if (by_pixel) {
+                p0 = (uint32_t)((uint64_t)L.npix * rank / W);
+                p1 = (uint32_t)((uint64_t)L.npix * (rank + 1) / W);
+                seg = p1 - p0;
+                stride = L.npix;
+                nseg = L.M;
+                L.v0 = 0;
+                L.v1 = (uint32_t)L.M;
+                L.e0 = p0;
+                L.e1 = p0; /* not a contiguous range: slice_count() counts the runs */
+            } else {
+                seg = stride = nseg = 0;
+                p0 = 0, p1 = L.npix;
+            }
+        }
+        if (seg) {
+            L.e0 = p0;
+            L.e1 = p0;
+        }
+        L.seg = seg, L.stride = stride, L.nseg = nseg;
+        L.p0 = p0, L.p1 = p1;
+    }
+}
+
 int dashb_set_shard(dashb_circuit* c, int rank, int world) {
     int rc = check_building(c);
     if (rc) return rc;
@@ -1259,10 +1310,7 @@ int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
     if (rc) return rc;
     if (max_batch == 0 || max_batch > (1u << 24)) return fail(DASHB_EINVAL, "bad max_batch");
     c->max_batch = max_batch;
-    for (int li = 0; li < (int)c->layers.size(); ++li) {
-        Layer& L = *c->layers[li];
-        layer_slice(c, li, c->shard_rank, &L.e0, &L.e1, &L.v0, &L.v1);
-    }
+    assign_slices(c);
     int n_lanes = max_batch >= 128 ? 4 : (max_batch >= 64 ? 2 : 1);
     if (c->shard_world > 1) n_lanes = c->shard_lanes > 0 ? c->shard_lanes : 1; /* NCCL path: whole planes, one lane */
     if (const char* env = getenv("DASHB_LANES")) {
@@ -1569,6 +1617,8 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
                 tp.Bp = Bp;
                 tp.v0 = L.v0;
                 tp.v1 = L.v1;
+                tp.p0 = L.p0;
+                tp.p1 = L.p1;
                 tp.nkb = L.tc_nkb;
                 const bool conv = L.type == DASHB_LAYER_CONV2D;
                 tp.conv = conv;
@@ -1613,6 +1663,8 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
             p.M = (uint32_t)L.M;
             p.v0 = L.v0;
             p.v1 = L.v1;
+            p.p0 = L.p0;
+            p.p1 = L.p1;
             p.K = (uint32_t)L.K;
             p.Kp = L.Kp;
             p.npix = L.npix;
@@ -1628,8 +1680,10 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
         case DASHB_LAYER_SIGN: {
             const bool relu = L.type == DASHB_LAYER_RELU;
             SignParams p;
-            fill_sign_params(c, p, L.e1 - L.e0, relu ? 1 : c->k);
+            fill_sign_params(c, p, L.slice_count(), relu ? 1 : c->k);
             p.e0 = L.e0;
+            p.seg = L.seg;
+            p.stride = L.stride;
             for (int j = 0; j < c->k; ++j) {
                 p.in[j] = cur.plane[j];
                 p.out[j] = out.plane[j];
@@ -1663,7 +1717,9 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
                 p.tm = (const u128*)(legacy ? L.it_tables[5 * it]->p : L.tm.p);
                 p.be = (const u128*)L.be.p;
                 p.e0 = L.e0;
-                p.n = L.e1 - L.e0;
+                p.n = L.slice_count();
+                p.seg = L.seg;
+                p.stride = L.stride;
                 p.batch = B;
                 p.Bp = Bp;
                 CU(launch_rescale(p, s));
@@ -1757,8 +1813,10 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
             ProjParams p;
             memset(&p, 0, sizeof(p));
             p.k = c->k;
-            p.n = L.e1 - L.e0;
+            p.n = L.slice_count();
             p.e0 = L.e0;
+            p.seg = L.seg;
+            p.stride = L.stride;
             p.batch = B;
             p.Bp = Bp;
             for (int j = 0; j < c->k; ++j) {
@@ -1860,6 +1918,9 @@ int dashb_set_shard_lanes(dashb_circuit* c, int lanes) {
 }
 
 int dashb_shard_lanes_used(const dashb_circuit* c) { return c ? c->lanes_used : 0; }
+void* dashb_lane_stream(const dashb_circuit* c, int lane) {
+    return (c && lane >= 0 && lane < (int)c->lanes.size()) ? (void*)c->lanes[lane]->s : nullptr;
+}
 
 /* 3 x 64 bytes: the IPC handles of lane `lane`'s two gather buffers and its flag array */
 int dashb_shard_export(dashb_circuit* c, int lane, void* handles) {
@@ -1929,15 +1990,16 @@ int dashb_shard_exchange(dashb_circuit* c, int lane, int layer) {
     const Tensor cur = ln.t_cur;
     Tensor dst;
     carve(dst, (uint8_t*)ln.gat[x].p, cur.n, cur.k, cur.q, ln.Bp);
-    uint64_t e0, e1;
-    uint32_t v0, v1;
-    layer_slice(c, layer, c->shard_rank, &e0, &e1, &v0, &v1);
+    const Layer& SL = *c->layers[layer];
     ShardPushParams p;
     memset(&p, 0, sizeof(p));
     p.k = cur.k;
     p.world = W;
-    p.e0 = e0;
-    p.e1 = e1;
+    p.e0 = SL.e0;
+    p.e1 = SL.e1;
+    p.seg = SL.seg;
+    p.stride = SL.stride;
+    p.nseg = SL.nseg;
     for (int j = 0; j < cur.k; ++j) {
         p.src[j] = cur.plane[j];
         p.dst_off[j] = (uint64_t)(dst.plane[j] - (uint8_t*)ln.gat[x].p);
@@ -1958,13 +2020,10 @@ int dashb_shard_exchange(dashb_circuit* c, int lane, int layer) {
 uint64_t dashb_shard_exchange_bytes(dashb_circuit* c, int lane, int layer) {
     if (!c || !c->finalized || lane < 0 || lane >= c->lanes_used || layer < 0 || layer >= (int)c->layers.size()) return 0;
     Lane& ln = *c->lanes[lane];
-    uint64_t e0, e1;
-    uint32_t v0, v1;
-    layer_slice(c, layer, c->shard_rank, &e0, &e1, &v0, &v1);
     const Layer& L = *c->layers[layer];
     uint64_t per = 0;
     for (int j = 0; j < c->k; ++j) per += (uint64_t)((nr_comps(L.out_q[j]) + 3) & ~3) * ln.Bp;
-    return (L.out_size - (e1 - e0)) * per;
+    return (L.out_size - L.slice_count()) * per;
 }
 
 /* 0, or the epoch at which a lane's wait for its peers timed out */
@@ -2019,6 +2078,8 @@ int dashb_current_slice_decompress(dashb_circuit* c, int j, uint64_t e0, uint64_
 int dashb_layer_slice(const dashb_circuit* c, int layer, int rank, uint64_t* e0, uint64_t* e1) {
     if (!c || !e0 || !e1 || layer < 0 || layer >= (int)c->layers.size() || rank < 0 || rank >= c->shard_world)
         return fail(DASHB_EINVAL, "bad argument");
+    if (pixel_sharding(c) && c->layers[layer]->seg)
+        return fail(DASHB_ESTATE, "layer %d is sharded by output pixels (peer-memory exchange): its slice is not one contiguous range", layer);
     uint32_t v0, v1;
     layer_slice(c, layer, rank, e0, e1, &v0, &v1);
     return DASHB_OK;

@@ -121,8 +121,9 @@ k_dense_tc(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ Den
     /* column sub-tiles that start inside the plane */
     const uint32_t nb_act = min((uint32_t)NB, (Nj - n0 + TC_BN - 1) / TC_BN);
     /* conv: blockIdx.y = filter block * npix + output pixel */
-    const uint32_t pix = CONV ? blockIdx.y % P.npix : 0u;
-    const uint32_t m0 = P.v0 + (CONV ? blockIdx.y / P.npix : blockIdx.y) * TC_BM;
+    /* (a launch covers the pixels [p0, p1): all of them, or this rank's share) */
+    const uint32_t pix = CONV ? P.p0 + blockIdx.y % (P.p1 - P.p0) : 0u;
+    const uint32_t m0 = P.v0 + (CONV ? blockIdx.y / (P.p1 - P.p0) : blockIdx.y) * TC_BM;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t nkb = P.nkb;
 
@@ -271,7 +272,7 @@ k_conv_tc_n(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ De
     const uint32_t Nj = nc4 * 4 * P.Bp;
     const uint32_t n0 = blockIdx.x * TC_BN;
     if (n0 >= Nj) return;
-    const uint32_t pix = blockIdx.y;
+    const uint32_t pix = P.p0 + blockIdx.y;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t nkb = P.nkb, npad = P.npad;
     const uint32_t tmem_cols = npad <= 32 ? 32u : npad <= 64 ? 64u : 128u; /* a power of two >= 32 */
@@ -444,8 +445,11 @@ cudaError_t conv_tc_make_map(void* map_out, const void* ptr, uint64_t row_bytes,
     return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
 
-cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p, cudaStream_t s) {
-    if (p.v1 <= p.v0) return cudaSuccess;
+cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p_in, cudaStream_t s) {
+    DenseTcParams p = p_in;
+    if (p.p1 == 0) p.p1 = p.npix ? p.npix : 1; /* no pixel range given: all of them */
+    if (p.v1 <= p.v0 || p.p1 <= p.p0) return cudaSuccess;
+    const uint32_t npix_l = p.p1 - p.p0;
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(k_dense_tc<false, TC_STAGES_DENSE, TC_NB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -467,12 +471,12 @@ cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p, cud
             if (e != cudaSuccess) return e;
             attr_n = true;
         }
-        dim3 grid((max_cols + TC_BN - 1) / TC_BN, p.npix, p.k);
+        dim3 grid((max_cols + TC_BN - 1) / TC_BN, npix_l, p.k);
         k_conv_tc_n<TC_STAGES_CONV><<<grid, TC_THREADS, smem_n, s>>>(maps, p);
         return cudaGetLastError();
     }
     if (p.npix > 1 || p.conv) {
-        dim3 grid((max_cols + TC_BN * TC_NB - 1) / (TC_BN * TC_NB), mblocks * p.npix, p.k);
+        dim3 grid((max_cols + TC_BN * TC_NB - 1) / (TC_BN * TC_NB), mblocks * npix_l, p.k);
         k_dense_tc<true, TC_STAGES_CONV, TC_NB><<<grid, TC_THREADS, tc_smem_bytes(TC_STAGES_CONV, TC_NB), s>>>(maps, p);
     } else {
         dim3 grid((max_cols + TC_BN * TC_NB - 1) / (TC_BN * TC_NB), mblocks, p.k);

@@ -476,8 +476,8 @@ __global__ void __launch_bounds__(LIN_THREADS, 8) k_linear(const __grid_constant
     const uint32_t by = P.y0 + blockIdx.y;
     const uint32_t vg = vg_first + by % nvg;
     const uint32_t nr = min((uint32_t)LIN_ROWS, P.v1 - vg * LIN_ROWS); /* rows of this group that exist */
-    const uint32_t pix0 = (by / nvg) * LIN_PIXC;
-    const uint32_t pix1 = min(pix0 + LIN_PIXC, P.npix);
+    const uint32_t pix0 = P.p0 + (by / nvg) * LIN_PIXC;
+    const uint32_t pix1 = min(pix0 + LIN_PIXC, P.p1);
     const uint64_t rowlen = ncols;
     const bool active = col < ncols;
     const uint32_t k4_total = P.Kp / 4;
@@ -560,7 +560,9 @@ cudaError_t launch_linear(const LinearParams& p, cudaStream_t s) {
     }
     /* (pixel group, row group) pairs sit on grid.y, which ends at 65535: a large
      * convolution (222x222 outputs, 64 filters: 98 568 pairs) goes out as several launches */
-    const uint64_t ny = (uint64_t)((p.npix + LIN_PIXC - 1) / LIN_PIXC) * nvg;
+    if (q.p1 == 0) q.p1 = p.npix; /* no pixel range given: all of them */
+    if (q.p1 <= q.p0) return cudaSuccess;
+    const uint64_t ny = (uint64_t)((q.p1 - q.p0 + LIN_PIXC - 1) / LIN_PIXC) * nvg;
     for (uint64_t y0 = 0; y0 < ny; y0 += 65535) {
         q.y0 = (uint32_t)y0;
         dim3 grid((max_cols / 4 + LIN_THREADS - 1) / LIN_THREADS, (unsigned)std::min<uint64_t>(65535, ny - y0), p.k);
@@ -618,7 +620,7 @@ __global__ void __launch_bounds__(128) k_projection(const __grid_constant__ Proj
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P.n * P.batch) return;
     const uint32_t b = (uint32_t)(idx % P.batch);
-    const uint64_t e = P.e0 + idx / P.batch;
+    const uint64_t e = slice_elem(P.e0, P.seg, P.stride, idx / P.batch);
     uint32_t colour;
     const ModInfo mi = pin(P.min[j]), mo = pin(P.mout[j]);
     const u128 key = load_compress(P.in[j], mi, e, b, P.Bp, colour);
@@ -736,12 +738,15 @@ namespace dashb {
  */
 __global__ void __launch_bounds__(256) k_shard_push(const __grid_constant__ ShardPushParams P) {
     const int j = blockIdx.y;
-    const uint64_t nvec = (P.e1 - P.e0) * P.row[j] / 16; /* rows are multiples of 64 bytes */
-    const uint4* src = reinterpret_cast<const uint4*>(P.src[j] + P.e0 * P.row[j]);
-    const uint64_t off = P.dst_off[j] + P.e0 * P.row[j];
+    /* the slice: nseg runs of seg elements (one run: the contiguous block [e0, e1)) */
+    const uint64_t seg = P.seg ? P.seg : P.e1 - P.e0, nseg = P.seg ? P.nseg : 1;
+    const uint64_t vrun = seg * P.row[j] / 16; /* rows are multiples of 64 bytes */
+    const uint64_t nvec = vrun * nseg;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (uint64_t)gridDim.x * blockDim.x) {
-        const uint4 v = src[i];
-        for (int r = 0; r < P.world; ++r) reinterpret_cast<uint4*>(P.peer[r] + off)[i] = v;
+        const uint64_t run = i / vrun, w = i - run * vrun;
+        const uint64_t at = (P.e0 + run * P.stride) * P.row[j] + 16 * w; /* byte offset inside the plane */
+        const uint4 v = *reinterpret_cast<const uint4*>(P.src[j] + at);
+        for (int r = 0; r < P.world; ++r) *reinterpret_cast<uint4*>(P.peer[r] + P.dst_off[j] + at) = v;
     }
     __threadfence_system();
 }
@@ -773,11 +778,13 @@ __global__ void k_shard_wait(uint32_t* flags, int world, uint32_t epoch) {
 }
 
 cudaError_t launch_shard_push(const ShardPushParams& p, cudaStream_t s) {
-    if (p.e1 <= p.e0) return cudaSuccess;
+    const uint64_t count = p.seg ? p.seg * p.nseg : (p.e1 > p.e0 ? p.e1 - p.e0 : 0);
+    if (count == 0) return cudaSuccess;
     uint64_t nvec = 0;
-    for (int j = 0; j < p.k; ++j) nvec = std::max<uint64_t>(nvec, (p.e1 - p.e0) * p.row[j] / 16);
+    for (int j = 0; j < p.k; ++j) nvec = std::max<uint64_t>(nvec, count * p.row[j] / 16);
     /* a modest grid: the exchange shares the GPU with the other lane's layer group */
-    dim3 grid((unsigned)std::min<uint64_t>((nvec + 255) / 256, 148 * 2), p.k);
+    static const int per_sm = getenv("DASHB_PUSH_CTAS_PER_SM") ? atoi(getenv("DASHB_PUSH_CTAS_PER_SM")) : 2;
+    dim3 grid((unsigned)std::min<uint64_t>((nvec + 255) / 256, (uint64_t)148 * std::max(1, per_sm)), p.k);
     k_shard_push<<<grid, 256, 0, s>>>(p);
     return cudaGetLastError();
 }
@@ -951,11 +958,23 @@ __device__ __forceinline__ void accumulate_t4(u128 x, const ModInfo& m, const gc
 
 /* compress(acc mod q) and the colour of the sum; absolute digit layout
  * (accumulate) */
+/* T > 1: the T threads of an element each hold a partial sum in their own
+ * accumulator column (adjacent words, acc[.. + 0 .. T-1]); the reader adds
+ * them up -- packed halves still cannot meet: the k + 1 summands are the same */
+template <int T>
+__device__ __forceinline__ uint32_t acc_word(const uint32_t* a) {
+    uint32_t v = a[0];
+#pragma unroll
+    for (int u = 1; u < T; ++u) v += a[u];
+    return v;
+}
+
+template <int T>
 __device__ __forceinline__ u128 compress_acc(const uint32_t* acc, const ModInfo& m, uint32_t& colour) {
     gc::Compressor c(m);
     uint32_t dg = 0;
     for (int d = (int)m.nc - 1; d >= 0; --d) {
-        const uint32_t w = acc[(d >> 1) * SIGN_THREADS];
+        const uint32_t w = acc_word<T>(acc + (d >> 1) * SIGN_THREADS);
         dg = gc::mod_q((d & 1) ? (w >> 16) : (w & 0xffffu), m);
         c.push(dg);
     }
@@ -969,6 +988,7 @@ __device__ __forceinline__ u128 compress_acc(const uint32_t* acc, const ModInfo&
  * the stage's multiplier, 2^sh removed for stage 0) that enters the 128-bit
  * value with one multiply-add.  An odd stage's top word has an empty high
  * half: a leading zero. */
+template <int T>
 __device__ __forceinline__ u128 compress_acc_ladder(const uint32_t* acc, const ModInfo& m, const gc::FracInfo& fi,
                                                     uint32_t& colour) {
     u128 x = gc::make_u128(0, 0);
@@ -980,7 +1000,7 @@ __device__ __forceinline__ u128 compress_acc_ladder(const uint32_t* acc, const M
         uint32_t chunk = 0;
 #pragma unroll 1
         for (int w = (int)nw - 1; w >= 0; --w) {
-            const uint32_t v = acc[w * SIGN_THREADS];
+            const uint32_t v = acc_word<T>(acc + w * SIGN_THREADS);
             const uint32_t hi = v >> 16;
             lo = v & 0xffffu;
             chunk = (chunk * q + (hi - gc::mulhi32(hi, mq) * q)) * q;
@@ -1079,26 +1099,39 @@ __device__ __forceinline__ void half_gate_ladder(u128 E, u128 G, const ModInfo& 
  * on H(top sum).  The per-digit sums of digits i >= 1 (mrs_sum, :615-622)
  * are never read by the reference and are not formed.
  */
-template <bool RELU>
+/* T threads per (element, inference), T = 1 or 4.  With T = 4 the residues
+ * are dealt round the four threads of a quad (thread t takes j = t, t+4, ...;
+ * the carry counts as residue k): the input hashes, the cast-1 projections of
+ * every mixed-radix digit and the half gates run four abreast, each thread
+ * accumulating into its own column; thread 0 adds the four columns up while it
+ * compresses, does the one cast-2 hash of the digit and hands the carry back
+ * by shuffle.  The dependent chain of an element shrinks from k + (k+2)(n-1)
+ * + 3 hashes to about a third, for ~1.4x the issue slots: launch_sign uses it
+ * for launches too small to fill the GPU, where the chain's latency -- not
+ * throughput -- is what the layer costs (the small ReLU layers of a CNN, a
+ * rank's share of a channel-sharded layer, a small batch). */
+template <bool RELU, int T>
 __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __grid_constant__ SignParams P) {
     __shared__ AesSmem aes;
     extern __shared__ uint32_t s_acc[]; /* [accumulator words][SIGN_THREADS] */
     aes_smem_load(aes);
-    const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P.n * P.batch) return;
+    const uint32_t t = T > 1 ? (threadIdx.x % T) : 0u;
+    const uint32_t qmask = T > 1 ? (((1u << T) - 1u) << ((threadIdx.x & 31u) & ~(uint32_t)(T - 1))) : 0xffffffffu; /* the element's threads */
+    const uint64_t idx = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / T;
+    if (idx >= P.n * P.batch) return; /* whole quads leave together */
     const uint32_t b = (uint32_t)(idx % P.batch);
-    const uint64_t e = P.e0 + idx / P.batch;
+    const uint64_t e = slice_elem(P.e0, P.seg, P.stride, idx / P.batch);
     const int k = P.k;
     const int nm = P.n_mrs;
 
     /* Step 1a: key and hash every CRT residue label once */
-    u128 h[MAXK];
-    uint32_t col[MAXK];
+    u128 h[(MAXK + T - 1) / T]; /* residue j lives at [j / T] of thread j % T */
+    uint32_t col[(MAXK + T - 1) / T];
 #pragma unroll 1
-    for (int j = 0; j < k; ++j) {
+    for (int j = t; j < k; j += T) {
         const ModInfo Pm = pin(P.crt[j]);
-        const u128 key = load_compress(P.in[j], Pm, e, b, P.Bp, col[j]);
-        h[j] = hash(aes, key);
+        const u128 key = load_compress(P.in[j], Pm, e, b, P.Bp, col[j / T]);
+        h[j / T] = hash(aes, key);
     }
 
     /* Step 2: mixed-radix addition from the least significant digit */
@@ -1142,14 +1175,15 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
          * them from their use: residue j+1's approximate-digit row before
          * label j is hashed, the cast-1 row (its index is the label's colour,
          * known before the hash) before the hash as well. */
-        auto approx_row = [&](int j) { return ldg128(approx_e + ((uint32_t)nm * P.prefix[j] + (uint32_t)i * P.crt[j].q + col[j])); };
-        u128 row = approx_row(0);
+        auto approx_row = [&](int j) { return ldg128(approx_e + ((uint32_t)nm * P.prefix[j] + (uint32_t)i * P.crt[j].q + col[j / T])); };
+        u128 row = gc::make_u128(0, 0);
+        if ((int)t < k) row = approx_row(t);
 #pragma unroll 1
-        for (int j = 0; j <= k; ++j) {
+        for (int j = t; j <= k; j += T) {
             /* Step 1b: approx. MRS digit i of residue j (j == k: the carry) */
             u128 lab = carry;
-            if (j < k) lab = gc::sub128(row, h[j]);
-            if (j + 1 < k) row = approx_row(j + 1);
+            if (j < k) lab = gc::sub128(row, h[j / T]);
+            if (j + T < k) row = approx_row(j + T);
             if (i > 0) {
                 /* Step 2.2: cast to modulus (k+1)*m_i */
                 const uint32_t c0 = gc::colour_of(lab, M, cc);
@@ -1163,26 +1197,41 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
             else
                 accumulate(lab, C, acc);
         }
-        /* Step 2.3 / 2.4: sum of the casts -> carry into digit i-1 */
-        uint32_t c2;
-        const u128 sum = ladder ? compress_acc_ladder(acc, C, fi, c2) : compress_acc(acc, C, c2);
+        /* Step 2.3 / 2.4: sum of the casts -> carry into digit i-1 (thread 0 of the element) */
+        if (T > 1) __syncwarp(qmask); /* every column of the element is complete */
+        if (t == 0) {
+            uint32_t c2;
+            const u128 sum = ladder ? compress_acc_ladder<T>(acc, C, fi, c2) : compress_acc<T>(acc, C, c2);
+            if (i > 0) {
+                carry = gc::sub128(ldg128(cast2_e + (cnt2 + c2)), hash(aes, sum));
+            } else {
+                top = sum;
+                ctop = c2;
+            }
+        }
         if (i > 0) {
-            carry = gc::sub128(ldg128(cast2_e + (cnt2 + c2)), hash(aes, sum));
             cnt1 += (uint32_t)(k + 1) * M.q;
             cnt2 += C.q;
-        } else {
-            top = sum;
-            ctop = c2;
+        }
+        if (T > 1) { /* the carry goes to the thread that owns residue k; also: columns may be cleared again */
+            carry.lo = __shfl_sync(qmask, carry.lo, 0, T);
+            carry.hi = __shfl_sync(qmask, carry.hi, 0, T);
         }
     }
-    const u128 htop = hash(aes, top);
+    u128 htop = gc::make_u128(0, 0);
+    if (t == 0) htop = hash(aes, top);
+    if (T > 1) {
+        htop.lo = __shfl_sync(qmask, htop.lo, 0, T);
+        htop.hi = __shfl_sync(qmask, htop.hi, 0, T);
+        ctop = __shfl_sync(qmask, ctop, 0, T);
+    }
     const uint32_t m0 = P.mrs[0].q;
 
     /* Step 3: sign projection(s) */
     const u128* sign_e = P.sign + et * (uint64_t)P.n_out * m0;
     if (!RELU) {
 #pragma unroll 1
-        for (int j = 0; j < P.n_out; ++j) {
+        for (int j = t; j < P.n_out; j += T) {
             const ModInfo mo = pin(P.outm[j]);
             store_digits(P.out[j], mo, e, b, P.Bp, gc::sub128(ldg128(sign_e + (uint64_t)j * m0 + ctop), htop));
         }
@@ -1190,14 +1239,19 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
     }
     /* Step 4 (ReLU): out_j = E_j + (y+r)*x_j - G_j  (mod p_j) */
     const u128 s = gc::sub128(ldg128(sign_e + ctop), htop); /* sign label, modulus 2 */
-    const u128 hs = hash(aes, s);
+    u128 hs = gc::make_u128(0, 0);
+    if (t == 0) hs = hash(aes, s);
+    if (T > 1) {
+        hs.lo = __shfl_sync(qmask, hs.lo, 0, T);
+        hs.hi = __shfl_sync(qmask, hs.hi, 0, T);
+    }
     const uint32_t cs = (uint32_t)s.lo & 1u;
     const u128* garbler_e = P.garbler + et * (uint64_t)P.S;
     const u128* ev_e = P.evaluator + et * (uint64_t)k * 3;
 #pragma unroll 1
-    for (int j = 0; j < k; ++j) {
+    for (int j = t; j < k; j += T) {
         const ModInfo Pm = pin(P.crt[j]);
-        const u128 G = gc::sub128(ldg128(garbler_e + (P.prefix[j] + col[j])), h[j]);
+        const u128 G = gc::sub128(ldg128(garbler_e + (P.prefix[j] + col[j / T])), h[j / T]);
         const u128* ev = ev_e + 3 * j;
         const u128 E = gc::sub128(ldg128(ev + cs), hs);
         /* mini gate: int16 row `cs` of the packed slot minus the low 16 hash
@@ -1286,7 +1340,7 @@ __global__ void __launch_bounds__(WIDE_WARPS * 32) k_sign_wide(const __grid_cons
     const uint64_t idx = (uint64_t)blockIdx.x * WIDE_WARPS + warp;
     if (idx >= P.n * P.batch) return; /* whole warps leave together */
     const uint32_t b = (uint32_t)(idx % P.batch);
-    const uint64_t e = P.e0 + idx / P.batch;
+    const uint64_t e = slice_elem(P.e0, P.seg, P.stride, idx / P.batch);
     const int k = P.k, nm = P.n_mrs;
     u128* h = s_h[warp];
     uint32_t* col = s_col[warp];
@@ -1422,10 +1476,21 @@ cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s) {
             return cudaGetLastError();
         }
     }
+    /* four threads per element while the launch could not fill the GPU anyway (148 SMs x 1024 threads):
+     * a third of the latency for 1.4x the issue slots */
+    static const long quad_max = getenv("DASHB_QUAD_MAX") ? atol(getenv("DASHB_QUAD_MAX")) : 75000;
+    if ((long)total * (p.lanes > 1 ? p.lanes : 1) <= quad_max && p.k >= 4) {
+        const unsigned qgrid = (unsigned)((total * 4 + SIGN_THREADS - 1) / SIGN_THREADS);
+        if (relu)
+            k_sign<true, 4><<<qgrid, SIGN_THREADS, smem, s>>>(p);
+        else
+            k_sign<false, 4><<<qgrid, SIGN_THREADS, smem, s>>>(p);
+        return cudaGetLastError();
+    }
     if (relu)
-        k_sign<true><<<grid, SIGN_THREADS, smem, s>>>(p);
+        k_sign<true, 1><<<grid, SIGN_THREADS, smem, s>>>(p);
     else
-        k_sign<false><<<grid, SIGN_THREADS, smem, s>>>(p);
+        k_sign<false, 1><<<grid, SIGN_THREADS, smem, s>>>(p);
     return cudaGetLastError();
 }
 
@@ -1739,7 +1804,7 @@ __global__ void __launch_bounds__(RS_THREADS, DASHB_RS_MINB) k_rescale(const __g
     aes_smem_load(aes);
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P.n * P.batch) return;
-    rescale_body<PACKED>(P, aes, s_rs + threadIdx.x, P.e0 + idx / P.batch, (uint32_t)(idx % P.batch));
+    rescale_body<PACKED>(P, aes, s_rs + threadIdx.x, slice_elem(P.e0, P.seg, P.stride, idx / P.batch), (uint32_t)(idx % P.batch));
 }
 
 cudaError_t launch_rescale(const RescaleParams& p, cudaStream_t s) {

@@ -33,6 +33,7 @@ struct LinearParams {
     const int32_t* koff;       /* [Kp] input element offset of tap k */
     uint32_t M, K, Kp;
     uint32_t v0, v1;           /* output rows [v0, v1) this launch computes (channel sharding) */
+    uint32_t p0, p1;           /* output pixels [p0, p1) this launch computes (pixel sharding of a convolution) */
     uint32_t npix, ow;         /* output pixels per filter, output width */
     uint32_t step_x, step_y;   /* element offset per output x / y step */
     uint32_t Bp;
@@ -60,9 +61,20 @@ struct DenseTcParams {
     uint32_t b_box_bytes;  /* bytes one B box brings in (dense: 128*128) */
     /* convolution: per output pixel one GEMM; box {128, f_w, f_h, cb} at {n, x*sx, y*sy, kb*cb} */
     uint32_t conv, npix, ow, sx, sy, cb;
+    uint32_t p0, p1;       /* output pixels [p0, p1) this launch computes (pixel sharding) */
     uint32_t npad;         /* != 0: filters on the N dimension (k_conv_tc_n), N = npad */
     int k;
 };
+
+/* element `le` (0 .. n-1) of a launch's slice: contiguous from e0, or -- a
+ * convolution sharded by output pixels, whose elements are (filter, pixel) --
+ * runs of `seg` pixels, one run per filter, `stride` = pixels per filter */
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline uint64_t slice_elem(uint64_t e0, uint64_t seg, uint64_t stride, uint64_t le) {
+    return seg ? e0 + (le / seg) * stride + le % seg : e0 + le;
+}
 
 struct SignParams {
     const uint8_t* in[MAXK];
@@ -77,6 +89,7 @@ struct SignParams {
     gc::u128 carry0;         /* compressed zero label of m_{n_mrs-1} */
     uint64_t n;   /* elements this launch processes ... */
     uint64_t e0;  /* ... starting at this element (channel sharding) */
+    uint64_t seg, stride; /* seg != 0: the n elements are runs of seg elements, run s starting at e0 + s * stride (slice_elem) */
     uint32_t prefix[MAXK];
     uint32_t S, Mp;
     uint32_t batch, Bp;
@@ -120,7 +133,8 @@ struct ShardPushParams {
     const uint8_t* src[MAXK]; /* plane j of the tensor the layer group produced */
     uint64_t dst_off[MAXK];   /* offset of plane j inside a gather buffer */
     uint64_t row[MAXK];       /* bytes per element of plane j */
-    uint64_t e0, e1;          /* this rank's elements */
+    uint64_t e0, e1;          /* this rank's elements: [e0, e1), or with seg != 0 ... */
+    uint64_t seg, stride, nseg; /* ... nseg runs of seg elements, run s starting at e0 + s * stride */
     uint8_t* peer[MAXR];      /* every rank's gather buffer (this rank's own at [rank]) */
     int k, world;
 };
@@ -132,6 +146,7 @@ struct ProjParams {
     const gc::u128* ciphers[MAXK];
     uint64_t n;   /* elements this launch processes ... */
     uint64_t e0;  /* ... starting at this element (channel sharding) */
+    uint64_t seg, stride; /* see SignParams */
     uint32_t batch, Bp;
     int k;
 };
@@ -159,6 +174,7 @@ struct RescaleParams {
     int extra_pos[MAXF];         /* its position in the swapped order */
     uint64_t n;   /* elements this launch processes ... */
     uint64_t e0;  /* ... starting at this element (channel sharding) */
+    uint64_t seg, stride; /* see SignParams */
     uint32_t batch, Bp;
     int k, nf, non_ext;
     int legacy;                  /* 1: stop after step 2.3 (sign gadget and downshift follow) */

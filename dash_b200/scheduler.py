@@ -220,6 +220,34 @@ class ChannelShardedEvaluator:
         """Plaintext inputs, encoded on the device (needs the input encoding in the material)."""
         self.c.garble_inputs(values)
 
+    def trace(self):
+        """One run with CUDA events on the lane streams: per layer group and
+        lane (ms since the start) when its layers finished and when its
+        exchange finished.  p2p mode only."""
+        import torch
+
+        lanes = list(range(self.c.lanes_used()))
+        streams = [torch.cuda.ExternalStream(self.c.L.dashb_lane_stream(self.c.h, l)) for l in lanes]
+        lib_stream = torch.cuda.ExternalStream(self.c.L.dashb_stream())
+        t0 = torch.cuda.Event(enable_timing=True)
+        t0.record(lib_stream)
+        ev = []
+        for first, last in self.groups:
+            row = []
+            for lane in lanes:
+                self.c.evaluate_layers_lane(lane, first, last)
+                a = torch.cuda.Event(enable_timing=True)
+                a.record(streams[lane])
+                row.append([a, None])
+            for lane in lanes:
+                self.c.shard_exchange(lane, last)
+                b = torch.cuda.Event(enable_timing=True)
+                b.record(streams[lane])
+                row[lane][1] = b
+            ev.append(row)
+        torch.cuda.synchronize()
+        return [[(t0.elapsed_time(a), t0.elapsed_time(b)) for a, b in row] for row in ev]
+
     def run(self):
         """All layer groups on the inputs loaded last, exchanges included; asynchronous."""
         if self.p2p:

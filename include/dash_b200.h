@@ -345,6 +345,8 @@ int dashb_current_plane(dashb_circuit* c, int j, void** dev_ptr, uint64_t* bytes
  * All ranks must issue the same sequence of exchanges. */
 int dashb_set_shard_lanes(dashb_circuit* c, int lanes);
 int dashb_shard_lanes_used(const dashb_circuit* c);
+/* the CUDA stream (cudaStream_t as void*) lane `lane` enqueues on, for a caller's own events */
+void* dashb_lane_stream(const dashb_circuit* c, int lane);
 int dashb_shard_export(dashb_circuit* c, int lane, void* handles_3x64);
 int dashb_shard_import(dashb_circuit* c, int lane, int peer_rank, const void* handles_3x64);
 int dashb_evaluate_layers_lane(dashb_circuit* c, int lane, int first, int last);

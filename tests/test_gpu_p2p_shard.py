@@ -23,7 +23,8 @@ def _free_port():
 
 
 @pytest.mark.parametrize("name,world,batch,lanes", [("MLP_TINY", 2, 40, 2), ("CONV_UNIT", 3, 33, 2), ("RESCALE_OPT", 2, 5, 1),
-                                                    ("SIGN_TINY", 4, 64, 2)])
+                                                    ("SIGN_TINY", 4, 64, 2), ("GARBLED:CIFAR_TINY_SCALE", 3, 40, 2),
+                                                    ("GARBLED:MNIST_TINY_CNN", 4, 48, 2)])
 def test_peer_memory_exchange_between_processes(gpu, name, world, batch, lanes):
     port = str(_free_port())
     worker = os.path.join(ROOT, "tests", "p2p_shard_worker.py")
