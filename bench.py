@@ -235,6 +235,7 @@ def run_c3(torch, dist, rank, world, local_rank, barrier, steps=5, batch=64):
            "material": "GPU garbler, %.0f ms of kernels, %.2f GB of tables per GPU" % (gst["kernel_ms"], gst["table_bytes"] / 1e9)}
     c.close()
     if rank == 0:
+        os.makedirs(CACHE, exist_ok=True)
         path = os.path.join(CACHE, "c3_gnnp.gcm")
         garble.garble_to_file(spec["crt"], spec["mrs"], n_in, plain, path, seed=seed)
         out["bit_exact_vs_oracle"] = oracle_parity(path, X, got, (0, batch - 1), host_threads())
@@ -261,7 +262,7 @@ def run_c4(torch, dist, rank, world, local_rank, barrier, steps=5, batch=64):
         c.evaluate_layers = lambda first, last: c.evaluate_device() if first == 0 else None
     else:
         c, gst = garble.garble_to_circuit(spec["crt"], spec["mrs"], n_in, plain, batch, seed=seed, shard=(rank, world),
-                                          shard_lanes=2 if mode == "p2p" else 0)
+                                          shard_lanes=int(os.environ.get("DASHB_C4_LANES", "2")) if mode == "p2p" else 0)
     ev = ChannelShardedEvaluator(c, rank, world, dist=dist if world > 1 else None, p2p=(mode == "p2p"))
     ev.load_values(X)
     ev.run()  # warm-up (peer mappings / NCCL channels, lazy module loading)
@@ -290,6 +291,7 @@ def run_c4(torch, dist, rank, world, local_rank, barrier, steps=5, batch=64):
         out["trace_ms_rank0_[group][lane](layers_done, exchange_done)"] = trace
     c.close()
     if rank == 0:
+        os.makedirs(CACHE, exist_ok=True)
         path = os.path.join(CACHE, "c4_minionn.gcm")
         garble.garble_to_file(spec["crt"], spec["mrs"], n_in, plain, path, seed=seed)
         out["bit_exact_vs_oracle"] = oracle_parity(path, X, got, (0,), host_threads())
@@ -310,6 +312,7 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="cpu_baseline leg budget")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the c3_batch_sharded / c4_channel_sharded legs")
+    ap.add_argument("--only", default="", choices=["", "c3", "c4"], help="run one extra leg alone and print its JSON (experiments)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -334,6 +337,15 @@ def main():
     def barrier():
         if world > 1:
             dist.barrier()
+
+    if args.only:
+        api.init(local_rank)
+        res = (run_c3 if args.only == "c3" else run_c4)(torch, dist, rank, world, local_rank, barrier)
+        if rank == 0:
+            print(json.dumps(res), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
 
     # ---- inputs of the path (outside the timed region) -------------------
     B = args.batch

@@ -79,6 +79,7 @@ def lib():
         L.dashb_shard_import.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.dashb_evaluate_layers_lane.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
         L.dashb_shard_exchange.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.dashb_evaluate_sharded.argtypes = [C.c_void_p]
         L.dashb_shard_exchange_bytes.restype = C.c_uint64
         L.dashb_shard_exchange_bytes.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.dashb_shard_status.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_uint32)]

@@ -34,7 +34,22 @@ def build(force=False, verbose=False):
         raise RuntimeError("nvcc failed building libdash_b200.so")
     if verbose:
         print(res.stderr)
+    build_examples()
     return LIB
+
+
+def build_examples():
+    """integration/example_sharded.cpp: plain C++ against the C ABI (no CUDA, no reference headers)."""
+    root = os.path.dirname(HERE)
+    out_dir = os.path.join(root, "integration", "bin")
+    os.makedirs(out_dir, exist_ok=True)
+    cmd = ["g++", "-std=c++17", "-O2", "-I" + os.path.join(root, "include"), os.path.join(root, "integration", "example_sharded.cpp"),
+           "-L" + HERE, "-ldash_b200", "-Wl,-rpath," + HERE, "-Wl,-rpath,$ORIGIN/../../dash_b200", "-pthread",
+           "-o", os.path.join(out_dir, "example_sharded")]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        sys.stderr.write(res.stdout + res.stderr)
+        raise RuntimeError("g++ failed building integration/bin/example_sharded")
 
 
 if __name__ == "__main__":

@@ -2016,6 +2016,35 @@ int dashb_shard_exchange(dashb_circuit* c, int lane, int layer) {
     return DASHB_OK;
 }
 
+/* Every layer group of every lane with its exchange, in the order all ranks
+ * must follow: a linear layer (dense / conv2d) needs all of its inputs, so
+ * each one starts a group; the element-wise layers behind it stay with it.
+ * Asynchronous; dashb_move_outputs / dashb_decode_outputs order themselves
+ * behind it. */
+int dashb_evaluate_sharded(dashb_circuit* c) {
+    if (!c) return fail(DASHB_EINVAL, "null circuit");
+    if (!c->finalized || c->shard_lanes < 1 || c->batch == 0) return fail(DASHB_ESTATE, "no inputs moved, or no peer exchange prepared");
+    const int nl = (int)c->layers.size();
+    int first = 0;
+    for (int li = 0; li <= nl; ++li) {
+        const bool linear = li < nl && (c->layers[li]->type == DASHB_LAYER_DENSE || c->layers[li]->type == DASHB_LAYER_CONV2D);
+        if ((linear && li > first) || li == nl) {
+            if (li == first) break;
+            for (int lane = 0; lane < c->lanes_used; ++lane) {
+                int rc = dashb_evaluate_layers_lane(c, lane, first, li - 1);
+                if (rc) return rc;
+            }
+            if (c->shard_world > 1)
+                for (int lane = 0; lane < c->lanes_used; ++lane) {
+                    int rc = dashb_shard_exchange(c, lane, li - 1);
+                    if (rc) return rc;
+                }
+            first = li;
+        }
+    }
+    return DASHB_OK;
+}
+
 /* bytes this rank receives from its peers in dashb_shard_exchange(lane, layer) */
 uint64_t dashb_shard_exchange_bytes(dashb_circuit* c, int lane, int layer) {
     if (!c || !c->finalized || lane < 0 || lane >= c->lanes_used || layer < 0 || layer >= (int)c->layers.size()) return 0;

@@ -351,6 +351,9 @@ int dashb_shard_export(dashb_circuit* c, int lane, void* handles_3x64);
 int dashb_shard_import(dashb_circuit* c, int lane, int peer_rank, const void* handles_3x64);
 int dashb_evaluate_layers_lane(dashb_circuit* c, int lane, int first, int last);
 int dashb_shard_exchange(dashb_circuit* c, int lane, int layer);
+/* all layer groups of all lanes with their exchanges (what a rank runs per
+ * batch once the peers' buffers are imported); asynchronous */
+int dashb_evaluate_sharded(dashb_circuit* c);
 uint64_t dashb_shard_exchange_bytes(dashb_circuit* c, int lane, int layer);
 int dashb_shard_status(dashb_circuit* c, int lane, uint32_t* timed_out_epoch);
 
