@@ -41,6 +41,7 @@ def lib():
         L.dashb_last_error.restype = C.c_char_p
         L.dashb_stream.restype = C.c_void_p
         L.dashb_circuit_load.argtypes = [C.POINTER(C.c_void_p), C.c_char_p]
+        L.dashb_circuit_load_replicated.argtypes = [C.POINTER(C.c_void_p), C.c_char_p, C.c_int]
         L.dashb_finalize.argtypes = [C.c_void_p, C.c_uint64]
         L.dashb_move_inputs.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
         L.dashb_evaluate_device.argtypes = [C.c_void_p]
@@ -142,7 +143,7 @@ class Circuit:
         self.in_moduli = [self.L.dashb_crt_modulus(self.h, j) for j in range(self.k)]
 
     @classmethod
-    def load(cls, path, max_batch=1, shard=None, shard_lanes=0):
+    def load(cls, path, max_batch=1, shard=None, shard_lanes=0, table_replicas=1):
         """Reads a DGCM material file and moves the circuit to the device.
         shard=(rank, world) makes it one rank of an output-channel-sharded
         evaluation (see dash_b200.scheduler.ChannelShardedEvaluator);
@@ -150,7 +151,10 @@ class Circuit:
         sub-batch lanes (otherwise the exchange goes through NCCL)."""
         L = lib()
         h = C.c_void_p()
-        _check(L.dashb_circuit_load(C.byref(h), os.fsencode(path)))
+        if table_replicas > 1:  # one copy of the sign / ReLU tables per inference (measurement; dashb_set_table_replicas)
+            _check(L.dashb_circuit_load_replicated(C.byref(h), os.fsencode(path), int(table_replicas)))
+        else:
+            _check(L.dashb_circuit_load(C.byref(h), os.fsencode(path)))
         if shard is not None:
             _check(L.dashb_set_shard(h, int(shard[0]), int(shard[1])))
             if shard_lanes:

@@ -31,6 +31,7 @@ namespace {
 thread_local std::string g_err;
 int g_device = -1;
 cudaStream_t g_stream = nullptr;
+int g_load_replicas = 1; /* consumed by dashb_circuit_create when dashb_circuit_load_replicated drives it */
 
 int fail(int code, const char* fmt, ...) {
     char buf[512];
@@ -458,6 +459,7 @@ struct dashb_circuit {
     int async_next{0};
     int shard_rank{0}, shard_world{1};
     int shard_lanes{0}; /* > 0: peer-memory exchange with that many sub-batch lanes (dashb_set_shard_lanes) */
+    int table_replicas{1}; /* dashb_set_table_replicas: the sign/ReLU tables exist this many times, interleaved by row */
     std::vector<void*> ipc_opened;
     uint32_t lane_cap{0};
     std::vector<uint32_t> lane_weights; /* DASHB_LANE_SPLIT */
@@ -552,9 +554,17 @@ int prep_linear(dashb_circuit* c, Layer& L, const std::vector<int64_t>& wrow /* 
     return DASHB_OK;
 }
 
-int upload_tables(DevMem& dst, const dashb_u128* src, size_t rows) {
+int upload_tables(DevMem& dst, const dashb_u128* src, size_t rows, int replicas = 1) {
     if (!src && rows) return fail(DASHB_EINVAL, "null ciphertext table");
-    CU(dst.upload(src, rows * 16));
+    if (replicas <= 1) {
+        CU(dst.upload(src, rows * 16));
+        return DASHB_OK;
+    }
+    DevMem once;
+    CU(once.upload(src, rows * 16));
+    CU(dst.alloc(rows * 16 * (size_t)replicas));
+    CU(launch_replicate_rows(once.p, dst.p, rows, (uint32_t)replicas, cudaStreamLegacy));
+    CU(cudaStreamSynchronize(cudaStreamLegacy));
     return DASHB_OK;
 }
 
@@ -595,6 +605,8 @@ void fill_sign_params(dashb_circuit* c, SignParams& p, uint64_t n, int n_out) {
     p.carry0 = c->carry0;
     p.tab_mul = 1;
     p.tab_add = 0;
+    p.rep = c->table_replicas > 1 ? (uint32_t)c->table_replicas : 1u;
+    p.b0 = 0;
 }
 
 double sign_inner_aes_ref(const dashb_circuit* c) {
@@ -712,6 +724,7 @@ int dashb_circuit_create(dashb_circuit** out, const int32_t* crt_base, int k, co
         }
     }
     c->has_up = upshift_labels != nullptr;
+    c->table_replicas = g_load_replicas;
     *out = c.release();
     return DASHB_OK;
 }
@@ -836,10 +849,11 @@ static int add_sign_common(dashb_circuit* c, Layer& L, uint64_t n, int n_out, co
     size_t rows[4];
     int rc = sign_table_rows(c, n, n_out, rows);
     if (rc) return rc;
-    if ((rc = upload_tables(L.approx, approx, rows[0]))) return rc;
-    if ((rc = upload_tables(L.cast1, cast1, rows[1]))) return rc;
-    if ((rc = upload_tables(L.cast2, cast2, rows[2]))) return rc;
-    return upload_tables(L.sign, sign, rows[3]);
+    const int R = c->table_replicas;
+    if ((rc = upload_tables(L.approx, approx, rows[0], R))) return rc;
+    if ((rc = upload_tables(L.cast1, cast1, rows[1], R))) return rc;
+    if ((rc = upload_tables(L.cast2, cast2, rows[2], R))) return rc;
+    return upload_tables(L.sign, sign, rows[3], R);
 }
 
 int dashb_add_relu(dashb_circuit* c, uint64_t n, const dashb_u128* approx, const dashb_u128* cast1,
@@ -857,8 +871,8 @@ int dashb_add_relu(dashb_circuit* c, uint64_t n, const dashb_u128* approx, const
     if ((rc = add_sign_common(c, *L, n, 1, approx, cast1, cast2, sign))) return rc;
     size_t S = 0;
     for (int j = 0; j < c->k; ++j) S += (size_t)c->crt[j];
-    if ((rc = upload_tables(L->garbler, garbler, n * S))) return rc;
-    if ((rc = upload_tables(L->evaluator, evaluator, n * (size_t)c->k * 3))) return rc;
+    if ((rc = upload_tables(L->garbler, garbler, n * S, c->table_replicas))) return rc;
+    if ((rc = upload_tables(L->evaluator, evaluator, n * (size_t)c->k * 3, c->table_replicas))) return rc;
     L->ref_aes = (double)n * (sign_inner_aes_ref(c) + 1 + 3.0 * c->k);
     L->aes = (double)n * (sign_inner_aes(c) + 1);
     L->label_bytes = (double)n * (32.0 * c->k + 16.0 * (sign_inner_aes_ref(c) + 1 + 3.0 * c->k));
@@ -882,6 +896,7 @@ int dashb_add_maxpool2d(dashb_circuit* c, uint64_t in_w, uint64_t in_h, uint64_t
         return fail(DASHB_EINVAL, "maxpool2d: %llux%llu windows do not match the reference's %llux%llu output tensor",
                     (unsigned long long)ow, (unsigned long long)oh, (unsigned long long)(in_w / k_w), (unsigned long long)(in_h / k_h));
     if (c->shard_world > 1) return fail(DASHB_EINVAL, "maxpool2d: not available in channel-sharded circuits");
+    if (c->table_replicas > 1) return fail(DASHB_EINVAL, "maxpool2d: table replicas are not supported");
     const uint64_t n_out = ow * oh * channels, T = k_w * k_h, n = n_out * T;
     auto L = std::make_unique<Layer>();
     L->type = DASHB_LAYER_MAXPOOL2D;
@@ -1087,6 +1102,7 @@ int dashb_add_rescale_legacy(dashb_circuit* c, uint64_t n, int l, const int16_t*
     if (n != c->cur_size) return fail(DASHB_EINVAL, "rescale: size mismatch");
     if (l < 1 || l > 16 || !trans_mod || !approx || !cast1 || !cast2 || !sign) return fail(DASHB_EINVAL, "rescale: bad arguments");
     if (c->crt[0] != 2 || c->k < 2) return fail(DASHB_EINVAL, "legacy rescale needs crt_base[0] == 2");
+    if (c->table_replicas > 1) return fail(DASHB_EINVAL, "legacy rescale: table replicas are not supported");
     auto L = std::make_unique<Layer>();
     L->type = DASHB_LAYER_RESCALE_LEGACY;
     L->in_size = L->out_size = n;
@@ -1697,6 +1713,7 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
             p.evaluator = (const u128*)L.evaluator.p;
             p.batch = B;
             p.Bp = Bp;
+            p.b0 = ln.b0;
             CU(launch_sign(p, relu, s));
             c->launches += 1;
             break;
@@ -1905,6 +1922,15 @@ int dashb_evaluate_layers(dashb_circuit* c, int first, int last) {
     }
     c->out_n = c->layers[last]->out_size;
     for (int j = 0; j < c->k; ++j) c->out_q[j] = c->layers[last]->out_q[j];
+    return DASHB_OK;
+}
+
+int dashb_set_table_replicas(dashb_circuit* c, int replicas) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if (!c->layers.empty()) return fail(DASHB_ESTATE, "set the table replicas before the first layer is added");
+    if (replicas < 1 || replicas > 65536) return fail(DASHB_EINVAL, "replicas %d outside 1..65536", replicas);
+    c->table_replicas = replicas;
     return DASHB_OK;
 }
 
@@ -2430,6 +2456,14 @@ int dashb_layer_time_ms(dashb_circuit* c, int layer, float* ms) {
     if (!c || !ms || layer < 0 || layer >= (int)c->layers.size()) return fail(DASHB_EINVAL, "bad argument");
     *ms = c->layers[layer]->ms;
     return DASHB_OK;
+}
+
+int dashb_circuit_load_replicated(dashb_circuit** out, const char* path, int table_replicas) {
+    if (table_replicas < 1 || table_replicas > 65536) return fail(DASHB_EINVAL, "replicas %d outside 1..65536", table_replicas);
+    g_load_replicas = table_replicas;
+    const int rc = dashb_circuit_load(out, path);
+    g_load_replicas = 1;
+    return rc;
 }
 
 int dashb_circuit_load(dashb_circuit** out, const char* path) {

@@ -721,6 +721,20 @@ extern "C" int dashb_projection_static(const int16_t* d_in, const dashb_u128* d_
 
 namespace dashb {
 
+/* ------------------------------------------------- table replication */
+/* out[r * rep + i] = in[r]: the tables of `rep` garblings interleaved row by
+ * row (here `rep` copies of one garbling: same results, the memory traffic
+ * of one garbling per inference; see SignParams::rep) */
+__global__ void k_replicate_rows(const uint4* __restrict__ in, uint4* __restrict__ out, uint64_t rows, uint32_t rep) {
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < rows * rep; i += (uint64_t)gridDim.x * blockDim.x)
+        out[i] = in[i / rep];
+}
+cudaError_t launch_replicate_rows(const void* in, void* out, uint64_t rows, uint32_t rep, cudaStream_t s) {
+    if (rows == 0) return cudaSuccess;
+    k_replicate_rows<<<148 * 8, 256, 0, s>>>((const uint4*)in, (uint4*)out, rows, rep);
+    return cudaGetLastError();
+}
+
 /* ------------------------------------ output-channel sharding exchange */
 /*
  * The all-gather of output-channel sharding as plain stores into peer
@@ -1145,9 +1159,12 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
     /* rows of this element's tables, as 32-bit row indices from the element's
      * first row (a table of one element never reaches 2^32 rows) */
     const uint64_t et = e * P.tab_mul + P.tab_add; /* the gadget instance whose tables this element uses */
-    const u128* approx_e = P.approx + et * (uint64_t)nm * P.S;
-    const u128* cast1_e = P.cast1 + et * (uint64_t)(k + 1) * P.Mp;
-    const u128* cast2_e = P.cast2 + et * (uint64_t)(k + 1) * P.Mp;
+    /* table replicas (SignParams::rep): row r of this inference sits at r * R + rb */
+    const uint32_t R = P.rep;
+    const uint32_t rb = R > 1 ? (P.b0 + b) % R : 0u;
+    const u128* approx_e = P.approx + (et * (uint64_t)nm * P.S) * R + rb;
+    const u128* cast1_e = P.cast1 + (et * (uint64_t)(k + 1) * P.Mp) * R + rb;
+    const u128* cast2_e = P.cast2 + (et * (uint64_t)(k + 1) * P.Mp) * R + rb;
     uint32_t cnt1 = 0, cnt2 = 0;
     uint32_t ctop = 0;
     u128 top = gc::make_u128(0, 0);
@@ -1175,7 +1192,7 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
          * them from their use: residue j+1's approximate-digit row before
          * label j is hashed, the cast-1 row (its index is the label's colour,
          * known before the hash) before the hash as well. */
-        auto approx_row = [&](int j) { return ldg128(approx_e + ((uint32_t)nm * P.prefix[j] + (uint32_t)i * P.crt[j].q + col[j / T])); };
+        auto approx_row = [&](int j) { return ldg128(approx_e + (uint64_t)((uint32_t)nm * P.prefix[j] + (uint32_t)i * P.crt[j].q + col[j / T]) * R); };
         u128 row = gc::make_u128(0, 0);
         if ((int)t < k) row = approx_row(t);
 #pragma unroll 1
@@ -1187,7 +1204,7 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
             if (i > 0) {
                 /* Step 2.2: cast to modulus (k+1)*m_i */
                 const uint32_t c0 = gc::colour_of(lab, M, cc);
-                const u128 crow = ldg128(cast1_e + (cnt1 + (uint32_t)j * M.q + c0));
+                const u128 crow = ldg128(cast1_e + (uint64_t)(cnt1 + (uint32_t)j * M.q + c0) * R);
                 lab = gc::sub128(crow, hash(aes, lab));
             }
             if (t4)
@@ -1203,7 +1220,7 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
             uint32_t c2;
             const u128 sum = ladder ? compress_acc_ladder<T>(acc, C, fi, c2) : compress_acc<T>(acc, C, c2);
             if (i > 0) {
-                carry = gc::sub128(ldg128(cast2_e + (cnt2 + c2)), hash(aes, sum));
+                carry = gc::sub128(ldg128(cast2_e + (uint64_t)(cnt2 + c2) * R), hash(aes, sum));
             } else {
                 top = sum;
                 ctop = c2;
@@ -1228,17 +1245,17 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
     const uint32_t m0 = P.mrs[0].q;
 
     /* Step 3: sign projection(s) */
-    const u128* sign_e = P.sign + et * (uint64_t)P.n_out * m0;
+    const u128* sign_e = P.sign + (et * (uint64_t)P.n_out * m0) * R + rb;
     if (!RELU) {
 #pragma unroll 1
         for (int j = t; j < P.n_out; j += T) {
             const ModInfo mo = pin(P.outm[j]);
-            store_digits(P.out[j], mo, e, b, P.Bp, gc::sub128(ldg128(sign_e + (uint64_t)j * m0 + ctop), htop));
+            store_digits(P.out[j], mo, e, b, P.Bp, gc::sub128(ldg128(sign_e + ((uint64_t)j * m0 + ctop) * R), htop));
         }
         return;
     }
     /* Step 4 (ReLU): out_j = E_j + (y+r)*x_j - G_j  (mod p_j) */
-    const u128 s = gc::sub128(ldg128(sign_e + ctop), htop); /* sign label, modulus 2 */
+    const u128 s = gc::sub128(ldg128(sign_e + (uint64_t)ctop * R), htop); /* sign label, modulus 2 */
     u128 hs = gc::make_u128(0, 0);
     if (t == 0) hs = hash(aes, s);
     if (T > 1) {
@@ -1246,17 +1263,17 @@ __global__ void __launch_bounds__(SIGN_THREADS, DASHB_SIGN_MINB) k_sign(const __
         hs.hi = __shfl_sync(qmask, hs.hi, 0, T);
     }
     const uint32_t cs = (uint32_t)s.lo & 1u;
-    const u128* garbler_e = P.garbler + et * (uint64_t)P.S;
-    const u128* ev_e = P.evaluator + et * (uint64_t)k * 3;
+    const u128* garbler_e = P.garbler + (et * (uint64_t)P.S) * R + rb;
+    const u128* ev_e = P.evaluator + (et * (uint64_t)k * 3) * R + rb;
 #pragma unroll 1
     for (int j = t; j < k; j += T) {
         const ModInfo Pm = pin(P.crt[j]);
-        const u128 G = gc::sub128(ldg128(garbler_e + (P.prefix[j] + col[j / T])), h[j / T]);
-        const u128* ev = ev_e + 3 * j;
-        const u128 E = gc::sub128(ldg128(ev + cs), hs);
+        const u128 G = gc::sub128(ldg128(garbler_e + (uint64_t)(P.prefix[j] + col[j / T]) * R), h[j / T]);
+        const u128* ev = ev_e + (uint64_t)(3 * j) * R;
+        const u128 E = gc::sub128(ldg128(ev + (uint64_t)cs * R), hs);
         /* mini gate: int16 row `cs` of the packed slot minus the low 16 hash
          * bits (gates/projection_gate_mini.h:45-56) */
-        const u128 mini = ldg128(ev + 2);
+        const u128 mini = ldg128(ev + (uint64_t)2 * R);
         const int16_t row16 = (int16_t)((mini.lo >> (16 * cs)) & 0xffff);
         const int16_t t16 = (int16_t)(row16 - (int16_t)(hs.lo & 0xffff));
         int tt = (int)t16 % (int)Pm.q;
@@ -1465,7 +1482,7 @@ cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s) {
     /* latency mode: one warp per (element, inference) while that still leaves SMs idle otherwise */
     static const long wide_max = getenv("DASHB_WIDE_MAX") ? atol(getenv("DASHB_WIDE_MAX")) : 8192;
     /* with other lanes in flight the GPU is busy anyway: only tiny launches go wide */
-    if ((long)total <= (p.lanes > 1 ? wide_max / 4 : wide_max) && p.k <= 32 && p.n_out <= 32) {
+    if ((long)total <= (p.lanes > 1 ? wide_max / 4 : wide_max) && p.k <= 32 && p.n_out <= 32 && p.rep <= 1) {
         const unsigned wgrid = (unsigned)((total + WIDE_WARPS - 1) / WIDE_WARPS);
         const size_t wsmem = (size_t)WIDE_WARPS * p.n_mrs * acc_digits * sizeof(uint32_t);
         if (wsmem <= 40 * 1024) {

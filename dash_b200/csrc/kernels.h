@@ -96,6 +96,9 @@ struct SignParams {
     int k, n_mrs, n_out;
     int lanes;               /* sub-batch lanes evaluating concurrently (picks latency vs throughput kernel) */
     uint32_t tab_mul, tab_add; /* element e uses the tables of gadget instance e * tab_mul + tab_add (1, 0 except max pooling) */
+    /* rep > 1: every table row exists rep times, row r of inference b at r * rep + (b0 + b) % rep -- the layout a
+     * garbling per inference gives a batch (one set of tables per inference, rows interleaved by inference) */
+    uint32_t rep, b0;
 };
 
 /* k_pool_step (max pooling, max(x, y) = x + relu(y - x)): per output element
@@ -308,6 +311,7 @@ cudaError_t launch_shard_push(const ShardPushParams& p, cudaStream_t s);
 cudaError_t launch_shard_signal(uint32_t* const* peer_flags, int world, int rank, uint32_t epoch, cudaStream_t s);
 cudaError_t launch_shard_wait(uint32_t* flags, int world, uint32_t epoch, cudaStream_t s);
 cudaError_t launch_pool_step(const PoolParams& p, cudaStream_t s);
+cudaError_t launch_replicate_rows(const void* in, void* out, uint64_t rows, uint32_t rep, cudaStream_t s);
 cudaError_t launch_rescale(const RescaleParams& p, cudaStream_t s);
 cudaError_t launch_add_label(const AddLabelParams& p, cudaStream_t s);
 cudaError_t launch_decode(const DecodeParams& p, cudaStream_t s);

@@ -245,6 +245,19 @@ int dashb_set_decoding_info(dashb_circuit* c, const dashb_u128* const* dec);
 int dashb_set_input_encoding(dashb_circuit* c, const int16_t* const* base_labels,
                              const int16_t* const* offset_labels);
 
+/* The memory behaviour of one garbling per inference, for measurement.  A
+ * batch normally shares one circuit's ciphertext tables (see the note on the
+ * batch dimension above), which keeps them L2-resident.  With replicas = R
+ * (before the first layer is added) every sign / ReLU table is stored R times,
+ * row r of inference b at r * R + b % R -- the layout R independent garblings
+ * would have for a batch (rows interleaved by inference), here filled with R
+ * copies of the one garbling, so results are unchanged and checkable while
+ * every inference streams its own rows from HBM.  Labels and linear-layer
+ * constants stay shared; rescale / max-pooling / legacy-rescale tables are
+ * not replicated (the latter two reject replicas).  bench.py reports the
+ * throughput in this mode next to the shared-table number. */
+int dashb_set_table_replicas(dashb_circuit* c, int replicas);
+
 /* Uploads weights and tables, re-lays them for the kernels and sizes the
  * activation buffers for up to max_batch concurrent inferences. */
 int dashb_finalize(dashb_circuit* c, uint64_t max_batch);
@@ -411,6 +424,8 @@ int dashb_layer_type(const dashb_circuit* c, int layer);
  *      a garbled circuit only in process memory; format in
  *      include/dash_gcm_format.h) ---------------------------------------- */
 int dashb_circuit_load(dashb_circuit** out, const char* path);
+/* ... with dashb_set_table_replicas(table_replicas) applied before the layers are added */
+int dashb_circuit_load_replicated(dashb_circuit** out, const char* path, int table_replicas);
 /* Parses a DGCM file on the host and checks every array's byte count against
  * what its layer's parameters imply (what dashb_circuit_load does before it
  * touches the device): DASHB_OK, DASHB_EIO (unreadable, truncated, a record

@@ -354,3 +354,18 @@ def test_async_evaluation_two_steps_in_flight(gpu, name):
     labels = tile_batch(g.inputs, 5)
     assert_labels_equal(c.evaluate(labels), tile_batch(g.layers[-1], 5), "%s sync after async" % name)
     c.close()
+
+
+@pytest.mark.parametrize("name", ["MLP_TINY", "CONV_UNIT", "SIGN_TINY", "RELU_EDGE"])
+@pytest.mark.parametrize("batch,replicas", [(37, 37), (130, 130), (40, 7)])
+def test_table_replicas_give_the_same_labels(gpu, name, batch, replicas):
+    """dashb_set_table_replicas: the sign / ReLU tables stored once per
+    inference (rows interleaved by inference) -- the memory layout of one
+    garbling per inference -- must evaluate to the same labels as the shared
+    tables, whatever lane an inference falls into (replica = global inference
+    index mod replicas)."""
+    g = Golden(name)
+    c = gpu.Circuit.load(g.gcm, max_batch=batch, table_replicas=replicas)
+    got = c.evaluate(tile_batch(g.inputs, batch))
+    assert_labels_equal(got, tile_batch(g.layers[-1], batch), "%s with %d table replicas" % (name, replicas))
+    c.close()
