@@ -120,7 +120,7 @@ def stream_handle():
 
 
 LAYER_NAMES = {1: "dense", 2: "conv2d", 3: "approx_relu", 4: "sign", 5: "rescale", 6: "rescale", 7: "projection",
-               8: "max_pool"}
+               8: "max_pool", 9: "base_extension"}
 
 
 def _ptr_array(arrs):

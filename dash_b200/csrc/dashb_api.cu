@@ -250,6 +250,7 @@ gc::FracInfo make_fracinfo(const ModInfo& m, bool aligned4 = false) {
         for (int i = 0; i < 5; ++i) fi.mu[i] = mu.w[i];
         fi.addc = addc;
         fi.nst = nst;
+        fi.aligned = aligned4 ? 1u : 0u;
         fi.ladder = fi.words = 0;
         for (uint32_t s = 0; s < nst; ++s) {
             fi.mult[s] = (uint32_t)mults[s];
@@ -382,11 +383,16 @@ struct Layer {
     bool use_tc{false};
     /* tensor-core convolution: geometry for the im2col TMA box, cb channels per 128-column K block */
     uint32_t cv_w{0}, cv_h{0}, cv_c{0}, cv_fw{0}, cv_fh{0}, cv_sw{0}, cv_sh{0}, cv_cb{0}, tc_nkb{0};
+    /* strip convolution (k_conv_tc_strip): weights in (channel block, filter column, filter)-major rows of 128 bytes */
+    uint32_t st_strip{0}, st_rows{0}, st_cblk{0}, st_ncb{0}, st_wboxes{0};
+    DevMem wst[MAXK];
+    TensorMapBlob map_st[MAXK];
     /* gadget tables */
     DevMem approx, cast1, cast2, sign, garbler, evaluator;
     /* rescale */
     int nf{0}, l_iter{0};
     DevMem down[MAXK], tm, be;
+    DevMem start[MAXK]; /* base extension layer: per-element start labels of the extra residues (u8 [n][4*nc4]) */
     std::vector<std::unique_ptr<DevMem>> it_tables; /* legacy: 5 per iteration */
     RescaleParams rp;
     /* projection */
@@ -440,6 +446,7 @@ struct dashb_circuit {
     uint64_t input_size{0};
     std::vector<std::vector<int16_t>> zero; /* by modulus-2 */
     DevMem d_zero[MAXK], d_up[MAXK];
+    DevMem d_nolabel; /* 512 zero bytes: "no upshift" for the standalone base extension */
     bool has_up{false};
     u128 carry0;
     std::vector<std::unique_ptr<Layer>> layers;
@@ -839,6 +846,49 @@ int dashb_add_conv2d(dashb_circuit* c, uint64_t in_w, uint64_t in_h, uint64_t ch
         L->cv_w = (uint32_t)in_w, L->cv_h = (uint32_t)in_h, L->cv_c = (uint32_t)channels;
         L->cv_fw = (uint32_t)f_w, L->cv_fh = (uint32_t)f_h, L->cv_sw = (uint32_t)s_w, L->cv_sh = (uint32_t)s_h;
         L->cv_cb = (uint32_t)cb;
+        /* strip kernel: stride 1 in x, 32 or 64 filters, cblk channels per block with cblk * f_h a multiple of
+         * the MMA's K = 32 and at most 128 rows per input column */
+        static const int strip_env = getenv("DASHB_CONV_STRIP") ? atoi(getenv("DASHB_CONV_STRIP")) : 4;
+        uint64_t cblk = 0;
+        for (uint64_t cand = 128 / f_h; cand >= 1; --cand)
+            if ((cand * f_h) % 32 == 0) {
+                cblk = cand;
+                break;
+            }
+        /* fewer channels than a block: the smallest block that still holds them */
+        for (uint64_t cand = 1; cblk && cand < cblk; ++cand)
+            if ((cand * f_h) % 32 == 0 && cand >= channels) {
+                cblk = cand;
+                break;
+            }
+        if (strip_env >= 1 && s_w == 1 && (filters == 32 || filters == 64) && cblk && f_w >= 1) {
+            uint32_t P = (uint32_t)strip_env;
+            const uint32_t R = (uint32_t)(cblk * f_h), wboxes = (uint32_t)((f_w * filters + 127) / 128);
+            while (P > 1 && (P + f_w - 1 > 8 || (P + f_w - 1) * R * 128ull + wboxes * 16384ull > 108 * 1024 || P * filters > 256)) --P;
+            if (P + f_w - 1 <= 8 && (P + f_w - 1) * R * 128ull + wboxes * 16384ull <= 196 * 1024 && P * filters <= 256) {
+                const uint64_t ncb = (channels + cblk - 1) / cblk;
+                const uint64_t rows = ncb * f_w * filters;
+                for (int j = 0; j < c->k; ++j) {
+                    const int64_t q = c->crt[j];
+                    std::vector<uint8_t> wt((size_t)rows * 128, 0);
+                    for (uint64_t v = 0; v < filters; ++v)
+                        for (uint64_t w = 0; w < channels; ++w)
+                            for (uint64_t i = 0; i < f_h; ++i)
+                                for (uint64_t jx = 0; jx < f_w; ++jx) {
+                                    int64_t wv = wrow[v * K + (w * f_h + i) * f_w + jx] % q;
+                                    if (wv < 0) wv += q;
+                                    wt[(((w / cblk) * f_w + jx) * filters + v) * 128 + (w % cblk) * f_h + i] = (uint8_t)wv;
+                                }
+                    CU(L->wst[j].upload(wt.data(), wt.size()));
+                    CU(dense_tc_make_map(&L->map_st[j], L->wst[j].p, 128, rows));
+                }
+                L->st_strip = P;
+                L->st_rows = R;
+                L->st_cblk = (uint32_t)cblk;
+                L->st_ncb = (uint32_t)ncb;
+                L->st_wboxes = wboxes;
+            }
+        }
     }
     push_layer(c, std::move(L));
     return DASHB_OK;
@@ -959,7 +1009,7 @@ static int fill_rescale_static(dashb_circuit* c, Layer& L, uint64_t n, const int
     uint32_t off = 0;
     for (int j = 0; j < k; ++j) {
         p.crt[j] = c->crt_mi[j];
-        p.crtf[j] = c->crt_fi[j];
+        p.crtf[j] = c->crt_fa[j].nst ? c->crt_fa[j] : c->crt_fi[j]; /* word-aligned stages where the modulus has them */
         p.loff[j] = off;
         off += (c->crt_mi[j].nc + 3) & ~3u;
     }
@@ -1088,6 +1138,51 @@ int dashb_add_rescale(dashb_circuit* c, uint64_t n, const int32_t* factors, int 
     L->ref_aes = (double)n * gates;
     L->aes = (double)n * hashes;
     L->label_bytes = (double)n * (32.0 * k + 16.0 * gates);
+    push_layer(c, std::move(L));
+    return DASHB_OK;
+}
+
+int dashb_add_base_extension(dashb_circuit* c, uint64_t n, const int32_t* extra_moduli, int n_extra,
+                             const int16_t* const* start_labels, const dashb_u128* be_ciphers) {
+    int rc = check_building(c);
+    if (rc) return rc;
+    if ((rc = check_all_crt(c, "base extension"))) return rc;
+    if (n != c->cur_size) return fail(DASHB_EINVAL, "base extension: size mismatch");
+    if (!extra_moduli || !start_labels || n_extra < 1 || n_extra > MAXF || n_extra >= c->k)
+        return fail(DASHB_EINVAL, "base extension: bad list of extra moduli");
+    auto L = std::make_unique<Layer>();
+    L->type = DASHB_LAYER_BASE_EXTENSION;
+    L->in_size = L->out_size = n;
+    L->nf = n_extra;
+    for (int j = 0; j < c->k; ++j) L->out_q[j] = c->crt[j];
+    /* the gadget's constants are those of the rescale layer's step 3 with the extra moduli as factors */
+    if ((rc = fill_rescale_static(c, *L, n, extra_moduli, n_extra, 0))) return rc;
+    RescaleParams& p = L->rp;
+    for (int i = 0; i < MAXF; ++i)
+        for (int j = 0; j < MAXK; ++j) p.tm_off[i][j] = ~0ull; /* no division step: nothing is projected from the extra residues */
+    for (int j = 0; j < c->k; ++j) p.a1[j] = 1;
+    for (int i = 0; i < MAXF; ++i) p.a1f[i] = 1;
+    for (int x = 0; x < n_extra; ++x) {
+        const int j = p.fidx[x];
+        if (!start_labels[x]) return fail(DASHB_EINVAL, "base extension: start labels %d missing", x);
+        const uint32_t nc = c->crt_mi[j].nc, ncp = (nc + 3) & ~3u;
+        std::vector<uint8_t> b((size_t)n * ncp, 0);
+        for (uint64_t e = 0; e < n; ++e)
+            for (uint32_t d = 0; d < nc; ++d) b[e * ncp + d] = (uint8_t)start_labels[x][e * nc + d];
+        CU(L->start[j].upload(b.data(), b.size()));
+    }
+    if (!c->d_nolabel.p) {
+        std::vector<uint8_t> z(512, 0);
+        CU(c->d_nolabel.upload(z.data(), z.size()));
+    }
+    size_t be_rows = 0;
+    for (int i = 0; i < p.non_ext; ++i) be_rows += (size_t)(c->k - i - 1) * n * (size_t)c->crt[p.perm[i]];
+    if ((rc = upload_tables(L->be, be_ciphers, be_rows))) return rc;
+    double gates = 0;
+    for (int i = 0; i < p.non_ext; ++i) gates += c->k - i - 1;
+    L->ref_aes = (double)n * gates;
+    L->aes = (double)n * p.non_ext;
+    L->label_bytes = (double)n * (32.0 * c->k + 16.0 * gates);
     push_layer(c, std::move(L));
     return DASHB_OK;
 }
@@ -1650,10 +1745,22 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
                  * kernel itself handles 32 | filters <= 128 (DASHB_CONV_N_MAX for experiments and tests) */
                 static const int conv_n_max = getenv("DASHB_CONV_N_MAX") ? atoi(getenv("DASHB_CONV_N_MAX")) : 32;
                 if (conv && !conv_n_off && L.M % 32 == 0 && L.M <= (uint64_t)conv_n_max) tp.npad = (uint32_t)L.M;
+                const bool strip = conv && L.st_strip != 0;
+                if (strip) { /* k_conv_tc_strip: a strip of output pixels per CTA, filters on N */
+                    tp.npad = (uint32_t)L.M;
+                    tp.strip = L.st_strip;
+                    tp.st_rows = L.st_rows;
+                    tp.st_cblk = L.st_cblk;
+                    tp.st_ncb = L.st_ncb;
+                    tp.st_fw = L.cv_fw;
+                    tp.st_wboxes = L.st_wboxes;
+                }
                 for (int j = 0; j < c->k; ++j) {
-                    maps.a[j] = L.map_a[j];
+                    maps.a[j] = strip ? L.map_st[j] : L.map_a[j];
                     const uint64_t Nj = (uint64_t)((c->crt_mi[j].nc + 3) & ~3u) * Bp;
-                    if (conv)
+                    if (strip)
+                        CU(conv_tc_make_map(&maps.b[j], cur.plane[j], Nj, L.cv_w, L.cv_h, L.cv_c, 1, L.cv_fh, L.st_cblk));
+                    else if (conv)
                         CU(conv_tc_make_map(&maps.b[j], cur.plane[j], Nj, L.cv_w, L.cv_h, L.cv_c, L.cv_fw, L.cv_fh, L.cv_cb));
                     else
                         CU(dense_tc_make_map(&maps.b[j], cur.plane[j], Nj, L.K));
@@ -1772,6 +1879,30 @@ static int run_layer(dashb_circuit* c, Lane& ln, int li, cudaStream_t s) {
                     c->launches += 2;
                 }
             }
+            break;
+        }
+        case DASHB_LAYER_BASE_EXTENSION: {
+            /* k_rescale without its division step and shifts: the other residues pass through (and are hashed
+             * as the sources of the mixed-radix conversion), the extra residues start from the layer's labels */
+            RescaleParams p = L.rp;
+            for (int j = 0; j < c->k; ++j) {
+                p.in[j] = cur.plane[j];
+                p.out[j] = out.plane[j];
+                p.up[j] = (const uint8_t*)c->d_nolabel.p;
+                p.down[j] = nullptr;
+                p.zero[j] = (const uint8_t*)(L.start[j].p ? L.start[j].p : c->d_zero[j].p);
+                p.zstride[j] = L.start[j].p ? ((c->crt_mi[j].nc + 3) & ~3u) : 0u;
+            }
+            p.tm = nullptr;
+            p.be = (const u128*)L.be.p;
+            p.e0 = L.e0;
+            p.n = L.slice_count();
+            p.seg = L.seg;
+            p.stride = L.stride;
+            p.batch = B;
+            p.Bp = Bp;
+            CU(launch_rescale(p, s));
+            c->launches += 1;
             break;
         }
         case DASHB_LAYER_MAXPOOL2D: {

@@ -398,6 +398,182 @@ k_conv_tc_n(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ De
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols));
 }
 
+/*
+ * Convolution, stride 1 in x, a STRIP of horizontally adjacent output pixels
+ * per CTA (filters on N as in k_conv_tc_n).  The kernels above give every
+ * output pixel a CTA of its own, so an input byte is fetched f_w * f_h times
+ * and the weight tile once per pixel: they are bound by L2 -> shared-memory
+ * traffic (GNNP 32->32 3x3: 5.5 TB/s for 3 % of the int8 tensor peak).  Here
+ * the K order is (filter column j; channel c, filter row i): ONE input column
+ * x contributes the rows (c, i) -- a TMA box {128 plane bytes, 1 column, f_h
+ * rows, cblk channels}, cblk * f_h a multiple of the MMA's K = 32 -- and
+ * output pixel p uses the columns p .. p + f_w - 1, each of them a contiguous,
+ * uniformly strided K block of the MN-major A operand.  A strip of P pixels
+ * loads P + f_w - 1 columns instead of P * f_w and the weights once: 3x less
+ * operand traffic for 3x3 filters at P = 4.  Accumulators: P * npad TMEM
+ * columns.  MMAs of pixel p are issued as soon as its last column has landed
+ * (one mbarrier per column slot), so the loads of the later columns overlap
+ * the MMAs of the earlier pixels; two CTAs per SM overlap the rest.
+ * Same results as Conv2dModZero / LabelTensor::conv2d (see k_dense_tc).
+ */
+constexpr int ST_MAXCOL = 8; /* column slots: P + f_w - 1 */
+__global__ void __launch_bounds__(TC_THREADS, 1)
+k_conv_tc_strip(const __grid_constant__ DenseTcMaps maps, const __grid_constant__ DenseTcParams P) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ uint64_t bar_col[ST_MAXCOL], bar_w, bar_free, bar_acc;
+    __shared__ uint32_t tmem_base_s;
+    const int j = blockIdx.z;
+    const ModInfo m = P.mod[j];
+    const uint32_t nc4 = (m.nc + 3) >> 2;
+    const uint32_t Nj = nc4 * 4 * P.Bp;
+    const uint32_t n0 = blockIdx.x * TC_BN;
+    if (n0 >= Nj) return;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t npad = P.npad, S = P.strip, R = P.st_rows, fw = P.st_fw, ncb = P.st_ncb;
+    const uint32_t ncol = S + fw - 1;
+    /* blockIdx.y = (output row - first row) * strips per row + strip */
+    const uint32_t spr = (P.ow + S - 1) / S;
+    const uint32_t oy = P.p0 / P.ow + blockIdx.y / spr;
+    const uint32_t x0 = (blockIdx.y % spr) * S;
+    const uint32_t col_bytes = R * 128u;
+    uint8_t* sCol = smem;                      /* [ncol][R][128] */
+    uint8_t* sW = smem + ncol * col_bytes;     /* [wboxes][128][128] */
+    const uint32_t tmem_cols = S * npad <= 32 ? 32u : S * npad <= 64 ? 64u : S * npad <= 128 ? 128u : 256u;
+
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(tmem_cols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (threadIdx.x == 0) {
+        for (int c = 0; c < ST_MAXCOL; ++c) mbar_init(&bar_col[c], 1);
+        mbar_init(&bar_w, 1);
+        mbar_init(&bar_free, 1);
+        mbar_init(&bar_acc, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;");
+        asm volatile("fence.proxy.async.shared::cta;");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const uint32_t tmem_base = tmem_base_s;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (uint32_t cb = 0; cb < ncb; ++cb) {
+                /* one buffer: the next channel block's operands replace this one's once its MMAs have read them */
+                if (cb > 0) mbar_wait(&bar_free, (cb - 1) & 1);
+                mbar_expect_tx(&bar_w, P.st_wboxes * 128u * 128u);
+                for (uint32_t b = 0; b < P.st_wboxes; ++b)
+                    tma_load_2d(sW + b * 128u * 128u, reinterpret_cast<const CUtensorMap*>(&maps.a[j]), &bar_w, 0,
+                                (int)(cb * fw * npad + b * 128u));
+                for (uint32_t c = 0; c < ncol; ++c) {
+                    mbar_expect_tx(&bar_col[c], col_bytes);
+                    tma_load_4d(sCol + c * col_bytes, reinterpret_cast<const CUtensorMap*>(&maps.b[j]), &bar_col[c], (int)n0,
+                                (int)(x0 + c), (int)(oy * P.sy), (int)(cb * P.st_cblk));
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            /* S32 accumulator, U8 x U8, A MN-major (bit 15), B K-major, M = 128, N = npad */
+            const uint32_t idesc = (2u << 4) | (1u << 15) | ((npad >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+            for (uint32_t cb = 0; cb < ncb; ++cb) {
+                mbar_wait(&bar_w, cb & 1);
+                uint32_t ready = 0; /* column slots known to have landed */
+                for (uint32_t p = 0; p < S; ++p) {
+                    for (uint32_t jx = 0; jx < fw; ++jx) {
+                        while (ready <= p + jx) {
+                            mbar_wait(&bar_col[ready], cb & 1);
+                            ++ready;
+                        }
+                        asm volatile("tcgen05.fence::after_thread_sync;");
+                        const uint32_t aC = smem_u32(sCol + (p + jx) * col_bytes);
+                        const uint32_t aW = smem_u32(sW + jx * npad * 128u);
+                        for (uint32_t k4 = 0; k4 < R / 32; ++k4) {
+                            const uint64_t da = umma_desc(aC + k4 * 32 * TC_BN, 16, 1024); /* +32 k-rows of 128 plane bytes */
+                            const uint64_t db = umma_desc(aW + k4 * 32, 16, 1024);         /* +32 B inside the swizzled weight row */
+                            const uint32_t acc = (cb | jx | k4) ? 1u : 0u;
+                            asm volatile(
+                                "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                                "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}" ::"r"(
+                                    tmem_base + p * npad),
+                                "l"(da), "l"(db), "r"(idesc), "r"(acc), "r"(0), "r"(0), "r"(0), "r"(0)
+                                : "memory");
+                        }
+                    }
+                }
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar_free))
+                             : "memory");
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar_acc))
+                         : "memory");
+        }
+    } else {
+        /* epilogue, one output pixel after the other: TMEM lane = plane byte, column = pixel * npad + filter;
+         * the reduced bytes are transposed through shared memory (the operand buffers are free once the
+         * accumulators are complete) so that the global stores are 16 bytes per thread along a filter's row */
+        mbar_wait(&bar_acc, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        const uint32_t sub = (uint32_t)warp & 3u;
+        const uint32_t te = threadIdx.x - 64; /* 0..127 among the epilogue threads */
+        const uint32_t l128 = sub * 32 + lane;
+        const uint32_t n = n0 + l128;
+        const uint32_t ncp = nc4 * 4;
+        const uint32_t d4_first = n0 / (4 * P.Bp);
+        uint8_t* s_out = smem;                                           /* [npad][128] */
+        uint32_t* s_cst = reinterpret_cast<uint32_t*>(smem + 128 * 128); /* [npad][4] words of 4 digits */
+        for (uint32_t i = te; i < npad * 4; i += 128) {
+            const uint32_t f = i >> 2, d4 = d4_first + (i & 3u);
+            s_cst[i] = d4 < nc4 ? __ldg(reinterpret_cast<const uint32_t*>(P.cst[j] + (uint64_t)f * ncp) + d4) : 0u;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const uint32_t q = (n < Nj ? n / (4 * P.Bp) : d4_first) - d4_first; /* < 4: a 128-byte chunk spans at most 3 digit words */
+        const uint32_t sh = 8 * (n & 3u);
+        const uint32_t col16 = (te & 7u) * 16;
+        for (uint32_t p = 0; p < S; ++p) {
+            const uint32_t pix = oy * P.ow + x0 + p;
+            const bool live = x0 + p < P.ow && pix >= P.p0 && pix < P.p1; /* uniform over the CTA */
+            if (!live) continue;
+            for (uint32_t c0 = 0; c0 < npad; c0 += 32) {
+                uint32_t v[32];
+                const uint32_t taddr = tmem_base + ((sub * 32u) << 16) + p * npad + c0;
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                      "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                      "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                    : "r"(taddr));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const uint32_t f = c0 + i; /* filter */
+                    uint32_t x = v[i] + ((s_cst[f * 4 + q] >> sh) & 0xffu);
+                    x -= gc::mulhi32(x, m.mq) * m.q;
+                    if ((int32_t)x < 0) x += m.q;
+                    s_out[f * 128 + l128] = (uint8_t)x;
+                }
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            /* 8 threads x 16 bytes per filter row, 16 rows per pass */
+            if (n0 + col16 < Nj) { /* Nj is a multiple of 64 */
+                for (uint32_t f = te >> 3; f < npad; f += 16) {
+                    if (f < P.v0 || f >= P.v1) continue;
+                    const uint4 w = *reinterpret_cast<const uint4*>(s_out + f * 128 + col16);
+                    *reinterpret_cast<uint4*>(P.out[j] + ((uint64_t)f * P.npix + pix) * Nj + n0 + col16) = w;
+                }
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory"); /* s_out is free for the next pixel */
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols));
+}
+
 /* ---- host side: tensor maps ---- */
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -463,6 +639,20 @@ cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p_in, 
     uint32_t max_cols = 0;
     for (int j = 0; j < p.k; ++j) max_cols = max(max_cols, ((p.mod[j].nc + 3) & ~3u) * p.Bp);
     const uint32_t mblocks = (p.v1 - p.v0 + TC_BM - 1) / TC_BM;
+    if (p.conv && p.npad && p.strip) {
+        static bool attr_s = false;
+        const uint32_t smem_s = (p.strip + p.st_fw - 1) * p.st_rows * 128u + p.st_wboxes * 128u * 128u + 1024;
+        if (!attr_s) {
+            cudaError_t e = cudaFuncSetAttribute(k_conv_tc_strip, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e != cudaSuccess) return e;
+            attr_s = true;
+        }
+        /* the output rows that hold pixels of [p0, p1), strips of `strip` pixels along each */
+        const uint32_t rows = (p.p1 - 1) / p.ow - p.p0 / p.ow + 1, spr = (p.ow + p.strip - 1) / p.strip;
+        dim3 grid((max_cols + TC_BN - 1) / TC_BN, rows * spr, p.k);
+        k_conv_tc_strip<<<grid, TC_THREADS, smem_s, s>>>(maps, p);
+        return cudaGetLastError();
+    }
     if (p.conv && p.npad) {
         static bool attr_n = false;
         constexpr uint32_t smem_n = TC_STAGES_CONV * (TC_BK * TC_BN + TC_BM * TC_BK) + 1024;

@@ -260,7 +260,9 @@ struct FracInfo {
     uint32_t t4;                /* 1: five or six stages of four digits (the last one of the six may hold fewer) with
                                  * widths 5,[5,]4,3,2,1 -- the shape of every cast modulus (k+1) m_i in 41..76; the sign
                                  * kernel runs it as straight-line code */
-    uint32_t pad[2];            /* 128 bytes: indexing an array of plans is a shift */
+    uint32_t aligned;           /* 1: every stage but the first delivers a multiple of four digits and the first one's range
+                                 * starts on a multiple of four (make_fracinfo(aligned4)): stages cover whole plane words */
+    uint32_t pad[1];            /* 128 bytes: indexing an array of plans is a shift */
 };
 
 GC_HD void frac_init(u128 x, const FracInfo& fi, uint32_t (&n)[5]) {

@@ -1614,6 +1614,36 @@ template <bool PACKED>
 __device__ __forceinline__ void rs_accumulate_frac(uint32_t* acc, u128 pr, const ModInfo& m, const gc::FracInfo& fi,
                                                    uint32_t bcoef) {
     const uint32_t c1 = 65536u - m.q, c2 = m.q << 16;
+    if (PACKED && fi.aligned) {
+        /* word-aligned stages (make_fracinfo(aligned4)): every chunk starts on an even accumulator word, the
+         * widths are known at compile time (gc::for_each_chunk_ladder) -- no parity case, no width dispatch */
+        const uint32_t nc2 = 0u - c2, mq = m.mq;
+        uint32_t d = m.nc;
+        gc::for_each_chunk_ladder(pr, fi, [&](uint32_t len, uint32_t r) {
+            d -= len;
+            uint32_t* a = acc + (d >> 1) * RS_THREADS;
+#pragma unroll 1
+            for (; len >= 4; len -= 4) { /* two words per trip */
+                const uint32_t q1 = gc::mulhi32(r, mq);
+                const uint32_t q2 = gc::mulhi32(q1, mq);
+                const uint32_t q3 = gc::mulhi32(q2, mq);
+                const uint32_t q4 = gc::mulhi32(q3, mq);
+                a[0] += (r + q1 * c1 + q2 * nc2) * bcoef;
+                a[RS_THREADS] += (q2 + q3 * c1 + q4 * nc2) * bcoef;
+                a += 2 * RS_THREADS;
+                r = q4;
+            }
+            if (len & 2) {
+                const uint32_t q1 = gc::mulhi32(r, mq);
+                const uint32_t q2 = gc::mulhi32(q1, mq);
+                a[0] += (r + q1 * c1 + q2 * nc2) * bcoef;
+                a += RS_THREADS;
+                r = q2;
+            }
+            if (len & 1) a[0] += r * bcoef; /* the chunk's last digit is what is left */
+        });
+        return;
+    }
     gc::for_each_chunk_msb(pr, m, fi, [&](uint32_t d0, uint32_t len, uint32_t r) {
         uint32_t i = 0;
         if (PACKED) {
@@ -1784,7 +1814,7 @@ __device__ __forceinline__ void rescale_body(const RescaleParams& P, const AesSm
             rs_set<PACKED>(acc, P.zero[jt], m, 1);
             rs_finish_store<PACKED>(acc, P.out[jt], nullptr, 1, 0, m, e, b, P.Bp);
         } else {
-            rs_set<PACKED>(acc, P.zero[jt], m, P.a2[t]);
+            rs_set<PACKED>(acc, P.zero[jt] + e * P.zstride[jt], m, P.a2[t]);
         }
         if (P.legacy) continue;
         /* step 3: garbled mixed-radix conversion, all eliminations of this target */

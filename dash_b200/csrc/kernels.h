@@ -63,6 +63,14 @@ struct DenseTcParams {
     uint32_t conv, npix, ow, sx, sy, cb;
     uint32_t p0, p1;       /* output pixels [p0, p1) this launch computes (pixel sharding) */
     uint32_t npad;         /* != 0: filters on the N dimension (k_conv_tc_n), N = npad */
+    /* strip != 0: k_conv_tc_strip -- a CTA computes `strip` horizontally adjacent output pixels from
+     * strip + f_w - 1 shared input columns (stride 1 in x) */
+    uint32_t strip;
+    uint32_t st_rows;      /* K rows one input column contributes per channel block: cblk * f_h, a multiple of 32, <= 128 */
+    uint32_t st_cblk;      /* channels per block */
+    uint32_t st_ncb;       /* channel blocks */
+    uint32_t st_fw;        /* filter width */
+    uint32_t st_wboxes;    /* 128-row weight boxes per channel block: ceil(f_w * npad / 128) */
     int k;
 };
 
@@ -162,6 +170,8 @@ struct RescaleParams {
     const uint8_t* up[MAXK];    /* upshift label digits (u8[4*nc4_j], zero padded) */
     const uint8_t* down[MAXK];  /* downshift label digits */
     const uint8_t* zero[MAXK];  /* zero label digits */
+    uint32_t zstride[MAXK];     /* 0: zero[j] is one label for every element; else element e's label starts at zero[j] + e * zstride[j]
+                                 * (standalone base extension: the labels the layer starts the extra residues from) */
     uint32_t loff[MAXK];        /* (unused by the kernel) running offset of residue j's digits */
     const gc::u128* tm;
     const gc::u128* be;

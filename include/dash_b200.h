@@ -172,6 +172,20 @@ int dashb_add_rescale(dashb_circuit* c, uint64_t n, const int32_t* factors,
                       const dashb_u128* trans_mod,
                       const dashb_u128* be_ciphers);
 
+/* GarbledBaseExtension (layer/garbled_base_extension.h:67-97; CPU-only and
+ * "just for testing purposes" in the reference, circuit/layer/
+ * base_extension.h:10-14): the residues of the `extra_moduli` (CRT moduli) are
+ * rebuilt from the other residues by BaseExtensionGadget::cpu_evaluate
+ * (gadgets/base_extension_gadget.h:197-295); the other residues pass through
+ * unchanged.  The reference first REPLACES each extra residue's incoming label
+ * by the circuit's input base label of the same index (:74-80):
+ * start_labels[x] = int16 [n][nc(extra_moduli[x])] are those labels
+ * (get_base_label().at(index of the modulus)).  be_ciphers as in
+ * dashb_add_rescale. */
+int dashb_add_base_extension(dashb_circuit* c, uint64_t n, const int32_t* extra_moduli,
+                             int n_extra, const int16_t* const* start_labels,
+                             const dashb_u128* be_ciphers);
+
 /* Legacy GarbledRescale{l}: l iterations of factor 2, each followed by a
  * SignGadget with bounds (1,0), out modulus {2} that regenerates residue 0
  * (layer/garbled_rescale.h:27-35,93-100; rescale_gadget.h:208-224,328-342).
@@ -419,6 +433,7 @@ int dashb_layer_type(const dashb_circuit* c, int layer);
 #define DASHB_LAYER_RESCALE_LEGACY 6
 #define DASHB_LAYER_PROJECTION 7
 #define DASHB_LAYER_MAXPOOL2D 8
+#define DASHB_LAYER_BASE_EXTENSION 9
 
 /* ---- garbled-material files (no counterpart in the reference, which keeps
  *      a garbled circuit only in process memory; format in

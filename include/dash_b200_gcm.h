@@ -118,6 +118,29 @@ static inline int gcm_layer_sizes_ok(const gcm_circuit* g, const gcm_layer* L, u
                 be += gcm__mul(gcm__mul((uint64_t)(k - i - 1), n, &bad), (uint64_t)g->crt_base[perm[i]], &bad);
             return gcm__is(&L->a[k], gcm__mul(tm, 16, &bad), bad) && gcm__is(&L->a[k + 1], gcm__mul(be, 16, &bad), bad);
         }
+        case GCM_BASE_EXTENSION: {
+            const int nx = (int)L->p[2];
+            if (nx < 1 || nx > 16 || nx >= k || L->n_arrays != 1 + nx || n != n_in) return 0;
+            int perm[32], fidx[16];
+            for (int j = 0; j < k; ++j) perm[j] = j;
+            for (int i = 0; i < nx; ++i) {
+                int f = -1;
+                for (int j = 0; j < k; ++j)
+                    if (g->crt_base[j] == (int32_t)L->p[3 + i] && f < 0) f = j;
+                if (f < 0) return 0;
+                fidx[i] = f;
+                if (!gcm__is(&L->a[1 + i], gcm__mul(gcm__mul(n, nc[f], &bad), 2, &bad), bad)) return 0;
+            }
+            for (int i = 1; i <= nx; ++i) {
+                const int a = fidx[nx - i], b = k - i, t = perm[a];
+                perm[a] = perm[b];
+                perm[b] = t;
+            }
+            uint64_t be = 0;
+            for (int i = 0; i < k - nx; ++i)
+                be += gcm__mul(gcm__mul((uint64_t)(k - i - 1), n, &bad), (uint64_t)g->crt_base[perm[i]], &bad);
+            return gcm__is(&L->a[0], gcm__mul(be, 16, &bad), bad);
+        }
         case GCM_RESCALE_LEGACY: {
             const int l_it = (int)L->p[2];
             if (l_it < 1 || l_it > 16 || L->n_arrays != k + 5 * l_it || n != n_in) return 0;
@@ -254,6 +277,18 @@ static inline int dashb_circuit_from_gcm(const gcm_circuit* g, dashb_circuit** o
                 for (int i = 0; i < nf; ++i) factors[i] = (int32_t)L->p[3 + i];
                 rc = dashb_add_rescale(c, (uint64_t)L->p[1], factors, nf, (const int16_t* const*)&ptr[0],
                                        (const dashb_u128*)ptr[k], (const dashb_u128*)ptr[k + 1]);
+                break;
+            }
+            case GCM_BASE_EXTENSION: {
+                int32_t extra[16];
+                int nx = (int)L->p[2];
+                if (nx < 1 || nx > 16 || L->n_arrays != 1 + nx) {
+                    rc = DASHB_EINVAL;
+                    break;
+                }
+                for (int i = 0; i < nx; ++i) extra[i] = (int32_t)L->p[3 + i];
+                rc = dashb_add_base_extension(c, (uint64_t)L->p[1], extra, nx, (const int16_t* const*)&ptr[1],
+                                              (const dashb_u128*)ptr[0]);
                 break;
             }
             case GCM_RESCALE_LEGACY: {

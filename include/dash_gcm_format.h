@@ -51,6 +51,7 @@
 #define GCM_RESCALE_LEGACY 6
 #define GCM_PROJECTION 7
 #define GCM_MAXPOOL2D 8
+#define GCM_BASE_EXTENSION 9
 
 typedef struct gcm_array {
     const void* data; /* not owned by views; owned (malloc) after gcm_load */
@@ -72,6 +73,9 @@ typedef struct gcm_array {
  *                         trans_mod approx cast1 cast2 sign
  *  PROJECTION     p[1]=n p[2..2+k)=in_moduli p[2+k..2+2k)=out_moduli
  *                 arrays: ciphers[k]
+ *  BASE_EXTENSION p[1]=n p[2]=n_extra p[3..3+n_extra)=extra moduli (CRT moduli)
+ *                 arrays: be_ciphers, then per extra modulus the labels the
+ *                 reference layer starts that residue from (int16 [n][nc])
  *  MAXPOOL2D      p[1..7] = in_w in_h channels k_w k_h s_w s_h
  *                 arrays: approx cast1 cast2 sign garbler evaluator of the
  *                 outputs*k_w*k_h ReLU gadget instances (see dashb_add_maxpool2d)

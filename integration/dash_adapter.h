@@ -25,6 +25,7 @@
 #ifndef DASH_ADAPTER_H
 #define DASH_ADAPTER_H
 
+#include <algorithm>
 #include <map>
 #include <memory>
 #include <numeric>
@@ -76,6 +77,7 @@ DASH_ADAPTER_MEMBER(RG_sg, RescaleGadget, SignGadget*, m_sign_gadget)
 DASH_ADAPTER_MEMBER(RG_be, RescaleGadget, BaseExtensionGadget*, m_be_gadget)
 DASH_ADAPTER_MEMBER(BE_c, BaseExtensionGadget, __uint128_t*, m_proj_gates_base_change_loop_ciphers)
 DASH_ADAPTER_MEMBER(GP_c, GarbledProjection, std::vector<__uint128_t*>, m_ciphers)
+DASH_ADAPTER_MEMBER(GBE_g, GarbledBaseExtension, BaseExtensionGadget*, m_base_extension_gadget)
 typedef std::map<std::vector<size_t>, MaxGadget*> MaxGadgetMap;
 DASH_ADAPTER_MEMBER(GMP_g, GarbledMaxPool2d, MaxGadgetMap, m_max_gadgets)
 DASH_ADAPTER_MEMBER(MG_r, MaxGadget, ReluGadget*, m_relu_gadget)
@@ -241,6 +243,27 @@ inline void dash_view_from_circuit(GarbledCircuit* gc, DashMaterialView& v, bool
                 }
                 break;
             }
+            case Layer::base_extension: {
+                auto* g = dynamic_cast<GarbledBaseExtension*>(gl);
+                const size_t n = pl->get_input_size();
+                const auto extra = dynamic_cast<BaseExtension*>(pl)->get_extra_moduli();
+                L.p[0] = GCM_BASE_EXTENSION;
+                L.p[1] = (int64_t)n;
+                L.p[2] = (int64_t)extra.size();
+                auto* be = g->*get(GBE_g());
+                auto swapped = be->get_out_moduli();
+                size_t be_rows = 0;
+                for (size_t i = 0; i + extra.size() < k; ++i) be_rows += (k - i - 1) * (size_t)swapped[i];
+                push(L, be->*get(BE_c()), be_rows * n * 16);
+                for (size_t x = 0; x < extra.size(); ++x) {
+                    L.p[3 + x] = extra[x];
+                    // the labels the layer starts the extra residue from: the circuit's input base labels (garbled_base_extension.h:74-80)
+                    const size_t idx = std::find(crt.begin(), crt.end(), extra[x]) - crt.begin();
+                    auto* base = gc->get_base_label().at(idx);
+                    push(L, base->get_components(), n * (size_t)LabelTensor::get_nr_comps(extra[x]) * sizeof(crt_val_t));
+                }
+                break;
+            }
             case Layer::max_pool: {
                 /* one MaxGadget -> ReluGadget -> SignGadget (one element each) per (output, kernel position):
                  * their arrays are concatenated into the six tables of a ReLU layer with outputs * k_w k_h
@@ -298,7 +321,7 @@ inline void dash_view_from_circuit(GarbledCircuit* gc, DashMaterialView& v, bool
             }
             default:
                 throw std::runtime_error(
-                    "dash_adapter: layer type outside the B200 hot path (mult / mixed-mod mult / max / base_extension layer)");
+                    "dash_adapter: layer type outside the B200 hot path (mult / mixed-mod mult / max layer)");
         }
         v.layers.push_back(L);
     }

@@ -697,6 +697,24 @@ int oracle_evaluate(const oracle_circuit* c, const int16_t* const* in, int upto,
                 break;
             case GCM_PROJECTION: eval_projection(c, L, &cur, &nxt, nr_threads); break;
             case GCM_MAXPOOL2D: eval_maxpool(c, L, &cur, &nxt, nr_threads); break;
+            case GCM_BASE_EXTENSION: {
+                /* GarbledBaseExtension::cpu_evaluate (layer/garbled_base_extension.h:67-97): the extra residues'
+                 * labels are replaced by the layer's start labels (the circuit's input base labels, :74-80),
+                 * then the gadget runs on all residues; the others pass through */
+                const int nx = (int)L->p[2];
+                int extra[16];
+                for (int j = 0; j < k; ++j) memcpy(nxt.d[j], cur.d[j], sizeof(int16_t) * cur.n * (uint64_t)cur.nc[j]);
+                for (int x = 0; x < nx; ++x) {
+                    extra[x] = (int)L->p[3 + x];
+                    for (int j = 0; j < k; ++j)
+                        if (c->g.crt_base[j] == extra[x]) {
+                            memcpy(nxt.d[j], L->a[1 + x].data, sizeof(int16_t) * cur.n * (uint64_t)cur.nc[j]);
+                            break;
+                        }
+                }
+                eval_base_extension(c, (const u128*)L->a[0].data, cur.n, extra, nx, &nxt, nr_threads);
+                break;
+            }
             default: rc = -1;
         }
         labels_free(&cur, k);
@@ -777,6 +795,11 @@ double oracle_aes_blocks(const oracle_circuit* c) {
             }
             case GCM_RESCALE_LEGACY: total += n * L->p[2] * ((k - 1) + sign_in + 1); break;
             case GCM_PROJECTION: total += n * k; break;
+            case GCM_BASE_EXTENSION: {
+                const int nx = (int)L->p[2];
+                for (int i = 0; i < k - nx; ++i) total += n * (k - i - 1);
+                break;
+            }
             default: break;
         }
     }

@@ -37,6 +37,7 @@ static inline int dash_ref_seeded_rdrand16(unsigned short* p) {
 #include "circuit/circuit.h"
 #include "circuit/layer/conv2d.h"
 #include "circuit/layer/dense.h"
+#include "circuit/layer/base_extension.h"
 #include "circuit/layer/flatten.h"
 #include "circuit/layer/max_pool2d.h"
 #include "circuit/layer/projection.h"
@@ -191,6 +192,12 @@ int ref_add_rescale_legacy(void* hv, int l, uint64_t d0, uint64_t d1, uint64_t d
 int ref_add_rescale(void* hv, const int* factors, int nf, uint64_t d0, uint64_t d1, uint64_t d2) {
     std::vector<crt_val_t> s(factors, factors + nf);
     static_cast<RefHandle*>(hv)->layers.push_back(new Rescale(s, dims3(d0, d1, d2)));
+    return 0;
+}
+/* BaseExtension(input_dims, extra_moduli) (circuit/layer/base_extension.h:20) */
+int ref_add_base_extension(void* hv, const int* extra, int nx, uint64_t d0, uint64_t d1, uint64_t d2) {
+    std::vector<crt_val_t> e(extra, extra + nx);
+    static_cast<RefHandle*>(hv)->layers.push_back(new BaseExtension(dims3(d0, d1, d2), e));
     return 0;
 }
 /* MaxPool2d(input_width, input_height, channel, kernel_width, kernel_height, stride_width, stride_height)

@@ -39,6 +39,7 @@ def lib():
         L.ref_add_rescale_legacy.argtypes = [C.c_void_p, C.c_int] + [C.c_uint64] * 3
         L.ref_add_rescale.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_uint64] * 3
         L.ref_add_maxpool2d.argtypes = [C.c_void_p] + [C.c_uint64] * 7
+        L.ref_add_base_extension.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_uint64] * 3
         L.ref_add_projection.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_int, C.c_int]
         L.ref_garble.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_uint64]
         for f in (L.ref_input_size, L.ref_output_size):
@@ -151,6 +152,10 @@ class RefCircuit:
     def add_rescale(self, factors, dims):
         f = np.asarray(factors, dtype=np.int32)
         self._chk(self.L.ref_add_rescale(self.h, f.ctypes.data, len(f), *self._d3(dims)))
+
+    def add_base_extension(self, extra_moduli, dims):
+        e = np.asarray(extra_moduli, dtype=np.int32)
+        self._chk(self.L.ref_add_base_extension(self.h, e.ctypes.data, len(e), *self._d3(dims)))
 
     def add_maxpool2d(self, w, h, c, kw, kh, sw=1, sh=1):
         self._chk(self.L.ref_add_maxpool2d(self.h, w, h, c, kw, kh, sw, sh))

@@ -22,7 +22,7 @@ from oracle import refbind as R  # noqa: E402
 
 GOLDEN = ["SIGN_TINY", "RELU_99", "RESCALE_LEGACY", "RESCALE_2", "RESCALE_2_3", "RESCALE_OPT", "PROJECTION",
           "MLP_TINY", "CONV_UNIT", "RELU_EDGE", "PROJ_UP_BACK", "PROJ_DOWN_BACK", "PROJ_2X2",
-          "MAXPOOL_2X2", "MAXPOOL_P9", "MAXPOOL_1X1", "MAXPOOL_4X4C2_DENSE"]
+          "MAXPOOL_2X2", "MAXPOOL_P9", "MAXPOOL_1X1", "MAXPOOL_4X4C2_DENSE", "BASE_EXT_1", "BASE_EXT_2"]
 
 # extra unit circuits only used as fixtures
 W.MODELS["CONV_UNIT"] = dict(  # stride 2, two channels, three filters (cf. test_conv2d.h:133-261)
@@ -54,6 +54,14 @@ W.MODELS["MAXPOOL_4X4C2_DENSE"] = dict(  # two channels, 2x2 / stride 2 windows,
     input=(4, 4, 2), layers=[("maxpool", 2, 2), ("flatten",), ("dense", 3)], quant=("simple", 0.1), crt=[2, 3, 5, 7],
     mrs=[26, 3], max_modulus=0)
 
+# the standalone base-extension layer (layer/garbled_base_extension.h; no test in the reference): one and two
+# extra moduli; the inputs are zero because the layer starts the extra residues from the circuit's input BASE
+# labels (:74-80), i.e. from the labels of the value 0
+W.MODELS["BASE_EXT_1"] = dict(input=(5, 1, 1), layers=[("flatten",), ("base_extension", (7,))], quant=("simple", 1.0),
+                              crt=[2, 3, 5, 7], mrs=[], max_modulus=0)
+W.MODELS["BASE_EXT_2"] = dict(input=(4, 1, 1), layers=[("flatten",), ("base_extension", (3, 11))], quant=("simple", 1.0),
+                              crt=[2, 3, 5, 7, 11, 13], mrs=[], max_modulus=0)
+
 BATCH = 3
 
 
@@ -62,6 +70,8 @@ def inputs_for(name, spec, n):
         P = 30  # 0, +-1, +-mid, +-extremes of the signed range (-P/2, P/2)
         row = np.array([0, 1, -1, 7, -7, 14, -14, 2, -2, 13, -13, 5, -5, 3], dtype=np.int64)
         return np.stack([row, -row, np.roll(row, 3)])[:, :n]
+    if name.startswith("BASE_EXT"):  # row 0: zeros (decodes); rows 1, 2: other labels on the non-extra residues
+        return np.array([[0] * n, list(range(1, n + 1)), [-(i + 1) for i in range(n)]], dtype=np.int64)
     if name in ("MAXPOOL_2X2", "MAXPOOL_1X1"):   # first row: mixed_high of the reference test
         return np.array([[3, -11, 5, 10], [0, 0, 0, 0], [-14, 1, 0, 7]], dtype=np.int64)
     if name == "MAXPOOL_P9":     # mid_p9, neg_high_p9, low_p9

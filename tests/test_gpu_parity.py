@@ -221,6 +221,13 @@ def test_dense_tensor_core_path(gpu, tmp_path, M, K, batch):
     (9, 9, 20, 64, 3, 1),    # 64 filters: filters-on-N kernel, two K blocks
     (6, 6, 40, 128, 3, 1),   # 128 filters on N, three K blocks
     (8, 8, 8, 96, 2, 2),     # 96 filters on N (TMEM allocation rounds up to 128 columns)
+    # stride 1, 32 or 64 filters: the strip kernel (k_conv_tc_strip, several output pixels per CTA)
+    (10, 10, 32, 32, 3, 1),  # one channel block of 32, strips of 4 over 8 output columns
+    (11, 9, 64, 64, 3, 1),   # two channel blocks, 9 output columns: last strip partly outside
+    (9, 9, 64, 64, 1, 1),    # 1x1 filter: one column per pixel
+    (7, 7, 33, 32, 3, 1),    # 33 channels: second block holds one channel, the rest zero-filled
+    (12, 12, 16, 32, 2, 1),  # 2x2 filter, 16 channels: 32 rows per column
+    (30, 30, 32, 32, 3, 1),  # the GNNP 32 -> 32 convolution at full width
 ])
 @pytest.mark.parametrize("batch", [1, 19])
 def test_conv_tensor_core_path(gpu, tmp_path, geom, batch, monkeypatch):

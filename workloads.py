@@ -161,6 +161,8 @@ def build_reference_circuit(spec, seed=42, weight_seed=42):
                 c.add_rescale_legacy(q_param, [w, h, ch])
             elif qname == "scaleplus":
                 c.add_rescale([q_param], [w, h, ch])
+        elif kind == "base_extension":
+            c.add_base_extension(list(layer[1]), dims)
         elif kind == "maxpool":
             _, ksz, stride = layer
             c.add_maxpool2d(w, h, ch, ksz, ksz, stride, stride)
