@@ -389,9 +389,12 @@ def main():
     L.dashb_evaluate_async.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
     L.dashb_evaluate_wait.argtypes = [C.c_void_p]
 
-    def timed_pipelined(steps, warmup):
+    def timed_pipelined(steps, warmup, call=None, ins=None, outs=None):
+        call = call or L.dashb_evaluate_async
+        ins = ins if ins is not None else in_ptrs
+        outs = outs or out_sets
         for i in range(warmup):
-            api._check(L.dashb_evaluate_async(circ.h, in_ptrs, B, out_sets[i & 1]))
+            api._check(call(circ.h, ins, B, outs[i & 1]))
         api._check(L.dashb_evaluate_wait(circ.h))
         torch.cuda.synchronize()
         barrier()
@@ -400,7 +403,7 @@ def main():
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for i in range(steps):
-            api._check(L.dashb_evaluate_async(circ.h, in_ptrs, B, out_sets[i & 1]))
+            api._check(call(circ.h, ins, B, outs[i & 1]))
         api._check(L.dashb_evaluate_wait(circ.h))  # host waits for the last step; e1 then closes the region
         e1.record(stream)
         e1.synchronize()
@@ -464,6 +467,10 @@ def main():
     def step_compressed():
         api._check(L.dashb_evaluate_compressed(circ.h, comp_in_ptrs, B, comp_out_ptrs))
 
+    comp_out2 = [torch.empty_like(t).pin_memory() for t in comp_out]
+    comp_out_sets = [comp_out_ptrs, (C.c_void_p * circ.k)(*[t.data_ptr() for t in comp_out2])]
+    L.dashb_evaluate_compressed_async.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+
     sampler = ClockSampler(local_rank)
     sampler.start()
     time.sleep(0.2)
@@ -474,6 +481,8 @@ def main():
     pipelined_equal = all(bool(torch.equal(a, b)) for a, b in zip(out_t, out_t2))
     ms_val = timed(step_values, args.steps, args.warmup)
     ms_comp = timed(step_compressed, args.steps, args.warmup)
+    ms_comp_pipe = timed_pipelined(args.steps, args.warmup, L.dashb_evaluate_compressed_async, comp_in_ptrs, comp_out_sets)
+    comp_pipelined_equal = all(bool(torch.equal(a, b)) for a, b in zip(comp_out, comp_out2))
     values_ok = bool(ok_t.numpy().all())
     circ.move_inputs(in_np)  # restore the label inputs for the profiling pass
     # Per-kernel durations for the roofline, taken in the step as it runs (sub-batch lanes concurrent on their own
@@ -598,6 +607,13 @@ def main():
                            "h2d_bytes_per_step": int(sum(t.numel() * 8 for t in comp_in)),
                            "d2h_bytes_per_step": int(sum(t.numel() * 8 for t in comp_out)),
                            "api": "dashb_evaluate_compressed (labels as 16-byte LabelTensor::compress values in pinned host memory)"},
+        "e2e_compressed_pipelined": {"value": total_inf / (ms_comp_pipe / 1e3), "unit": "inferences/s",
+                                     "ms_per_step": ms_comp_pipe / args.steps,
+                                     "h2d_bytes_per_step": int(sum(t.numel() * 8 for t in comp_in)),
+                                     "d2h_bytes_per_step": int(sum(t.numel() * 8 for t in comp_out)),
+                                     "both_output_sets_equal": comp_pipelined_equal,
+                                     "api": "dashb_evaluate_compressed_async x steps + dashb_evaluate_wait: the compressed wire "
+                                            "form with two steps in flight (13 % of the int16 layout's PCIe bytes)"},
         "gpu_launches": int(launches * args.steps),
         "clocks": sampler.summary(),
         "roofline": roofline,

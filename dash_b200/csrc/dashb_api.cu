@@ -2478,6 +2478,10 @@ int dashb_evaluate_async(dashb_circuit* c, const int16_t* const* in, uint64_t ba
     return evaluate_any(c, reinterpret_cast<const void* const*>(in), batch, reinterpret_cast<void* const*>(out), false, true);
 }
 
+int dashb_evaluate_compressed_async(dashb_circuit* c, const dashb_u128* const* in, uint64_t batch, dashb_u128* const* out) {
+    return evaluate_any(c, reinterpret_cast<const void* const*>(in), batch, reinterpret_cast<void* const*>(out), true, true);
+}
+
 int dashb_evaluate_wait(dashb_circuit* c) {
     if (!c) return fail(DASHB_EINVAL, "null circuit");
     return wait_async(c);

@@ -1549,6 +1549,18 @@ constexpr int RS_THREADS = 128;
  * halves never meet, so one multiply-add updates both.  Otherwise one digit
  * per word. */
 
+/* Two digits in the 16-bit halves of a word, each below 2q: subtract q from
+ * the halves that reached it.  cq = (0x8000 - q) in both halves, so that bit 15
+ * of (half + 0x8000 - q) says half >= q. */
+__device__ __forceinline__ uint32_t pair_csub(uint32_t x, uint32_t q, uint32_t cq) {
+    return x - (((x + cq) >> 15) & 0x00010001u) * q;
+}
+/* bytes 0,1 (HI = false) or 2,3 of a word of four digits as a pair of halves */
+template <bool HI>
+__device__ __forceinline__ uint32_t pair_of(uint32_t w) {
+    return __byte_perm(w, 0, HI ? 0x4342 : 0x4140);
+}
+
 /* acc[d] = ((x_j[d] + upshift_j[d]) mod q) * a   (step 1, pre-multiplied) */
 template <bool PACKED>
 __device__ __forceinline__ void rs_init(uint32_t* acc, const uint8_t* plane, const uint8_t* up, const ModInfo& m, uint64_t e,
@@ -1558,24 +1570,24 @@ __device__ __forceinline__ void rs_init(uint32_t* acc, const uint8_t* plane, con
     const uint32_t nw = nc4_of(m);
     auto word = [&](uint32_t d4) { return d4 < nw ? *reinterpret_cast<const uint32_t*>(p + (uint64_t)d4 * 4 * Bp) : 0u; };
     uint32_t n0 = word(0), n1 = word(1);
+    const uint32_t cq = (0x8000u - m.q) * 0x10001u;
     for (uint32_t d4 = 0; d4 < nw; ++d4) {
         const uint32_t xw = n0;
         n0 = n1;
         n1 = word(d4 + 2);
         const uint32_t uw = __ldg(reinterpret_cast<const uint32_t*>(up) + d4);
-        uint32_t v[4];
-#pragma unroll
-        for (uint32_t t = 0; t < 4; ++t) {
-            v[t] = ((xw >> (8 * t)) & 0xff) + ((uw >> (8 * t)) & 0xff);
-            v[t] = (v[t] >= m.q ? v[t] - m.q : v[t]) * a;
-        }
-        if (PACKED) { /* the padding digits of the last word are zero in both labels */
-            acc[(2 * d4) * RS_THREADS] = v[0] | (v[1] << 16);
-            acc[(2 * d4 + 1) * RS_THREADS] = v[2] | (v[3] << 16);
+        if (PACKED) {
+            /* pairs of digits all the way: add, reduce and scale both halves at once (the padding digits of
+             * the last word are zero in both labels and stay zero) */
+            acc[(2 * d4) * RS_THREADS] = pair_csub(pair_of<false>(xw) + pair_of<false>(uw), m.q, cq) * a;
+            acc[(2 * d4 + 1) * RS_THREADS] = pair_csub(pair_of<true>(xw) + pair_of<true>(uw), m.q, cq) * a;
         } else {
 #pragma unroll
-            for (uint32_t t = 0; t < 4; ++t)
-                if (4 * d4 + t < m.nc) acc[(4 * d4 + t) * RS_THREADS] = v[t];
+            for (uint32_t t = 0; t < 4; ++t) {
+                uint32_t v = ((xw >> (8 * t)) & 0xff) + ((uw >> (8 * t)) & 0xff);
+                v = (v >= m.q ? v - m.q : v) * a;
+                if (4 * d4 + t < m.nc) acc[(4 * d4 + t) * RS_THREADS] = v;
+            }
         }
     }
 }
@@ -1701,6 +1713,20 @@ __device__ __forceinline__ uint32_t rs_field(const uint32_t* acc, uint32_t d) {
 /* reduce, compress and return the colour digit */
 template <bool PACKED>
 __device__ __forceinline__ u128 rs_finish_compress(const uint32_t* acc, const ModInfo& m, uint32_t& colour) {
+    if (PACKED && m.cw) {
+        /* four digits per trip, most significant word first: two accumulator words, four reductions, the
+         * bytes of one label word, folded in by gc::WordCompressor (the top word's padding digits are zero) */
+        gc::WordCompressor c(m);
+        uint32_t v0 = 0;
+        for (int d4 = (int)nc4_of(m) - 1; d4 >= 0; --d4) {
+            const uint32_t w0 = acc[(2 * d4) * RS_THREADS], w1 = acc[(2 * d4 + 1) * RS_THREADS];
+            v0 = gc::mod_q(w0 & 0xffffu, m);
+            const uint32_t v1 = gc::mod_q(w0 >> 16, m), v2 = gc::mod_q(w1 & 0xffffu, m), v3 = gc::mod_q(w1 >> 16, m);
+            c.push(v0 | (v1 << 8) | (v2 << 16) | (v3 << 24));
+        }
+        colour = v0;
+        return c.value();
+    }
     gc::Compressor c(m);
     uint32_t dg = 0;
     for (int d = (int)m.nc - 1; d >= 0; --d) {
@@ -1718,27 +1744,50 @@ template <bool PACKED>
 __device__ __forceinline__ void rs_finish_store(uint32_t* acc, uint8_t* plane, const uint8_t* down, uint32_t mul, uint32_t next_a,
                                                 const ModInfo& m, uint64_t e, uint32_t b, uint32_t Bp) {
     uint8_t* p = plane + plane_off(m, e, b, Bp);
+    if (PACKED) {
+        /* pairs of digits: the subtraction of the downshift label and the restart of the accumulator work on
+         * both halves of a word at once; only the reductions mod q take the digits one by one.  Padding
+         * digits are zero in the accumulator and in `down`, and come out zero. */
+        const uint32_t cq = (0x8000u - m.q) * 0x10001u, qq = m.q * 0x10001u;
+        for (uint32_t d4 = 0; d4 < nc4_of(m); ++d4) {
+            const uint32_t w0 = acc[(2 * d4) * RS_THREADS], w1 = acc[(2 * d4 + 1) * RS_THREADS];
+            uint32_t v0 = gc::mod_q(w0 & 0xffffu, m), v1 = gc::mod_q(w0 >> 16, m);
+            uint32_t v2 = gc::mod_q(w1 & 0xffffu, m), v3 = gc::mod_q(w1 >> 16, m);
+            if (next_a) {
+                acc[(2 * d4) * RS_THREADS] = (v0 | (v1 << 16)) * next_a;
+                acc[(2 * d4 + 1) * RS_THREADS] = (v2 | (v3 << 16)) * next_a;
+            }
+            if (mul != 1) {
+                v0 = gc::mod_q(v0 * mul, m);
+                v1 = gc::mod_q(v1 * mul, m);
+                v2 = gc::mod_q(v2 * mul, m);
+                v3 = gc::mod_q(v3 * mul, m);
+            }
+            uint32_t p0 = v0 | (v1 << 16), p1 = v2 | (v3 << 16);
+            if (down) {
+                const uint32_t dw = __ldg(reinterpret_cast<const uint32_t*>(down) + d4);
+                p0 = pair_csub(p0 + qq - pair_of<false>(dw), m.q, cq);
+                p1 = pair_csub(p1 + qq - pair_of<true>(dw), m.q, cq);
+            }
+            *reinterpret_cast<uint32_t*>(p + (uint64_t)d4 * 4 * Bp) = __byte_perm(p0, p1, 0x6420);
+        }
+        return;
+    }
     for (uint32_t d4 = 0; d4 < nc4_of(m); ++d4) {
         const uint32_t dw = down ? __ldg(reinterpret_cast<const uint32_t*>(down) + d4) : 0u;
         uint32_t ow = 0;
-        uint32_t nv[4] = {0, 0, 0, 0};
 #pragma unroll
         for (uint32_t t = 0; t < 4; ++t) {
             const uint32_t d = 4 * d4 + t;
             if (d >= m.nc) break;
-            uint32_t v = gc::mod_q(rs_field<PACKED>(acc, d), m);
-            nv[t] = v * next_a;
-            if (!PACKED && next_a) acc[d * RS_THREADS] = nv[t];
+            uint32_t v = gc::mod_q(acc[d * RS_THREADS], m);
+            if (next_a) acc[d * RS_THREADS] = v * next_a;
             if (mul != 1) v = gc::mod_q(v * mul, m);
             if (down) {
                 v = v + m.q - ((dw >> (8 * t)) & 0xff);
                 v = v >= m.q ? v - m.q : v;
             }
             ow |= v << (8 * t);
-        }
-        if (PACKED && next_a) {
-            acc[(2 * d4) * RS_THREADS] = nv[0] | (nv[1] << 16);
-            acc[(2 * d4 + 1) * RS_THREADS] = nv[2] | (nv[3] << 16);
         }
         *reinterpret_cast<uint32_t*>(p + (uint64_t)d4 * 4 * Bp) = ow;
     }

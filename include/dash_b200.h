@@ -326,6 +326,8 @@ int dashb_evaluate_wait(dashb_circuit* c);
 int dashb_move_inputs_compressed(dashb_circuit* c, const dashb_u128* const* in, uint64_t batch);
 int dashb_move_outputs_compressed(dashb_circuit* c, dashb_u128* const* out);
 int dashb_evaluate_compressed(dashb_circuit* c, const dashb_u128* const* in, uint64_t batch, dashb_u128* const* out);
+/* dashb_evaluate_async with compressed labels on both sides (same rules; completes with dashb_evaluate_wait). */
+int dashb_evaluate_compressed_async(dashb_circuit* c, const dashb_u128* const* in, uint64_t batch, dashb_u128* const* out);
 
 /* Debug/parity hook: copies the output labels of layer `layer` (index into
  * the layers added, flatten not counted) of the last evaluation. */

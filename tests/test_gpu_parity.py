@@ -363,6 +363,48 @@ def test_async_evaluation_two_steps_in_flight(gpu, name):
     c.close()
 
 
+@pytest.mark.parametrize("name", ["MLP_TINY", "CONV_UNIT"])
+def test_async_evaluation_compressed_labels(gpu, name):
+    """dashb_evaluate_compressed_async: the streaming call with 128-bit labels
+    on both sides returns, batch for batch, what the synchronous compressed
+    call returns."""
+    import ctypes as C
+
+    import torch
+
+    from dash_b200 import gcm as gcm_io
+    from dash_b200.api import _check
+
+    g = Golden(name)
+    crt = gcm_io.read_gcm(g.gcm)["crt"]
+    c = gpu.Circuit.load(g.gcm, max_batch=96)
+    L = c.L
+    L.dashb_evaluate_compressed_async.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+    L.dashb_evaluate_wait.argtypes = [C.c_void_p]
+    batches = [96, 5, 64, 33, 96]
+    keep, want = [], []
+    for r, b in enumerate(batches):
+        labels = [np.roll(l, r, axis=0) for l in tile_batch(g.inputs, b)]
+        comp = [np.ascontiguousarray(gcm_io.compress_labels(q, l)) for q, l in zip(crt, labels)]
+        want.append(c.evaluate_compressed(comp))
+        ins = []
+        for l in comp:
+            t = torch.empty(l.shape, dtype=torch.uint64).pin_memory()
+            t.numpy()[...] = l
+            ins.append(t)
+        outs = [torch.zeros(w.shape, dtype=torch.uint64).pin_memory() for w in want[-1]]
+        keep.append((ins, outs))
+    for (ins, outs), b in zip(keep, batches):
+        ip = (C.c_void_p * len(ins))(*[t.data_ptr() for t in ins])
+        op = (C.c_void_p * len(outs))(*[t.data_ptr() for t in outs])
+        _check(L.dashb_evaluate_compressed_async(c.h, ip, b, op))
+    _check(L.dashb_evaluate_wait(c.h))
+    for r, ((ins, outs), w) in enumerate(zip(keep, want)):
+        for j, (o, x) in enumerate(zip(outs, w)):
+            assert np.array_equal(o.numpy(), x), "%s compressed async step %d modulus %d" % (name, r, j)
+    c.close()
+
+
 @pytest.mark.parametrize("name", ["MLP_TINY", "CONV_UNIT", "SIGN_TINY", "RELU_EDGE"])
 @pytest.mark.parametrize("batch,replicas", [(37, 37), (130, 130), (40, 7)])
 def test_table_replicas_give_the_same_labels(gpu, name, batch, replicas):
