@@ -160,7 +160,15 @@ __device__ __forceinline__ uint32_t sbox_at(const AesSmem& a, uint32_t s) {
 #define DASHB_AES_UNROLL 1
 #endif
 constexpr int AES_UNROLL = DASHB_AES_UNROLL; /* rounds per trip of the middle-round loop (1, 3 or 9) */
-__device__ __noinline__ u128 hash(const AesSmem& a, u128 x) {
+#ifndef DASHB_HASH_INLINE
+#define DASHB_HASH_INLINE 0
+#endif
+#if DASHB_HASH_INLINE
+__device__ __forceinline__
+#else
+__device__ __noinline__
+#endif
+u128 hash(const AesSmem& a, u128 x) {
     const uint32_t four = c_four;
     uint32_t s0 = gc::bswap32((uint32_t)x.lo) ^ c_rk[0];
     uint32_t s1 = gc::bswap32((uint32_t)(x.lo >> 32)) ^ c_rk[1];

@@ -23,6 +23,7 @@ VARIANTS = {
     "rs12": "-DDASHB_RS_MINB=12",
     "sign64": "-DDASHB_SIGN_THREADS=64 -DDASHB_SIGN_MINB=16",
     "sign256": "-DDASHB_SIGN_THREADS=256 -DDASHB_SIGN_MINB=4",
+    "hash_inline": "-DDASHB_HASH_INLINE=1",
 }
 
 if __name__ == "__main__":
