@@ -16,6 +16,7 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <chrono>
 #include <vector>
 
 #include "../../include/dash_b200.h"
@@ -422,6 +423,7 @@ struct Lane {
     cudaEvent_t done{nullptr}, in_done{nullptr}, ing_done{nullptr};
     cudaEvent_t in_done_x[3] = {nullptr, nullptr, nullptr}; /* the lane's copies on the further copy streams */
     DevMem buf_in, buf_a, buf_b, stage_in, stage_out, xvals;
+    DevMem buf_in2; /* dashb_evaluate_async, in-order mode: the input planes of the step after the one computing */
     DevMem pool; /* max pooling: the ReLU gadget's input (y - x) and output, two tensors of the layer's output size */
     /* output-channel sharding over peer memory: two gather buffers, the epoch flags, and every rank's copies of them */
     DevMem gat[2], flags;
@@ -462,6 +464,18 @@ struct dashb_circuit {
      * flight (step n+1's inputs cross PCIe while step n computes) */
     std::vector<std::unique_ptr<Lane>> lanes_alt;
     cudaEvent_t async_done[2] = {nullptr, nullptr};
+    cudaStream_t join_s{nullptr}; /* waits for every lane's end of step without holding a lane back */
+    /* DASHB_TRACE_ASYNC: per step the host time of the call and, per lane, events after inputs / layers /
+     * outputs; printed relative to the first step's enqueue at dashb_evaluate_wait (experiments only) */
+    struct AsyncTrace {
+        int step, set, lanes;
+        double host_in_ms, host_out_ms;
+        cudaEvent_t ev[1 + 4 * 8];
+    };
+    std::vector<AsyncTrace> atrace;
+    cudaEvent_t atrace_base{nullptr};
+    std::chrono::steady_clock::time_point atrace_t0;
+    int atrace_steps{0};
     bool async_busy[2] = {false, false};
     int async_next{0};
     int shard_rank{0}, shard_world{1};
@@ -498,6 +512,7 @@ struct dashb_circuit {
         for (auto x : copy_x)
             if (x) cudaStreamDestroy(x);
         if (ingest_s) cudaStreamDestroy(ingest_s);
+        if (join_s) cudaStreamDestroy(join_s);
         for (auto e : async_done)
             if (e) cudaEventDestroy(e);
         for (void* p : ipc_opened) cudaIpcCloseMemHandle(p);
@@ -1578,7 +1593,7 @@ static bool mapped_host_inputs(const dashb_circuit* c, const void* const* in, co
 
 /* `in`: per CRT modulus int16 [batch][label][nc], or (compressed) dashb_u128 [batch][label] */
 static int enqueue_inputs(dashb_circuit* c, Lane& ln, const void* const* in, bool compressed, cudaStream_t cs, cudaStream_t s,
-                          const void* const* mapped = nullptr) {
+                          const void* const* mapped = nullptr, cudaEvent_t copied = nullptr) {
     /* timing experiments only (tools/probe_async.py): evaluate whatever the planes hold, move no input */
     static const bool skip = getenv("DASHB_DEBUG_SKIP_INPUTS") != nullptr;
     if (skip) {
@@ -1627,6 +1642,7 @@ static int enqueue_inputs(dashb_circuit* c, Lane& ln, const void* const* in, boo
      * high-priority stream so that they are not queued behind the thousands
      * of CTAs of the lanes that already compute */
     cudaStream_t is = (cs != s) ? c->ingest_s : s;
+    if (copied) CU(cudaEventRecord(copied, cs)); /* DASHB_TRACE_ASYNC */
     if (cs != s) {
         CU(cudaEventRecord(ln.in_done, cs));
         CU(cudaStreamWaitEvent(is, ln.in_done, 0));
@@ -2293,20 +2309,59 @@ int dashb_evaluate_device(dashb_circuit* c) {
     return DASHB_OK;
 }
 
+/* Device-visible addresses of the caller's output buffers when all of them are mapped pinned host memory
+ * (see mapped_host_inputs): the egress kernels then store into them directly, no staging copy.
+ * DASHB_DIRECT_EGRESS=0 keeps the staged path. */
+static bool mapped_host_outputs(const dashb_circuit* c, void* const* out, void** dev) {
+    static const bool off = getenv("DASHB_DIRECT_EGRESS") != nullptr && atoi(getenv("DASHB_DIRECT_EGRESS")) == 0;
+    if (off) return false;
+    for (int j = 0; j < c->k; ++j) {
+        cudaPointerAttributes a;
+        if (cudaPointerGetAttributes(&a, out[j]) != cudaSuccess) {
+            cudaGetLastError();
+            return false;
+        }
+        if (a.type != cudaMemoryTypeHost || !a.devicePointer) return false;
+        dev[j] = a.devicePointer;
+    }
+    return true;
+}
+
 static int enqueue_outputs(dashb_circuit* c, Lane& ln, void* const* out, bool compressed, cudaStream_t s) {
+    void* dev[MAXK];
+    const bool direct = mapped_host_outputs(c, out, dev);
     size_t off = 0;
+    EgressParams ep;
+    memset(&ep, 0, sizeof(ep));
+    ep.k = c->k;
+    ep.n = ln.t_cur.n;
+    ep.batch = ln.batch;
+    ep.Bp = ln.Bp;
+    size_t pers[MAXK], offs[MAXK];
     for (int j = 0; j < c->k; ++j) {
         const ModInfo m = make_modinfo((uint32_t)ln.t_cur.q[j]);
         const size_t per = ln.t_cur.n * (compressed ? 16 : (size_t)m.nc * 2);
-        const size_t bytes = (size_t)ln.batch * per;
-        void* st = (char*)ln.stage_out.p + off;
-        if (compressed)
-            CU(launch_egress_compressed(ln.t_cur.plane[j], st, ln.t_cur.n, m, ln.batch, ln.Bp, s));
-        else
-            CU(launch_egress(ln.t_cur.plane[j], (int16_t*)st, ln.t_cur.n, m.nc, ln.batch, ln.Bp, s));
-        CU(cudaMemcpyAsync((char*)out[j] + (size_t)ln.b0 * per, st, bytes, cudaMemcpyDeviceToHost, s));
-        off += bytes;
+        pers[j] = per;
+        offs[j] = off;
+        void* dst = direct ? (void*)((char*)dev[j] + (size_t)ln.b0 * per) : (void*)((char*)ln.stage_out.p + off);
+        if (compressed) {
+            CU(launch_egress_compressed(ln.t_cur.plane[j], dst, ln.t_cur.n, m, ln.batch, ln.Bp, s));
+            c->launches += 1;
+        } else {
+            ep.plane[j] = ln.t_cur.plane[j];
+            ep.dst[j] = (int16_t*)dst;
+            ep.nc[j] = m.nc;
+        }
+        off += (size_t)ln.batch * per;
     }
+    if (!compressed) {
+        CU(launch_egress_all(ep, s));
+        c->launches += 1;
+    }
+    if (!direct)
+        for (int j = 0; j < c->k; ++j)
+            CU(cudaMemcpyAsync((char*)out[j] + (size_t)ln.b0 * pers[j], (char*)ln.stage_out.p + offs[j], (size_t)ln.batch * pers[j],
+                               cudaMemcpyDeviceToHost, s));
     return DASHB_OK;
 }
 
@@ -2343,6 +2398,29 @@ static int wait_async(dashb_circuit* c) {
             c->async_busy[set] = false;
             CU(cudaEventSynchronize(c->async_done[set]));
         }
+    if (!c->atrace.empty()) {
+        for (auto& t : c->atrace) {
+            float t0 = 0;
+            cudaEventElapsedTime(&t0, c->atrace_base, t.ev[0]);
+            fprintf(stderr, "[dashb async] step %d set %d: call %.2f..%.2f ms (host), enqueue mark %.2f ms;", t.step, t.set, t.host_in_ms,
+                    t.host_out_ms, t0);
+            for (int i = 0; i < t.lanes; ++i) {
+                float a = 0, b = 0, d = 0;
+                cudaEventElapsedTime(&a, c->atrace_base, t.ev[1 + 3 * i]);
+                cudaEventElapsedTime(&b, c->atrace_base, t.ev[2 + 3 * i]);
+                cudaEventElapsedTime(&d, c->atrace_base, t.ev[3 + 3 * i]);
+                float cp = 0;
+                if (cudaEventElapsedTime(&cp, c->atrace_base, t.ev[1 + 3 * t.lanes + i]) != cudaSuccess) {
+                    cudaGetLastError(); /* not recorded: the zero-copy path has no copies */
+                    cp = 0;
+                }
+                fprintf(stderr, " lane %d copied %.2f in %.2f layers %.2f out %.2f;", i, cp, a, b, d);
+            }
+            fprintf(stderr, "\n");
+            for (int i = 0; i < 1 + 4 * t.lanes; ++i) cudaEventDestroy(t.ev[i]);
+        }
+        c->atrace.clear();
+    }
     return DASHB_OK;
 }
 
@@ -2351,6 +2429,7 @@ static int evaluate_any(dashb_circuit* c, const void* const* in, uint64_t batch,
     if (!c || !in || !out) return fail(DASHB_EINVAL, "null argument");
     if (!c->finalized) return fail(DASHB_ESTATE, "circuit not finalized");
     if (async) {
+        const auto t_call = std::chrono::steady_clock::now();
         if (c->shard_world > 1) return fail(DASHB_ESTATE, "channel-sharded circuits evaluate synchronously");
         for (int j = 0; j < c->k; ++j)
             if (!in[j] || !out[j]) return fail(DASHB_EINVAL, "label buffer %d missing", j);
@@ -2360,35 +2439,96 @@ static int evaluate_any(dashb_circuit* c, const void* const* in, uint64_t batch,
             c->async_busy[set] = false;
             CU(cudaEventSynchronize(c->async_done[set]));
         }
-        if (set == 1 && c->lanes_alt.empty()) {
+        /* Two ways to keep two steps in flight (DASHB_ASYNC_MODE):
+         * "inorder" (default): ONE set of lanes; a lane's stream runs step after step in order, only the input
+         *   planes are double-buffered, so step n+1's labels are copied and re-laid-out while step n computes
+         *   and lane i starts step n+1 the moment it has finished step n -- no second set of lanes competing
+         *   for the SMs, the small late layers of step n run under the big first layers of step n+1.
+         * "sets": a second set of lanes (streams + all buffers) computes step n+1 beside step n. */
+        static const bool two_sets = getenv("DASHB_ASYNC_MODE") != nullptr && !strcmp(getenv("DASHB_ASYNC_MODE"), "sets");
+        if (two_sets && set == 1 && c->lanes_alt.empty()) {
             int rc = make_lanes(c, c->lanes_alt);
             if (rc) return rc;
             CU(cudaStreamSynchronize(cudaStreamLegacy)); /* the clears of the new buffers */
         }
-        if (set == 1) std::swap(c->lanes, c->lanes_alt);
-        /* nothing here is ordered behind dashb_stream(): the set's own streams
-         * carry the order (the host waited for the set's previous step above) */
+        if (two_sets && set == 1) std::swap(c->lanes, c->lanes_alt);
+        if (!two_sets && !c->join_s) {
+            CU(cudaStreamCreateWithFlags(&c->join_s, cudaStreamNonBlocking));
+            const size_t in_bytes = tensor_bytes(c->input_size, c->k, c->crt, c->lane_cap);
+            for (auto& l : c->lanes) {
+                CU(l->buf_in2.alloc(in_bytes));
+                CU(cudaMemsetAsync(l->buf_in2.p, 0, in_bytes, cudaStreamLegacy));
+            }
+            CU(cudaStreamSynchronize(cudaStreamLegacy));
+        }
+        /* nothing here is ordered behind dashb_stream(): the lanes' own streams
+         * carry the order (the host waited for the step before the last above) */
         int rc = split_batch(c, batch);
+        if (!rc && !two_sets) {
+            for (int i = 0; i < c->lanes_used; ++i) {
+                Lane& ln = *c->lanes[i];
+                if (set == 1) {
+                    carve(ln.t_in, (uint8_t*)ln.buf_in2.p, c->input_size, c->k, c->crt, ln.Bp);
+                    ln.t_cur = ln.t_in;
+                }
+                /* the lane's staging area is read by the previous step's ingest kernels */
+                CU(cudaStreamWaitEvent(c->copy_s, ln.ing_done, 0));
+            }
+        }
         const void* dev[MAXK];
-        const bool direct = !rc && !compressed && mapped_host_inputs(c, in, dev);
+        /* in-order mode: the copy engine by default (52-55 GB/s next to the kernels; the zero-copy ingest kernel
+         * reads the host at 36-38 GB/s, which is below the compute rate of the benchmark model) */
+        static const bool async_direct = getenv("DASHB_ASYNC_DIRECT") != nullptr && atoi(getenv("DASHB_ASYNC_DIRECT")) != 0;
+        const bool direct = !rc && !compressed && (two_sets || async_direct) && mapped_host_inputs(c, in, dev);
         c->launches = 0;
-        for (int i = 0; !rc && i < c->lanes_used; ++i)
-            rc = enqueue_inputs(c, *c->lanes[i], in, compressed, c->copy_s, c->lanes[i]->s, direct ? dev : nullptr);
+        static const bool atrace = getenv("DASHB_TRACE_ASYNC") != nullptr;
+        dashb_circuit::AsyncTrace* tr = nullptr;
+        if (atrace && !rc && c->lanes_used <= 8 && c->atrace.size() < 64) {
+            if (!c->atrace_base) {
+                cudaEventCreate(&c->atrace_base);
+                cudaEventRecord(c->atrace_base, c->ingest_s);
+                c->atrace_t0 = t_call;
+            }
+            c->atrace.emplace_back();
+            tr = &c->atrace.back();
+            tr->step = c->atrace_steps++;
+            tr->set = set;
+            tr->lanes = c->lanes_used;
+            tr->host_in_ms = std::chrono::duration<double, std::milli>(t_call - c->atrace_t0).count();
+            for (int i = 0; i < 1 + 4 * tr->lanes; ++i) cudaEventCreate(&tr->ev[i]);
+            cudaEventRecord(tr->ev[0], c->ingest_s);
+        }
+        for (int i = 0; !rc && i < c->lanes_used; ++i) {
+            rc = enqueue_inputs(c, *c->lanes[i], in, compressed, c->copy_s, c->lanes[i]->s, direct ? dev : nullptr,
+                                tr ? tr->ev[1 + 3 * tr->lanes + i] : nullptr);
+            if (tr) cudaEventRecord(tr->ev[1 + 3 * i], c->lanes[i]->s);
+        }
+        /* experiment: no lane computes before the whole step's inputs are in */
+        static const bool gather = getenv("DASHB_ASYNC_GATHER") != nullptr && atoi(getenv("DASHB_ASYNC_GATHER")) != 0;
+        if (gather && !rc && c->lanes_used > 1)
+            for (int i = 0; i + 1 < c->lanes_used; ++i) cudaStreamWaitEvent(c->lanes[i]->s, c->lanes[c->lanes_used - 1]->ing_done, 0);
         const int nl = (int)c->layers.size();
         for (int li = 0; !rc && li < nl; ++li)
             for (int i = 0; !rc && i < c->lanes_used; ++i) rc = run_layer(c, *c->lanes[i], li, c->lanes[i]->s);
+        if (tr)
+            for (int i = 0; i < c->lanes_used; ++i) cudaEventRecord(tr->ev[2 + 3 * i], c->lanes[i]->s);
         if (!rc && nl > 0) {
             c->out_n = c->layers[nl - 1]->out_size;
             for (int j = 0; j < c->k; ++j) c->out_q[j] = c->layers[nl - 1]->out_q[j];
         }
-        for (int i = 0; !rc && i < c->lanes_used; ++i) rc = enqueue_outputs(c, *c->lanes[i], out, compressed, c->lanes[i]->s);
-        cudaError_t e = cudaSuccess;
-        for (int i = 1; e == cudaSuccess && i < c->lanes_used; ++i) {
-            e = cudaEventRecord(c->lanes[i]->done, c->lanes[i]->s);
-            if (e == cudaSuccess) e = cudaStreamWaitEvent(c->lanes[0]->s, c->lanes[i]->done, 0);
+        for (int i = 0; !rc && i < c->lanes_used; ++i) {
+            rc = enqueue_outputs(c, *c->lanes[i], out, compressed, c->lanes[i]->s);
+            if (tr) cudaEventRecord(tr->ev[3 + 3 * i], c->lanes[i]->s);
         }
-        if (e == cudaSuccess) e = cudaEventRecord(c->async_done[set], c->lanes[0]->s);
-        if (set == 1) std::swap(c->lanes, c->lanes_alt);
+        if (tr) tr->host_out_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - c->atrace_t0).count();
+        cudaError_t e = cudaSuccess;
+        cudaStream_t js = two_sets ? c->lanes[0]->s : c->join_s;
+        for (int i = two_sets ? 1 : 0; e == cudaSuccess && i < c->lanes_used; ++i) {
+            e = cudaEventRecord(c->lanes[i]->done, c->lanes[i]->s);
+            if (e == cudaSuccess) e = cudaStreamWaitEvent(js, c->lanes[i]->done, 0);
+        }
+        if (e == cudaSuccess) e = cudaEventRecord(c->async_done[set], js);
+        if (two_sets && set == 1) std::swap(c->lanes, c->lanes_alt);
         if (e != cudaSuccess) return fail(DASHB_ECUDA, "dashb_evaluate_async: %s", cudaGetErrorString(e));
         c->async_busy[set] = true;
         c->async_next = set ^ 1;

@@ -318,6 +318,38 @@ __global__ void __launch_bounds__(128) k_egress(const uint8_t* __restrict__ plan
     }
 }
 
+/* k_egress for all moduli at once (blockIdx.z): one launch per lane instead of k -- at the end of a step every
+ * launch queues behind the other lanes' grids -- and a destination that may be the caller's mapped host buffer
+ * (2-byte stores, 64 contiguous bytes per warp; the outputs of a step are a few MB). */
+__global__ void __launch_bounds__(128) k_egress_all(const __grid_constant__ EgressParams P) {
+    __shared__ uint32_t tile[32][33];
+    const int j = blockIdx.z;
+    const uint32_t nc = P.nc[j], nc4 = (nc + 3) >> 2;
+    const uint8_t* plane = P.plane[j];
+    const uint64_t e = blockIdx.x;
+    const uint32_t b0 = blockIdx.y * 32;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t d4 = warp; d4 < nc4; d4 += 4) {
+        const uint32_t b = b0 + lane;
+        tile[lane][d4] = b < P.Bp ? *reinterpret_cast<const uint32_t*>(plane + ((e * nc4 + d4) * (uint64_t)P.Bp + b) * 4) : 0;
+    }
+    __syncthreads();
+    for (uint32_t i = warp; i < 32; i += 4) {
+        const uint32_t b = b0 + i;
+        if (b >= P.batch) continue;
+        int16_t* row = P.dst[j] + ((uint64_t)b * P.n + e) * nc;
+        for (uint32_t d = lane; d < nc; d += 32) row[d] = (int16_t)((tile[i][d >> 2] >> (8 * (d & 3))) & 0xff);
+    }
+}
+
+cudaError_t launch_egress_all(const EgressParams& p, cudaStream_t s) {
+    if (p.n == 0 || p.batch == 0) return cudaSuccess;
+    dim3 grid((unsigned)p.n, (p.Bp + 31) / 32, (unsigned)p.k);
+    if (p.n > 0x7fffffffull || grid.y > 65535u) return cudaErrorInvalidValue;
+    k_egress_all<<<grid, 128, 0, s>>>(p);
+    return cudaGetLastError();
+}
+
 /*
  * The same layout change without the staging copy: the caller's pinned host
  * buffers are mapped into the device's address space, so the kernel reads

@@ -137,6 +137,16 @@ struct IngestParams {
     int k;
 };
 
+/* k_egress_all: the output planes of every modulus back to int16 [batch][n][nc_j] in one launch */
+struct EgressParams {
+    const uint8_t* plane[MAXK];
+    int16_t* dst[MAXK]; /* the lane's first inference; device memory or mapped pinned host memory */
+    uint32_t nc[MAXK];
+    uint64_t n;
+    uint32_t batch, Bp;
+    int k;
+};
+
 /* k_shard_push: one rank's slice of an activation tensor stored into the
  * gather buffer of every rank (its own included) over NVLink peer memory */
 constexpr int MAXR = 16; /* ranks of an output-channel-sharded evaluation */
@@ -316,6 +326,7 @@ cudaError_t conv_tc_make_map(void* map_out, const void* ptr, uint64_t row_bytes,
                              uint64_t channels, uint32_t f_w, uint32_t f_h, uint32_t cb);
 cudaError_t launch_dense_tc(const DenseTcMaps& maps, const DenseTcParams& p, cudaStream_t s);
 cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s);
+cudaError_t launch_egress_all(const EgressParams& p, cudaStream_t s);
 cudaError_t launch_projection(const ProjParams& p, cudaStream_t s);
 cudaError_t launch_shard_push(const ShardPushParams& p, cudaStream_t s);
 cudaError_t launch_shard_signal(uint32_t* const* peer_flags, int world, int rank, uint32_t epoch, cudaStream_t s);
