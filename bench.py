@@ -300,6 +300,31 @@ def run_c4(torch, dist, rank, world, local_rank, barrier, steps=5, batch=64):
     return out
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Multi-rank runs: keep this process (and the pinned host buffers it first-touches) on the CPUs of the NUMA node
+    the GPU hangs off (sysfs local_cpulist of the GPU's PCI function), so that the step's host->device traffic does not
+    cross the socket interconnect.  Returns a description for the JSON line, None when nothing was done."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(local_rank)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        dom, rest = bus.split(":", 1)
+        path = "/sys/bus/pci/devices/%s:%s/local_cpulist" % (dom[-4:].lower(), rest.lower())
+        cpus = set()
+        for part in open(path).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return "%d cpus local to %s" % (len(cpus), bus)
+    except Exception:  # no NVML, no sysfs entry, a container without the right: run unbound
+        return None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -323,6 +348,7 @@ def main():
         return
     if args.warmup < 3:
         args.warmup = 3
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else None
 
     import torch
     import torch.distributed as dist
@@ -616,6 +642,7 @@ def main():
                                             "form with two steps in flight (13 % of the int16 layout's PCIe bytes)"},
         "gpu_launches": int(launches * args.steps),
         "clocks": sampler.summary(),
+        "host_affinity": numa,
         "roofline": roofline,
     }
 

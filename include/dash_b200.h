@@ -301,9 +301,11 @@ int dashb_evaluate(dashb_circuit* c, const int16_t* const* in, uint64_t batch,
                    int16_t* const* out);
 /*
  * dashb_evaluate for a caller that streams batches: returns as soon as the
- * step is enqueued; up to two steps are in flight on two sets of lanes, so
- * that step n+1's input labels cross PCIe while step n computes (the third
- * call first waits for the oldest step).  `in` and `out` must stay valid and
+ * step is enqueued; up to two steps are in flight (the lanes' streams run the
+ * steps in order, the input planes are double-buffered), so that step n+1's
+ * input labels cross PCIe while step n computes (the third call first waits
+ * for the oldest step).  Output buffers in pinned, mapped host memory are
+ * written by the egress kernel directly; pageable ones through a staging copy.  `in` and `out` must stay valid and
  * untouched until that step is done: after dashb_evaluate_wait(), or after
  * the second-next dashb_evaluate_async returns.  Steps complete in order.
  * The work is NOT ordered with dashb_stream(); dashb_move_outputs /
