@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdash_b200.so")
 SOURCES = ["kernels.cu", "dense_tc.cu", "dashb_api.cu", "garbler.cu"]
-HEADERS = ["kernels.h", "gc_common.cuh", "garble_kernels.cuh", "../../include/dash_b200.h",
+HEADERS = ["kernels.h", "gc_common.cuh", "garble_kernels.cuh", "shard_kernels.cuh", "../../include/dash_b200.h",
            "../../include/dash_b200_gcm.h", "../../include/dash_gcm_format.h", "../../include/dash_b200_garble.h"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--extended-lambda",

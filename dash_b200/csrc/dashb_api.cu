@@ -2149,6 +2149,12 @@ int dashb_evaluate_layers_lane(dashb_circuit* c, int lane, int first, int last) 
     return DASHB_OK;
 }
 
+/* DASHB_SHARD_COMPRESS=0: the exchange moves digit planes as they are instead of compressed labels */
+static bool shard_compressed() {
+    static const bool on = !(getenv("DASHB_SHARD_COMPRESS") != nullptr && atoi(getenv("DASHB_SHARD_COMPRESS")) == 0);
+    return on;
+}
+
 /* After layer `layer`: this rank's slice of the lane's current tensor goes to
  * every rank's gather buffer; the lane's stream continues once every rank's
  * slice has arrived here.  The lane's current tensor is then the gathered one. */
@@ -2161,9 +2167,36 @@ int dashb_shard_exchange(dashb_circuit* c, int lane, int layer) {
     for (int r = 0; r < W; ++r)
         if (!ln.peer_gat[x][r] || !ln.peer_flags[r]) return fail(DASHB_ESTATE, "rank %d's buffers were not imported (dashb_shard_import)", r);
     const Tensor cur = ln.t_cur;
+    const Layer& SL = *c->layers[layer];
+    if (shard_compressed()) {
+        /* labels cross NVLink as 16 bytes each; the gathered tensor is expanded back into the lane's own planes */
+        ShardCompParams q;
+        memset(&q, 0, sizeof(q));
+        q.k = cur.k;
+        q.world = W;
+        q.n = cur.n;
+        q.e0 = SL.e0;
+        q.seg = SL.seg;
+        q.stride = SL.stride;
+        q.count = SL.slice_count();
+        q.Bp = ln.Bp;
+        q.local = (const uint8_t*)ln.gat[x].p;
+        for (int j = 0; j < cur.k; ++j) {
+            q.plane[j] = cur.plane[j];
+            q.mod[j] = make_modinfo((uint32_t)cur.q[j]);
+        }
+        for (int r = 0; r < W; ++r) q.peer[r] = ln.peer_gat[x][r];
+        const uint32_t epoch = ++ln.epoch;
+        CU(launch_shard_push_comp(q, ln.s));
+        CU(launch_shard_signal(ln.peer_flags, W, c->shard_rank, epoch, ln.s));
+        CU(launch_shard_wait((uint32_t*)ln.flags.p, W, epoch, ln.s));
+        CU(launch_shard_unpack(q, ln.s));
+        c->launches += 4;
+        ln.gcur ^= 1;
+        return DASHB_OK;
+    }
     Tensor dst;
     carve(dst, (uint8_t*)ln.gat[x].p, cur.n, cur.k, cur.q, ln.Bp);
-    const Layer& SL = *c->layers[layer];
     ShardPushParams p;
     memset(&p, 0, sizeof(p));
     p.k = cur.k;
@@ -2224,7 +2257,7 @@ uint64_t dashb_shard_exchange_bytes(dashb_circuit* c, int lane, int layer) {
     Lane& ln = *c->lanes[lane];
     const Layer& L = *c->layers[layer];
     uint64_t per = 0;
-    for (int j = 0; j < c->k; ++j) per += (uint64_t)((nr_comps(L.out_q[j]) + 3) & ~3) * ln.Bp;
+    for (int j = 0; j < c->k; ++j) per += (shard_compressed() ? 16ull : (uint64_t)((nr_comps(L.out_q[j]) + 3) & ~3)) * ln.Bp;
     return (L.out_size - L.slice_count()) * per;
 }
 

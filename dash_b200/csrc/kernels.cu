@@ -2079,3 +2079,4 @@ cudaError_t launch_decode(const DecodeParams& p, cudaStream_t s) {
 }  // namespace dashb
 
 #include "garble_kernels.cuh"
+#include "shard_kernels.cuh"

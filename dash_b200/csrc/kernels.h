@@ -160,6 +160,18 @@ struct ShardPushParams {
     int k, world;
 };
 
+/* k_shard_push_comp / k_shard_unpack: the same exchange with 16-byte compressed labels (shard_kernels.cuh) */
+struct ShardCompParams {
+    const uint8_t* plane[MAXK]; /* the lane's current tensor: read by the push, rewritten by the unpack */
+    gc::ModInfo mod[MAXK];
+    uint8_t* peer[MAXR];  /* every rank's gather buffer: u128 [modulus][element][inference] */
+    const uint8_t* local; /* this rank's own gather buffer */
+    uint64_t n;           /* elements of the tensor */
+    uint64_t e0, seg, stride, count; /* this rank's slice: `count` elements, see slice_elem */
+    uint32_t Bp;
+    int k, world;
+};
+
 struct ProjParams {
     const uint8_t* in[MAXK];
     uint8_t* out[MAXK];
@@ -329,6 +341,8 @@ cudaError_t launch_sign(const SignParams& p, bool relu, cudaStream_t s);
 cudaError_t launch_egress_all(const EgressParams& p, cudaStream_t s);
 cudaError_t launch_projection(const ProjParams& p, cudaStream_t s);
 cudaError_t launch_shard_push(const ShardPushParams& p, cudaStream_t s);
+cudaError_t launch_shard_push_comp(const ShardCompParams& p, cudaStream_t s);
+cudaError_t launch_shard_unpack(const ShardCompParams& p, cudaStream_t s);
 cudaError_t launch_shard_signal(uint32_t* const* peer_flags, int world, int rank, uint32_t epoch, cudaStream_t s);
 cudaError_t launch_shard_wait(uint32_t* flags, int world, uint32_t epoch, cudaStream_t s);
 cudaError_t launch_pool_step(const PoolParams& p, cudaStream_t s);
