@@ -1501,6 +1501,8 @@ int dashb_finalize(dashb_circuit* c, uint64_t max_batch) {
 }
 
 /* lane streams start after everything already enqueued on the library stream */
+static int wait_async(dashb_circuit* c); /* drains dashb_evaluate_async steps in flight */
+
 static int fork_lanes(dashb_circuit* c) {
     CU(cudaEventRecord(c->ev_fork, g_stream));
     for (int i = 0; i < c->lanes_used; ++i) CU(cudaStreamWaitEvent(c->lanes[i]->s, c->ev_fork, 0));
@@ -1675,8 +1677,9 @@ static int move_inputs_any(dashb_circuit* c, const void* const* in, uint64_t bat
     if (!c->finalized) return fail(DASHB_ESTATE, "circuit not finalized");
     for (int j = 0; j < c->k; ++j)
         if (!in[j]) return fail(DASHB_EINVAL, "input labels %d missing", j);
-    int rc = split_batch(c, batch);
+    int rc = wait_async(c); /* the lanes and their input planes may still belong to a streamed step */
     if (rc) return rc;
+    if ((rc = split_batch(c, batch))) return rc;
     const void* dev[MAXK];
     const bool direct = !compressed && mapped_host_inputs(c, in, dev);
     if ((rc = fork_lanes(c))) return rc;
@@ -1697,8 +1700,9 @@ int dashb_garble_inputs(dashb_circuit* c, const int64_t* values, uint64_t batch)
     if (!c || !values) return fail(DASHB_EINVAL, "null argument");
     if (!c->finalized) return fail(DASHB_ESTATE, "circuit not finalized");
     if (!c->has_ginp) return fail(DASHB_ESTATE, "no input encoding (dashb_set_input_encoding)");
-    int rc = split_batch(c, batch);
+    int rc = wait_async(c);
     if (rc) return rc;
+    if ((rc = split_batch(c, batch))) return rc;
     if ((rc = fork_lanes(c))) return rc;
     for (int i = 0; i < c->lanes_used; ++i) {
         Lane& ln = *c->lanes[i];
@@ -2325,8 +2329,9 @@ int dashb_evaluate_device(dashb_circuit* c) {
     if (!c->finalized || c->batch == 0) return fail(DASHB_ESTATE, "no inputs moved");
     if (c->shard_world > 1)
         return fail(DASHB_ESTATE, "channel-sharded circuit: use dashb_evaluate_layers and gather between layer groups");
-    int rc = run_layers(c, (int)c->layers.size() - 1);
+    int rc = wait_async(c);
     if (rc) return rc;
+    if ((rc = run_layers(c, (int)c->layers.size() - 1))) return rc;
     if (c->timing == 1) {
         CU(cudaStreamSynchronize(g_stream));
         for (size_t i = 0; i < c->layers.size(); ++i) CU(cudaEventElapsedTime(&c->layers[i]->ms, c->ev[i], c->ev[i + 1]));
